@@ -1,0 +1,648 @@
+/*
+ * pcb_capi.cu -- host side of cpp_functions.so: the C ABI declared in include/porechop_b200.h.
+ *
+ * Replaces the reference's native library (porechop_abi/src/adapter_align.cpp, src/alignment.cpp) behind
+ * the same two symbols its ctypes wrapper binds (porechop_abi/cpp_function_wrappers.py:27-39), and adds the
+ * batched submit/collect entry points.  No CPU alignment code lives here: every result comes out of the
+ * kernels in pcb_kernels.cu.  The only arithmetic done on the host is the final
+ * 100.0 * matches / length in double (alignment.cpp:81,89) when a result string is printed.
+ */
+#include "pcb_kernels.h"
+#include "align_stats.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace {
+
+template <typename T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t cap = 0;      // elements
+    cudaError_t reserve(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = n + n / 8 + 64;
+        cudaError_t e = cudaMalloc((void **)&p, want * sizeof(T));
+        if (e != cudaSuccess) { want = n; e = cudaMalloc((void **)&p, want * sizeof(T)); }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct pcb_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, kev0 = nullptr, kev1 = nullptr;
+    std::string err;
+    PcbScores sc{3, -6, -5, -2, 0};
+    // adapters
+    std::vector<int64_t> ad_off;          // host copy
+    int32_t n_adapters = 0;
+    DevBuf<uint8_t> d_ad_codes;
+    DevBuf<int64_t> d_ad_off;
+    // staged inputs
+    DevBuf<char> d_ascii;
+    DevBuf<uint8_t> d_arena;
+    uint64_t arena_len = 0;
+    DevBuf<int32_t> d_winlen, d_ids;
+    std::vector<int32_t> h_ids;
+    int64_t n_windows = 0; int32_t stride = 0, n_ids = 0, win_mmax = 0;
+    // explicit tasks
+    struct HostTask { int64_t off; int32_t len; int32_t adapter; };
+    std::vector<HostTask> h_tasks;
+    DevBuf<PcbTask> d_tasks;
+    DevBuf<PcbUnit> d_units;
+    DevBuf<int32_t> d_scan;
+    // outputs / scratch
+    DevBuf<pcb_result> d_out;
+    int64_t n_results = 0;
+    DevBuf<uint32_t> d_scratch;
+    DevBuf<int32_t> d_err;
+    int grid_trace = 0, grid_scan = 0;
+    pcb_counters cnt{};
+    bool ktiming = false;
+
+    int fail(int code, const char *fmt, ...)
+    {
+        char buf[512];
+        va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+        err = buf;
+        return code;
+    }
+    int cuda_fail(cudaError_t e, const char *what)
+    {
+        return fail(PCB_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+    }
+};
+
+#define PCB_CUDA(ctx, call)                                                                  \
+    do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return (ctx)->cuda_fail(e__, #call); } while (0)
+
+static std::string g_global_err;
+
+extern "C" int pcb_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int pcb_create(int device, pcb_context **out)
+{
+    if (!out) return PCB_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        g_global_err = std::string("no usable CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        cudaGetLastError();
+        return PCB_ERR_CUDA;
+    }
+    if (device < 0 || device >= n) { g_global_err = "device index out of range"; return PCB_ERR_ARG; }
+    pcb_context *c = new pcb_context();
+    c->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
+        (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
+        g_global_err = std::string("context setup failed: ") + cudaGetErrorString(e);
+        delete c;
+        return PCB_ERR_CUDA;
+    }
+    c->grid_trace = pcb_occupancy_grid(0);
+    c->grid_scan = pcb_occupancy_grid(1);
+    if (c->d_err.reserve(1) != cudaSuccess) { g_global_err = "cudaMalloc failed"; delete c; return PCB_ERR_NOMEM; }
+    *out = c;
+    return PCB_OK;
+}
+
+extern "C" void pcb_destroy(pcb_context *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_arena.release();
+    c->d_winlen.release(); c->d_ids.release(); c->d_tasks.release(); c->d_units.release(); c->d_scan.release();
+    c->d_out.release(); c->d_scratch.release(); c->d_err.release();
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->kev0); cudaEventDestroy(c->kev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" const char *pcb_last_error(pcb_context *c) { return c ? c->err.c_str() : g_global_err.c_str(); }
+
+extern "C" int pcb_set_scoring(pcb_context *c, int match, int mismatch, int gap_open, int gap_extend)
+{
+    if (!c) return PCB_ERR_ARG;
+    c->sc.match = match; c->sc.mismatch = mismatch; c->sc.gap_open = gap_open; c->sc.gap_extend = gap_extend;
+    c->sc.linear = (gap_open == gap_extend);     // seqan/align/global_alignment_unbanded.h:216-219
+    return PCB_OK;
+}
+
+extern "C" int pcb_set_adapters(pcb_context *c, const char *blob, const int64_t *offsets, int32_t n_adapters)
+{
+    if (!c || n_adapters < 0 || (n_adapters > 0 && (!blob || !offsets))) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    c->ad_off.assign(offsets, offsets + n_adapters + 1);
+    c->n_adapters = n_adapters;
+    const int64_t base = n_adapters ? offsets[0] : 0;
+    const int64_t total = n_adapters ? offsets[n_adapters] - base : 0;
+    for (auto &o : c->ad_off) o -= base;
+    for (int i = 0; i < n_adapters; ++i)
+        if (c->ad_off[i + 1] < c->ad_off[i]) return c->fail(PCB_ERR_ARG, "adapter offsets must be non-decreasing");
+    PCB_CUDA(c, c->d_ad_codes.reserve((size_t)total + 16));
+    PCB_CUDA(c, c->d_ad_off.reserve((size_t)n_adapters + 1));
+    PCB_CUDA(c, c->d_ascii.reserve((size_t)total + 16));
+    if (total) PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, blob + base, (size_t)total, cudaMemcpyHostToDevice, c->stream));
+    PCB_CUDA(c, cudaMemcpyAsync(c->d_ad_off.p, c->ad_off.data(), sizeof(int64_t) * (n_adapters + 1), cudaMemcpyHostToDevice, c->stream));
+    PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_ad_codes.p, (uint64_t)total, c->stream));
+    c->cnt.kernel_launches += total ? 1 : 0;
+    c->cnt.h2d_bytes += total + (int64_t)sizeof(int64_t) * (n_adapters + 1);
+    PCB_CUDA(c, cudaStreamSynchronize(c->stream));     // d_ascii is reused by the staging calls
+    return PCB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// range checks: the kernels compute in signed 16-bit lanes
+// ------------------------------------------------------------------------------------------------
+static int check_range(pcb_context *c, int nmax, int mmax)
+{
+    const PcbScores &s = c->sc;
+    const int64_t maxabs = std::max(std::max(std::abs((int64_t)s.match), std::abs((int64_t)s.mismatch)),
+                                    std::max(std::abs((int64_t)s.gap_open), std::abs((int64_t)s.gap_extend)));
+    // with negative gap scores every DP value is bounded by the adapter length alone (a vertical gap from
+    // row 0 is always available); otherwise values can grow with the read length too
+    const bool neg_gaps = s.gap_open < 0 && s.gap_extend < 0;
+    const int64_t bound = maxabs * ((int64_t)nmax + 3 + (neg_gaps ? 0 : mmax));
+    if (bound > 8000)
+        return c->fail(PCB_ERR_RANGE, "scoring scheme %d,%d,%d,%d with adapter length %d exceeds the 16-bit DP range",
+                       s.match, s.mismatch, s.gap_open, s.gap_extend, nmax);
+    if (mmax + nmax > 0x3FFF - 2 || mmax > PCB_MAX_TRACE_M)
+        return c->fail(PCB_ERR_RANGE, "segment of %d columns is too long for a single trace launch", mmax);
+    return PCB_OK;
+}
+
+static int ensure_scratch(pcb_context *c, uint64_t words_per_slot, int grid)
+{
+    const uint64_t need = words_per_slot * (uint64_t)grid * PCB_BLOCK;
+    cudaError_t e = c->d_scratch.reserve((size_t)need);
+    if (e != cudaSuccess) { cudaGetLastError(); return c->fail(PCB_ERR_NOMEM, "scratch of %.1f MB: %s", need * 4 / 1e6, cudaGetErrorString(e)); }
+    return PCB_OK;
+}
+
+static int max_adapter_len(pcb_context *c, const int32_t *ids, int n)
+{
+    int mx = 0;
+    for (int i = 0; i < n; ++i) mx = std::max<int>(mx, (int)(c->ad_off[ids[i] + 1] - c->ad_off[ids[i]]));
+    return mx;
+}
+
+static void fill_launch_common(pcb_context *c, PcbLaunch &L)
+{
+    memset(&L, 0, sizeof L);
+    L.ad.codes = c->d_ad_codes.p; L.ad.off = c->d_ad_off.p;
+    L.sc = c->sc;
+    L.arena = c->d_arena.p; L.arena_len = c->arena_len;
+    L.out = c->d_out.p; L.scan_out = c->d_scan.p;
+    L.scratch = c->d_scratch.p; L.err_flag = c->d_err.p;
+}
+
+// launch with optional per-kernel event timing
+static int launch_dp(pcb_context *c, const PcbLaunch &L, bool trace, int64_t cells)
+{
+    if (c->ktiming) PCB_CUDA(c, cudaEventRecord(c->kev0, c->stream));
+    PCB_CUDA(c, trace ? pcb_launch_trace(L, c->stream) : pcb_launch_scan(L, c->stream));
+    if (c->ktiming) {
+        PCB_CUDA(c, cudaEventRecord(c->kev1, c->stream));
+        PCB_CUDA(c, cudaEventSynchronize(c->kev1));
+        float ms = 0; PCB_CUDA(c, cudaEventElapsedTime(&ms, c->kev0, c->kev1));
+        c->cnt.dp_kernel_ms += ms;
+    }
+    c->cnt.kernel_launches++; c->cnt.dp_kernel_launches++; c->cnt.dp_cells += cells;
+    return PCB_OK;
+}
+
+static int check_err_flag(pcb_context *c)
+{
+    int32_t f = 0;
+    PCB_CUDA(c, cudaMemcpyAsync(&f, c->d_err.p, sizeof f, cudaMemcpyDeviceToHost, c->stream));
+    PCB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (f) return c->fail(PCB_ERR_RANGE, "device reported alignment-window violation (flag %d)", f);
+    return PCB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// windows x adapters cross product
+// ------------------------------------------------------------------------------------------------
+extern "C" int pcb_stage_windows(pcb_context *c, const char *windows, int64_t n_windows, int32_t stride, const int32_t *win_len)
+{
+    if (!c || n_windows < 0 || stride <= 0 || (n_windows > 0 && (!windows || !win_len))) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    int mmax = 0;
+    for (int64_t w = 0; w < n_windows; ++w) {
+        if (win_len[w] < 0 || win_len[w] > stride) return c->fail(PCB_ERR_ARG, "win_len[%lld] = %d outside [0, stride]", (long long)w, win_len[w]);
+        mmax = std::max(mmax, win_len[w]);
+    }
+    const uint64_t bytes = (uint64_t)n_windows * stride;
+    PCB_CUDA(c, c->d_ascii.reserve((size_t)bytes + 16));
+    PCB_CUDA(c, c->d_arena.reserve((size_t)bytes + 16));
+    PCB_CUDA(c, c->d_winlen.reserve((size_t)n_windows + 1));
+    if (bytes) {
+        PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, windows, bytes, cudaMemcpyHostToDevice, c->stream));
+        PCB_CUDA(c, cudaMemcpyAsync(c->d_winlen.p, win_len, sizeof(int32_t) * n_windows, cudaMemcpyHostToDevice, c->stream));
+        PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena.p, bytes, c->stream));
+        c->cnt.kernel_launches++;
+    }
+    c->cnt.h2d_bytes += (int64_t)bytes + (int64_t)sizeof(int32_t) * n_windows;
+    c->arena_len = bytes; c->n_windows = n_windows; c->stride = stride; c->win_mmax = mmax;
+    return PCB_OK;
+}
+
+extern "C" int pcb_stage_ids(pcb_context *c, const int32_t *ids, int32_t n_ids)
+{
+    if (!c || n_ids < 0 || (n_ids > 0 && !ids)) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    for (int i = 0; i < n_ids; ++i)
+        if (ids[i] < 0 || ids[i] >= c->n_adapters) return c->fail(PCB_ERR_ARG, "adapter id %d out of range", ids[i]);
+    c->h_ids.assign(ids, ids + n_ids);
+    c->n_ids = n_ids;
+    PCB_CUDA(c, c->d_ids.reserve((size_t)n_ids + 1));
+    if (n_ids) PCB_CUDA(c, cudaMemcpyAsync(c->d_ids.p, ids, sizeof(int32_t) * n_ids, cudaMemcpyHostToDevice, c->stream));
+    c->cnt.h2d_bytes += (int64_t)sizeof(int32_t) * n_ids;
+    return PCB_OK;
+}
+
+extern "C" int pcb_run_windows_resident(pcb_context *c)
+{
+    if (!c) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    const int64_t n_res = c->n_windows * c->n_ids;
+    c->n_results = n_res;
+    if (n_res == 0) return PCB_OK;
+    const int nmax = max_adapter_len(c, c->h_ids.data(), c->n_ids);
+    const int mmax = std::max(1, c->win_mmax);
+    int rc = check_range(c, nmax, mmax);
+    if (rc) return rc;
+    const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
+    PCB_CUDA(c, c->d_out.reserve((size_t)n_res));
+    const int64_t n_units = ((c->n_windows + 63) / 64) * c->n_ids;
+    const int grid = (int)std::min<int64_t>(c->grid_trace, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
+    rc = ensure_scratch(c, pcb_scratch_words_trace(mmax, smax), grid);
+    if (rc) return rc;
+    PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
+    PcbLaunch L; fill_launch_common(c, L);
+    L.src.units = nullptr; L.src.tasks = nullptr;
+    L.src.n_windows = c->n_windows; L.src.stride = c->stride; L.src.win_len = c->d_winlen.p;
+    L.src.ids = c->d_ids.p; L.src.n_ids = c->n_ids; L.src.n_units = n_units;
+    L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
+    // algorithmic cell count: sum over windows of len x sum over ids of adapter length
+    int64_t sum_n = 0;
+    for (int i = 0; i < c->n_ids; ++i) sum_n += c->ad_off[c->h_ids[i] + 1] - c->ad_off[c->h_ids[i]];
+    // (window lengths were only seen at staging time; use mmax * n_windows as the upper figure when all
+    //  windows are full, which is what the bench workload is; exact sum is tracked by the caller)
+    return launch_dp(c, L, true, (int64_t)c->n_windows * mmax * sum_n);
+}
+
+extern "C" int pcb_fetch_results(pcb_context *c, pcb_result *out, int64_t n_results)
+{
+    if (!c || n_results < 0 || (n_results > 0 && !out)) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    if (n_results > c->n_results) return c->fail(PCB_ERR_ARG, "asked for %lld results, last run produced %lld", (long long)n_results, (long long)c->n_results);
+    if (n_results) PCB_CUDA(c, cudaMemcpyAsync(out, c->d_out.p, sizeof(pcb_result) * n_results, cudaMemcpyDeviceToHost, c->stream));
+    c->cnt.d2h_bytes += (int64_t)sizeof(pcb_result) * n_results;
+    return check_err_flag(c);
+}
+
+extern "C" int pcb_align_windows(pcb_context *c, const char *windows, int64_t n_windows, int32_t stride,
+                                 const int32_t *win_len, const int32_t *adapter_ids, int32_t n_ids, pcb_result *out)
+{
+    int rc;
+    if ((rc = pcb_stage_windows(c, windows, n_windows, stride, win_len))) return rc;
+    if ((rc = pcb_stage_ids(c, adapter_ids, n_ids))) return rc;
+    if ((rc = pcb_run_windows_resident(c))) return rc;
+    return pcb_fetch_results(c, out, n_windows * n_ids);
+}
+
+extern "C" int pcb_timer_start(pcb_context *c) { if (!c) return PCB_ERR_ARG; cudaSetDevice(c->device); PCB_CUDA(c, cudaEventRecord(c->ev0, c->stream)); return PCB_OK; }
+extern "C" int pcb_timer_stop(pcb_context *c, float *ms)
+{
+    if (!c || !ms) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    PCB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    PCB_CUDA(c, cudaEventSynchronize(c->ev1));
+    PCB_CUDA(c, cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    return PCB_OK;
+}
+extern "C" int pcb_synchronize(pcb_context *c) { if (!c) return PCB_ERR_ARG; cudaSetDevice(c->device); PCB_CUDA(c, cudaStreamSynchronize(c->stream)); return PCB_OK; }
+extern "C" int pcb_get_counters(pcb_context *c, pcb_counters *out) { if (!c || !out) return PCB_ERR_ARG; *out = c->cnt; return PCB_OK; }
+extern "C" int pcb_reset_counters(pcb_context *c) { if (!c) return PCB_ERR_ARG; memset(&c->cnt, 0, sizeof c->cnt); return PCB_OK; }
+extern "C" int pcb_set_kernel_timing(pcb_context *c, int on) { if (!c) return PCB_ERR_ARG; c->ktiming = on != 0; return PCB_OK; }
+
+// ------------------------------------------------------------------------------------------------
+// explicit task list (any segment length).
+//   len <= direct_max : one trace task.
+//   longer            : phase 1 = score-only scan in column chunks (each chunk re-computes a warm-up margin
+//                       so that its owned columns are exact), host picks the best end
+//                       cell per task in SeqAn's visiting order, phase 2 = trace task on the window that
+//                       provably contains the whole path.
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+struct WindowBounds { int warm; int span; bool ok; };
+
+// Margins for adapter length n under the current scoring scheme (derivation in DESIGN.md section 4).
+WindowBounds window_bounds(const PcbScores &s, int n)
+{
+    WindowBounds b{0, 0, false};
+    if (!(s.gap_open < 0 && s.gap_extend < 0)) return b;
+    const int64_t smax = std::max(0, std::max(s.match, s.mismatch));
+    const int64_t gH = -(int64_t)std::max(s.gap_open, s.gap_extend);          // cheapest horizontal step, > 0
+    const int64_t lb = ((int64_t)std::abs(s.gap_open) + std::abs(s.gap_extend)) * (n + 2);
+    b.warm = (int)(n + (smax * n + lb + gH - 1) / gH + 2);
+    b.span = (int)(n + (smax * n + gH - 1) / gH + 2);
+    b.ok = true;
+    return b;
+}
+
+// group tasks (already sorted by adapter) into units of <= 64
+void build_units(const std::vector<PcbTask> &tasks, const std::vector<int32_t> &adapter_of, std::vector<PcbUnit> &units)
+{
+    units.clear();
+    size_t i = 0;
+    while (i < tasks.size()) {
+        size_t j = i;
+        while (j < tasks.size() && adapter_of[j] == adapter_of[i] && j - i < 64) ++j;
+        PcbUnit u; u.adapter = adapter_of[i]; u.ntask = (int32_t)(j - i); u.task0 = (int64_t)i;
+        units.push_back(u);
+        i = j;
+    }
+}
+
+}  // namespace
+
+extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, const int64_t *seg_off,
+                               const int32_t *seg_len, const int32_t *task_adapter, int64_t n_tasks)
+{
+    if (!c || blob_len < 0 || n_tasks < 0 || (n_tasks > 0 && (!seg_off || !seg_len || !task_adapter)) || (blob_len > 0 && !seq_blob))
+        return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    c->h_tasks.resize((size_t)n_tasks);
+    for (int64_t t = 0; t < n_tasks; ++t) {
+        if (seg_len[t] < 0 || seg_off[t] < 0 || seg_off[t] + seg_len[t] > blob_len)
+            return c->fail(PCB_ERR_ARG, "task %lld: segment [%lld, +%d) outside the blob", (long long)t, (long long)seg_off[t], seg_len[t]);
+        if (task_adapter[t] < 0 || task_adapter[t] >= c->n_adapters)
+            return c->fail(PCB_ERR_ARG, "task %lld: adapter id %d out of range", (long long)t, task_adapter[t]);
+        c->h_tasks[(size_t)t] = { seg_off[t], seg_len[t], task_adapter[t] };
+    }
+    PCB_CUDA(c, c->d_ascii.reserve((size_t)blob_len + 16));
+    PCB_CUDA(c, c->d_arena.reserve((size_t)blob_len + 16));
+    if (blob_len) {
+        PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, seq_blob, (size_t)blob_len, cudaMemcpyHostToDevice, c->stream));
+        PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena.p, (uint64_t)blob_len, c->stream));
+        c->cnt.kernel_launches++;
+    }
+    c->cnt.h2d_bytes += blob_len;
+    c->arena_len = (uint64_t)blob_len;
+    return PCB_OK;
+}
+
+// runs one explicit launch (tasks sorted by adapter) through the trace or scan kernel
+static int run_explicit(pcb_context *c, std::vector<PcbTask> &tasks, std::vector<int32_t> &adapter_of, bool trace,
+                        int mmax, int nmax, int64_t cells)
+{
+    if (tasks.empty()) return PCB_OK;
+    std::vector<PcbUnit> units;
+    build_units(tasks, adapter_of, units);
+    PCB_CUDA(c, c->d_tasks.reserve(tasks.size()));
+    PCB_CUDA(c, c->d_units.reserve(units.size()));
+    PCB_CUDA(c, cudaMemcpyAsync(c->d_tasks.p, tasks.data(), sizeof(PcbTask) * tasks.size(), cudaMemcpyHostToDevice, c->stream));
+    PCB_CUDA(c, cudaMemcpyAsync(c->d_units.p, units.data(), sizeof(PcbUnit) * units.size(), cudaMemcpyHostToDevice, c->stream));
+    c->cnt.h2d_bytes += (int64_t)(sizeof(PcbTask) * tasks.size() + sizeof(PcbUnit) * units.size());
+    const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
+    const int64_t n_units = (int64_t)units.size();
+    const int gmax = trace ? c->grid_trace : c->grid_scan;
+    const int grid = (int)std::min<int64_t>(gmax, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
+    int rc = ensure_scratch(c, trace ? pcb_scratch_words_trace(mmax, smax) : pcb_scratch_words_scan(mmax, smax), grid);
+    if (rc) return rc;
+    PcbLaunch L; fill_launch_common(c, L);
+    L.src.units = c->d_units.p; L.src.tasks = c->d_tasks.p; L.src.n_units = n_units;
+    L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
+    rc = launch_dp(c, L, trace, cells);
+    if (rc) return rc;
+    // the host vectors are about to go out of scope: the copies above must have completed
+    PCB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PCB_OK;
+}
+
+extern "C" int pcb_run_tasks_resident(pcb_context *c)
+{
+    if (!c) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    const size_t nt = c->h_tasks.size();
+    c->n_results = (int64_t)nt;
+    if (nt == 0) return PCB_OK;
+    PCB_CUDA(c, c->d_out.reserve(nt));
+    PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
+
+    // order tasks by adapter (counting sort keeps the input order inside a group)
+    std::vector<int64_t> start((size_t)c->n_adapters + 1, 0);
+    for (auto &t : c->h_tasks) start[(size_t)t.adapter + 1]++;
+    for (int a = 0; a < c->n_adapters; ++a) start[(size_t)a + 1] += start[(size_t)a];
+    std::vector<int64_t> order(nt);
+    {
+        std::vector<int64_t> pos(start.begin(), start.end() - 1);
+        for (size_t t = 0; t < nt; ++t) order[(size_t)pos[(size_t)c->h_tasks[t].adapter]++] = (int64_t)t;
+    }
+
+    const int direct_default = 1024;
+    std::vector<PcbTask> direct, chunks;          // phase-0 trace tasks, phase-1 scan chunks
+    std::vector<int32_t> direct_ad, chunk_ad;
+    struct LongTask { int64_t task; int64_t chunk0; int32_t nchunks; };
+    std::vector<LongTask> longs;
+    int direct_mmax = 1, direct_nmax = 1, scan_mmax = 1, scan_nmax = 1;
+    int64_t direct_cells = 0, scan_cells = 0;
+
+    // chunk length: enough chunks to fill the machine, but long enough to amortise the warm-up margin
+    int64_t long_cols = 0;
+    for (auto &t : c->h_tasks) if (t.len > direct_default) long_cols += t.len;
+    int chunk = (int)std::min<int64_t>(4096, std::max<int64_t>(1024, long_cols / (2 * 64 * (int64_t)std::max(1, c->grid_scan) * (PCB_BLOCK / 32))));
+
+    for (size_t k = 0; k < nt; ++k) {
+        const int64_t ti = order[k];
+        const auto &t = c->h_tasks[(size_t)ti];
+        const int n = (int)(c->ad_off[(size_t)t.adapter + 1] - c->ad_off[(size_t)t.adapter]);
+        const WindowBounds wb = window_bounds(c->sc, n);
+        const int direct_max = std::max(direct_default, wb.ok ? wb.warm + wb.span + 8 : 0);
+        if (t.len <= direct_max || !wb.ok || n == 0) {
+            PcbTask d{}; d.off = (uint64_t)t.off; d.len = t.len; d.col0 = 0; d.m_true = t.len; d.forced_ord = -1;
+            d.out_idx = (int32_t)ti; d.own0 = 0;
+            direct.push_back(d); direct_ad.push_back(t.adapter);
+            direct_mmax = std::max(direct_mmax, t.len); direct_nmax = std::max(direct_nmax, n);
+            direct_cells += (int64_t)t.len * n;
+        } else {
+            LongTask lt{ ti, (int64_t)chunks.size(), 0 };
+            for (int64_t c0 = 0; c0 < t.len; c0 += chunk) {
+                const int64_t col0 = std::max<int64_t>(0, c0 - wb.warm);
+                const int64_t cend = std::min<int64_t>(t.len, c0 + chunk);
+                PcbTask d{}; d.off = (uint64_t)(t.off + col0); d.len = (int32_t)(cend - col0); d.col0 = (int32_t)col0;
+                d.m_true = t.len; d.forced_ord = -1; d.out_idx = (int32_t)chunks.size(); d.own0 = (int32_t)(c0 - col0);
+                chunks.push_back(d); chunk_ad.push_back(t.adapter);
+                scan_mmax = std::max(scan_mmax, d.len);
+                lt.nchunks++;
+            }
+            scan_nmax = std::max(scan_nmax, n);
+            scan_cells += (int64_t)t.len * n;
+            longs.push_back(lt);
+        }
+    }
+
+    int rc;
+    if (!direct.empty()) {
+        if ((rc = check_range(c, direct_nmax, direct_mmax))) return rc;
+        if ((rc = run_explicit(c, direct, direct_ad, true, direct_mmax, direct_nmax, direct_cells))) return rc;
+    }
+    if (!chunks.empty()) {
+        if ((rc = check_range(c, scan_nmax, scan_mmax))) return rc;
+        PCB_CUDA(c, c->d_scan.reserve(chunks.size()));
+        if ((rc = run_explicit(c, chunks, chunk_ad, false, scan_mmax, scan_nmax, scan_cells))) return rc;
+        std::vector<int32_t> keys(chunks.size());
+        PCB_CUDA(c, cudaMemcpyAsync(keys.data(), c->d_scan.p, sizeof(int32_t) * keys.size(), cudaMemcpyDeviceToHost, c->stream));
+        PCB_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->cnt.d2h_bytes += (int64_t)(sizeof(int32_t) * keys.size());
+        // best end cell per long task: highest score, then SeqAn's visiting order (dp_scout.h:167-180)
+        std::vector<PcbTask> wins; std::vector<int32_t> win_ad;
+        int win_mmax = 1, win_nmax = 1; int64_t win_cells = 0;
+        for (auto &lt : longs) {
+            const auto &t = c->h_tasks[(size_t)lt.task];
+            const int n = (int)(c->ad_off[(size_t)t.adapter + 1] - c->ad_off[(size_t)t.adapter]);
+            const WindowBounds wb = window_bounds(c->sc, n);
+            int best_score = INT32_MIN; int64_t best_ord = 0; bool have = false;
+            for (int q = 0; q < lt.nchunks; ++q) {
+                const PcbTask &ch = chunks[(size_t)(lt.chunk0 + q)];
+                const int32_t key = keys[(size_t)(lt.chunk0 + q)];
+                if (key == INT32_MIN) continue;
+                const int score = key >> 16;
+                const int ord_l = 0x3FFF - ((key >> 2) & 0x3FFF);
+                // global order: column for last-row cells, m + row for final-column cells
+                const int64_t ord_g = ord_l <= ch.len ? (int64_t)ch.col0 + ord_l : (int64_t)t.len + (ord_l - ch.len);
+                if (!have || score > best_score || (score == best_score && ord_g < best_ord)) { best_score = score; best_ord = ord_g; have = true; }
+            }
+            if (!have) return c->fail(PCB_ERR_RANGE, "scan produced no candidate for task %lld", (long long)lt.task);
+            const bool rowclass = best_ord < t.len;
+            const int64_t cj = rowclass ? best_ord : t.len;
+            const int64_t ws = std::max<int64_t>(0, cj - (wb.warm + wb.span));
+            PcbTask d{};
+            d.col0 = (int32_t)ws; d.len = (int32_t)std::max<int64_t>(1, cj - ws); d.off = (uint64_t)(t.off + ws);
+            d.m_true = t.len; d.own0 = 0; d.out_idx = (int32_t)lt.task;
+            d.forced_ord = rowclass ? (int32_t)(cj - ws) : (int32_t)(d.len + (best_ord - t.len));
+            wins.push_back(d); win_ad.push_back(t.adapter);
+            win_mmax = std::max(win_mmax, d.len); win_nmax = std::max(win_nmax, n);
+            win_cells += (int64_t)d.len * n;
+        }
+        if ((rc = check_range(c, win_nmax, win_mmax))) return rc;
+        (void)win_cells;   // re-computed cells are not counted as algorithmic work
+        if ((rc = run_explicit(c, wins, win_ad, true, win_mmax, win_nmax, 0))) return rc;
+    }
+    return PCB_OK;
+}
+
+extern "C" int pcb_align_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, const int64_t *seg_off,
+                               const int32_t *seg_len, const int32_t *task_adapter, int64_t n_tasks, pcb_result *out)
+{
+    int rc;
+    if ((rc = pcb_stage_tasks(c, seq_blob, blob_len, seg_off, seg_len, task_adapter, n_tasks))) return rc;
+    if ((rc = pcb_run_tasks_resident(c))) return rc;
+    return pcb_fetch_results(c, out, n_tasks);
+}
+
+// ------------------------------------------------------------------------------------------------
+// result formatting and the reference's two symbols
+// ------------------------------------------------------------------------------------------------
+extern "C" void pcb_format_result(const pcb_result *r, char *buf, uint64_t buflen)
+{
+    // ScoredAlignment::getString (alignment.cpp:112-120): std::to_string = "%d" / "%f";
+    // identities exactly as alignment.cpp:81,89: 100.0 * count / length, evaluated in double.
+    double aligned = 0.0, full = 0.0;
+    if (r->read_start != -1) {
+        aligned = 100.0 * r->matches / r->aligned_len;
+        full = 100.0 * r->matches / r->full_len;
+    }
+    snprintf(buf, (size_t)buflen, "%d,%d,%d,%d,%d,%f,%f", r->read_start, r->read_end, r->adapter_start,
+             r->adapter_end, r->raw_score, aligned, full);
+}
+
+extern "C" int pcb_stats_from_path(const char *ops, int64_t n_ops, int64_t head_h, int64_t head_v, int64_t tail_h,
+                                   int64_t tail_v, const uint8_t *match_flags, int32_t raw_score, pcb_result *out)
+{
+    if (!out || n_ops < 0 || (n_ops > 0 && (!ops || !match_flags))) return PCB_ERR_ARG;
+    PathAcc acc; path_acc_init(acc);
+    int64_t m = head_h + tail_h, n = head_v + tail_v;
+    for (int64_t k = n_ops - 1; k >= 0; --k) {              // the kernels walk the path back to front
+        const int op = ops[k] == 'D' ? 0 : (ops[k] == 'V' ? 1 : 2);
+        path_acc_step(acc, op, match_flags[k]);
+        if (op != 2) ++n;
+        if (op != 1) ++m;
+    }
+    PathStats st; path_finalize(acc, head_h, head_v, tail_h, tail_v, m, n, st);
+    out->read_start = st.read_start; out->read_end = st.read_end; out->adapter_start = st.adapter_start;
+    out->adapter_end = st.adapter_end; out->raw_score = raw_score; out->matches = st.matches;
+    out->aligned_len = st.aligned_len; out->full_len = st.full_len;
+    return PCB_OK;
+}
+
+static std::mutex g_mu;
+static pcb_context *g_ctx = nullptr;
+
+static char *dup_cstring(const char *s)
+{
+    const size_t n = strlen(s);
+    char *p = (char *)malloc(n + 1);      // released by freeCString, as adapter_align.cpp:34-44 does
+    if (p) memcpy(p, s, n + 1);
+    return p;
+}
+
+extern "C" char *adapterAlignment(char *readSeq, char *adapterSeq, int matchScore, int mismatchScore,
+                                  int gapOpenScore, int gapExtensionScore)
+{
+    static const char *kFailed = "-1,0,-1,0,-2147483648,0.000000,0.000000";
+    std::lock_guard<std::mutex> lock(g_mu);
+    g_global_err.clear();
+    if (!readSeq || !adapterSeq) { g_global_err = "null sequence"; return dup_cstring(kFailed); }
+    if (!g_ctx) {
+        int dev = 0;
+        if (const char *e = getenv("PCB_DEVICE")) dev = atoi(e);
+        if (pcb_create(dev, &g_ctx) != PCB_OK) {
+            fprintf(stderr, "cpp_functions.so (B200): %s\n", g_global_err.c_str());
+            return dup_cstring(kFailed);
+        }
+    }
+    pcb_context *c = g_ctx;
+    const int64_t m = (int64_t)strlen(readSeq), n = (int64_t)strlen(adapterSeq);
+    const int64_t aoff[2] = { 0, n };
+    const int64_t soff = 0; const int32_t slen = (int32_t)m, aid = 0;
+    pcb_result r;
+    int rc = pcb_set_scoring(c, matchScore, mismatchScore, gapOpenScore, gapExtensionScore);
+    if (!rc) rc = pcb_set_adapters(c, adapterSeq, aoff, 1);
+    if (!rc) rc = pcb_align_tasks(c, readSeq, m, &soff, &slen, &aid, 1, &r);
+    if (rc) {
+        g_global_err = c->err;
+        fprintf(stderr, "cpp_functions.so (B200): adapterAlignment failed: %s\n", c->err.c_str());
+        return dup_cstring(kFailed);
+    }
+    char buf[192];
+    pcb_format_result(&r, buf, sizeof buf);
+    return dup_cstring(buf);
+}
+
+extern "C" void freeCString(char *p) { free(p); }

@@ -1,0 +1,190 @@
+"""
+AlignmentEngine -- batched submit/collect over the C ABI (include/porechop_b200.h).
+
+This is the host-side replacement for the reference's per-pair call inside a thread pool
+(porechop_abi.py:228-239, :406-432, :500-517 -> nanopore_read.align_adapter, nanopore_read.py:485-500):
+one engine per GPU, adapters and scoring scheme set once, then whole phases submitted at a time.
+Results come back as a numpy structured array with the integer fields the reference's result string is
+printed from; ``identities()`` evaluates the two percent identities in double exactly as
+src/alignment.cpp:81,89 does, and ``to_align_adapter_tuple`` reproduces what nanopore_read.align_adapter
+returns from the string.
+"""
+import ctypes
+from ctypes import byref, c_float, c_void_p
+
+import numpy as np
+
+from . import cpp_function_wrappers as w
+
+RESULT_DTYPE = np.dtype([('read_start', '<i4'), ('read_end', '<i4'), ('adapter_start', '<i4'),
+                         ('adapter_end', '<i4'), ('raw_score', '<i4'), ('matches', '<i4'),
+                         ('aligned_len', '<i4'), ('full_len', '<i4')])
+assert RESULT_DTYPE.itemsize == ctypes.sizeof(w.PcbResult)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(c_void_p)
+
+
+class AlignmentEngine(object):
+    def __init__(self, device=0, scoring_scheme_vals=(3, -6, -5, -2)):
+        self._h = c_void_p()
+        rc = w.C_LIB.pcb_create(int(device), byref(self._h))
+        if rc != 0:
+            raise w.AlignmentError('pcb_create failed (%d): %s' % (rc, w.C_LIB.pcb_last_error(None).decode()))
+        self.device = device
+        self.adapters = []
+        self.set_scoring(scoring_scheme_vals)
+
+    # -- plumbing -----------------------------------------------------------------------------
+    def _check(self, rc, what):
+        if rc != 0:
+            raise w.AlignmentError('%s failed (%d): %s' % (what, rc, w.C_LIB.pcb_last_error(self._h).decode()))
+
+    def close(self):
+        if self._h:
+            w.C_LIB.pcb_destroy(self._h)
+            self._h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- configuration ------------------------------------------------------------------------
+    def set_scoring(self, vals):
+        """[match, mismatch, gap_open, gap_extend], the order of --scoring_scheme (arg_parser.py:178,230-236)."""
+        self.scoring = tuple(int(v) for v in vals)
+        self._check(w.C_LIB.pcb_set_scoring(self._h, *self.scoring), 'pcb_set_scoring')
+
+    def set_adapters(self, sequences):
+        """sequences: list of str / bytes. Adapter ids used everywhere else are indices into this list."""
+        seqs = [s.encode() if isinstance(s, str) else bytes(s) for s in sequences]
+        blob = b''.join(seqs)
+        off = np.zeros(len(seqs) + 1, dtype=np.int64)
+        if seqs:
+            off[1:] = np.cumsum([len(s) for s in seqs])
+        self._check(w.C_LIB.pcb_set_adapters(self._h, blob, off.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
+                                             len(seqs)), 'pcb_set_adapters')
+        self.adapters = seqs
+
+    # -- windows x adapters (phases A and B) --------------------------------------------------------
+    @staticmethod
+    def pack_windows(windows, stride=None):
+        """list of str/bytes windows -> (uint8 array [n, stride], int32 lengths)."""
+        ws = [x.encode() if isinstance(x, str) else bytes(x) for x in windows]
+        lens = np.array([len(x) for x in ws], dtype=np.int32)
+        if stride is None:
+            stride = max(16, int(-(-max([1] + [len(x) for x in ws]) // 16) * 16))
+        buf = np.zeros((len(ws), stride), dtype=np.uint8)
+        for i, x in enumerate(ws):
+            buf[i, :len(x)] = np.frombuffer(x, dtype=np.uint8)
+        return buf, lens
+
+    def align_windows(self, win_buf, win_len, adapter_ids):
+        """Every window against every listed adapter. Returns records of shape [n_windows, len(adapter_ids)]."""
+        win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)
+        win_len = np.ascontiguousarray(win_len, dtype=np.int32)
+        ids = np.ascontiguousarray(adapter_ids, dtype=np.int32)
+        n, stride = win_buf.shape
+        out = np.empty((n, len(ids)), dtype=RESULT_DTYPE)
+        self._check(w.C_LIB.pcb_align_windows(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids),
+                                              _ptr(out)), 'pcb_align_windows')
+        return out
+
+    def stage_windows(self, win_buf, win_len, adapter_ids):
+        win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)
+        win_len = np.ascontiguousarray(win_len, dtype=np.int32)
+        ids = np.ascontiguousarray(adapter_ids, dtype=np.int32)
+        n, stride = win_buf.shape
+        self._check(w.C_LIB.pcb_stage_windows(self._h, _ptr(win_buf), n, stride, _ptr(win_len)), 'pcb_stage_windows')
+        self._check(w.C_LIB.pcb_stage_ids(self._h, _ptr(ids), len(ids)), 'pcb_stage_ids')
+        self.synchronize()
+        self._staged_shape = (n, len(ids))
+
+    def run_windows_resident(self):
+        self._check(w.C_LIB.pcb_run_windows_resident(self._h), 'pcb_run_windows_resident')
+
+    def fetch(self, shape=None):
+        shape = shape or self._staged_shape
+        out = np.empty(shape, dtype=RESULT_DTYPE)
+        self._check(w.C_LIB.pcb_fetch_results(self._h, _ptr(out), int(np.prod(shape))), 'pcb_fetch_results')
+        return out
+
+    # -- explicit tasks (phase C and anything irregular) ------------------------------------------------
+    def align_tasks(self, blob, seg_off, seg_len, task_adapter):
+        """task t = blob[seg_off[t] : seg_off[t] + seg_len[t]] vs adapter task_adapter[t]; any length."""
+        blob = np.frombuffer(blob, dtype=np.uint8) if isinstance(blob, (bytes, bytearray)) else np.ascontiguousarray(blob, dtype=np.uint8)
+        seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+        seg_len = np.ascontiguousarray(seg_len, dtype=np.int32)
+        ad = np.ascontiguousarray(task_adapter, dtype=np.int32)
+        out = np.empty(len(ad), dtype=RESULT_DTYPE)
+        self._check(w.C_LIB.pcb_align_tasks(self._h, _ptr(blob), blob.size, _ptr(seg_off), _ptr(seg_len), _ptr(ad),
+                                            len(ad), _ptr(out)), 'pcb_align_tasks')
+        return out
+
+    def stage_tasks(self, blob, seg_off, seg_len, task_adapter):
+        blob = np.frombuffer(blob, dtype=np.uint8) if isinstance(blob, (bytes, bytearray)) else np.ascontiguousarray(blob, dtype=np.uint8)
+        seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+        seg_len = np.ascontiguousarray(seg_len, dtype=np.int32)
+        ad = np.ascontiguousarray(task_adapter, dtype=np.int32)
+        self._check(w.C_LIB.pcb_stage_tasks(self._h, _ptr(blob), blob.size, _ptr(seg_off), _ptr(seg_len), _ptr(ad),
+                                            len(ad)), 'pcb_stage_tasks')
+        self.synchronize()
+        self._staged_shape = (len(ad),)
+
+    def run_tasks_resident(self):
+        self._check(w.C_LIB.pcb_run_tasks_resident(self._h), 'pcb_run_tasks_resident')
+
+    def align_pairs(self, pairs):
+        """Convenience: list of (read_str, adapter_id) -> records."""
+        seqs = [p[0].encode() if isinstance(p[0], str) else bytes(p[0]) for p in pairs]
+        lens = np.array([len(s) for s in seqs], dtype=np.int32)
+        off = np.zeros(len(seqs), dtype=np.int64)
+        if len(seqs) > 1:
+            off[1:] = np.cumsum(lens[:-1], dtype=np.int64)
+        return self.align_tasks(b''.join(seqs), off, lens, [p[1] for p in pairs])
+
+    # -- timing / counters ---------------------------------------------------------------------
+    def timer_start(self):
+        self._check(w.C_LIB.pcb_timer_start(self._h), 'pcb_timer_start')
+
+    def timer_stop(self):
+        ms = c_float()
+        self._check(w.C_LIB.pcb_timer_stop(self._h, byref(ms)), 'pcb_timer_stop')
+        return ms.value
+
+    def synchronize(self):
+        self._check(w.C_LIB.pcb_synchronize(self._h), 'pcb_synchronize')
+
+    def counters(self):
+        c = w.PcbCounters()
+        self._check(w.C_LIB.pcb_get_counters(self._h, byref(c)), 'pcb_get_counters')
+        return {f: getattr(c, f) for f, _ in w.PcbCounters._fields_}
+
+    def reset_counters(self):
+        self._check(w.C_LIB.pcb_reset_counters(self._h), 'pcb_reset_counters')
+
+    def set_kernel_timing(self, on):
+        self._check(w.C_LIB.pcb_set_kernel_timing(self._h, 1 if on else 0), 'pcb_set_kernel_timing')
+
+
+def identities(rec):
+    """(aligned_region_percent_identity, full_adapter_percent_identity) as src/alignment.cpp:81,89."""
+    with np.errstate(divide='ignore', invalid='ignore'):
+        aligned = 100.0 * rec['matches'].astype(np.float64) / rec['aligned_len'].astype(np.float64)
+        full = 100.0 * rec['matches'].astype(np.float64) / rec['full_len'].astype(np.float64)
+    return aligned, full
+
+
+def to_align_adapter_tuple(rec):
+    """
+    One record -> what nanopore_read.align_adapter returns (nanopore_read.py:485-500):
+    (full_adapter_percent_identity, aligned_region_percent_identity, read_start, read_end [exclusive]).
+    The reference parses the printed string, so the identities go through the same "%f" round trip.
+    """
+    if int(rec['read_start']) == -1:
+        return 0.0, 0.0, -1, 0
+    parts = w.format_result(rec).split(',')
+    return float(parts[6]), float(parts[5]), int(parts[0]), int(parts[1]) + 1

@@ -1,0 +1,140 @@
+/*
+ * porechop_b200.h -- C ABI of the B200-native adapter-alignment library (cpp_functions.so).
+ *
+ * This is the drop-in boundary.  The first two entry points are EXACTLY what the reference's
+ * ctypes wrapper binds (reference: porechop_abi/cpp_function_wrappers.py:27-39, declared in
+ * porechop_abi/include/adapter_align.h:12-16, implemented in porechop_abi/src/adapter_align.cpp:11-36).
+ * The pcb_* entry points are the batched form of the same call: the reference makes one
+ * adapterAlignment call per (sequence window, adapter) pair from
+ *   nanopore_read.py:158-173 (align_adapter_set), :175-217 (find_start_trim / find_end_trim),
+ *   :219-252 (find_middle_adapters);
+ * the batched entry points take all those pairs at once and return, per pair, the integers the
+ * result string is printed from (porechop_abi/src/alignment.cpp:112-120).
+ *
+ * Plain pointers and sizes only; no torch / CUDA types appear in any signature.  All compute runs
+ * in hand-written sm_100a CUDA kernels; there is no CPU fallback: every compute entry point fails
+ * (non-zero return, pcb_last_error() says why) when no CUDA device is usable.
+ */
+#ifndef PORECHOP_B200_H
+#define PORECHOP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- 1. the reference's own two symbols (adapter_align.h:12-16) ------------------------------ */
+
+/* Returns a malloc'd "readStart,readEnd,adapterStart,adapterEnd,rawScore,alignedId,fullId" string
+ * (alignment.cpp:112-120), to be released with freeCString.  On a device error it returns the
+ * reference's own failure encoding (readStart == -1, alignment.cpp:7-21) and pcb_last_error(NULL)
+ * holds the reason. */
+char *adapterAlignment(char *readSeq, char *adapterSeq,
+                       int matchScore, int mismatchScore, int gapOpenScore, int gapExtensionScore);
+void freeCString(char *p);
+
+/* ---- 2. batched form ------------------------------------------------------------------------- */
+
+typedef struct pcb_context pcb_context;
+
+/* The integers ScoredAlignment holds (alignment.h:17-25).  alignedRegionPercentIdentity is
+ * 100.0 * matches / aligned_len and fullAdapterPercentIdentity is 100.0 * matches / full_len,
+ * evaluated in double exactly as alignment.cpp:81,89 do (the two match counts of the reference are
+ * always equal).  read_start == -1 marks the reference's "alignment failed" case
+ * (empty sequence). read_end is inclusive, as the C++ prints it. */
+typedef struct pcb_result {
+    int32_t read_start;
+    int32_t read_end;
+    int32_t adapter_start;
+    int32_t adapter_end;
+    int32_t raw_score;
+    int32_t matches;
+    int32_t aligned_len;
+    int32_t full_len;
+} pcb_result;
+
+/* Error codes returned by the pcb_* calls (0 = ok). */
+#define PCB_OK            0
+#define PCB_ERR_CUDA      1   /* a CUDA runtime call failed or no device is present       */
+#define PCB_ERR_ARG       2   /* bad argument                                              */
+#define PCB_ERR_RANGE     3   /* scoring scheme / lengths outside what the kernels support */
+#define PCB_ERR_NOMEM     4
+
+int  pcb_create(int device, pcb_context **out);
+void pcb_destroy(pcb_context *ctx);
+/* Last error text of this context (ctx == NULL: of the process-wide context adapterAlignment uses). */
+const char *pcb_last_error(pcb_context *ctx);
+int  pcb_device_count(void);
+
+/* Scoring scheme, argument order as adapterAlignment's. */
+int pcb_set_scoring(pcb_context *ctx, int match, int mismatch, int gap_open, int gap_extend);
+
+/* Adapter set: ASCII blob + n_adapters+1 offsets.  Converted with SeqAn's Dna5 table
+ * (seqan/basic/alphabet_residue_tabs.h:113-140) on the device. */
+int pcb_set_adapters(pcb_context *ctx, const char *blob, const int64_t *offsets, int32_t n_adapters);
+
+/* Cross product "every window x every listed adapter" (phases A and B of the reference:
+ * porechop_abi.py:200-245, :359-438).  windows: n_windows records of `stride` bytes each, of which
+ * the first win_len[w] bytes are the window (ASCII).  out[w * n_ids + k] = window w vs adapter_ids[k].
+ * HOST buffers; copies are part of the call. */
+int pcb_align_windows(pcb_context *ctx, const char *windows, int64_t n_windows, int32_t stride,
+                      const int32_t *win_len, const int32_t *adapter_ids, int32_t n_ids,
+                      pcb_result *out);
+
+/* Explicit task list (phase C, porechop_abi.py:457-522, and anything irregular): task t aligns
+ * seq_blob[seg_off[t] .. seg_off[t]+seg_len[t]) against adapter task_adapter[t].  Any length.
+ * HOST buffers. */
+int pcb_align_tasks(pcb_context *ctx, const char *seq_blob, int64_t blob_len,
+                    const int64_t *seg_off, const int32_t *seg_len, const int32_t *task_adapter,
+                    int64_t n_tasks, pcb_result *out);
+
+/* ---- 3. device-resident form (same kernels; used to time the kernels without PCIe) ---------- */
+
+/* Stage inputs in HBM (H2D + Dna5 encode). */
+int pcb_stage_windows(pcb_context *ctx, const char *windows, int64_t n_windows, int32_t stride,
+                      const int32_t *win_len);
+int pcb_stage_ids(pcb_context *ctx, const int32_t *adapter_ids, int32_t n_ids);
+/* Run the cross product on the staged windows; results stay in HBM. */
+int pcb_run_windows_resident(pcb_context *ctx);
+/* Copy the staged run's results to the host (n_windows * n_ids records). */
+int pcb_fetch_results(pcb_context *ctx, pcb_result *out, int64_t n_results);
+
+int pcb_stage_tasks(pcb_context *ctx, const char *seq_blob, int64_t blob_len,
+                    const int64_t *seg_off, const int32_t *seg_len, const int32_t *task_adapter,
+                    int64_t n_tasks);
+int pcb_run_tasks_resident(pcb_context *ctx);
+
+/* CUDA-event timer on the library's own stream. */
+int pcb_timer_start(pcb_context *ctx);
+int pcb_timer_stop(pcb_context *ctx, float *ms);
+int pcb_synchronize(pcb_context *ctx);
+
+/* Counters since context creation: kernel launches, DP cell updates issued, H2D / D2H bytes. */
+typedef struct pcb_counters {
+    int64_t kernel_launches;
+    int64_t dp_cells;
+    int64_t h2d_bytes;
+    int64_t d2h_bytes;
+    int64_t dp_kernel_launches;
+    float   dp_kernel_ms;      /* summed CUDA-event time of the DP kernels (when profiling enabled) */
+} pcb_counters;
+int pcb_get_counters(pcb_context *ctx, pcb_counters *out);
+int pcb_reset_counters(pcb_context *ctx);
+/* When on, every DP kernel launch is bracketed by its own event pair (adds sync at fetch time). */
+int pcb_set_kernel_timing(pcb_context *ctx, int on);
+
+/* Formats one record exactly as ScoredAlignment::getString(); buf >= 160 bytes. */
+void pcb_format_result(const pcb_result *r, char *buf, uint64_t buflen);
+
+/* Host-only helper (no device needed): the ScoredAlignment statistics from an explicit alignment
+ * path.  ops = core path front to back, 'D' / 'V' (adapter base over read gap) / 'H'.  Exposed so that
+ * the CPU test-suite can check the same code the kernels run for their statistics. */
+int pcb_stats_from_path(const char *ops, int64_t n_ops, int64_t head_h, int64_t head_v,
+                        int64_t tail_h, int64_t tail_v, const uint8_t *match_flags,
+                        int32_t raw_score, pcb_result *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -49,10 +49,13 @@ static void failed_result(pc_oracle_result *out)
     out->full_matches = 0; out->full_len = 0;
 }
 
-int pc_oracle_align_n(const char *read_seq, long m, const char *adapter_seq, long n,
+/* path_ops / path_flags / path_meta may be NULL; when given they receive the core path front to back
+ * ('D','V','H'), a 1 per column whose two bases are equal, and {head_h, head_v, tail_h, tail_v, score}. */
+static int align_impl(const char *read_seq, long m, const char *adapter_seq, long n,
                       int match, int mismatch, int gap_open, int gap_extend,
-                      pc_oracle_result *out)
+                      pc_oracle_result *out, char *path_ops, char *path_flags, long *path_meta, long *path_n)
 {
+    if (path_n) *path_n = 0;
     if (m <= 0 || n <= 0) { failed_result(out); return 0; }
 
     const int affine = (gap_open != gap_extend);   /* global_alignment_unbanded.h:216-219 */
@@ -185,7 +188,10 @@ int pc_oracle_align_n(const char *read_seq, long m, const char *adapter_seq, lon
         long p = 0, ri = 0, ai = 0;
         for (long k = 0; k < headH; ++k) { rrow[p] = letters[h[ri++]]; arow[p] = '-'; ++p; }
         for (long k = 0; k < headV; ++k) { rrow[p] = '-'; arow[p] = letters[v[ai++]]; ++p; }
+        if (path_meta) { path_meta[0] = headH; path_meta[1] = headV; path_meta[2] = tailH; path_meta[3] = tailV; path_meta[4] = best; }
+        if (path_n) *path_n = nops;
         for (long k = nops - 1; k >= 0; --k) {
+            if (path_ops) { path_ops[nops - 1 - k] = ops[k]; path_flags[nops - 1 - k] = (char)(ops[k] == 'D' && h[ri] == v[ai]); }
             if (ops[k] == 'D')      { rrow[p] = letters[h[ri++]]; arow[p] = letters[v[ai++]]; }
             else if (ops[k] == 'V') { rrow[p] = '-';              arow[p] = letters[v[ai++]]; }
             else                    { rrow[p] = letters[h[ri++]]; arow[p] = '-'; }
@@ -235,6 +241,21 @@ int pc_oracle_align_n(const char *read_seq, long m, const char *adapter_seq, lon
     }
     free(rrow); free(arow); free(h); free(v); free(colM); free(colH); free(trace); free(ops);
     return 0;
+}
+
+int pc_oracle_align_n(const char *read_seq, long m, const char *adapter_seq, long n,
+                      int match, int mismatch, int gap_open, int gap_extend, pc_oracle_result *out)
+{
+    return align_impl(read_seq, m, adapter_seq, n, match, mismatch, gap_open, gap_extend, out, NULL, NULL, NULL, NULL);
+}
+
+long pc_oracle_path(const char *read_seq, long m, const char *adapter_seq, long n,
+                    int match, int mismatch, int gap_open, int gap_extend,
+                    char *ops, char *flags, long *meta)
+{
+    pc_oracle_result r; long k = 0;
+    if (align_impl(read_seq, m, adapter_seq, n, match, mismatch, gap_open, gap_extend, &r, ops, flags, meta, &k) != 0) return -1;
+    return k;
 }
 
 int pc_oracle_align(const char *read_seq, const char *adapter_seq,

@@ -47,6 +47,12 @@ int pc_oracle_align_n(const char *read_seq, long read_len, const char *adapter_s
                       int match, int mismatch, int gap_open, int gap_extend,
                       pc_oracle_result *out);
 
+/* Test helper: the alignment path itself. ops/flags need read_len + adapter_len + 1 bytes; meta = 5 longs
+ * {head_h, head_v, tail_h, tail_v, score}. Returns the number of core columns, -1 on failure. */
+long pc_oracle_path(const char *read_seq, long read_len, const char *adapter_seq, long adapter_len,
+                    int match, int mismatch, int gap_open, int gap_extend,
+                    char *ops, char *flags, long *meta);
+
 /* Formats a result exactly as ScoredAlignment::getString() (alignment.cpp:112-120). buf >= 160 bytes. */
 void pc_oracle_format(const pc_oracle_result *r, char *buf, unsigned long buflen);
 

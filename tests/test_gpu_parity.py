@@ -1,0 +1,130 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle on the same seeded inputs.
+Bit-exact bar: every integer field; the printed string (identities via "%f") must be identical too."""
+import random
+
+import numpy as np
+import pytest
+
+from oracle_lib import oracle_align, oracle_string, random_case, rec_matches_oracle
+
+pytestmark = pytest.mark.gpu
+
+DEFAULT = (3, -6, -5, -2)
+
+
+def _check_pairs(engine, pairs, adapters, scores):
+    engine.set_scoring(scores)
+    engine.set_adapters(adapters)
+    recs = engine.align_pairs(pairs)
+    from custom_porechop_abi_b200.cpp_function_wrappers import format_result
+    bad = []
+    for (read, aid), rec in zip(pairs, recs):
+        o = oracle_align(read, adapters[aid], scores)
+        if not rec_matches_oracle(rec, o) or format_result(rec) != oracle_string(read, adapters[aid], scores):
+            bad.append((read, adapters[aid], scores, format_result(rec), oracle_string(read, adapters[aid], scores)))
+    assert not bad, bad[:5]
+
+
+def test_single_pair_dropin_symbol():
+    from custom_porechop_abi_b200.cpp_function_wrappers import adapter_alignment
+    cases = [("ACGTACGTTTGACCA", "GGGGGGG"), ("ACGTACGTTTGACCA", "TTGACCATTAGC"), ("ACGTACGTTTGACCA", "CCCACGTACG"),
+             ("ACGTACGTTTGACCA", "ACGTTTG"), ("A", "C"), ("A", "A"), ("ACGT", "ACGTACGTTTGACCA"), ("NNNN", "ACGT"),
+             ("acgtuu--xx", "ACGTTTNNNN"), ("", "ACGT"), ("ACGT", ""), ("", "")]
+    for r, a in cases:
+        for s in (DEFAULT, (3, -6, -5, -5), (1, -1, -3, -2)):
+            assert adapter_alignment(r, a, list(s)) == oracle_string(r, a, s), (r, a, s)
+
+
+@pytest.mark.parametrize('seed', [1, 2, 3])
+def test_random_pairs_default_scheme(engine, seed):
+    rng = random.Random(seed)
+    adapters, pairs = [], []
+    for _ in range(40):
+        r, a = random_case(rng)
+        adapters.append(a)
+    for _ in range(3000):
+        aid = rng.randrange(len(adapters))
+        r, _ = random_case(rng)
+        if rng.random() < 0.5:
+            from oracle_lib import mutate
+            a = adapters[aid]
+            p = rng.randrange(0, max(1, len(r)))
+            r = (r[:p] + mutate(rng, a, rng.choice([0, 0.1, 0.2])) + r[p:])[:max(len(r), 1)]
+        pairs.append((r, aid))
+    _check_pairs(engine, pairs, adapters, DEFAULT)
+
+
+@pytest.mark.parametrize('scores', [(3, -6, -5, -5), (1, -1, -1, -1), (2, -3, -4, -1), (5, -4, -10, -1), (1, -1, -3, -2),
+                                    (3, -6, -2, -5), (1, 0, 0, 0), (1, -1, 1, 1), (0, 0, 0, 0), (2, 2, -1, -2)])
+def test_random_pairs_other_schemes(engine, scores):
+    rng = random.Random(hash(scores) & 0xffff)
+    adapters = [random_case(rng)[1] for _ in range(12)]
+    pairs = []
+    for _ in range(600):
+        r, _ = random_case(rng, m_choices=(1, 2, 3, 7, 20, 60, 150))
+        pairs.append((r, rng.randrange(len(adapters))))
+    _check_pairs(engine, pairs, adapters, scores)
+
+
+def test_long_adapters_multi_stripe(engine):
+    rng = random.Random(5)
+    adapters = [''.join(rng.choice('ACGT') for _ in range(n)) for n in (31, 32, 33, 63, 64, 65, 96, 111, 130)]
+    pairs = []
+    from oracle_lib import mutate
+    for _ in range(400):
+        aid = rng.randrange(len(adapters))
+        m = rng.choice([1, 5, 40, 150, 150, 400])
+        r = ''.join(rng.choice('ACGT') for _ in range(m))
+        if rng.random() < 0.7:
+            p = rng.randrange(-len(adapters[aid]), m)
+            ins = mutate(rng, adapters[aid], rng.choice([0, 0.05, 0.2]))
+            r = (ins[-p:] + r)[:m] if p < 0 else (r[:p] + ins + r[p:])[:m]
+            r = r or 'A'
+        pairs.append((r, aid))
+    _check_pairs(engine, pairs, adapters, DEFAULT)
+
+
+def test_windows_cross_product(engine):
+    rng = random.Random(9)
+    adapters = [''.join(rng.choice('ACGT') for _ in range(rng.choice([22, 24, 28, 30, 50]))) for _ in range(9)]
+    from oracle_lib import mutate
+    windows = []
+    for _ in range(333):
+        m = rng.choice([150] * 6 + [0, 1, 17, 149])
+        r = ''.join(rng.choice('ACGT') for _ in range(m))
+        if m > 60 and rng.random() < 0.6:
+            a = rng.choice(adapters)
+            p = rng.randrange(-10, m - 10)
+            ins = mutate(rng, a, 0.1)
+            r = (ins[-p:] + r)[:m] if p < 0 else (r[:p] + ins + r[p:])[:m]
+        windows.append(r)
+    engine.set_scoring(DEFAULT)
+    engine.set_adapters(adapters)
+    buf, lens = engine.pack_windows(windows, stride=160)
+    ids = [0, 3, 4, 8, 1]
+    out = engine.align_windows(buf, lens, ids)
+    assert out.shape == (len(windows), len(ids))
+    for w, r in enumerate(windows):
+        for k, aid in enumerate(ids):
+            assert rec_matches_oracle(out[w, k], oracle_align(r, adapters[aid], DEFAULT)), (r, adapters[aid])
+
+
+def test_long_reads_scan_then_window(engine):
+    rng = random.Random(21)
+    adapters = ['AATGTACTTCGTTCAGTTACGTATTGCT', 'GCAATACGTAACTGAACGAAGT', ''.join(rng.choice('ACGT') for _ in range(70))]
+    from oracle_lib import mutate
+    pairs = []
+    for _ in range(60):
+        m = rng.choice([1100, 2500, 5000, 12000, 30000])
+        r = ''.join(rng.choice('ACGT') for _ in range(m))
+        aid = rng.randrange(len(adapters))
+        k = rng.choice([0, 1, 1, 2])
+        for _ in range(k):
+            p = rng.randrange(-20, m)
+            ins = mutate(rng, adapters[aid], rng.choice([0, 0.05, 0.15]))
+            r = (ins[-p:] + r)[:m] if p < 0 else (r[:p] + ins + r[p:])[:m]
+        if rng.random() < 0.2:
+            q = rng.randrange(0, m - 50)
+            r = r[:q] + '-' * 40 + r[q + 40:]      # masked stretch, as find_middle_adapters produces (nanopore_read.py:233-234)
+        pairs.append((r, aid))
+    _check_pairs(engine, pairs, adapters, DEFAULT)
