@@ -59,6 +59,7 @@ C_LIB.pcb_destroy.restype = None
 C_LIB.pcb_last_error.argtypes = [_P]
 C_LIB.pcb_last_error.restype = c_char_p
 C_LIB.pcb_device_count.argtypes = []
+C_LIB.pcb_select_slot.argtypes = [_P, c_int]
 C_LIB.pcb_set_scoring.argtypes = [_P, c_int, c_int, c_int, c_int]
 C_LIB.pcb_set_adapters.argtypes = [_P, c_char_p, POINTER(c_int64), c_int32]
 C_LIB.pcb_align_windows.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, c_void_p]

@@ -54,11 +54,23 @@ struct pcb_context {
     DevBuf<int64_t> d_ad_off;
     // staged inputs
     DevBuf<char> d_ascii;
-    DevBuf<uint8_t> d_arena;
-    uint64_t arena_len = 0;
-    DevBuf<int32_t> d_winlen, d_ids;
-    std::vector<int32_t> h_ids;
-    int64_t n_windows = 0; int32_t stride = 0, n_ids = 0, win_mmax = 0;
+    DevBuf<uint8_t> d_arena_t;        // explicit-task arena (kept apart so both inputs can stay resident)
+    uint64_t arena_t_len = 0;
+    // staged window sets + their results: a context holds PCB_SLOTS independent sets so that several inputs
+    // (start windows, end windows, full-length tasks) can be resident at once; pcb_select_slot picks one
+    struct Slot {
+        DevBuf<uint8_t> d_arena;          // window arena
+        uint64_t arena_len = 0;
+        int64_t sum_winlen = 0;
+        DevBuf<int32_t> d_winlen, d_ids;
+        std::vector<int32_t> h_ids;
+        int64_t n_windows = 0; int32_t stride = 0, n_ids = 0, win_mmax = 0;
+        DevBuf<pcb_result> d_out;
+        int64_t n_results = 0;
+    };
+    Slot slots[4];
+    int cur = 0;
+    Slot &S() { return slots[cur]; }
     // explicit tasks
     struct HostTask { int64_t off; int32_t len; int32_t adapter; };
     std::vector<HostTask> h_tasks;
@@ -66,8 +78,6 @@ struct pcb_context {
     DevBuf<PcbUnit> d_units;
     DevBuf<int32_t> d_scan;
     // outputs / scratch
-    DevBuf<pcb_result> d_out;
-    int64_t n_results = 0;
     DevBuf<uint32_t> d_scratch;
     DevBuf<int32_t> d_err;
     int grid_trace = 0, grid_scan = 0;
@@ -132,15 +142,23 @@ extern "C" void pcb_destroy(pcb_context *c)
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_arena.release();
-    c->d_winlen.release(); c->d_ids.release(); c->d_tasks.release(); c->d_units.release(); c->d_scan.release();
-    c->d_out.release(); c->d_scratch.release(); c->d_err.release();
+    c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_arena_t.release();
+    for (auto &sl : c->slots) { sl.d_arena.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release(); }
+    c->d_tasks.release(); c->d_units.release(); c->d_scan.release();
+    c->d_scratch.release(); c->d_err.release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->kev0); cudaEventDestroy(c->kev1);
     cudaStreamDestroy(c->stream);
     delete c;
 }
 
 extern "C" const char *pcb_last_error(pcb_context *c) { return c ? c->err.c_str() : g_global_err.c_str(); }
+
+extern "C" int pcb_select_slot(pcb_context *c, int slot)
+{
+    if (!c || slot < 0 || slot >= 4) return PCB_ERR_ARG;
+    c->cur = slot;
+    return PCB_OK;
+}
 
 extern "C" int pcb_set_scoring(pcb_context *c, int match, int mismatch, int gap_open, int gap_extend)
 {
@@ -208,13 +226,13 @@ static int max_adapter_len(pcb_context *c, const int32_t *ids, int n)
     return mx;
 }
 
-static void fill_launch_common(pcb_context *c, PcbLaunch &L)
+static void fill_launch_common(pcb_context *c, PcbLaunch &L, bool task_arena = false)
 {
     memset(&L, 0, sizeof L);
     L.ad.codes = c->d_ad_codes.p; L.ad.off = c->d_ad_off.p;
     L.sc = c->sc;
-    L.arena = c->d_arena.p; L.arena_len = c->arena_len;
-    L.out = c->d_out.p; L.scan_out = c->d_scan.p;
+    L.arena = task_arena ? c->d_arena_t.p : c->S().d_arena.p; L.arena_len = task_arena ? c->arena_t_len : c->S().arena_len;
+    L.out = c->S().d_out.p; L.scan_out = c->d_scan.p;
     L.scratch = c->d_scratch.p; L.err_flag = c->d_err.p;
 }
 
@@ -249,23 +267,24 @@ extern "C" int pcb_stage_windows(pcb_context *c, const char *windows, int64_t n_
 {
     if (!c || n_windows < 0 || stride <= 0 || (n_windows > 0 && (!windows || !win_len))) return PCB_ERR_ARG;
     cudaSetDevice(c->device);
-    int mmax = 0;
+    int mmax = 0; int64_t sumlen = 0;
     for (int64_t w = 0; w < n_windows; ++w) {
         if (win_len[w] < 0 || win_len[w] > stride) return c->fail(PCB_ERR_ARG, "win_len[%lld] = %d outside [0, stride]", (long long)w, win_len[w]);
-        mmax = std::max(mmax, win_len[w]);
+        mmax = std::max(mmax, win_len[w]); sumlen += win_len[w];
     }
+    c->S().sum_winlen = sumlen;
     const uint64_t bytes = (uint64_t)n_windows * stride;
     PCB_CUDA(c, c->d_ascii.reserve((size_t)bytes + 16));
-    PCB_CUDA(c, c->d_arena.reserve((size_t)bytes + 16));
-    PCB_CUDA(c, c->d_winlen.reserve((size_t)n_windows + 1));
+    PCB_CUDA(c, c->S().d_arena.reserve((size_t)bytes + 16));
+    PCB_CUDA(c, c->S().d_winlen.reserve((size_t)n_windows + 1));
     if (bytes) {
         PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, windows, bytes, cudaMemcpyHostToDevice, c->stream));
-        PCB_CUDA(c, cudaMemcpyAsync(c->d_winlen.p, win_len, sizeof(int32_t) * n_windows, cudaMemcpyHostToDevice, c->stream));
-        PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena.p, bytes, c->stream));
+        PCB_CUDA(c, cudaMemcpyAsync(c->S().d_winlen.p, win_len, sizeof(int32_t) * n_windows, cudaMemcpyHostToDevice, c->stream));
+        PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->S().d_arena.p, bytes, c->stream));
         c->cnt.kernel_launches++;
     }
     c->cnt.h2d_bytes += (int64_t)bytes + (int64_t)sizeof(int32_t) * n_windows;
-    c->arena_len = bytes; c->n_windows = n_windows; c->stride = stride; c->win_mmax = mmax;
+    c->S().arena_len = bytes; c->S().n_windows = n_windows; c->S().stride = stride; c->S().win_mmax = mmax;
     return PCB_OK;
 }
 
@@ -275,10 +294,10 @@ extern "C" int pcb_stage_ids(pcb_context *c, const int32_t *ids, int32_t n_ids)
     cudaSetDevice(c->device);
     for (int i = 0; i < n_ids; ++i)
         if (ids[i] < 0 || ids[i] >= c->n_adapters) return c->fail(PCB_ERR_ARG, "adapter id %d out of range", ids[i]);
-    c->h_ids.assign(ids, ids + n_ids);
-    c->n_ids = n_ids;
-    PCB_CUDA(c, c->d_ids.reserve((size_t)n_ids + 1));
-    if (n_ids) PCB_CUDA(c, cudaMemcpyAsync(c->d_ids.p, ids, sizeof(int32_t) * n_ids, cudaMemcpyHostToDevice, c->stream));
+    c->S().h_ids.assign(ids, ids + n_ids);
+    c->S().n_ids = n_ids;
+    PCB_CUDA(c, c->S().d_ids.reserve((size_t)n_ids + 1));
+    if (n_ids) PCB_CUDA(c, cudaMemcpyAsync(c->S().d_ids.p, ids, sizeof(int32_t) * n_ids, cudaMemcpyHostToDevice, c->stream));
     c->cnt.h2d_bytes += (int64_t)sizeof(int32_t) * n_ids;
     return PCB_OK;
 }
@@ -287,39 +306,37 @@ extern "C" int pcb_run_windows_resident(pcb_context *c)
 {
     if (!c) return PCB_ERR_ARG;
     cudaSetDevice(c->device);
-    const int64_t n_res = c->n_windows * c->n_ids;
-    c->n_results = n_res;
+    const int64_t n_res = c->S().n_windows * c->S().n_ids;
+    c->S().n_results = n_res;
     if (n_res == 0) return PCB_OK;
-    const int nmax = max_adapter_len(c, c->h_ids.data(), c->n_ids);
-    const int mmax = std::max(1, c->win_mmax);
+    const int nmax = max_adapter_len(c, c->S().h_ids.data(), c->S().n_ids);
+    const int mmax = std::max(1, c->S().win_mmax);
     int rc = check_range(c, nmax, mmax);
     if (rc) return rc;
     const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
-    PCB_CUDA(c, c->d_out.reserve((size_t)n_res));
-    const int64_t n_units = ((c->n_windows + 63) / 64) * c->n_ids;
+    PCB_CUDA(c, c->S().d_out.reserve((size_t)n_res));
+    const int64_t n_units = ((c->S().n_windows + 63) / 64) * c->S().n_ids;
     const int grid = (int)std::min<int64_t>(c->grid_trace, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
     rc = ensure_scratch(c, pcb_scratch_words_trace(mmax, smax), grid);
     if (rc) return rc;
     PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
     PcbLaunch L; fill_launch_common(c, L);
     L.src.units = nullptr; L.src.tasks = nullptr;
-    L.src.n_windows = c->n_windows; L.src.stride = c->stride; L.src.win_len = c->d_winlen.p;
-    L.src.ids = c->d_ids.p; L.src.n_ids = c->n_ids; L.src.n_units = n_units;
+    L.src.n_windows = c->S().n_windows; L.src.stride = c->S().stride; L.src.win_len = c->S().d_winlen.p;
+    L.src.ids = c->S().d_ids.p; L.src.n_ids = c->S().n_ids; L.src.n_units = n_units;
     L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
     // algorithmic cell count: sum over windows of len x sum over ids of adapter length
     int64_t sum_n = 0;
-    for (int i = 0; i < c->n_ids; ++i) sum_n += c->ad_off[c->h_ids[i] + 1] - c->ad_off[c->h_ids[i]];
-    // (window lengths were only seen at staging time; use mmax * n_windows as the upper figure when all
-    //  windows are full, which is what the bench workload is; exact sum is tracked by the caller)
-    return launch_dp(c, L, true, (int64_t)c->n_windows * mmax * sum_n);
+    for (int i = 0; i < c->S().n_ids; ++i) sum_n += c->ad_off[c->S().h_ids[i] + 1] - c->ad_off[c->S().h_ids[i]];
+    return launch_dp(c, L, true, c->S().sum_winlen * sum_n);
 }
 
 extern "C" int pcb_fetch_results(pcb_context *c, pcb_result *out, int64_t n_results)
 {
     if (!c || n_results < 0 || (n_results > 0 && !out)) return PCB_ERR_ARG;
     cudaSetDevice(c->device);
-    if (n_results > c->n_results) return c->fail(PCB_ERR_ARG, "asked for %lld results, last run produced %lld", (long long)n_results, (long long)c->n_results);
-    if (n_results) PCB_CUDA(c, cudaMemcpyAsync(out, c->d_out.p, sizeof(pcb_result) * n_results, cudaMemcpyDeviceToHost, c->stream));
+    if (n_results > c->S().n_results) return c->fail(PCB_ERR_ARG, "asked for %lld results, last run produced %lld", (long long)n_results, (long long)c->S().n_results);
+    if (n_results) PCB_CUDA(c, cudaMemcpyAsync(out, c->S().d_out.p, sizeof(pcb_result) * n_results, cudaMemcpyDeviceToHost, c->stream));
     c->cnt.d2h_bytes += (int64_t)sizeof(pcb_result) * n_results;
     return check_err_flag(c);
 }
@@ -406,14 +423,14 @@ extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blo
         c->h_tasks[(size_t)t] = { seg_off[t], seg_len[t], task_adapter[t] };
     }
     PCB_CUDA(c, c->d_ascii.reserve((size_t)blob_len + 16));
-    PCB_CUDA(c, c->d_arena.reserve((size_t)blob_len + 16));
+    PCB_CUDA(c, c->d_arena_t.reserve((size_t)blob_len + 16));
     if (blob_len) {
         PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, seq_blob, (size_t)blob_len, cudaMemcpyHostToDevice, c->stream));
-        PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena.p, (uint64_t)blob_len, c->stream));
+        PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena_t.p, (uint64_t)blob_len, c->stream));
         c->cnt.kernel_launches++;
     }
     c->cnt.h2d_bytes += blob_len;
-    c->arena_len = (uint64_t)blob_len;
+    c->arena_t_len = (uint64_t)blob_len;
     return PCB_OK;
 }
 
@@ -435,7 +452,7 @@ static int run_explicit(pcb_context *c, std::vector<PcbTask> &tasks, std::vector
     const int grid = (int)std::min<int64_t>(gmax, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
     int rc = ensure_scratch(c, trace ? pcb_scratch_words_trace(mmax, smax) : pcb_scratch_words_scan(mmax, smax), grid);
     if (rc) return rc;
-    PcbLaunch L; fill_launch_common(c, L);
+    PcbLaunch L; fill_launch_common(c, L, true);
     L.src.units = c->d_units.p; L.src.tasks = c->d_tasks.p; L.src.n_units = n_units;
     L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
     rc = launch_dp(c, L, trace, cells);
@@ -450,9 +467,9 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
     if (!c) return PCB_ERR_ARG;
     cudaSetDevice(c->device);
     const size_t nt = c->h_tasks.size();
-    c->n_results = (int64_t)nt;
+    c->S().n_results = (int64_t)nt;
     if (nt == 0) return PCB_OK;
-    PCB_CUDA(c, c->d_out.reserve(nt));
+    PCB_CUDA(c, c->S().d_out.reserve(nt));
     PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
 
     // order tasks by adapter (counting sort keeps the input order inside a group)

@@ -34,6 +34,8 @@ class AlignmentEngine(object):
             raise w.AlignmentError('pcb_create failed (%d): %s' % (rc, w.C_LIB.pcb_last_error(None).decode()))
         self.device = device
         self.adapters = []
+        self._slot = 0
+        self._shapes = {}
         self.set_scoring(scoring_scheme_vals)
 
     # -- plumbing -----------------------------------------------------------------------------
@@ -57,6 +59,11 @@ class AlignmentEngine(object):
         """[match, mismatch, gap_open, gap_extend], the order of --scoring_scheme (arg_parser.py:178,230-236)."""
         self.scoring = tuple(int(v) for v in vals)
         self._check(w.C_LIB.pcb_set_scoring(self._h, *self.scoring), 'pcb_set_scoring')
+
+    def select_slot(self, slot):
+        """Pick one of the 4 staging slots (inputs + results) the following stage/run/fetch calls act on."""
+        self._check(w.C_LIB.pcb_select_slot(self._h, int(slot)), 'pcb_select_slot')
+        self._slot = int(slot)
 
     def set_adapters(self, sequences):
         """sequences: list of str / bytes. Adapter ids used everywhere else are indices into this list."""
@@ -101,13 +108,13 @@ class AlignmentEngine(object):
         self._check(w.C_LIB.pcb_stage_windows(self._h, _ptr(win_buf), n, stride, _ptr(win_len)), 'pcb_stage_windows')
         self._check(w.C_LIB.pcb_stage_ids(self._h, _ptr(ids), len(ids)), 'pcb_stage_ids')
         self.synchronize()
-        self._staged_shape = (n, len(ids))
+        self._shapes[self._slot] = (n, len(ids))
 
     def run_windows_resident(self):
         self._check(w.C_LIB.pcb_run_windows_resident(self._h), 'pcb_run_windows_resident')
 
     def fetch(self, shape=None):
-        shape = shape or self._staged_shape
+        shape = shape or self._shapes[self._slot]
         out = np.empty(shape, dtype=RESULT_DTYPE)
         self._check(w.C_LIB.pcb_fetch_results(self._h, _ptr(out), int(np.prod(shape))), 'pcb_fetch_results')
         return out
@@ -132,7 +139,7 @@ class AlignmentEngine(object):
         self._check(w.C_LIB.pcb_stage_tasks(self._h, _ptr(blob), blob.size, _ptr(seg_off), _ptr(seg_len), _ptr(ad),
                                             len(ad)), 'pcb_stage_tasks')
         self.synchronize()
-        self._staged_shape = (len(ad),)
+        self._shapes[self._slot] = (len(ad),)
 
     def run_tasks_resident(self):
         self._check(w.C_LIB.pcb_run_tasks_resident(self._h), 'pcb_run_tasks_resident')

@@ -91,6 +91,11 @@ int pcb_align_tasks(pcb_context *ctx, const char *seq_blob, int64_t blob_len,
 
 /* ---- 3. device-resident form (same kernels; used to time the kernels without PCIe) ---------- */
 
+/* A context holds 4 independent staging slots (inputs + results); all stage/run/fetch calls, and the host-buffer
+ * calls above, act on the selected one (default 0).  Lets start windows, end windows and full-length tasks stay
+ * resident side by side. */
+int pcb_select_slot(pcb_context *ctx, int slot);
+
 /* Stage inputs in HBM (H2D + Dna5 encode). */
 int pcb_stage_windows(pcb_context *ctx, const char *windows, int64_t n_windows, int32_t stride,
                       const int32_t *win_len);
