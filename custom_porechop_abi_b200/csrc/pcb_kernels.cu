@@ -154,7 +154,7 @@ __device__ __forceinline__ void write_failed(pcb_result *out, int64_t idx)
         const uint32_t Mn = vmax(D, G);                                                               \
         const uint32_t MoN = vadd(Mn, GO);                                                            \
         if (TRACE) {                                                                                  \
-            const uint32_t dh = vadd(vadd(Hl[R], GE1), nMo[R]);     /* <0: H opened   */              \
+            const uint32_t dh = vadd(vadd(Hl[R], GE1), ~Mo[R]);     /* <0: H opened   */              \
             const uint32_t dv = vadd(vadd(Vu, GE1), nMo_u);         /* <0: V opened   */              \
             const uint32_t dg = vadd(Hn, ~Vn);                      /* <0: V >= H     */              \
             const uint32_t dd = vadd(G, ~D);                        /* <0: diag >= gap */             \
@@ -163,13 +163,13 @@ __device__ __forceinline__ void write_failed(pcb_result *out, int64_t idx)
             else if (((R) & 3) == 1) Wacc = (Wacc & 0x03030303u) | (W & 0xFCFCFCFCu);                 \
             else if (((R) & 3) == 2) Wacc = (Wacc & 0x0F0F0F0Fu) | (W & 0xF0F0F0F0u);                 \
             else Wacc = (Wacc & 0x3F3F3F3Fu) | (W & 0xC0C0C0C0u);                                     \
-            nMo[R] = ~MoN; nMo_u = ~MoN;                                                              \
+            nMo_u = ~MoN;                                                                             \
         }                                                                                             \
         Mo_d = Mo[R]; Mo[R] = MoN; Hl[R] = Hn; Mo_u = MoN; Vu = Vn;                                   \
     }
 
 #define PCB_FLUSH(Q)                                                                                  \
-    if (TRACE) { tcol[(uint64_t)(Q) * T] = Wacc; }
+    if (TRACE) { *tp = Wacc; tp += T; }
 
 #define PCB_GROUP(Q)                                                                                  \
     case 4 * (Q):     PCB_CELL(4 * (Q))                                                               \
@@ -189,7 +189,7 @@ namespace {
 // dynamic smem: (PCB_BLOCK/32) * smax * PCB_RT words (adapter base pairs of each warp's unit)
 // ------------------------------------------------------------------------------------------------
 template <bool TRACE>
-__global__ void __launch_bounds__(PCB_BLOCK) k_align(const PcbLaunch L)
+__global__ void __launch_bounds__(PCB_BLOCK, PCB_MIN_BLOCKS) k_align(const PcbLaunch L)
 {
     extern __shared__ uint32_t s_ad_all[];
     constexpr int RT = PCB_RT;
@@ -246,9 +246,9 @@ __global__ void __launch_bounds__(PCB_BLOCK) k_align(const PcbLaunch L)
         const int lim0 = max(tk[0].len - 1, 0), lim1 = max(tk[1].len - 1, 0);
 
         for (int s = 0; s < S; ++s) {
-            uint32_t Mo[RT], nMo[RT], Hl[RT];
+            uint32_t Mo[RT], Hl[RT];
 #pragma unroll
-            for (int r = 0; r < RT; ++r) { Mo[r] = GO; nMo[r] = ~GO; Hl[r] = NEGINF; }   // column 0: M = 0, H = -inf
+            for (int r = 0; r < RT; ++r) { Mo[r] = GO; Hl[r] = NEGINF; }   // column 0: M = 0, H = -inf
             const int r0s = (s == 0) ? r0 : 0;
             const uint32_t *const s_adp = s_ad + s * RT;
             const bool last_stripe = (s == S - 1);
@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(PCB_BLOCK) k_align(const PcbLaunch L)
                     Mo_d = prevTop; prevTop = Mo_u;
                 }
                 nMo_u = ~Mo_u;
-                uint32_t *const tcol = tr_base + ((uint64_t)(s * L.mmax + (j - 1)) * (RT / 4)) * T;
+                uint32_t *tp = tr_base + ((uint64_t)(s * L.mmax + (j - 1)) * (RT / 4) + (r0s >> 2)) * T;
                 switch (r0s) {
                     PCB_GROUP(0) PCB_GROUP(1) PCB_GROUP(2) PCB_GROUP(3)
                     PCB_GROUP(4) PCB_GROUP(5) PCB_GROUP(6) PCB_GROUP(7)
@@ -286,14 +286,17 @@ __global__ void __launch_bounds__(PCB_BLOCK) k_align(const PcbLaunch L)
                     }
                 }
                 // final column of a half: keep the whole column (M+go and H of every row) for the post-pass
-                if (fin0 && j == tk[0].len) {
+                const bool dmp0 = fin0 && j == tk[0].len, dmp1 = fin1 && j == tk[1].len;
+                if (dmp0 || dmp1) {
+                    uint32_t *p0 = dump + 2ull * (s * RT) * T, *p1 = p0 + 2ull * L.smax * RT * T;
+                    if (!dmp0) p0 = p1;            // both areas get the same column when both halves end here
+                    if (!dmp1) p1 = p0;
+                    asm volatile("" : "+l"(p0), "+l"(p1));      // keep the address arithmetic inside this rare branch
 #pragma unroll
-                    for (int r = 0; r < RT; ++r) { dump[(2ull * (s * RT + r)) * T] = Mo[r]; dump[(2ull * (s * RT + r) + 1) * T] = Hl[r]; }
-                }
-                if (fin1 && j == tk[1].len) {
-                    uint32_t *const d1 = dump + 2ull * L.smax * RT * T;
-#pragma unroll
-                    for (int r = 0; r < RT; ++r) { d1[(2ull * (s * RT + r)) * T] = Mo[r]; d1[(2ull * (s * RT + r) + 1) * T] = Hl[r]; }
+                    for (int r = 0; r < RT; ++r) {
+                        p0[0] = Mo[r]; p0[T] = Hl[r]; p1[0] = Mo[r]; p1[T] = Hl[r];
+                        p0 += 2 * T; p1 += 2 * T;
+                    }
                 }
             }
         }

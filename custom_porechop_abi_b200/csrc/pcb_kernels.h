@@ -10,6 +10,9 @@
 
 #define PCB_RT          32        /* adapter rows held in registers per stripe                    */
 #define PCB_BLOCK       128       /* threads per CTA (4 warps = 4 work units in flight)           */
+#ifndef PCB_MIN_BLOCKS
+#define PCB_MIN_BLOCKS  4         /* CTAs per SM the register allocation is held to               */
+#endif
 #define PCB_NEG_INF     (-8192)   /* "minus infinity" in a signed 16-bit lane                     */
 #define PCB_MAX_TRACE_M 8000      /* widest segment the trace kernel takes (order key is 14 bit)  */
 
