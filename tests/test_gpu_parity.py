@@ -128,3 +128,46 @@ def test_long_reads_scan_then_window(engine):
             r = r[:q] + '-' * 40 + r[q + 40:]      # masked stretch, as find_middle_adapters produces (nanopore_read.py:233-234)
         pairs.append((r, aid))
     _check_pairs(engine, pairs, adapters, DEFAULT)
+
+
+def test_golden_vectors_from_the_reference(engine):
+    """The committed vectors were produced by the reference's own library (tests/golden/make_golden.py)."""
+    import json
+    import os
+    from custom_porechop_abi_b200.cpp_function_wrappers import format_result
+    cases = json.load(open(os.path.join(os.path.dirname(__file__), 'golden', 'adapter_alignment_golden.json')))['cases']
+    by_scheme = {}
+    for c in cases:
+        by_scheme.setdefault(tuple(c['scores']), []).append(c)
+    for scores, group in by_scheme.items():
+        adapters = sorted(set(c['adapter'] for c in group))
+        idx = {a: i for i, a in enumerate(adapters)}
+        engine.set_scoring(scores)
+        engine.set_adapters(adapters)
+        recs = engine.align_pairs([(c['read'], idx[c['adapter']]) for c in group])
+        for c, rec in zip(group, recs):
+            assert format_result(rec) == c['expect'], (c['read'][:80], c['adapter'], scores)
+
+
+def test_full_size_windows_properties(engine):
+    """BASELINE-sized batch (tens of millions of pairs is too many for the oracle): size-independent checks --
+    determinism across two runs, agreement of the cross-product path with the explicit-task path on a sample, and
+    oracle agreement on a random sample of pairs."""
+    from custom_porechop_abi_b200 import synthetic
+    adapters, s_ids, e_ids = synthetic.adapter_set()
+    blob, off = synthetic.make_reads(20000, adapters, s_ids, e_ids, seed=11, lengths=np.full(20000, 300))
+    sbuf, ebuf, lens = synthetic.end_windows(blob, off)
+    engine.set_scoring(DEFAULT)
+    engine.set_adapters(adapters)
+    a = engine.align_windows(sbuf, lens, s_ids)
+    b = engine.align_windows(sbuf, lens, s_ids)
+    assert a.tobytes() == b.tobytes()
+    assert int((a['raw_score'] >= 0).sum()) == a.size and int((a['read_start'] >= 0).sum()) == a.size
+    rng = random.Random(4)
+    sample = [(rng.randrange(len(lens)), rng.randrange(len(s_ids))) for _ in range(1500)]
+    for w, k in sample:
+        assert rec_matches_oracle(a[w, k], oracle_align(bytes(sbuf[w, :lens[w]]), adapters[s_ids[k]], DEFAULT))
+    pairs = [(bytes(sbuf[w, :lens[w]]), s_ids[k]) for w, k in sample[:500]]
+    recs = engine.align_pairs(pairs)
+    for (w, k), rec in zip(sample[:500], recs):
+        assert rec.tobytes() == a[w, k].tobytes()
