@@ -49,6 +49,8 @@ struct pcb_context {
     PcbScores sc{3, -6, -5, -2, 0};
     // adapters
     std::vector<int64_t> ad_off;          // host copy
+    std::vector<uint8_t> ad_fast;         // kernel class of an adapter: 0 = exactly 24 bases, 1 = 1..32 bases (both ACGT only), 2 = general kernels
+    uint64_t stamp = 1;                   // bumped when the scoring scheme or the adapter set changes
     int32_t n_adapters = 0;
     DevBuf<uint8_t> d_ad_codes;
     DevBuf<int64_t> d_ad_off;
@@ -62,8 +64,9 @@ struct pcb_context {
         DevBuf<uint8_t> d_arena;          // window arena
         uint64_t arena_len = 0;
         int64_t sum_winlen = 0;
-        DevBuf<int32_t> d_winlen, d_ids;
-        std::vector<int32_t> h_ids;
+        DevBuf<int32_t> d_winlen, d_ids;      // d_ids: [fast ids | other ids | fast positions | other positions]
+        std::vector<int32_t> h_ids, h_split;
+        int32_t n_cls[3] = {0, 0, 0}; uint64_t split_stamp = 0;
         int64_t n_windows = 0; int32_t stride = 0, n_ids = 0, win_mmax = 0;
         DevBuf<pcb_result> d_out;
         int64_t n_results = 0;
@@ -80,7 +83,7 @@ struct pcb_context {
     // outputs / scratch
     DevBuf<uint32_t> d_scratch;
     DevBuf<int32_t> d_err;
-    int grid_trace = 0, grid_scan = 0;
+    int grid_trace = 0, grid_scan = 0, grid_ftrace[2] = {0, 0}, grid_fscan[2] = {0, 0};
     pcb_counters cnt{};
     bool ktiming = false;
 
@@ -132,6 +135,7 @@ extern "C" int pcb_create(int device, pcb_context **out)
     }
     c->grid_trace = pcb_occupancy_grid(0);
     c->grid_scan = pcb_occupancy_grid(1);
+    for (int cls = 0; cls < 2; ++cls) { c->grid_ftrace[cls] = pcf_occupancy_grid(true, cls); c->grid_fscan[cls] = pcf_occupancy_grid(false, cls); }
     if (c->d_err.reserve(1) != cudaSuccess) { g_global_err = "cudaMalloc failed"; delete c; return PCB_ERR_NOMEM; }
     *out = c;
     return PCB_OK;
@@ -165,6 +169,7 @@ extern "C" int pcb_set_scoring(pcb_context *c, int match, int mismatch, int gap_
     if (!c) return PCB_ERR_ARG;
     c->sc.match = match; c->sc.mismatch = mismatch; c->sc.gap_open = gap_open; c->sc.gap_extend = gap_extend;
     c->sc.linear = (gap_open == gap_extend);     // seqan/align/global_alignment_unbanded.h:216-219
+    c->stamp++;
     return PCB_OK;
 }
 
@@ -179,6 +184,14 @@ extern "C" int pcb_set_adapters(pcb_context *c, const char *blob, const int64_t 
     for (auto &o : c->ad_off) o -= base;
     for (int i = 0; i < n_adapters; ++i)
         if (c->ad_off[i + 1] < c->ad_off[i]) return c->fail(PCB_ERR_ARG, "adapter offsets must be non-decreasing");
+    c->ad_fast.assign((size_t)n_adapters, 0);
+    for (int i = 0; i < n_adapters; ++i) {
+        const int64_t len = c->ad_off[i + 1] - c->ad_off[i];
+        bool ok = len >= 1 && len <= PCB_RT;
+        for (int64_t k = c->ad_off[i]; ok && k < c->ad_off[i + 1]; ++k) ok = strchr("ACGTUacgtu", blob[base + k]) != nullptr && blob[base + k] != 0;
+        c->ad_fast[(size_t)i] = !ok ? 2 : (len == PCF_EXACT_N ? 0 : 1);
+    }
+    c->stamp++;
     PCB_CUDA(c, c->d_ad_codes.reserve((size_t)total + 16));
     PCB_CUDA(c, c->d_ad_off.reserve((size_t)n_adapters + 1));
     PCB_CUDA(c, c->d_ascii.reserve((size_t)total + 16));
@@ -211,6 +224,15 @@ static int check_range(pcb_context *c, int nmax, int mmax)
     return PCB_OK;
 }
 
+// Scoring schemes the fast kernels (pcb_fast.cu) take: affine with gapOpen < gapExtend < 0, match > 0, and substitution
+// scores that stay in [0, 127] after the anti-diagonal bias b = -gapOpen is added twice.
+static bool fast_scheme(const PcbScores &s)
+{
+    const int b = -s.gap_open;
+    return s.gap_open < 0 && s.gap_extend < 0 && s.gap_extend > s.gap_open && b <= 20 && s.match > 0 &&
+           s.match > s.mismatch && s.mismatch + 2 * b >= 0 && s.match + 2 * b <= 127;
+}
+
 static int ensure_scratch(pcb_context *c, uint64_t words_per_slot, int grid)
 {
     const uint64_t need = words_per_slot * (uint64_t)grid * PCB_BLOCK;
@@ -237,10 +259,12 @@ static void fill_launch_common(pcb_context *c, PcbLaunch &L, bool task_arena = f
 }
 
 // launch with optional per-kernel event timing
-static int launch_dp(pcb_context *c, const PcbLaunch &L, bool trace, int64_t cells)
+// cls: 0 / 1 = fast kernels (pcb_fast.cu), 2 = general kernels (pcb_kernels.cu)
+static int launch_dp(pcb_context *c, const PcbLaunch &L, bool trace, int64_t cells, int cls = 2)
 {
     if (c->ktiming) PCB_CUDA(c, cudaEventRecord(c->kev0, c->stream));
-    PCB_CUDA(c, trace ? pcb_launch_trace(L, c->stream) : pcb_launch_scan(L, c->stream));
+    if (cls < 2) PCB_CUDA(c, pcf_launch(L, trace, cls, c->stream));
+    else         PCB_CUDA(c, trace ? pcb_launch_trace(L, c->stream) : pcb_launch_scan(L, c->stream));
     if (c->ktiming) {
         PCB_CUDA(c, cudaEventRecord(c->kev1, c->stream));
         PCB_CUDA(c, cudaEventSynchronize(c->kev1));
@@ -296,9 +320,31 @@ extern "C" int pcb_stage_ids(pcb_context *c, const int32_t *ids, int32_t n_ids)
         if (ids[i] < 0 || ids[i] >= c->n_adapters) return c->fail(PCB_ERR_ARG, "adapter id %d out of range", ids[i]);
     c->S().h_ids.assign(ids, ids + n_ids);
     c->S().n_ids = n_ids;
-    PCB_CUDA(c, c->S().d_ids.reserve((size_t)n_ids + 1));
-    if (n_ids) PCB_CUDA(c, cudaMemcpyAsync(c->S().d_ids.p, ids, sizeof(int32_t) * n_ids, cudaMemcpyHostToDevice, c->stream));
-    c->cnt.h2d_bytes += (int64_t)sizeof(int32_t) * n_ids;
+    c->S().split_stamp = 0;
+    return PCB_OK;
+}
+
+// Splits the slot's id list by kernel class and uploads [ids of class 0 | class 1 | class 2 | their positions in the same
+// order] (position = index in the caller's list).
+static int split_ids(pcb_context *c, bool fast_ok)
+{
+    pcb_context::Slot &S = c->S();
+    if (S.split_stamp == c->stamp) return PCB_OK;
+    const int n = S.n_ids;
+    std::vector<int32_t> id[3], pos[3];
+    for (int k = 0; k < n; ++k) {
+        const int32_t a = S.h_ids[(size_t)k];
+        const int cls = fast_ok ? c->ad_fast[(size_t)a] : 2;
+        id[cls].push_back(a); pos[cls].push_back(k);
+    }
+    S.h_split.clear();
+    for (int q = 0; q < 3; ++q) { S.n_cls[q] = (int32_t)id[q].size(); S.h_split.insert(S.h_split.end(), id[q].begin(), id[q].end()); }
+    for (int q = 0; q < 3; ++q) S.h_split.insert(S.h_split.end(), pos[q].begin(), pos[q].end());
+    PCB_CUDA(c, S.d_ids.reserve((size_t)2 * n + 1));
+    // h_split lives in the slot until the next split, so the asynchronous copy may read it later
+    if (n) PCB_CUDA(c, cudaMemcpyAsync(S.d_ids.p, S.h_split.data(), sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, c->stream));
+    c->cnt.h2d_bytes += (int64_t)sizeof(int32_t) * 2 * n;
+    S.split_stamp = c->stamp;
     return PCB_OK;
 }
 
@@ -306,29 +352,48 @@ extern "C" int pcb_run_windows_resident(pcb_context *c)
 {
     if (!c) return PCB_ERR_ARG;
     cudaSetDevice(c->device);
-    const int64_t n_res = c->S().n_windows * c->S().n_ids;
-    c->S().n_results = n_res;
+    pcb_context::Slot &S = c->S();
+    const int64_t n_res = S.n_windows * S.n_ids;
+    S.n_results = n_res;
     if (n_res == 0) return PCB_OK;
-    const int nmax = max_adapter_len(c, c->S().h_ids.data(), c->S().n_ids);
-    const int mmax = std::max(1, c->S().win_mmax);
-    int rc = check_range(c, nmax, mmax);
+    const int mmax = std::max(1, S.win_mmax);
+    const bool fast_ok = fast_scheme(c->sc) && mmax <= PCF_MAX_TRACE_M && !getenv("PCB_NO_FAST");
+    int rc = split_ids(c, fast_ok);
     if (rc) return rc;
-    const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
-    PCB_CUDA(c, c->S().d_out.reserve((size_t)n_res));
-    const int64_t n_units = ((c->S().n_windows + 63) / 64) * c->S().n_ids;
-    const int grid = (int)std::min<int64_t>(c->grid_trace, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
-    rc = ensure_scratch(c, pcb_scratch_words_trace(mmax, smax), grid);
-    if (rc) return rc;
+    PCB_CUDA(c, S.d_out.reserve((size_t)n_res));
     PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
-    PcbLaunch L; fill_launch_common(c, L);
-    L.src.units = nullptr; L.src.tasks = nullptr;
-    L.src.n_windows = c->S().n_windows; L.src.stride = c->S().stride; L.src.win_len = c->S().d_winlen.p;
-    L.src.ids = c->S().d_ids.p; L.src.n_ids = c->S().n_ids; L.src.n_units = n_units;
-    L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
-    // algorithmic cell count: sum over windows of len x sum over ids of adapter length
-    int64_t sum_n = 0;
-    for (int i = 0; i < c->S().n_ids; ++i) sum_n += c->ad_off[c->S().h_ids[i] + 1] - c->ad_off[c->S().h_ids[i]];
-    return launch_dp(c, L, true, c->S().sum_winlen * sum_n);
+    const int n = S.n_ids;
+    const int64_t groups = (S.n_windows + 63) / 64;
+    // the small launches first: their tails then overlap nothing bigger than themselves
+    int first = 0;
+    for (int cls = 2; cls >= 0; --cls) {
+        const int cnt = S.n_cls[cls];
+        if (cnt == 0) continue;
+        int start = 0;
+        for (int q = 0; q < cls; ++q) start += S.n_cls[q];
+        const int32_t *h_list = S.h_split.data() + start;
+        const int nmax = max_adapter_len(c, h_list, cnt);
+        const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
+        if (cls == 2 && (rc = check_range(c, nmax, mmax))) return rc;
+        const int64_t n_units = groups * cnt;
+        const int gmax = cls < 2 ? c->grid_ftrace[cls] : c->grid_trace;
+        const int grid = (int)std::min<int64_t>(gmax, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
+        rc = ensure_scratch(c, cls < 2 ? pcf_scratch_words_trace(mmax, cls) : pcb_scratch_words_trace(mmax, smax), grid);
+        if (rc) return rc;
+        PcbLaunch L; fill_launch_common(c, L);
+        L.src.units = nullptr; L.src.tasks = nullptr;
+        L.src.n_windows = S.n_windows; L.src.stride = S.stride; L.src.win_len = S.d_winlen.p;
+        L.src.ids = S.d_ids.p + start; L.src.n_ids = cnt;
+        L.src.id_pos = S.d_ids.p + n + start; L.src.n_ids_total = n;
+        L.src.n_units = n_units;
+        L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
+        // algorithmic cell count: sum over windows of len x sum over ids of adapter length
+        int64_t sum_n = 0;
+        for (int i = 0; i < cnt; ++i) sum_n += c->ad_off[h_list[i] + 1] - c->ad_off[h_list[i]];
+        if ((rc = launch_dp(c, L, true, S.sum_winlen * sum_n, cls))) return rc;
+        (void)first;
+    }
+    return PCB_OK;
 }
 
 extern "C" int pcb_fetch_results(pcb_context *c, pcb_result *out, int64_t n_results)
@@ -392,14 +457,14 @@ WindowBounds window_bounds(const PcbScores &s, int n)
     return b;
 }
 
-// group tasks (already sorted by adapter) into units of <= 64
-void build_units(const std::vector<PcbTask> &tasks, const std::vector<int32_t> &adapter_of, std::vector<PcbUnit> &units)
+// group tasks (already sorted by adapter) into units of <= per_unit (<= 64) tasks
+void build_units(const std::vector<PcbTask> &tasks, const std::vector<int32_t> &adapter_of, int per_unit, std::vector<PcbUnit> &units)
 {
     units.clear();
     size_t i = 0;
     while (i < tasks.size()) {
         size_t j = i;
-        while (j < tasks.size() && adapter_of[j] == adapter_of[i] && j - i < 64) ++j;
+        while (j < tasks.size() && adapter_of[j] == adapter_of[i] && j - i < (size_t)per_unit) ++j;
         PcbUnit u; u.adapter = adapter_of[i]; u.ntask = (int32_t)(j - i); u.task0 = (int64_t)i;
         units.push_back(u);
         i = j;
@@ -434,13 +499,26 @@ extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blo
     return PCB_OK;
 }
 
-// runs one explicit launch (tasks sorted by adapter) through the trace or scan kernel
-static int run_explicit(pcb_context *c, std::vector<PcbTask> &tasks, std::vector<int32_t> &adapter_of, bool trace,
-                        int mmax, int nmax, int64_t cells)
+// One explicit launch: tasks (sorted by adapter) through the trace or scan kernel, fast or general flavour.
+static int run_explicit(pcb_context *c, std::vector<PcbTask> &tasks, std::vector<int32_t> &adapter_of, bool trace, int cls,
+                        int64_t cells)
 {
     if (tasks.empty()) return PCB_OK;
+    int mmax = 1, nmax = 1;
+    for (size_t i = 0; i < tasks.size(); ++i) {
+        mmax = std::max(mmax, tasks[i].len);
+        nmax = std::max(nmax, (int)(c->ad_off[(size_t)adapter_of[i] + 1] - c->ad_off[(size_t)adapter_of[i]]));
+    }
+    int rc;
+    const bool fast = cls < 2;
+    if (!fast && (rc = check_range(c, nmax, mmax))) return rc;
+    if (fast && mmax > (trace ? PCF_MAX_TRACE_M : PCF_MAX_SCAN_M)) return c->fail(PCB_ERR_RANGE, "internal: segment of %d columns sent to the fast kernels", mmax);
+    const int gmax = fast ? (trace ? c->grid_ftrace[cls] : c->grid_fscan[cls]) : (trace ? c->grid_trace : c->grid_scan);
+    // fewer tasks per warp when there is not enough work to fill the machine (a warp's time does not depend on its lanes)
+    const int64_t warps = (int64_t)gmax * (PCB_BLOCK / 32);
+    const int per_unit = (int)std::min<int64_t>(64, std::max<int64_t>(2, ((int64_t)tasks.size() + warps - 1) / warps));
     std::vector<PcbUnit> units;
-    build_units(tasks, adapter_of, units);
+    build_units(tasks, adapter_of, per_unit, units);
     PCB_CUDA(c, c->d_tasks.reserve(tasks.size()));
     PCB_CUDA(c, c->d_units.reserve(units.size()));
     PCB_CUDA(c, cudaMemcpyAsync(c->d_tasks.p, tasks.data(), sizeof(PcbTask) * tasks.size(), cudaMemcpyHostToDevice, c->stream));
@@ -448,18 +526,27 @@ static int run_explicit(pcb_context *c, std::vector<PcbTask> &tasks, std::vector
     c->cnt.h2d_bytes += (int64_t)(sizeof(PcbTask) * tasks.size() + sizeof(PcbUnit) * units.size());
     const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
     const int64_t n_units = (int64_t)units.size();
-    const int gmax = trace ? c->grid_trace : c->grid_scan;
     const int grid = (int)std::min<int64_t>(gmax, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
-    int rc = ensure_scratch(c, trace ? pcb_scratch_words_trace(mmax, smax) : pcb_scratch_words_scan(mmax, smax), grid);
-    if (rc) return rc;
+    const uint64_t words = fast ? (trace ? pcf_scratch_words_trace(mmax, cls) : 1)
+                                : (trace ? pcb_scratch_words_trace(mmax, smax) : pcb_scratch_words_scan(mmax, smax));
+    if ((rc = ensure_scratch(c, words, grid))) return rc;
     PcbLaunch L; fill_launch_common(c, L, true);
     L.src.units = c->d_units.p; L.src.tasks = c->d_tasks.p; L.src.n_units = n_units;
     L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
-    rc = launch_dp(c, L, trace, cells);
+    rc = launch_dp(c, L, trace, cells, cls);
     if (rc) return rc;
     // the host vectors are about to go out of scope: the copies above must have completed
     PCB_CUDA(c, cudaStreamSynchronize(c->stream));
     return PCB_OK;
+}
+
+namespace {
+struct TaskList {                       // tasks of one launch, in adapter order
+    std::vector<PcbTask> tasks;
+    std::vector<int32_t> ad;
+    int64_t cells = 0;
+    void add(const PcbTask &t, int32_t adapter, int64_t ncells) { tasks.push_back(t); ad.push_back(adapter); cells += ncells; }
+};
 }
 
 extern "C" int pcb_run_tasks_resident(pcb_context *c)
@@ -471,42 +558,46 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
     if (nt == 0) return PCB_OK;
     PCB_CUDA(c, c->S().d_out.reserve(nt));
     PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
+    const bool fast_sc = fast_scheme(c->sc) && !getenv("PCB_NO_FAST");
 
-    // order tasks by adapter (counting sort keeps the input order inside a group)
-    std::vector<int64_t> start((size_t)c->n_adapters + 1, 0);
-    for (auto &t : c->h_tasks) start[(size_t)t.adapter + 1]++;
-    for (int a = 0; a < c->n_adapters; ++a) start[(size_t)a + 1] += start[(size_t)a];
+    // order tasks by (adapter, length / 16): two counting sorts, stable, so equal keys keep the input order.
+    // Tasks of one warp share the adapter and run in lockstep over the longest of their segments.
     std::vector<int64_t> order(nt);
     {
-        std::vector<int64_t> pos(start.begin(), start.end() - 1);
-        for (size_t t = 0; t < nt; ++t) order[(size_t)pos[(size_t)c->h_tasks[t].adapter]++] = (int64_t)t;
+        const int LB = 64;                                   // length buckets (only short segments are bucketed finely)
+        auto lbucket = [](int32_t len) { return std::min<int32_t>(len >> 4, 63); };
+        std::vector<int64_t> tmp(nt), cnt((size_t)std::max<int64_t>(LB, c->n_adapters) + 1, 0);
+        for (auto &t : c->h_tasks) cnt[(size_t)lbucket(t.len) + 1]++;
+        for (int k = 0; k < LB; ++k) cnt[(size_t)k + 1] += cnt[(size_t)k];
+        for (size_t t = 0; t < nt; ++t) tmp[(size_t)cnt[(size_t)lbucket(c->h_tasks[t].len)]++] = (int64_t)t;
+        std::fill(cnt.begin(), cnt.end(), 0);
+        for (auto &t : c->h_tasks) cnt[(size_t)t.adapter + 1]++;
+        for (int a = 0; a < c->n_adapters; ++a) cnt[(size_t)a + 1] += cnt[(size_t)a];
+        for (size_t k = 0; k < nt; ++k) order[(size_t)cnt[(size_t)c->h_tasks[(size_t)tmp[k]].adapter]++] = tmp[k];
     }
 
-    const int direct_default = 1024;
-    std::vector<PcbTask> direct, chunks;          // phase-0 trace tasks, phase-1 scan chunks
-    std::vector<int32_t> direct_ad, chunk_ad;
+    const int direct_default = 960;
+    TaskList direct[3], scan[3];             // by kernel class: 0 / 1 fast kernels, 2 general kernels
+    std::vector<PcbTask> chunks;             // all scan chunks, out_idx = index here
     struct LongTask { int64_t task; int64_t chunk0; int32_t nchunks; };
     std::vector<LongTask> longs;
-    int direct_mmax = 1, direct_nmax = 1, scan_mmax = 1, scan_nmax = 1;
-    int64_t direct_cells = 0, scan_cells = 0;
 
     // chunk length: enough chunks to fill the machine, but long enough to amortise the warm-up margin
     int64_t long_cols = 0;
     for (auto &t : c->h_tasks) if (t.len > direct_default) long_cols += t.len;
-    int chunk = (int)std::min<int64_t>(4096, std::max<int64_t>(1024, long_cols / (2 * 64 * (int64_t)std::max(1, c->grid_scan) * (PCB_BLOCK / 32))));
+    int chunk = (int)std::min<int64_t>(4096, std::max<int64_t>(1024, long_cols / (2 * 64 * (int64_t)std::max(1, c->grid_fscan[0]) * (PCB_BLOCK / 32))));
 
     for (size_t k = 0; k < nt; ++k) {
         const int64_t ti = order[k];
         const auto &t = c->h_tasks[(size_t)ti];
         const int n = (int)(c->ad_off[(size_t)t.adapter + 1] - c->ad_off[(size_t)t.adapter]);
+        const int cls = fast_sc ? c->ad_fast[(size_t)t.adapter] : 2;
         const WindowBounds wb = window_bounds(c->sc, n);
         const int direct_max = std::max(direct_default, wb.ok ? wb.warm + wb.span + 8 : 0);
         if (t.len <= direct_max || !wb.ok || n == 0) {
             PcbTask d{}; d.off = (uint64_t)t.off; d.len = t.len; d.col0 = 0; d.m_true = t.len; d.forced_ord = -1;
             d.out_idx = (int32_t)ti; d.own0 = 0;
-            direct.push_back(d); direct_ad.push_back(t.adapter);
-            direct_mmax = std::max(direct_mmax, t.len); direct_nmax = std::max(direct_nmax, n);
-            direct_cells += (int64_t)t.len * n;
+            direct[t.len <= PCF_MAX_TRACE_M ? cls : 2].add(d, t.adapter, (int64_t)t.len * n);
         } else {
             LongTask lt{ ti, (int64_t)chunks.size(), 0 };
             for (int64_t c0 = 0; c0 < t.len; c0 += chunk) {
@@ -514,35 +605,32 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
                 const int64_t cend = std::min<int64_t>(t.len, c0 + chunk);
                 PcbTask d{}; d.off = (uint64_t)(t.off + col0); d.len = (int32_t)(cend - col0); d.col0 = (int32_t)col0;
                 d.m_true = t.len; d.forced_ord = -1; d.out_idx = (int32_t)chunks.size(); d.own0 = (int32_t)(c0 - col0);
-                chunks.push_back(d); chunk_ad.push_back(t.adapter);
-                scan_mmax = std::max(scan_mmax, d.len);
+                chunks.push_back(d);
+                scan[cls].add(d, t.adapter, 0);
                 lt.nchunks++;
             }
-            scan_nmax = std::max(scan_nmax, n);
-            scan_cells += (int64_t)t.len * n;
+            scan[cls].cells += (int64_t)t.len * n;
             longs.push_back(lt);
         }
     }
 
     int rc;
-    if (!direct.empty()) {
-        if ((rc = check_range(c, direct_nmax, direct_mmax))) return rc;
-        if ((rc = run_explicit(c, direct, direct_ad, true, direct_mmax, direct_nmax, direct_cells))) return rc;
-    }
+    for (int q = 2; q >= 0; --q)
+        if ((rc = run_explicit(c, direct[q].tasks, direct[q].ad, true, q, direct[q].cells))) return rc;
     if (!chunks.empty()) {
-        if ((rc = check_range(c, scan_nmax, scan_mmax))) return rc;
         PCB_CUDA(c, c->d_scan.reserve(chunks.size()));
-        if ((rc = run_explicit(c, chunks, chunk_ad, false, scan_mmax, scan_nmax, scan_cells))) return rc;
+        for (int q = 2; q >= 0; --q)
+            if ((rc = run_explicit(c, scan[q].tasks, scan[q].ad, false, q, scan[q].cells))) return rc;
         std::vector<int32_t> keys(chunks.size());
         PCB_CUDA(c, cudaMemcpyAsync(keys.data(), c->d_scan.p, sizeof(int32_t) * keys.size(), cudaMemcpyDeviceToHost, c->stream));
         PCB_CUDA(c, cudaStreamSynchronize(c->stream));
         c->cnt.d2h_bytes += (int64_t)(sizeof(int32_t) * keys.size());
         // best end cell per long task: highest score, then SeqAn's visiting order (dp_scout.h:167-180)
-        std::vector<PcbTask> wins; std::vector<int32_t> win_ad;
-        int win_mmax = 1, win_nmax = 1; int64_t win_cells = 0;
+        TaskList wins[3];
         for (auto &lt : longs) {
             const auto &t = c->h_tasks[(size_t)lt.task];
             const int n = (int)(c->ad_off[(size_t)t.adapter + 1] - c->ad_off[(size_t)t.adapter]);
+            const int cls = fast_sc ? c->ad_fast[(size_t)t.adapter] : 2;
             const WindowBounds wb = window_bounds(c->sc, n);
             int best_score = INT32_MIN; int64_t best_ord = 0; bool have = false;
             for (int q = 0; q < lt.nchunks; ++q) {
@@ -563,13 +651,10 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
             d.col0 = (int32_t)ws; d.len = (int32_t)std::max<int64_t>(1, cj - ws); d.off = (uint64_t)(t.off + ws);
             d.m_true = t.len; d.own0 = 0; d.out_idx = (int32_t)lt.task;
             d.forced_ord = rowclass ? (int32_t)(cj - ws) : (int32_t)(d.len + (best_ord - t.len));
-            wins.push_back(d); win_ad.push_back(t.adapter);
-            win_mmax = std::max(win_mmax, d.len); win_nmax = std::max(win_nmax, n);
-            win_cells += (int64_t)d.len * n;
+            wins[d.len <= PCF_MAX_TRACE_M ? cls : 2].add(d, t.adapter, 0);   // re-computed cells are not algorithmic work
         }
-        if ((rc = check_range(c, win_nmax, win_mmax))) return rc;
-        (void)win_cells;   // re-computed cells are not counted as algorithmic work
-        if ((rc = run_explicit(c, wins, win_ad, true, win_mmax, win_nmax, 0))) return rc;
+        for (int q = 2; q >= 0; --q)
+            if ((rc = run_explicit(c, wins[q].tasks, wins[q].ad, true, q, 0))) return rc;
     }
     return PCB_OK;
 }

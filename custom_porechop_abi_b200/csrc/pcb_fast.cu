@@ -1,0 +1,522 @@
+/*
+ * pcb_fast.cu -- the fast sm_100a kernels of the adapter-alignment hot path (affine schemes, adapters of <= 32 bases).
+ *
+ * Same result contract as pcb_kernels.cu (reference: porechop_abi/src/adapter_align.cpp:11-31 = SeqAn 2.4.0 globalAlignment
+ * with all four end gaps free, Gotoh recursion seqan/align/dp_formula_affine.h:65-124, single trace, then
+ * porechop_abi/src/alignment.cpp:5-110), but organised around what the B200 integer pipes cost (measured with
+ * scripts/microbench/pipes.cu: every packed 16x2 / DPX / PRMT / LOP3 instruction is 2 clk per warp on the ALU pipe,
+ * 32-bit adds about 1.4 clk, and FMA-pipe work does not hide under ALU work), i.e. around the instruction count per cell:
+ *
+ *   1. anti-diagonal bias.  Every DP value is stored as  x + b*(i+j) + B0  with b = -gapOpen.  All four candidates of a
+ *      cell share the bias, so every comparison (and therefore every tie-break) is unchanged, but
+ *        - M + gapOpen needs no instruction (gapOpen + b == 0),
+ *        - all stored values and the substitution scores (s + 2b) are non-negative, so the diagonal add is a plain
+ *          32-bit add on the packed pair (no carry can cross the halves).
+ *      Score-only cell for two tasks: PRMT (score of this read base against the adapter base, by byte select from a
+ *      per-column profile word), 32-bit add, 2 x VIADDMNMX.S16x2 (H and V), VIMNMX3.S16x2 (M) = 5 instructions.
+ *   2. two passes instead of a trace matrix.  Pass 1 is score-only: it finds SeqAn's end cell (dp_scout.h:167-180) and
+ *      checkpoints the DP column every PCF_C columns (a few hundred bytes per task pair, L2 resident).  Pass 2 recomputes,
+ *      with trace flags, only the PCF_C-column blocks the traceback actually walks through (usually 1-2 of them), keeps the
+ *      flags in shared memory and walks them.  Values are 15-bit non-negative, so "a >= b" is bit 15 of
+ *      (a + 0x8000 - b): one IADD3 per flag, extracted four at a time with PRMT in sign-replicate mode.
+ *   3. the scan kernel for long reads (middle-adapter search) is pass 1 alone, with the bias re-based every 1024 columns.
+ *
+ *   4. no copies, no waits.  The column body is straight-line code over NR rows (template parameter: 24 = the length of
+ *      almost every Porechop adapter and barcode, exact; 32 = any shorter-or-equal adapter, top-aligned, the rows below the
+ *      adapter compute harmless garbage), so ptxas updates the DP registers in place; read bases are fetched four columns
+ *      at a time, one group ahead of their use, so that no column waits on a global load.
+ *
+ * One thread = two tasks (the halves of each 32-bit register), one warp = 64 tasks sharing an adapter, as in pcb_kernels.cu.
+ * Sequence codes in the arenas are Dna5 code * 8 (0, 8, 16, 24, 32 = N), so that a code is directly a byte shift.
+ */
+#include "pcb_kernels.h"
+#include "align_stats.h"
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace {
+
+constexpr int RT = PCB_RT;            // 32 adapter rows in registers
+constexpr int C = PCF_C;              // checkpoint distance / flag block width (columns)
+constexpr int B0 = 64;                // base bias: keeps every stored value > 0
+constexpr int OFF = 2048;             // offset of un-biased scores in the best-cell comparison (true score + OFF > 0)
+constexpr int REBASE = 1024;          // scan: columns between two re-basings of the anti-diagonal bias
+constexpr uint32_t GUARD = 0x80008000u;
+
+__device__ __forceinline__ uint32_t pk2(int v) { return ((uint32_t)v & 0xFFFFu) * 0x10001u; }
+__device__ __forceinline__ uint32_t pk(int lo, int hi) { return ((uint32_t)lo & 0xFFFFu) | ((uint32_t)hi << 16); }
+__device__ __forceinline__ int lo16(uint32_t x) { return (int)(short)(x & 0xFFFFu); }
+__device__ __forceinline__ int hi16(uint32_t x) { return (int)x >> 16; }
+__device__ __forceinline__ int half16(uint32_t x, int h) { return h ? hi16(x) : lo16(x); }
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t s)
+{
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(s));
+    return d;
+}
+// bytes: sign(a.lo), sign(a.hi), sign(b.lo), sign(b.hi), each replicated to 0x00 / 0xFF
+__device__ __forceinline__ uint32_t sign4(uint32_t a, uint32_t b)
+{
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, 0xfdb9;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+// per-half max(a, b) with keep_x = (a_x >= b_x).  Same PTX pattern as the toolkit's __vibmax_s16x2 (ptxas turns it into one
+// VIMNMX.S16x2 with two predicate outputs), but with an early-clobber result: the header's version lets the result share
+// a register with `a`, and then compares the result with itself.
+__device__ __forceinline__ uint32_t vmax_keep(uint32_t a, uint32_t b, bool &keep_hi, bool &keep_lo)
+{
+    uint32_t val, ph, pl;
+    asm("{.reg .pred pu, pv; \n\t"
+        ".reg .s16 rs0, rs1, rs2, rs3; \n\t"
+        "max.s16x2 %0, %3, %4; \n\t"
+        "mov.b32 {rs0, rs1}, %0; \n\t"
+        "mov.b32 {rs2, rs3}, %3; \n\t"
+        "setp.eq.s16 pv, rs0, rs2; \n\t"
+        "setp.eq.s16 pu, rs1, rs3; \n\t"
+        "selp.b32 %1, 1, 0, pu; \n\t"
+        "selp.b32 %2, 1, 0, pv;} \n\t"
+        : "=&r"(val), "=r"(ph), "=r"(pl) : "r"(a), "r"(b));
+    keep_hi = ph != 0; keep_lo = pl != 0;
+    return val;
+}
+// a + GUARD - b on the packed pair: bit 15 / 31 = (a >= b) per half, for 15-bit non-negative a, b
+__device__ __forceinline__ uint32_t cmpge(uint32_t a, uint32_t b) { return a + GUARD - b; }
+
+struct HalfTask {            // one of the two tasks of a thread
+    uint64_t off;
+    int32_t  len, col0, m_true, forced, own0;
+    int64_t  out_idx;        // < 0: no task in this half
+};
+
+__device__ __forceinline__ void fetch_task(const PcbSource &src, int64_t unit, int slot, int32_t &adapter, HalfTask &t)
+{
+    t.off = 0; t.len = 0; t.col0 = 0; t.m_true = 0; t.forced = -1; t.own0 = 0; t.out_idx = -1;
+    if (src.units) {
+        const PcbUnit u = src.units[unit];
+        adapter = u.adapter;
+        if (slot < u.ntask) {
+            const PcbTask k = src.tasks[u.task0 + slot];
+            t.off = k.off; t.len = k.len; t.col0 = k.col0; t.m_true = k.m_true; t.forced = k.forced_ord;
+            t.own0 = k.own0; t.out_idx = k.out_idx;
+        }
+    } else {
+        const int64_t g = unit / src.n_ids;
+        const int32_t k = (int32_t)(unit - g * src.n_ids);
+        adapter = src.ids[k];
+        const int64_t w = g * 64 + slot;
+        if (w < src.n_windows) {
+            t.off = (uint64_t)w * (uint64_t)src.stride;
+            t.len = src.win_len[w]; t.m_true = t.len;
+            t.out_idx = w * src.n_ids_total + (src.id_pos ? src.id_pos[k] : k);
+        }
+    }
+}
+
+__device__ __forceinline__ void write_failed(pcb_result *out, int64_t idx)
+{
+    pcb_result r;
+    r.read_start = -1; r.read_end = 0; r.adapter_start = -1; r.adapter_end = 0;
+    r.raw_score = (int32_t)0x80000000; r.matches = 0; r.aligned_len = 0; r.full_len = 0;
+    out[idx] = r;
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// One DP column, score only, for the two tasks of this thread.  Mo[r] / Hl[r]: M and H of the left neighbour (biased),
+// updated in place.  rowTp / rowT: biased M(0, j-1) / M(0, j).  The diagonal term of the NEXT row (old Mo[r] + score)
+// is formed before Mo[r] is overwritten, so nothing has to be copied.  5 instructions per row:
+// PRMT, IADD, VIADDMNMX (H), VIADDMNMX (V), VIMNMX3 (M).  Recurrence: seqan/align/dp_formula_affine.h:65-124.
+// Returns V of row NR-1; with !EXACT also captures M, V, H of row nm1 (the adapter's last row).
+// ------------------------------------------------------------------------------------------------
+template <int NR, bool EXACT>
+__device__ __forceinline__ void col_score(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *s_sel, uint32_t Q0, uint32_t Q1,
+                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, int nm1, uint32_t &Ml, uint32_t &Vl, uint32_t &Hlast)
+{
+    uint32_t Dn = rowTp + prmt(Q0, Q1, s_sel[0]);
+    uint32_t Vu = rowT;                              // V(1, j) = M(0, j) + gapOpen  (row 0: V = -inf)
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        const uint32_t Hn = __viaddmax_s16x2(Hl[r], GEB, Mo[r]);
+        if (r > 0) Vu = __viaddmax_s16x2(Vu, GEB, Mo[r - 1]);
+        const uint32_t D = Dn;
+        if (r < NR - 1) Dn = Mo[r] + prmt(Q0, Q1, s_sel[r + 1]);
+        Mo[r] = __vimax3_s16x2(D, Vu, Hn); Hl[r] = Hn;
+        if (!EXACT && r == nm1) { Ml = Mo[r]; Vl = Vu; Hlast = Hn; }
+    }
+    if (EXACT) { Ml = Mo[NR - 1]; Vl = Vu; Hlast = Hl[NR - 1]; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// The same column with trace flags (pass 2).  Flag bits of row r, half h, in flag word r >> 2 with q = r & 3:
+//      bit 8h+2q   : H extended (H_left + ge >= M_left + go)     bit 8h+2q+1    : V >= H
+//      bit 16+8h+2q: V extended                                  bit 16+8h+2q+1 : diagonal >= max(V, H)
+// (tie rules of dp_formula_affine.h:65-124 / dp_formula.h:147-163: the left operand of each _maxScore wins ties).
+// fp: this thread's flag words of the column, stride PCB_BLOCK.
+// ------------------------------------------------------------------------------------------------
+template <int NR, bool EXACT>
+__device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *s_sel, uint32_t Q0, uint32_t Q1,
+                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, int nm1, uint32_t *fp,
+                                          uint32_t &Ml, uint32_t &Vl, uint32_t &Hlast)
+{
+    uint32_t Dn = rowTp + prmt(Q0, Q1, s_sel[0]);
+    uint32_t Vu = 0, Wacc = 0;
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        const uint32_t D = Dn;
+        const uint32_t Mup = (r == 0) ? rowT : Mo[(r > 0) ? r - 1 : 0];
+        const uint32_t he = Hl[r] + GEB, ve = Vu + GEB;
+        const uint32_t Hn = __vmaxs2(he, Mo[r]), Vn = __vmaxs2(ve, Mup);
+        const uint32_t G = __vmaxs2(Vn, Hn);
+        const uint32_t W = (sign4(cmpge(he, Mo[r]), cmpge(ve, Mup)) & 0x55555555u) |
+                           (sign4(cmpge(Vn, Hn), cmpge(D, G)) & 0xAAAAAAAAu);
+        if ((r & 3) == 0) Wacc = W;
+        else if ((r & 3) == 1) Wacc = (Wacc & 0x03030303u) | (W & 0xFCFCFCFCu);
+        else if ((r & 3) == 2) Wacc = (Wacc & 0x0F0F0F0Fu) | (W & 0xF0F0F0F0u);
+        else Wacc = (Wacc & 0x3F3F3F3Fu) | (W & 0xC0C0C0C0u);
+        if ((r & 3) == 3 || r == NR - 1) fp[(r >> 2) * PCB_BLOCK] = Wacc;
+        if (r < NR - 1) Dn = Mo[r] + prmt(Q0, Q1, s_sel[r + 1]);
+        Vu = Vn; Mo[r] = __vmaxs2(D, G); Hl[r] = Hn;
+        if (!EXACT && r == nm1) { Ml = Mo[r]; Vl = Vn; Hlast = Hn; }
+    }
+    if (EXACT) { Ml = Mo[NR - 1]; Vl = Vu; Hlast = Hl[NR - 1]; }
+}
+
+// four consecutive sequence bytes starting at seq[pos] (pos clamped to lim), through two aligned word loads
+__device__ __forceinline__ uint32_t load4(const uint8_t *seq, int pos, int lim)
+{
+    const uintptr_t a = (uintptr_t)(seq + min(pos, lim));
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+    return __funnelshift_r(p[0], p[1], (uint32_t)(a & 3) * 8u);
+}
+// profile word of one read base: byte c = score of this base against adapter base c, + 2b   (code8 = Dna5 code * 8)
+__device__ __forceinline__ uint32_t profile(uint32_t code8, uint32_t DELTA, uint32_t MISW)
+{
+    uint32_t q;
+    asm("shl.b32 %0, %1, %2;" : "=r"(q) : "r"(DELTA), "r"(code8));      // shift >= 32 (N) gives 0
+    return q + MISW;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_fast<TRACE, NR, EXACT>
+//   TRACE=true  -> pass 1 (score only + checkpoints + end cell), pass 2 (flags for the blocks the traceback crosses,
+//                  traceback, statistics) -> pcb_result
+//   TRACE=false -> pass 1 only -> order key per task (scan chunks of long reads)
+//   NR / EXACT  -> adapter rows in registers; EXACT: every adapter of the launch has exactly NR bases
+// grid: persistent, blockDim = PCB_BLOCK; warp w of the grid takes units w, w + nwarps, ...
+// dynamic smem: [PCB_BLOCK/32][NR] PRMT selectors of each warp's adapter, then a per-thread area strided by PCB_BLOCK
+//               (TRACE: C*NR/4 flag words; always >= 2*NR words for the final-column dump).
+// ------------------------------------------------------------------------------------------------
+template <bool TRACE, int NR, bool EXACT>
+__global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(const PcbLaunch L)
+{
+    extern __shared__ uint32_t smem[];
+    constexpr int FW = NR / 4;                           // flag words per column
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t T = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t slot = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t *const s_sel = smem + warp * NR;
+    uint32_t *const s_fl = smem + (PCB_BLOCK / 32) * NR + threadIdx.x;
+    uint32_t *const ck = L.scratch + slot;               // checkpoints [k][2*NR], element stride T
+
+    const int b = -L.sc.gap_open;
+    const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b), OFFp = pk2(OFF);
+    const uint32_t MISW = (uint32_t)(L.sc.mismatch + 2 * b) * 0x01010101u;
+    const uint32_t DELTA = (uint32_t)(L.sc.match - L.sc.mismatch);
+    const int geb = L.sc.gap_extend + b;
+
+    const int64_t nwarps = (int64_t)gridDim.x * (PCB_BLOCK / 32);
+    for (int64_t unit = (int64_t)blockIdx.x * (PCB_BLOCK / 32) + warp; unit < L.src.n_units; unit += nwarps) {
+        int32_t adapter = 0;
+        HalfTask tk[2];
+        fetch_task(L.src, unit, 2 * lane, adapter, tk[0]);
+        fetch_task(L.src, unit, 2 * lane + 1, adapter, tk[1]);
+        const int64_t aoff = L.ad.off[adapter];
+        const int n = (int)(L.ad.off[adapter + 1] - aoff);
+        if (n <= 0 || n > NR || (EXACT && n != NR)) {          // the host never sends these here; fail loudly if it does
+            atomicOr(L.err_flag, 4);
+            for (int h = 0; h < 2; ++h) if (tk[h].out_idx >= 0) {
+                if (TRACE) write_failed(L.out, tk[h].out_idx); else L.scan_out[tk[h].out_idx] = (int)0x80000000;
+            }
+            continue;
+        }
+        const int nm1 = n - 1;
+        __syncwarp();
+        for (int i = lane; i < NR; i += 32) {
+            const uint32_t c = i < n ? (uint32_t)(L.ad.codes[aoff + i] / PCB_CODE_SCALE) & 3u : 0u;
+            s_sel[i] = c | ((8u | c) << 4) | ((4u + c) << 8) | ((12u + c) << 12);
+        }
+        __syncwarp();
+
+        const int len0 = tk[0].len, len1 = tk[1].len;
+        const int mw = __reduce_max_sync(0xffffffffu, max(len0, len1));
+        const bool fin0 = len0 > 0 && tk[0].col0 + len0 == tk[0].m_true;
+        const bool fin1 = len1 > 0 && tk[1].col0 + len1 == tk[1].m_true;
+        // row-class (last adapter row) candidate columns [lo, hi] per half
+        int lo0 = tk[0].own0 + 1, hi0 = fin0 ? len0 - 1 : len0;
+        int lo1 = tk[1].own0 + 1, hi1 = fin1 ? len1 - 1 : len1;
+        if (tk[0].forced >= 0) { if (tk[0].forced <= hi0) { lo0 = max(lo0, tk[0].forced); hi0 = tk[0].forced; } else hi0 = -1; }
+        if (tk[1].forced >= 0) { if (tk[1].forced <= hi1) { lo1 = max(lo1, tk[1].forced); hi1 = tk[1].forced; } else hi1 = -1; }
+        // columns in which every task of the warp takes its candidate (no masking needed), and the first column in
+        // which some task of the warp reaches its final column
+        const bool act0 = tk[0].out_idx >= 0 && len0 > 0, act1 = tk[1].out_idx >= 0 && len1 > 0;
+        const int ulo = __reduce_max_sync(0xffffffffu, max(act0 ? lo0 : 0, act1 ? lo1 : 0));
+        const int uhi = __reduce_min_sync(0xffffffffu, min(act0 ? hi0 : 0x7fffffff, act1 ? hi1 : 0x7fffffff));
+        const int ufin = __reduce_min_sync(0xffffffffu, min(fin0 ? len0 : 0x7fffffff, fin1 ? len1 : 0x7fffffff));
+        // cell (n, 0): first tracked cell of the matrix, score 0 (dp_meta_info.h:211-213)
+        const bool z0 = len0 > 0 && tk[0].col0 == 0 && tk[0].own0 == 0 && (tk[0].forced < 0 || tk[0].forced == 0);
+        const bool z1 = len1 > 0 && tk[1].col0 == 0 && tk[1].own0 == 0 && (tk[1].forced < 0 || tk[1].forced == 0);
+        uint32_t bestS = pk(z0 ? OFF : 0, z1 ? OFF : 0);        // un-biased score + OFF per half; 0 = none yet
+        int ord0 = 0, ord1 = 0;
+        int finS0 = 0, finS1 = 0, finI0 = 0, finI1 = 0, finE0 = 0, finE1 = 0;   // best final-column cell: score+OFF, row, eq bits
+        const uint8_t *const seq0 = L.arena + tk[0].off;
+        const uint8_t *const seq1 = L.arena + tk[1].off;
+        const int lim0 = max(len0 - 1, 0), lim1 = max(len1 - 1, 0);
+
+        uint32_t Mo[NR], Hl[NR];
+#pragma unroll
+        for (int r = 0; r < NR; ++r) { Mo[r] = pk2(B0 + b * (r + 1)); Hl[r] = 0; }   // column 0: M = 0, H = -inf
+        uint32_t rowT = pk2(B0);                                 // biased M(0, j) = bias of row 0 at the current column
+        const uint32_t nB = pk2(b * n);
+        uint32_t *ckp = ck;
+        uint32_t cur0 = load4(seq0, 0, lim0), cur1 = load4(seq1, 0, lim1);
+
+        // =========================== pass 1: score only ===========================
+        for (int j0 = 1; j0 <= mw; j0 += 4) {
+            const uint32_t nxt0 = load4(seq0, j0 + 3, lim0), nxt1 = load4(seq1, j0 + 3, lim1);   // used one group later
+            if (TRACE && ((j0 - 1) & (C - 1)) == 0) {            // checkpoint = state after column j0-1 (a multiple of C)
+#pragma unroll
+                for (int r = 0; r < NR; ++r) { ckp[(2 * r) * T] = Mo[r]; ckp[(2 * r + 1) * T] = Hl[r]; }
+                ckp += 2ull * NR * T;
+            }
+            if (!TRACE && ((j0 - 1) & (REBASE - 1)) == 0 && j0 > 1) {   // keep the growing bias inside 15 bits
+                const uint32_t d = pk2(b * REBASE);
+#pragma unroll
+                for (int r = 0; r < NR; ++r) { Mo[r] -= d; Hl[r] -= d; }
+                rowT -= d;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int j = j0 + k;
+                const uint32_t Q0 = profile(prmt(cur0, 0, 0x4440 + k), DELTA, MISW);
+                const uint32_t Q1 = profile(prmt(cur1, 0, 0x4440 + k), DELTA, MISW);
+                const uint32_t rowTp = rowT;
+                rowT += Bp;
+                uint32_t Ml, Vl, Hlast;
+                col_score<NR, EXACT>(Mo, Hl, s_sel, Q0, Q1, rowTp, rowT, GEB, nm1, Ml, Vl, Hlast);
+                {   // scout, row class: strict '>' in visiting order (dp_scout.h:167-180)
+                    uint32_t cand = Ml + OFFp - (rowT + nB);
+                    if (j < ulo || j > uhi)
+                        cand &= ((j >= lo0 && j <= hi0) ? 0x0000FFFFu : 0u) | ((j >= lo1 && j <= hi1) ? 0xFFFF0000u : 0u);
+                    bool keep_hi, keep_lo;
+                    bestS = vmax_keep(bestS, cand, keep_hi, keep_lo);
+                    if (!keep_lo) ord0 = j;
+                    if (!keep_hi) ord1 = j;
+                }
+                if (j >= ufin) {
+                    const bool d0 = fin0 && j == len0, d1 = fin1 && j == len1;
+                    if (d0 || d1) {
+                        // final column of a half (adapter overhanging the read end): rows 1..n in order; V rebuilt as the
+                        // forward pass computed it.  Through shared memory, so that the row loop is not unrolled.
+#pragma unroll
+                        for (int r = 0; r < NR; ++r) { s_fl[(2 * r) * PCB_BLOCK] = Mo[r]; s_fl[(2 * r + 1) * PCB_BLOCK] = Hl[r]; }
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            if (!(h ? d1 : d0)) continue;
+                            const int forced = tk[h].forced, len = tk[h].len;
+                            int Tn = half16(rowT, h), Vp = 0, Mp = Tn, best = 0, bi = 0, be = 0;
+                            for (int i = 1; i <= n; ++i) {
+                                const int M = half16(s_fl[(2 * (i - 1)) * PCB_BLOCK], h), H = half16(s_fl[(2 * (i - 1) + 1) * PCB_BLOCK], h);
+                                const int V = max(Vp + geb, Mp);
+                                Tn += b;
+                                const int c = M + OFF - Tn;
+                                if ((forced < 0 || forced == len + i) && c > best) { best = c; bi = i; be = ((V == M) ? 2 : 0) | ((H == M) ? 1 : 0); }
+                                Vp = V; Mp = M;
+                            }
+                            if (h) { finS1 = best; finI1 = bi; finE1 = be; } else { finS0 = best; finI0 = bi; finE0 = be; }
+                        }
+                    }
+                }
+            }
+            cur0 = nxt0; cur1 = nxt1;
+        }
+
+        // merge row class and final-column class (final-column cells are visited last: they win only if strictly better)
+        int sc0 = (int)(bestS & 0xFFFFu), sc1 = (int)(bestS >> 16);
+        bool fc0 = false, fc1 = false;
+        if (finS0 > sc0) { sc0 = finS0; ord0 = len0 + finI0; fc0 = true; }
+        if (finS1 > sc1) { sc1 = finS1; ord1 = len1 + finI1; fc1 = true; }
+
+        if (!TRACE) {
+            // order key as pcb_kernels.cu: (score << 16) | ((0x3FFF - ord) << 2); the eq bits are re-derived by the trace launch
+            if (tk[0].out_idx >= 0) L.scan_out[tk[0].out_idx] = (len0 > 0 && sc0 > 0) ? (int)(((uint32_t)(sc0 - OFF) << 16) | ((uint32_t)(0x3FFF - ord0) << 2)) : (int)0x80000000;
+            if (tk[1].out_idx >= 0) L.scan_out[tk[1].out_idx] = (len1 > 0 && sc1 > 0) ? (int)(((uint32_t)(sc1 - OFF) << 16) | ((uint32_t)(0x3FFF - ord1) << 2)) : (int)0x80000000;
+            continue;
+        }
+
+        // =========================== pass 2: flags for the blocks the traceback crosses ===========================
+        int ci[2], cj[2], endi[2], endj[2], state[2], score[2];
+        bool done[2], first[2], rowcls[2];
+        PathAcc acc[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const HalfTask &t = tk[h];
+            const int sc = h ? sc1 : sc0, ord = h ? ord1 : ord0;
+            const bool fc = h ? fc1 : fc0;
+            done[h] = true; first[h] = true; rowcls[h] = !fc; state[h] = 0; score[h] = sc - OFF;
+            ci[h] = cj[h] = endi[h] = endj[h] = 0;
+            path_acc_init(acc[h]);
+            if (t.out_idx < 0) continue;
+            if (t.len <= 0) { write_failed(L.out, t.out_idx); continue; }
+            if (sc <= 0) { atomicOr(L.err_flag, 2); write_failed(L.out, t.out_idx); continue; }   // forced cell not found
+            if (fc) { ci[h] = ord - t.len; cj[h] = t.len; const int e = h ? finE1 : finE0; state[h] = (e & 2) ? 1 : ((e & 1) ? 2 : 0); }
+            else    { ci[h] = n; cj[h] = ord; }
+            endi[h] = ci[h]; endj[h] = cj[h];
+            done[h] = false;
+        }
+
+        for (;;) {
+            // a half whose walk already stands on row 0 / column 0 is finished (this also covers the empty path)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (done[h] || (ci[h] > 0 && cj[h] > 0)) continue;
+                const HalfTask &t = tk[h];
+                if (cj[h] == 0 && ci[h] > 0 && t.col0 > 0) atomicOr(L.err_flag, 1);   // window too narrow for this path
+                PathStats st;
+                path_finalize(acc[h], (int64_t)t.col0 + cj[h], ci[h], (int64_t)t.m_true - (t.col0 + endj[h]), n - endi[h],
+                              t.m_true, n, st);
+                pcb_result res;
+                res.read_start = st.read_start; res.read_end = st.read_end;
+                res.adapter_start = st.adapter_start; res.adapter_end = st.adapter_end;
+                res.raw_score = score[h]; res.matches = st.matches;
+                res.aligned_len = st.aligned_len; res.full_len = st.full_len;
+                L.out[t.out_idx] = res;
+                done[h] = true;
+            }
+            if (!__any_sync(0xffffffffu, !done[0] || !done[1])) break;
+
+            // block of each half: columns k*C+1 .. k*C+C, holding its current column
+            const int k0 = done[0] ? 0 : (cj[0] - 1) / C, k1 = done[1] ? 0 : (cj[1] - 1) / C;
+            const int need = max(done[0] ? 0 : cj[0] - k0 * C, done[1] ? 0 : cj[1] - k1 * C);
+            const int tmax = __reduce_max_sync(0xffffffffu, need);
+            const int jb0 = k0 * C, jb1 = k1 * C;
+            // the block's read bases (16 per half), then the checkpointed column the block starts from
+            uint32_t q0[C / 4], q1[C / 4];
+#pragma unroll
+            for (int g = 0; g < C / 4; ++g) { q0[g] = load4(seq0, jb0 + 4 * g, lim0); q1[g] = load4(seq1, jb1 + 4 * g, lim1); }
+            {
+                const uint32_t *p0 = ck + (uint64_t)k0 * 2ull * NR * T, *p1 = ck + (uint64_t)k1 * 2ull * NR * T;
+#pragma unroll
+                for (int r = 0; r < NR; ++r) {
+                    Mo[r] = prmt(p0[(2 * r) * T], p1[(2 * r) * T], 0x7610);
+                    Hl[r] = prmt(p0[(2 * r + 1) * T], p1[(2 * r + 1) * T], 0x7610);
+                }
+            }
+            uint32_t rT = pk(B0 + b * jb0, B0 + b * jb1);
+            for (int t = 1; t <= tmax; ++t) {
+                const uint32_t Q0 = profile(q0[0] & 0xFFu, DELTA, MISW), Q1 = profile(q1[0] & 0xFFu, DELTA, MISW);
+#pragma unroll
+                for (int g = 0; g < C / 4; ++g) {                  // shift the base queues by one byte
+                    q0[g] = __funnelshift_r(q0[g], g + 1 < C / 4 ? q0[(g + 1) % (C / 4)] : 0u, 8);
+                    q1[g] = __funnelshift_r(q1[g], g + 1 < C / 4 ? q1[(g + 1) % (C / 4)] : 0u, 8);
+                }
+                const uint32_t rowTp = rT;
+                rT += Bp;
+                uint32_t Ml, Vl, Hlast;
+                col_flags<NR, EXACT>(Mo, Hl, s_sel, Q0, Q1, rowTp, rT, GEB, nm1, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
+                // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
+                // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
+                const uint32_t xv = Ml ^ Vl, xh = Ml ^ Hlast;
+                if (!done[0] && first[0] && rowcls[0] && jb0 + t == cj[0]) state[0] = ((xv & 0xFFFFu) == 0) ? 1 : (((xh & 0xFFFFu) == 0) ? 2 : 0);
+                if (!done[1] && first[1] && rowcls[1] && jb1 + t == cj[1]) state[1] = ((xv >> 16) == 0) ? 1 : (((xh >> 16) == 0) ? 2 : 0);
+            }
+            __syncwarp();
+            // walk (dp_traceback_impl.h:379-451, :498-545) inside the block
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (done[h]) continue;
+                first[h] = false;
+                const int base = h ? jb1 : jb0;
+                const uint8_t *const seq = h ? seq1 : seq0;
+                int i = ci[h], j = cj[h], s = state[h];
+                PathAcc a = acc[h];
+                while (i > 0 && j > base) {
+                    const int ar = i - 1;
+                    const uint32_t w = s_fl[((j - base - 1) * FW + (ar >> 2)) * PCB_BLOCK];
+                    const int sh = 8 * h + 2 * (ar & 3);
+                    if (s == 0) {
+                        if ((w >> (17 + sh)) & 1) {
+                            path_acc_step(a, 0, (uint32_t)(seq[j - 1] / PCB_CODE_SCALE) == (s_sel[ar] & 7u));
+                            --i; --j;
+                        } else {
+                            s = ((w >> (sh + 1)) & 1) ? 1 : 2;
+                        }
+                    } else if (s == 1) {
+                        path_acc_step(a, 1, 0);
+                        --i;
+                        s = ((w >> (16 + sh)) & 1) ? 1 : 0;
+                    } else {
+                        path_acc_step(a, 2, 0);
+                        --j;
+                        s = ((w >> sh) & 1) ? 2 : 0;
+                    }
+                }
+                ci[h] = i; cj[h] = j; state[h] = s; acc[h] = a;
+            }
+            __syncwarp();
+        }
+    }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// host-side launchers.  cls 0: every adapter of the launch has exactly 24 bases; cls 1: adapters of 1..32 bases.
+// ------------------------------------------------------------------------------------------------
+static size_t fast_smem(bool trace, int nr)
+{
+    const size_t per_thread = trace ? (size_t)C * (nr / 4) : (size_t)2 * nr;
+    return ((size_t)(PCB_BLOCK / 32) * nr + (size_t)PCB_BLOCK * per_thread) * sizeof(uint32_t);
+}
+
+template <bool TRACE, int NR, bool EXACT>
+static cudaError_t launch_one(const PcbLaunch &L, cudaStream_t st)
+{
+    static bool attr = false;
+    const size_t sm = fast_smem(TRACE, NR);
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(k_fast<TRACE, NR, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if (e != cudaSuccess) return e;
+        attr = true;
+    }
+    k_fast<TRACE, NR, EXACT><<<L.grid, PCB_BLOCK, sm, st>>>(L);
+    return cudaGetLastError();
+}
+
+cudaError_t pcf_launch(const PcbLaunch &L, bool trace, int cls, cudaStream_t st)
+{
+    if (L.src.n_units == 0) return cudaSuccess;
+    if (cls == 0) return trace ? launch_one<true, 24, true>(L, st) : launch_one<false, 24, true>(L, st);
+    return trace ? launch_one<true, 32, false>(L, st) : launch_one<false, 32, false>(L, st);
+}
+
+template <bool TRACE, int NR, bool EXACT>
+static int occ_one()
+{
+    int per = 0;
+    const size_t sm = fast_smem(TRACE, NR);
+    cudaFuncSetAttribute(k_fast<TRACE, NR, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_fast<TRACE, NR, EXACT>, PCB_BLOCK, sm);
+    return per < 1 ? 1 : per;
+}
+
+int pcf_occupancy_grid(bool trace, int cls)
+{
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int per = cls == 0 ? (trace ? occ_one<true, 24, true>() : occ_one<false, 24, true>())
+                             : (trace ? occ_one<true, 32, false>() : occ_one<false, 32, false>());
+    return sms * per;
+}

@@ -52,15 +52,15 @@ __device__ __forceinline__ int lo16(uint32_t x) { return (int)(short)(x & 0xFFFF
 __device__ __forceinline__ int hi16(uint32_t x) { return (int)x >> 16; }
 __device__ __forceinline__ int half16(uint32_t x, int h) { return h ? hi16(x) : lo16(x); }
 
-// SeqAn's char -> Dna5 table (seqan/basic/alphabet_residue_tabs.h:113-140)
+// SeqAn's char -> Dna5 table (seqan/basic/alphabet_residue_tabs.h:113-140); stored as code * PCB_CODE_SCALE
 __device__ __forceinline__ uint8_t dna5_code(unsigned char c)
 {
     switch (c) {
     case 'A': case 'a': return 0;
-    case 'C': case 'c': return 1;
-    case 'G': case 'g': return 2;
-    case 'T': case 't': case 'U': case 'u': return 3;
-    default: return 4;
+    case 'C': case 'c': return 1 * PCB_CODE_SCALE;
+    case 'G': case 'g': return 2 * PCB_CODE_SCALE;
+    case 'T': case 't': case 'U': case 'u': return 3 * PCB_CODE_SCALE;
+    default: return 4 * PCB_CODE_SCALE;
     }
 }
 
@@ -122,7 +122,7 @@ __device__ __forceinline__ void fetch_task(const PcbSource &src, int64_t unit, i
         if (w < src.n_windows) {
             t.off = (uint64_t)w * (uint64_t)src.stride;
             t.len = src.win_len[w]; t.m_true = t.len;
-            t.out_idx = w * src.n_ids + k;
+            t.out_idx = w * src.n_ids_total + (src.id_pos ? src.id_pos[k] : k);
         }
     }
 }

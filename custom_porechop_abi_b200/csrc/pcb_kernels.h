@@ -13,8 +13,14 @@
 #ifndef PCB_MIN_BLOCKS
 #define PCB_MIN_BLOCKS  4         /* CTAs per SM the register allocation is held to               */
 #endif
+#define PCB_CODE_SCALE  8         /* arena bytes = Dna5 code * 8 (a byte shift for the fast kernels) */
 #define PCB_NEG_INF     (-8192)   /* "minus infinity" in a signed 16-bit lane                     */
 #define PCB_MAX_TRACE_M 8000      /* widest segment the trace kernel takes (order key is 14 bit)  */
+
+/* fast kernels (pcb_fast.cu): affine schemes, adapters of <= PCB_RT bases */
+#define PCF_C             16      /* checkpoint distance = width of a flag block (columns)        */
+#define PCF_MAX_TRACE_M   1000    /* widest segment of the two-pass trace kernel (no bias re-basing) */
+#define PCF_MAX_SCAN_M    12000   /* widest scan chunk (order key is 14 bit)                      */
 
 /* One alignment task as the kernels see it. 32 bytes. */
 struct PcbTask {
@@ -48,8 +54,10 @@ struct PcbSource {
     int64_t  n_windows;
     int32_t  stride;
     const int32_t *win_len;
-    const int32_t *ids;
+    const int32_t *ids;          /* adapters of this launch                                      */
     int32_t  n_ids;
+    const int32_t *id_pos;       /* position of ids[k] in the caller's id list (NULL: k)         */
+    int32_t  n_ids_total;        /* length of the caller's id list: out[w * n_ids_total + pos]   */
     int64_t  n_units;
 };
 
@@ -96,5 +104,14 @@ cudaError_t pcb_launch_encode(const char *ascii, uint8_t *codes, uint64_t n, cud
 cudaError_t pcb_launch_trace(const PcbLaunch &L, cudaStream_t st);
 cudaError_t pcb_launch_scan(const PcbLaunch &L, cudaStream_t st);
 int pcb_occupancy_grid(int which /*0 trace, 1 scan*/);
+
+/* fast kernels: cls 0 = adapters of exactly 24 bases, cls 1 = adapters of 1..32 bases */
+#define PCF_EXACT_N 24
+cudaError_t pcf_launch(const PcbLaunch &L, bool trace, int cls, cudaStream_t st);
+int pcf_occupancy_grid(bool trace, int cls);
+static inline uint64_t pcf_scratch_words_trace(int mmax, int cls)
+{
+    return (uint64_t)((mmax + PCF_C - 1) / PCF_C + 1) * 2ull * (cls == 0 ? PCF_EXACT_N : PCB_RT);     /* checkpoints */
+}
 
 #endif
