@@ -21,7 +21,7 @@ import sys
 from ctypes import CDLL, POINTER, Structure, byref, c_char_p, c_float, c_int, c_int32, c_int64, c_uint64, c_void_p, cast
 
 SO_FILE = 'cpp_functions.so'
-SO_FILE_FULL = os.path.join(os.path.dirname(os.path.realpath(__file__)), SO_FILE)
+SO_FILE_FULL = os.environ.get('PCB_SO') or os.path.join(os.path.dirname(os.path.realpath(__file__)), SO_FILE)
 if not os.path.isfile(SO_FILE_FULL):
     sys.exit('could not find ' + SO_FILE + ' - build it with: python -c "import __graft_entry__ as g; g.build()"')
 C_LIB = CDLL(SO_FILE_FULL)

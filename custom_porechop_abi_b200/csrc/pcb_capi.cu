@@ -307,6 +307,8 @@ extern "C" int pcb_stage_windows(pcb_context *c, const char *windows, int64_t n_
         PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->S().d_arena.p, bytes, c->stream));
         c->cnt.kernel_launches++;
     }
+    // the kernels fetch bases a few bytes past a segment's end: keep valid codes there
+    PCB_CUDA(c, cudaMemsetAsync(c->S().d_arena.p + bytes, 0, 16, c->stream));
     c->cnt.h2d_bytes += (int64_t)bytes + (int64_t)sizeof(int32_t) * n_windows;
     c->S().arena_len = bytes; c->S().n_windows = n_windows; c->S().stride = stride; c->S().win_mmax = mmax;
     return PCB_OK;
@@ -494,6 +496,7 @@ extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blo
         PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena_t.p, (uint64_t)blob_len, c->stream));
         c->cnt.kernel_launches++;
     }
+    PCB_CUDA(c, cudaMemsetAsync(c->d_arena_t.p + blob_len, 0, 16, c->stream));   // valid codes past the last segment
     c->cnt.h2d_bytes += blob_len;
     c->arena_t_len = (uint64_t)blob_len;
     return PCB_OK;

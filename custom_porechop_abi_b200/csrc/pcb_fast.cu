@@ -37,6 +37,15 @@
 
 namespace {
 
+#ifdef PCF_FORCE_MINB
+#define PCF_MINB(TRACE, NR) PCF_FORCE_MINB
+#else
+#define PCF_MINB(TRACE, NR) (((TRACE) && (NR) > 24) ? 3 : 4)
+#endif
+#ifndef PCF_UNROLL
+#define PCF_UNROLL 4
+#endif
+constexpr int UNR = PCF_UNROLL;
 constexpr int RT = PCB_RT;            // 32 adapter rows in registers
 constexpr int C = PCF_C;              // checkpoint distance / flag block width (columns)
 constexpr int B0 = 64;                // base bias: keeps every stored value > 0
@@ -124,79 +133,83 @@ __device__ __forceinline__ void write_failed(pcb_result *out, int64_t idx)
 
 
 // ------------------------------------------------------------------------------------------------
-// One DP column, score only, for the two tasks of this thread.  Mo[r] / Hl[r]: M and H of the left neighbour (biased),
-// updated in place.  rowTp / rowT: biased M(0, j-1) / M(0, j).  The diagonal term of the NEXT row (old Mo[r] + score)
-// is formed before Mo[r] is overwritten, so nothing has to be copied.  5 instructions per row:
-// PRMT, IADD, VIADDMNMX (H), VIADDMNMX (V), VIMNMX3 (M).  Recurrence: seqan/align/dp_formula_affine.h:65-124.
-// Returns V of row NR-1; with !EXACT also captures M, V, H of row nm1 (the adapter's last row).
+// Score table of a warp's adapter, in shared memory: tbl[r * 25 + p] = packed (score(b0, adapter[r]) + 2b,
+// score(b1, adapter[r]) + 2b) for the pair p = 5 * code(b0) + code(b1) of read bases the two tasks of a thread see in
+// a column.  A cell's substitution score is then ONE shared-memory load at [per-column pointer + constant row offset]:
+// no ALU instruction (the 25 words of a row lie in 25 different banks: conflict-free for any mix of lanes).
 // ------------------------------------------------------------------------------------------------
+constexpr int TP = 25;
+
+// One DP column, score only, for the two tasks of this thread.  Mo[r] / Hl[r]: M and H of the left neighbour (biased),
+// updated in place.  rowTp / rowT: biased M(0, j-1) / M(0, j).  tp = tbl + p of this column.  The diagonal term of the
+// NEXT row (old Mo[r] + score) is formed before Mo[r] is overwritten.  Per row: LDS, IADD, VIADDMNMX (H),
+// VIADDMNMX (V), VIMNMX3 (M).  Recurrence: seqan/align/dp_formula_affine.h:65-124.
+// Ml / Vl / Hlast: M, V, H of the adapter's last row (row nm1; with EXACT that is row NR-1).
 template <int NR, bool EXACT>
-__device__ __forceinline__ void col_score(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *s_sel, uint32_t Q0, uint32_t Q1,
-                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, int nm1, uint32_t &Ml, uint32_t &Vl, uint32_t &Hlast)
+__device__ __forceinline__ void col_score(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *tp,
+                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, int nm1, uint32_t &Ml)
 {
-    uint32_t Dn = rowTp + prmt(Q0, Q1, s_sel[0]);
+    uint32_t Dn = rowTp + tp[0];
     uint32_t Vu = rowT;                              // V(1, j) = M(0, j) + gapOpen  (row 0: V = -inf)
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
         const uint32_t Hn = __viaddmax_s16x2(Hl[r], GEB, Mo[r]);
         if (r > 0) Vu = __viaddmax_s16x2(Vu, GEB, Mo[r - 1]);
         const uint32_t D = Dn;
-        if (r < NR - 1) Dn = Mo[r] + prmt(Q0, Q1, s_sel[r + 1]);
+        if (r < NR - 1) Dn = Mo[r] + tp[(r + 1) * TP];
         Mo[r] = __vimax3_s16x2(D, Vu, Hn); Hl[r] = Hn;
-        if (!EXACT && r == nm1) { Ml = Mo[r]; Vl = Vu; Hlast = Hn; }
+        if (!EXACT && r == nm1) Ml = Mo[r];
     }
-    if (EXACT) { Ml = Mo[NR - 1]; Vl = Vu; Hlast = Hl[NR - 1]; }
+    if (EXACT) Ml = Mo[NR - 1];
 }
 
-// ------------------------------------------------------------------------------------------------
 // The same column with trace flags (pass 2).  Flag bits of row r, half h, in flag word r >> 2 with q = r & 3:
 //      bit 8h+2q   : H extended (H_left + ge >= M_left + go)     bit 8h+2q+1    : V >= H
 //      bit 16+8h+2q: V extended                                  bit 16+8h+2q+1 : diagonal >= max(V, H)
 // (tie rules of dp_formula_affine.h:65-124 / dp_formula.h:147-163: the left operand of each _maxScore wins ties).
-// fp: this thread's flag words of the column, stride PCB_BLOCK.
-// ------------------------------------------------------------------------------------------------
+// "x >= y" is bit 15 of x + GUARD - y (one IADD3) for 15-bit non-negative x, y.  fp: this thread's flag words of the
+// column, stride PCB_BLOCK.
 template <int NR, bool EXACT>
-__device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *s_sel, uint32_t Q0, uint32_t Q1,
+__device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *tp,
                                           uint32_t rowTp, uint32_t rowT, uint32_t GEB, int nm1, uint32_t *fp,
                                           uint32_t &Ml, uint32_t &Vl, uint32_t &Hlast)
 {
-    uint32_t Dn = rowTp + prmt(Q0, Q1, s_sel[0]);
+    uint32_t Dn = rowTp + tp[0];
     uint32_t Vu = 0, Wacc = 0;
+    const uint32_t GEBG = GEB + GUARD;
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
         const uint32_t D = Dn;
         const uint32_t Mup = (r == 0) ? rowT : Mo[(r > 0) ? r - 1 : 0];
-        const uint32_t he = Hl[r] + GEB, ve = Vu + GEB;
-        const uint32_t Hn = __vmaxs2(he, Mo[r]), Vn = __vmaxs2(ve, Mup);
+        const uint32_t ch = Hl[r] + GEBG - Mo[r], cv = Vu + GEBG - Mup;
+        const uint32_t Hn = __viaddmax_s16x2(Hl[r], GEB, Mo[r]), Vn = __viaddmax_s16x2(Vu, GEB, Mup);
         const uint32_t G = __vmaxs2(Vn, Hn);
-        const uint32_t W = (sign4(cmpge(he, Mo[r]), cmpge(ve, Mup)) & 0x55555555u) |
-                           (sign4(cmpge(Vn, Hn), cmpge(D, G)) & 0xAAAAAAAAu);
+        const uint32_t W = (sign4(ch, cv) & 0x55555555u) | (sign4(cmpge(Vn, Hn), cmpge(D, G)) & 0xAAAAAAAAu);
         if ((r & 3) == 0) Wacc = W;
         else if ((r & 3) == 1) Wacc = (Wacc & 0x03030303u) | (W & 0xFCFCFCFCu);
         else if ((r & 3) == 2) Wacc = (Wacc & 0x0F0F0F0Fu) | (W & 0xF0F0F0F0u);
         else Wacc = (Wacc & 0x3F3F3F3Fu) | (W & 0xC0C0C0C0u);
         if ((r & 3) == 3 || r == NR - 1) fp[(r >> 2) * PCB_BLOCK] = Wacc;
-        if (r < NR - 1) Dn = Mo[r] + prmt(Q0, Q1, s_sel[r + 1]);
+        if (r < NR - 1) Dn = Mo[r] + tp[(r + 1) * TP];
         Vu = Vn; Mo[r] = __vmaxs2(D, G); Hl[r] = Hn;
         if (!EXACT && r == nm1) { Ml = Mo[r]; Vl = Vn; Hlast = Hn; }
     }
     if (EXACT) { Ml = Mo[NR - 1]; Vl = Vu; Hlast = Hl[NR - 1]; }
 }
 
-// four consecutive sequence bytes starting at seq[pos] (pos clamped to lim), through two aligned word loads
-__device__ __forceinline__ uint32_t load4(const uint8_t *seq, int pos, int lim)
+// Four consecutive sequence bytes starting at seq[pos] (pos clamped to lim) come from two aligned words; the funnel shift
+// that joins them is done where the bytes are used, so that the loads can be issued a group of columns ahead.
+struct Raw4 { uint32_t w0, w1, sh; };
+__device__ __forceinline__ Raw4 load4(const uint8_t *seq, int pos, int lim)
 {
     const uintptr_t a = (uintptr_t)(seq + min(pos, lim));
     const uint32_t *p = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
-    return __funnelshift_r(p[0], p[1], (uint32_t)(a & 3) * 8u);
+    Raw4 r; r.w0 = p[0]; r.w1 = p[1]; r.sh = (uint32_t)(a & 3) * 8u;
+    return r;
 }
-// profile word of one read base: byte c = score of this base against adapter base c, + 2b   (code8 = Dna5 code * 8)
-__device__ __forceinline__ uint32_t profile(uint32_t code8, uint32_t DELTA, uint32_t MISW)
-{
-    uint32_t q;
-    asm("shl.b32 %0, %1, %2;" : "=r"(q) : "r"(DELTA), "r"(code8));      // shift >= 32 (N) gives 0
-    return q + MISW;
-}
+__device__ __forceinline__ uint32_t join4(const Raw4 &r) { return __funnelshift_r(r.w0, r.w1, r.sh); }
+// offset (in words) into a row of the score table for the two code bytes (Dna5 code * 8) of a column
+__device__ __forceinline__ uint32_t pair_index(uint32_t c8_0, uint32_t c8_1) { return (c8_0 * 5u + c8_1) >> 3; }
 
 // ------------------------------------------------------------------------------------------------
 // k_fast<TRACE, NR, EXACT>
@@ -204,34 +217,59 @@ __device__ __forceinline__ uint32_t profile(uint32_t code8, uint32_t DELTA, uint
 //                  traceback, statistics) -> pcb_result
 //   TRACE=false -> pass 1 only -> order key per task (scan chunks of long reads)
 //   NR / EXACT  -> adapter rows in registers; EXACT: every adapter of the launch has exactly NR bases
-// grid: persistent, blockDim = PCB_BLOCK; warp w of the grid takes units w, w + nwarps, ...
-// dynamic smem: [PCB_BLOCK/32][NR] PRMT selectors of each warp's adapter, then a per-thread area strided by PCB_BLOCK
-//               (TRACE: C*NR/4 flag words; always >= 2*NR words for the final-column dump).
+// grid: persistent, blockDim = PCB_BLOCK.  Cross-product launches are walked adapter-major in contiguous per-warp ranges
+// (a warp re-builds its score table only when the adapter changes); explicit task lists are walked strided.
+// dynamic smem: [W][NR*25] score tables, [W][NR] adapter codes, then a per-thread area strided by PCB_BLOCK
+//               (TRACE: C*NR/4 flag words + 2*C/4 words of block bases; always >= 2*NR words for the final-column dump).
 // ------------------------------------------------------------------------------------------------
 template <bool TRACE, int NR, bool EXACT>
-__global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(const PcbLaunch L)
+__global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const PcbLaunch L)
 {
     extern __shared__ uint32_t smem[];
     constexpr int FW = NR / 4;                           // flag words per column
+    constexpr int W = PCB_BLOCK / 32;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t T = (uint64_t)gridDim.x * blockDim.x;
     const uint64_t slot = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t *const s_sel = smem + warp * NR;
-    uint32_t *const s_fl = smem + (PCB_BLOCK / 32) * NR + threadIdx.x;
+    uint32_t *const tbl = smem + warp * (NR * TP);
+    uint32_t *const s_code = smem + W * (NR * TP) + warp * NR;
+    uint32_t *const s_fl = smem + W * (NR * TP + NR) + threadIdx.x;
     uint32_t *const ck = L.scratch + slot;               // checkpoints [k][2*NR], element stride T
 
     const int b = -L.sc.gap_open;
-    const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b), OFFp = pk2(OFF);
-    const uint32_t MISW = (uint32_t)(L.sc.mismatch + 2 * b) * 0x01010101u;
-    const uint32_t DELTA = (uint32_t)(L.sc.match - L.sc.mismatch);
+    const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b);
+    const int s_match = L.sc.match + 2 * b, s_mis = L.sc.mismatch + 2 * b;
     const int geb = L.sc.gap_extend + b;
 
-    const int64_t nwarps = (int64_t)gridDim.x * (PCB_BLOCK / 32);
-    for (int64_t unit = (int64_t)blockIdx.x * (PCB_BLOCK / 32) + warp; unit < L.src.n_units; unit += nwarps) {
+    const int64_t nwarps = (int64_t)gridDim.x * W, gw = (int64_t)blockIdx.x * W + warp;
+    const bool cross = L.src.units == nullptr;
+    const int64_t groups = cross ? (L.src.n_windows + 63) / 64 : 0;
+    int64_t u_begin, u_end, u_step;
+    if (cross) { u_begin = gw * L.src.n_units / nwarps; u_end = (gw + 1) * L.src.n_units / nwarps; u_step = 1; }
+    else       { u_begin = gw; u_end = L.src.n_units; u_step = nwarps; }
+    int32_t tbl_adapter = -1;
+
+    for (int64_t unit = u_begin; unit < u_end; unit += u_step) {
         int32_t adapter = 0;
         HalfTask tk[2];
-        fetch_task(L.src, unit, 2 * lane, adapter, tk[0]);
-        fetch_task(L.src, unit, 2 * lane + 1, adapter, tk[1]);
+        if (cross) {                                     // adapter-major: unit = k * groups + g
+            const int64_t k = unit / groups, g = unit - k * groups;
+            adapter = L.src.ids[k];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                HalfTask &t = tk[h];
+                t.off = 0; t.len = 0; t.col0 = 0; t.m_true = 0; t.forced = -1; t.own0 = 0; t.out_idx = -1;
+                const int64_t w = g * 64 + 2 * lane + h;
+                if (w < L.src.n_windows) {
+                    t.off = (uint64_t)w * (uint64_t)L.src.stride;
+                    t.len = L.src.win_len[w]; t.m_true = t.len;
+                    t.out_idx = w * L.src.n_ids_total + (L.src.id_pos ? L.src.id_pos[k] : (int32_t)k);
+                }
+            }
+        } else {
+            fetch_task(L.src, unit, 2 * lane, adapter, tk[0]);
+            fetch_task(L.src, unit, 2 * lane + 1, adapter, tk[1]);
+        }
         const int64_t aoff = L.ad.off[adapter];
         const int n = (int)(L.ad.off[adapter + 1] - aoff);
         if (n <= 0 || n > NR || (EXACT && n != NR)) {          // the host never sends these here; fail loudly if it does
@@ -242,12 +280,18 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
             continue;
         }
         const int nm1 = n - 1;
-        __syncwarp();
-        for (int i = lane; i < NR; i += 32) {
-            const uint32_t c = i < n ? (uint32_t)(L.ad.codes[aoff + i] / PCB_CODE_SCALE) & 3u : 0u;
-            s_sel[i] = c | ((8u | c) << 4) | ((4u + c) << 8) | ((12u + c) << 12);
+        if (adapter != tbl_adapter) {
+            __syncwarp();
+            for (int i = lane; i < NR; i += 32) s_code[i] = i < n ? (uint32_t)(L.ad.codes[aoff + i] / PCB_CODE_SCALE) : 0u;
+            __syncwarp();
+            for (int e = lane; e < NR * TP; e += 32) {
+                const int r = e / TP, p = e - r * TP;
+                const uint32_t a = s_code[r], c0 = (uint32_t)(p / 5), c1 = (uint32_t)(p % 5);
+                tbl[e] = pk(c0 == a ? s_match : s_mis, c1 == a ? s_match : s_mis);
+            }
+            __syncwarp();
+            tbl_adapter = adapter;
         }
-        __syncwarp();
 
         const int len0 = tk[0].len, len1 = tk[1].len;
         const int mw = __reduce_max_sync(0xffffffffu, max(len0, len1));
@@ -258,12 +302,11 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
         int lo1 = tk[1].own0 + 1, hi1 = fin1 ? len1 - 1 : len1;
         if (tk[0].forced >= 0) { if (tk[0].forced <= hi0) { lo0 = max(lo0, tk[0].forced); hi0 = tk[0].forced; } else hi0 = -1; }
         if (tk[1].forced >= 0) { if (tk[1].forced <= hi1) { lo1 = max(lo1, tk[1].forced); hi1 = tk[1].forced; } else hi1 = -1; }
-        // columns in which every task of the warp takes its candidate (no masking needed), and the first column in
-        // which some task of the warp reaches its final column
+        // "lean" columns [ulo, uhi]: every task of the warp takes its row-class candidate and none is at its final column
         const bool act0 = tk[0].out_idx >= 0 && len0 > 0, act1 = tk[1].out_idx >= 0 && len1 > 0;
         const int ulo = __reduce_max_sync(0xffffffffu, max(act0 ? lo0 : 0, act1 ? lo1 : 0));
-        const int uhi = __reduce_min_sync(0xffffffffu, min(act0 ? hi0 : 0x7fffffff, act1 ? hi1 : 0x7fffffff));
         const int ufin = __reduce_min_sync(0xffffffffu, min(fin0 ? len0 : 0x7fffffff, fin1 ? len1 : 0x7fffffff));
+        const int uhi = min(__reduce_min_sync(0xffffffffu, min(act0 ? hi0 : 0x7fffffff, act1 ? hi1 : 0x7fffffff)), ufin - 1);
         // cell (n, 0): first tracked cell of the matrix, score 0 (dp_meta_info.h:211-213)
         const bool z0 = len0 > 0 && tk[0].col0 == 0 && tk[0].own0 == 0 && (tk[0].forced < 0 || tk[0].forced == 0);
         const bool z1 = len1 > 0 && tk[1].col0 == 0 && tk[1].own0 == 0 && (tk[1].forced < 0 || tk[1].forced == 0);
@@ -278,13 +321,54 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
 #pragma unroll
         for (int r = 0; r < NR; ++r) { Mo[r] = pk2(B0 + b * (r + 1)); Hl[r] = 0; }   // column 0: M = 0, H = -inf
         uint32_t rowT = pk2(B0);                                 // biased M(0, j) = bias of row 0 at the current column
-        const uint32_t nB = pk2(b * n);
+        const uint32_t candK = pk2(OFF - b * n);                 // candidate = M(n, j) + candK - rowT = score + OFF
         uint32_t *ckp = ck;
-        uint32_t cur0 = load4(seq0, 0, lim0), cur1 = load4(seq1, 0, lim1);
+        Raw4 nx0 = load4(seq0, 0, lim0), nx1 = load4(seq1, 0, lim1);
+
+        // one column; `general` (compile-time after inlining): candidate masks and final-column handling
+        auto column = [&](const int j, const uint32_t c8_0, const uint32_t c8_1, const bool general) {
+            const uint32_t *tp = tbl + pair_index(c8_0, c8_1);
+            const uint32_t rowTp = rowT;
+            rowT += Bp;
+            uint32_t Ml;
+            col_score<NR, EXACT>(Mo, Hl, tp, rowTp, rowT, GEB, nm1, Ml);
+            uint32_t cand = Ml + candK - rowT;                    // scout, row class: strict '>' in visiting order (dp_scout.h:167-180)
+            if (general)
+                cand &= ((j >= lo0 && j <= hi0) ? 0x0000FFFFu : 0u) | ((j >= lo1 && j <= hi1) ? 0xFFFF0000u : 0u);
+            bool keep_hi, keep_lo;
+            bestS = vmax_keep(bestS, cand, keep_hi, keep_lo);
+            if (!keep_lo) ord0 = j;
+            if (!keep_hi) ord1 = j;
+            if (general) {
+                const bool d0 = fin0 && j == len0, d1 = fin1 && j == len1;
+                if (d0 || d1) {
+                    // final column of a half (adapter overhanging the read end): rows 1..n in order; V rebuilt as the
+                    // forward pass computed it.  Through shared memory, so that the row loop is not unrolled.
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) { s_fl[(2 * r) * PCB_BLOCK] = Mo[r]; s_fl[(2 * r + 1) * PCB_BLOCK] = Hl[r]; }
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        if (!(h ? d1 : d0)) continue;
+                        const int forced = tk[h].forced, len = tk[h].len;
+                        int Tn = half16(rowT, h), Vp = 0, Mp = Tn, best = 0, bi = 0, be = 0;
+                        for (int i = 1; i <= n; ++i) {
+                            const int M = half16(s_fl[(2 * (i - 1)) * PCB_BLOCK], h), H = half16(s_fl[(2 * (i - 1) + 1) * PCB_BLOCK], h);
+                            const int V = max(Vp + geb, Mp);
+                            Tn += b;
+                            const int c = M + OFF - Tn;
+                            if ((forced < 0 || forced == len + i) && c > best) { best = c; bi = i; be = ((V == M) ? 2 : 0) | ((H == M) ? 1 : 0); }
+                            Vp = V; Mp = M;
+                        }
+                        if (h) { finS1 = best; finI1 = bi; finE1 = be; } else { finS0 = best; finI0 = bi; finE0 = be; }
+                    }
+                }
+            }
+        };
 
         // =========================== pass 1: score only ===========================
         for (int j0 = 1; j0 <= mw; j0 += 4) {
-            const uint32_t nxt0 = load4(seq0, j0 + 3, lim0), nxt1 = load4(seq1, j0 + 3, lim1);   // used one group later
+            uint32_t cur0 = join4(nx0), cur1 = join4(nx1);
+            nx0 = load4(seq0, j0 + 3, lim0); nx1 = load4(seq1, j0 + 3, lim1);       // used one group later
             if (TRACE && ((j0 - 1) & (C - 1)) == 0) {            // checkpoint = state after column j0-1 (a multiple of C)
 #pragma unroll
                 for (int r = 0; r < NR; ++r) { ckp[(2 * r) * T] = Mo[r]; ckp[(2 * r + 1) * T] = Hl[r]; }
@@ -296,50 +380,13 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
                 for (int r = 0; r < NR; ++r) { Mo[r] -= d; Hl[r] -= d; }
                 rowT -= d;
             }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int j = j0 + k;
-                const uint32_t Q0 = profile(prmt(cur0, 0, 0x4440 + k), DELTA, MISW);
-                const uint32_t Q1 = profile(prmt(cur1, 0, 0x4440 + k), DELTA, MISW);
-                const uint32_t rowTp = rowT;
-                rowT += Bp;
-                uint32_t Ml, Vl, Hlast;
-                col_score<NR, EXACT>(Mo, Hl, s_sel, Q0, Q1, rowTp, rowT, GEB, nm1, Ml, Vl, Hlast);
-                {   // scout, row class: strict '>' in visiting order (dp_scout.h:167-180)
-                    uint32_t cand = Ml + OFFp - (rowT + nB);
-                    if (j < ulo || j > uhi)
-                        cand &= ((j >= lo0 && j <= hi0) ? 0x0000FFFFu : 0u) | ((j >= lo1 && j <= hi1) ? 0xFFFF0000u : 0u);
-                    bool keep_hi, keep_lo;
-                    bestS = vmax_keep(bestS, cand, keep_hi, keep_lo);
-                    if (!keep_lo) ord0 = j;
-                    if (!keep_hi) ord1 = j;
-                }
-                if (j >= ufin) {
-                    const bool d0 = fin0 && j == len0, d1 = fin1 && j == len1;
-                    if (d0 || d1) {
-                        // final column of a half (adapter overhanging the read end): rows 1..n in order; V rebuilt as the
-                        // forward pass computed it.  Through shared memory, so that the row loop is not unrolled.
-#pragma unroll
-                        for (int r = 0; r < NR; ++r) { s_fl[(2 * r) * PCB_BLOCK] = Mo[r]; s_fl[(2 * r + 1) * PCB_BLOCK] = Hl[r]; }
-#pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            if (!(h ? d1 : d0)) continue;
-                            const int forced = tk[h].forced, len = tk[h].len;
-                            int Tn = half16(rowT, h), Vp = 0, Mp = Tn, best = 0, bi = 0, be = 0;
-                            for (int i = 1; i <= n; ++i) {
-                                const int M = half16(s_fl[(2 * (i - 1)) * PCB_BLOCK], h), H = half16(s_fl[(2 * (i - 1) + 1) * PCB_BLOCK], h);
-                                const int V = max(Vp + geb, Mp);
-                                Tn += b;
-                                const int c = M + OFF - Tn;
-                                if ((forced < 0 || forced == len + i) && c > best) { best = c; bi = i; be = ((V == M) ? 2 : 0) | ((H == M) ? 1 : 0); }
-                                Vp = V; Mp = M;
-                            }
-                            if (h) { finS1 = best; finI1 = bi; finE1 = be; } else { finS0 = best; finI0 = bi; finE0 = be; }
-                        }
-                    }
-                }
+            if (j0 >= ulo && j0 + 3 <= uhi) {
+#pragma unroll UNR
+                for (int k = 0; k < 4; ++k) { column(j0 + k, cur0 & 0xFFu, cur1 & 0xFFu, false); cur0 >>= 8; cur1 >>= 8; }
+            } else {
+#pragma unroll 1
+                for (int k = 0; k < 4; ++k) { column(j0 + k, cur0 & 0xFFu, cur1 & 0xFFu, true); cur0 >>= 8; cur1 >>= 8; }
             }
-            cur0 = nxt0; cur1 = nxt1;
         }
 
         // merge row class and final-column class (final-column cells are visited last: they win only if strictly better)
@@ -354,17 +401,21 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
             if (tk[1].out_idx >= 0) L.scan_out[tk[1].out_idx] = (len1 > 0 && sc1 > 0) ? (int)(((uint32_t)(sc1 - OFF) << 16) | ((uint32_t)(0x3FFF - ord1) << 2)) : (int)0x80000000;
             continue;
         }
+#ifdef PCF_SKIP_PASS2
+        { pcb_result r{}; r.raw_score = sc0 - OFF; r.read_end = ord0; if (tk[0].out_idx >= 0) L.out[tk[0].out_idx] = r;
+          r.raw_score = sc1 - OFF; r.read_end = ord1; if (tk[1].out_idx >= 0) L.out[tk[1].out_idx] = r; continue; }
+#endif
 
         // =========================== pass 2: flags for the blocks the traceback crosses ===========================
         int ci[2], cj[2], endi[2], endj[2], state[2], score[2];
-        bool done[2], first[2], rowcls[2];
+        bool done[2], rowcls[2];
         PathAcc acc[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const HalfTask &t = tk[h];
             const int sc = h ? sc1 : sc0, ord = h ? ord1 : ord0;
             const bool fc = h ? fc1 : fc0;
-            done[h] = true; first[h] = true; rowcls[h] = !fc; state[h] = 0; score[h] = sc - OFF;
+            done[h] = true; rowcls[h] = !fc; state[h] = 0; score[h] = sc - OFF;
             ci[h] = cj[h] = endi[h] = endj[h] = 0;
             path_acc_init(acc[h]);
             if (t.out_idx < 0) continue;
@@ -376,7 +427,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
             done[h] = false;
         }
 
-        for (;;) {
+        for (int iter = 0;; ++iter) {
             // a half whose walk already stands on row 0 / column 0 is finished (this also covers the empty path)
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
@@ -404,7 +455,10 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
             // the block's read bases (16 per half), then the checkpointed column the block starts from
             uint32_t q0[C / 4], q1[C / 4];
 #pragma unroll
-            for (int g = 0; g < C / 4; ++g) { q0[g] = load4(seq0, jb0 + 4 * g, lim0); q1[g] = load4(seq1, jb1 + 4 * g, lim1); }
+            for (int g = 0; g < C / 4; ++g) {
+                q0[g] = join4(load4(seq0, jb0 + 4 * g, lim0)); q1[g] = join4(load4(seq1, jb1 + 4 * g, lim1));
+                s_fl[(C * FW + g) * PCB_BLOCK] = q0[g]; s_fl[(C * FW + C / 4 + g) * PCB_BLOCK] = q1[g];   // for the walk
+            }
             {
                 const uint32_t *p0 = ck + (uint64_t)k0 * 2ull * NR * T, *p1 = ck + (uint64_t)k1 * 2ull * NR * T;
 #pragma unroll
@@ -415,7 +469,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
             }
             uint32_t rT = pk(B0 + b * jb0, B0 + b * jb1);
             for (int t = 1; t <= tmax; ++t) {
-                const uint32_t Q0 = profile(q0[0] & 0xFFu, DELTA, MISW), Q1 = profile(q1[0] & 0xFFu, DELTA, MISW);
+                const uint32_t *tp = tbl + pair_index(q0[0] & 0xFFu, q1[0] & 0xFFu);
 #pragma unroll
                 for (int g = 0; g < C / 4; ++g) {                  // shift the base queues by one byte
                     q0[g] = __funnelshift_r(q0[g], g + 1 < C / 4 ? q0[(g + 1) % (C / 4)] : 0u, 8);
@@ -424,21 +478,22 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
                 const uint32_t rowTp = rT;
                 rT += Bp;
                 uint32_t Ml, Vl, Hlast;
-                col_flags<NR, EXACT>(Mo, Hl, s_sel, Q0, Q1, rowTp, rT, GEB, nm1, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
-                // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
-                // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
-                const uint32_t xv = Ml ^ Vl, xh = Ml ^ Hlast;
-                if (!done[0] && first[0] && rowcls[0] && jb0 + t == cj[0]) state[0] = ((xv & 0xFFFFu) == 0) ? 1 : (((xh & 0xFFFFu) == 0) ? 2 : 0);
-                if (!done[1] && first[1] && rowcls[1] && jb1 + t == cj[1]) state[1] = ((xv >> 16) == 0) ? 1 : (((xh >> 16) == 0) ? 2 : 0);
+                col_flags<NR, EXACT>(Mo, Hl, tp, rowTp, rT, GEB, nm1, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
+                if (iter == 0) {
+                    // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
+                    // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
+                    const uint32_t xv = Ml ^ Vl, xh = Ml ^ Hlast;
+                    if (!done[0] && rowcls[0] && jb0 + t == cj[0]) state[0] = ((xv & 0xFFFFu) == 0) ? 1 : (((xh & 0xFFFFu) == 0) ? 2 : 0);
+                    if (!done[1] && rowcls[1] && jb1 + t == cj[1]) state[1] = ((xv >> 16) == 0) ? 1 : (((xh >> 16) == 0) ? 2 : 0);
+                }
             }
             __syncwarp();
             // walk (dp_traceback_impl.h:379-451, :498-545) inside the block
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if (done[h]) continue;
-                first[h] = false;
                 const int base = h ? jb1 : jb0;
-                const uint8_t *const seq = h ? seq1 : seq0;
+                const uint32_t *const sb = s_fl + (C * FW + h * (C / 4)) * PCB_BLOCK;     // the block's bases
                 int i = ci[h], j = cj[h], s = state[h];
                 PathAcc a = acc[h];
                 while (i > 0 && j > base) {
@@ -447,7 +502,8 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
                     const int sh = 8 * h + 2 * (ar & 3);
                     if (s == 0) {
                         if ((w >> (17 + sh)) & 1) {
-                            path_acc_step(a, 0, (uint32_t)(seq[j - 1] / PCB_CODE_SCALE) == (s_sel[ar] & 7u));
+                            const uint32_t code8 = (sb[((j - base - 1) >> 2) * PCB_BLOCK] >> (8 * ((j - base - 1) & 3))) & 0xFFu;
+                            path_acc_step(a, 0, code8 == s_code[ar] * PCB_CODE_SCALE);
                             --i; --j;
                         } else {
                             s = ((w >> (sh + 1)) & 1) ? 1 : 2;
@@ -476,8 +532,8 @@ __global__ void __launch_bounds__(PCB_BLOCK, (TRACE && NR > 24) ? 3 : 4) k_fast(
 // ------------------------------------------------------------------------------------------------
 static size_t fast_smem(bool trace, int nr)
 {
-    const size_t per_thread = trace ? (size_t)C * (nr / 4) : (size_t)2 * nr;
-    return ((size_t)(PCB_BLOCK / 32) * nr + (size_t)PCB_BLOCK * per_thread) * sizeof(uint32_t);
+    const size_t per_thread = trace ? (size_t)C * (nr / 4) + 2 * (C / 4) : (size_t)2 * nr;   // flags + block bases | column dump
+    return ((size_t)(PCB_BLOCK / 32) * (nr * TP + nr) + (size_t)PCB_BLOCK * per_thread) * sizeof(uint32_t);
 }
 
 template <bool TRACE, int NR, bool EXACT>
