@@ -77,3 +77,17 @@ def test_synthetic_workload_shape():
     for r in (0, 17, 199):
         read = bytes(blob[off[r]:off[r + 1]])
         assert bytes(sbuf[r, :lens[r]]) == read[:150] and bytes(ebuf[r, :lens[r]]) == read[-150:]
+
+
+def test_no_oracle_in_product():
+    """The product path may not reach the oracle (or any CPU alignment code): nothing under the package, the public
+    header or the C sources names oracle/ or its symbols."""
+    bad = []
+    for base in (os.path.join(ROOT, 'custom_porechop_abi_b200'), os.path.join(ROOT, 'include')):
+        for dp, _, files in os.walk(base):
+            for f in files:
+                if f.endswith(('.py', '.cu', '.h', '.cpp', '.c')):
+                    text = open(os.path.join(dp, f), errors='replace').read()
+                    if re.search(r'oracle|pc_oracle_|libporechop_oracle|cpp_functions_ref', text):
+                        bad.append(os.path.join(dp, f))
+    assert not bad, bad
