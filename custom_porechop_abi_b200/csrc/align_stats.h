@@ -52,6 +52,34 @@ PCB_HD void path_acc_step(PathAcc &a, int op, int is_match)
     a.K = k + 1;
 }
 
+/* Cheaper accumulation for the fast kernels' walk: instead of step indices it keeps cell coordinates, and the step
+ * indices PathAcc wants are recovered at the end (rows and columns only ever decrease along the reverse walk):
+ *   kA = max over ops holding an adapter base (D, V) of 2*j + isV, j = column before the op: the FIRST such op has the
+ *        largest j, and if V ops share that column they come before the D that leaves it;
+ *   kR = the same for read bases (D, H) with rows: 2*i + isH;
+ *   jA / iR = column / row after the LAST op holding an adapter / read base.  */
+struct WalkAcc {
+    int32_t nD, matches, kA, kR, jA, iR;
+};
+PCB_HD void walk_acc_init(WalkAcc &a) { a.nD = 0; a.matches = 0; a.kA = -1; a.kR = -1; a.jA = 0; a.iR = 0; }
+PCB_HD void walk_acc_D(WalkAcc &a, int i, int j, int is_match)
+{
+    a.nD++; a.matches += is_match;
+    a.kA = a.kA > 2 * j ? a.kA : 2 * j; a.kR = a.kR > 2 * i ? a.kR : 2 * i;
+    a.jA = j - 1; a.iR = i - 1;
+}
+PCB_HD void walk_acc_V(WalkAcc &a, int i, int j) { (void)i; a.kA = a.kA > 2 * j + 1 ? a.kA : 2 * j + 1; a.jA = j; }
+PCB_HD void walk_acc_H(WalkAcc &a, int i, int j) { (void)j; a.kR = a.kR > 2 * i + 1 ? a.kR : 2 * i + 1; a.iR = i; }
+/* (endi, endj): cell the walk started from; (ci, cj): cell it stopped at. */
+PCB_HD void walk_acc_finish(const WalkAcc &w, int endi, int endj, int ci, int cj, PathAcc &a)
+{
+    const int K = (endi - ci) + (endj - cj) - w.nD;
+    a.K = K; a.matches = w.matches;
+    a.kA_last_rev = -1; a.kA_first_rev = -1; a.kR_last_rev = -1; a.kR_first_rev = -1; a.A_last_isD = 0; a.R_last_isD = 0;
+    if (w.kA >= 0) { a.kA_last_rev = endj - (w.kA >> 1); a.A_last_isD = !(w.kA & 1); a.kA_first_rev = K - 1 - (w.jA - cj); }
+    if (w.kR >= 0) { a.kR_last_rev = endi - (w.kR >> 1); a.R_last_isD = !(w.kR & 1); a.kR_first_rev = K - 1 - (w.iR - ci); }
+}
+
 struct PathStats {
     int32_t read_start, read_end, adapter_start, adapter_end, matches, aligned_len, full_len;
 };

@@ -49,7 +49,7 @@ struct pcb_context {
     PcbScores sc{3, -6, -5, -2, 0};
     // adapters
     std::vector<int64_t> ad_off;          // host copy
-    std::vector<uint8_t> ad_fast;         // kernel class of an adapter: 0 = exactly 24 bases, 1 = 1..32 bases (both ACGT only), 2 = general kernels
+    std::vector<uint8_t> ad_fast;         // kernel class of an adapter (pcb_kernels.h): 0..PCF_NCLS-1 fast kernels (ACGT only), PCF_NCLS = general kernels
     uint64_t stamp = 1;                   // bumped when the scoring scheme or the adapter set changes
     int32_t n_adapters = 0;
     DevBuf<uint8_t> d_ad_codes;
@@ -66,7 +66,7 @@ struct pcb_context {
         int64_t sum_winlen = 0;
         DevBuf<int32_t> d_winlen, d_ids;      // d_ids: [fast ids | other ids | fast positions | other positions]
         std::vector<int32_t> h_ids, h_split;
-        int32_t n_cls[3] = {0, 0, 0}; uint64_t split_stamp = 0;
+        int32_t n_cls[PCF_NCLS + 1] = {}; uint64_t split_stamp = 0;
         int64_t n_windows = 0; int32_t stride = 0, n_ids = 0, win_mmax = 0;
         DevBuf<pcb_result> d_out;
         int64_t n_results = 0;
@@ -75,15 +75,25 @@ struct pcb_context {
     int cur = 0;
     Slot &S() { return slots[cur]; }
     // explicit tasks
-    struct HostTask { int64_t off; int32_t len; int32_t adapter; };
-    std::vector<HostTask> h_tasks;
+    int64_t n_tasks = 0, task_long_cols = 0, task_cells = 0;
+    DevBuf<int64_t> d_seg_off, d_plan_i64;
+    DevBuf<int32_t> d_seg_len, d_seg_ad, d_plan_i32;
+    DevBuf<PcbAdInfo> d_adinfo;
     DevBuf<PcbTask> d_tasks;
     DevBuf<PcbUnit> d_units;
     DevBuf<int32_t> d_scan;
+    DevBuf<PcbLong> d_longs;
+    struct TaskPlan {
+        struct Launch { bool trace; int cls, kind /*0 direct, 1 scan, 2 window*/; int64_t cells, task0, unit0, n_units; int mmax, nmax, smax, grid; };
+        std::vector<Launch> launches;
+        int64_t n_long = 0, n_chunks = 0, win_task0 = 0;
+        uint64_t scratch_words = 0, stamp = 0;
+        bool valid = false;
+    } plan;
     // outputs / scratch
     DevBuf<uint32_t> d_scratch;
     DevBuf<int32_t> d_err;
-    int grid_trace = 0, grid_scan = 0, grid_ftrace[2] = {0, 0}, grid_fscan[2] = {0, 0};
+    int grid_trace = 0, grid_scan = 0, grid_ftrace[PCF_NCLS] = {}, grid_fscan[PCF_NCLS] = {};
     pcb_counters cnt{};
     bool ktiming = false;
 
@@ -135,7 +145,7 @@ extern "C" int pcb_create(int device, pcb_context **out)
     }
     c->grid_trace = pcb_occupancy_grid(0);
     c->grid_scan = pcb_occupancy_grid(1);
-    for (int cls = 0; cls < 2; ++cls) { c->grid_ftrace[cls] = pcf_occupancy_grid(true, cls); c->grid_fscan[cls] = pcf_occupancy_grid(false, cls); }
+    for (int cls = 0; cls < PCF_NCLS; ++cls) { c->grid_ftrace[cls] = pcf_occupancy_grid(true, cls); c->grid_fscan[cls] = pcf_occupancy_grid(false, cls); }
     if (c->d_err.reserve(1) != cudaSuccess) { g_global_err = "cudaMalloc failed"; delete c; return PCB_ERR_NOMEM; }
     *out = c;
     return PCB_OK;
@@ -148,7 +158,8 @@ extern "C" void pcb_destroy(pcb_context *c)
     cudaStreamSynchronize(c->stream);
     c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_arena_t.release();
     for (auto &sl : c->slots) { sl.d_arena.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release(); }
-    c->d_tasks.release(); c->d_units.release(); c->d_scan.release();
+    c->d_tasks.release(); c->d_units.release(); c->d_scan.release(); c->d_longs.release();
+    c->d_seg_off.release(); c->d_plan_i64.release(); c->d_seg_len.release(); c->d_seg_ad.release(); c->d_plan_i32.release(); c->d_adinfo.release();
     c->d_scratch.release(); c->d_err.release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->kev0); cudaEventDestroy(c->kev1);
     cudaStreamDestroy(c->stream);
@@ -187,9 +198,9 @@ extern "C" int pcb_set_adapters(pcb_context *c, const char *blob, const int64_t 
     c->ad_fast.assign((size_t)n_adapters, 0);
     for (int i = 0; i < n_adapters; ++i) {
         const int64_t len = c->ad_off[i + 1] - c->ad_off[i];
-        bool ok = len >= 1 && len <= PCB_RT;
+        bool ok = len >= 1 && len <= PCF_MAX_N;
         for (int64_t k = c->ad_off[i]; ok && k < c->ad_off[i + 1]; ++k) ok = strchr("ACGTUacgtu", blob[base + k]) != nullptr && blob[base + k] != 0;
-        c->ad_fast[(size_t)i] = !ok ? 2 : (len == PCF_EXACT_N ? 0 : 1);
+        c->ad_fast[(size_t)i] = (uint8_t)(ok ? pcf_class_of_len((long)len) : PCF_NCLS);
     }
     c->stamp++;
     PCB_CUDA(c, c->d_ad_codes.reserve((size_t)total + 16));
@@ -259,11 +270,11 @@ static void fill_launch_common(pcb_context *c, PcbLaunch &L, bool task_arena = f
 }
 
 // launch with optional per-kernel event timing
-// cls: 0 / 1 = fast kernels (pcb_fast.cu), 2 = general kernels (pcb_kernels.cu)
-static int launch_dp(pcb_context *c, const PcbLaunch &L, bool trace, int64_t cells, int cls = 2)
+// cls: 0 .. PCF_NCLS-1 = fast kernels (pcb_fast.cu), PCF_NCLS = general kernels (pcb_kernels.cu)
+static int launch_dp(pcb_context *c, const PcbLaunch &L, bool trace, int64_t cells, int cls = PCF_NCLS)
 {
     if (c->ktiming) PCB_CUDA(c, cudaEventRecord(c->kev0, c->stream));
-    if (cls < 2) PCB_CUDA(c, pcf_launch(L, trace, cls, c->stream));
+    if (cls < PCF_NCLS) PCB_CUDA(c, pcf_launch(L, trace, cls, c->stream));
     else         PCB_CUDA(c, trace ? pcb_launch_trace(L, c->stream) : pcb_launch_scan(L, c->stream));
     if (c->ktiming) {
         PCB_CUDA(c, cudaEventRecord(c->kev1, c->stream));
@@ -333,15 +344,15 @@ static int split_ids(pcb_context *c, bool fast_ok)
     pcb_context::Slot &S = c->S();
     if (S.split_stamp == c->stamp) return PCB_OK;
     const int n = S.n_ids;
-    std::vector<int32_t> id[3], pos[3];
+    std::vector<int32_t> id[PCF_NCLS + 1], pos[PCF_NCLS + 1];
     for (int k = 0; k < n; ++k) {
         const int32_t a = S.h_ids[(size_t)k];
-        const int cls = fast_ok ? c->ad_fast[(size_t)a] : 2;
+        const int cls = fast_ok ? c->ad_fast[(size_t)a] : PCF_NCLS;
         id[cls].push_back(a); pos[cls].push_back(k);
     }
     S.h_split.clear();
-    for (int q = 0; q < 3; ++q) { S.n_cls[q] = (int32_t)id[q].size(); S.h_split.insert(S.h_split.end(), id[q].begin(), id[q].end()); }
-    for (int q = 0; q < 3; ++q) S.h_split.insert(S.h_split.end(), pos[q].begin(), pos[q].end());
+    for (int q = 0; q <= PCF_NCLS; ++q) { S.n_cls[q] = (int32_t)id[q].size(); S.h_split.insert(S.h_split.end(), id[q].begin(), id[q].end()); }
+    for (int q = 0; q <= PCF_NCLS; ++q) S.h_split.insert(S.h_split.end(), pos[q].begin(), pos[q].end());
     PCB_CUDA(c, S.d_ids.reserve((size_t)2 * n + 1));
     // h_split lives in the slot until the next split, so the asynchronous copy may read it later
     if (n) PCB_CUDA(c, cudaMemcpyAsync(S.d_ids.p, S.h_split.data(), sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, c->stream));
@@ -368,7 +379,7 @@ extern "C" int pcb_run_windows_resident(pcb_context *c)
     const int64_t groups = (S.n_windows + 63) / 64;
     // the small launches first: their tails then overlap nothing bigger than themselves
     int first = 0;
-    for (int cls = 2; cls >= 0; --cls) {
+    for (int cls = PCF_NCLS; cls >= 0; --cls) {
         const int cnt = S.n_cls[cls];
         if (cnt == 0) continue;
         int start = 0;
@@ -376,11 +387,11 @@ extern "C" int pcb_run_windows_resident(pcb_context *c)
         const int32_t *h_list = S.h_split.data() + start;
         const int nmax = max_adapter_len(c, h_list, cnt);
         const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
-        if (cls == 2 && (rc = check_range(c, nmax, mmax))) return rc;
+        if (cls == PCF_NCLS && (rc = check_range(c, nmax, mmax))) return rc;
         const int64_t n_units = groups * cnt;
-        const int gmax = cls < 2 ? c->grid_ftrace[cls] : c->grid_trace;
+        const int gmax = cls < PCF_NCLS ? c->grid_ftrace[cls] : c->grid_trace;
         const int grid = (int)std::min<int64_t>(gmax, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
-        rc = ensure_scratch(c, cls < 2 ? pcf_scratch_words_trace(mmax, cls) : pcb_scratch_words_trace(mmax, smax), grid);
+        rc = ensure_scratch(c, cls < PCF_NCLS ? pcf_scratch_words_trace(mmax, cls) : pcb_scratch_words_trace(mmax, smax), grid);
         if (rc) return rc;
         PcbLaunch L; fill_launch_common(c, L);
         L.src.units = nullptr; L.src.tasks = nullptr;
@@ -459,20 +470,6 @@ WindowBounds window_bounds(const PcbScores &s, int n)
     return b;
 }
 
-// group tasks (already sorted by adapter) into units of <= per_unit (<= 64) tasks
-void build_units(const std::vector<PcbTask> &tasks, const std::vector<int32_t> &adapter_of, int per_unit, std::vector<PcbUnit> &units)
-{
-    units.clear();
-    size_t i = 0;
-    while (i < tasks.size()) {
-        size_t j = i;
-        while (j < tasks.size() && adapter_of[j] == adapter_of[i] && j - i < (size_t)per_unit) ++j;
-        PcbUnit u; u.adapter = adapter_of[i]; u.ntask = (int32_t)(j - i); u.task0 = (int64_t)i;
-        units.push_back(u);
-        i = j;
-    }
-}
-
 }  // namespace
 
 extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, const int64_t *seg_off,
@@ -481,183 +478,192 @@ extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blo
     if (!c || blob_len < 0 || n_tasks < 0 || (n_tasks > 0 && (!seg_off || !seg_len || !task_adapter)) || (blob_len > 0 && !seq_blob))
         return PCB_ERR_ARG;
     cudaSetDevice(c->device);
-    c->h_tasks.resize((size_t)n_tasks);
-    for (int64_t t = 0; t < n_tasks; ++t) {
-        if (seg_len[t] < 0 || seg_off[t] < 0 || seg_off[t] + seg_len[t] > blob_len)
-            return c->fail(PCB_ERR_ARG, "task %lld: segment [%lld, +%d) outside the blob", (long long)t, (long long)seg_off[t], seg_len[t]);
-        if (task_adapter[t] < 0 || task_adapter[t] >= c->n_adapters)
-            return c->fail(PCB_ERR_ARG, "task %lld: adapter id %d out of range", (long long)t, task_adapter[t]);
-        c->h_tasks[(size_t)t] = { seg_off[t], seg_len[t], task_adapter[t] };
-    }
+    c->plan.valid = false; c->n_tasks = 0;
+    // copies first (asynchronous from pinned memory), so that the host-side checks below run under them
     PCB_CUDA(c, c->d_ascii.reserve((size_t)blob_len + 16));
     PCB_CUDA(c, c->d_arena_t.reserve((size_t)blob_len + 16));
+    PCB_CUDA(c, c->d_seg_off.reserve((size_t)n_tasks + 1));
+    PCB_CUDA(c, c->d_seg_len.reserve((size_t)n_tasks + 1));
+    PCB_CUDA(c, c->d_seg_ad.reserve((size_t)n_tasks + 1));
     if (blob_len) {
         PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, seq_blob, (size_t)blob_len, cudaMemcpyHostToDevice, c->stream));
         PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena_t.p, (uint64_t)blob_len, c->stream));
         c->cnt.kernel_launches++;
     }
     PCB_CUDA(c, cudaMemsetAsync(c->d_arena_t.p + blob_len, 0, 16, c->stream));   // valid codes past the last segment
+    if (n_tasks) {
+        PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_off.p, seg_off, sizeof(int64_t) * n_tasks, cudaMemcpyHostToDevice, c->stream));
+        PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_len.p, seg_len, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->stream));
+        PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_ad.p, task_adapter, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->stream));
+    }
+    int64_t long_cols = 0, cells = 0;
+    for (int64_t t = 0; t < n_tasks; ++t) {
+        const bool bad_seg = seg_len[t] < 0 || seg_off[t] < 0 || seg_off[t] + seg_len[t] > blob_len;
+        const bool bad_ad = task_adapter[t] < 0 || task_adapter[t] >= c->n_adapters;
+        if (bad_seg || bad_ad) {
+            cudaStreamSynchronize(c->stream);               // the caller's buffers are still being read
+            if (bad_seg) return c->fail(PCB_ERR_ARG, "task %lld: segment [%lld, +%d) outside the blob", (long long)t, (long long)seg_off[t], seg_len[t]);
+            return c->fail(PCB_ERR_ARG, "task %lld: adapter id %d out of range", (long long)t, task_adapter[t]);
+        }
+        if (seg_len[t] > 960) long_cols += seg_len[t];
+        cells += (int64_t)seg_len[t] * (c->ad_off[(size_t)task_adapter[t] + 1] - c->ad_off[(size_t)task_adapter[t]]);
+    }
+    c->n_tasks = n_tasks; c->task_long_cols = long_cols; c->task_cells = cells;
+    c->cnt.h2d_bytes += 16 * n_tasks;
     c->cnt.h2d_bytes += blob_len;
     c->arena_t_len = (uint64_t)blob_len;
     return PCB_OK;
 }
 
-// One explicit launch: tasks (sorted by adapter) through the trace or scan kernel, fast or general flavour.
-static int run_explicit(pcb_context *c, std::vector<PcbTask> &tasks, std::vector<int32_t> &adapter_of, bool trace, int cls,
-                        int64_t cells)
+// ------------------------------------------------------------------------------------------------
+// The plan of a staged task list: every launch the run needs, with its task / unit arrays already in HBM.  It depends
+// only on the staged segments, the adapter set and the scoring scheme, so it is built once per staging (or when one
+// of those changes) and a run is nothing but a sequence of kernel launches on the context's stream: direct traces,
+// chunk scans, one merge kernel (best end cell per long read -> its trace-window task), window traces.  No host
+// round trip inside a run.
+// ------------------------------------------------------------------------------------------------
+static int build_task_plan(pcb_context *c)
 {
-    if (tasks.empty()) return PCB_OK;
-    int mmax = 1, nmax = 1;
-    for (size_t i = 0; i < tasks.size(); ++i) {
-        mmax = std::max(mmax, tasks[i].len);
-        nmax = std::max(nmax, (int)(c->ad_off[(size_t)adapter_of[i] + 1] - c->ad_off[(size_t)adapter_of[i]]));
-    }
-    int rc;
-    const bool fast = cls < 2;
-    if (!fast && (rc = check_range(c, nmax, mmax))) return rc;
-    if (fast && mmax > (trace ? PCF_MAX_TRACE_M : PCF_MAX_SCAN_M)) return c->fail(PCB_ERR_RANGE, "internal: segment of %d columns sent to the fast kernels", mmax);
-    const int gmax = fast ? (trace ? c->grid_ftrace[cls] : c->grid_fscan[cls]) : (trace ? c->grid_trace : c->grid_scan);
-    // fewer tasks per warp when there is not enough work to fill the machine (a warp's time does not depend on its lanes)
-    const int64_t warps = (int64_t)gmax * (PCB_BLOCK / 32);
-    const int per_unit = (int)std::min<int64_t>(64, std::max<int64_t>(2, ((int64_t)tasks.size() + warps - 1) / warps));
-    std::vector<PcbUnit> units;
-    build_units(tasks, adapter_of, per_unit, units);
-    PCB_CUDA(c, c->d_tasks.reserve(tasks.size()));
-    PCB_CUDA(c, c->d_units.reserve(units.size()));
-    PCB_CUDA(c, cudaMemcpyAsync(c->d_tasks.p, tasks.data(), sizeof(PcbTask) * tasks.size(), cudaMemcpyHostToDevice, c->stream));
-    PCB_CUDA(c, cudaMemcpyAsync(c->d_units.p, units.data(), sizeof(PcbUnit) * units.size(), cudaMemcpyHostToDevice, c->stream));
-    c->cnt.h2d_bytes += (int64_t)(sizeof(PcbTask) * tasks.size() + sizeof(PcbUnit) * units.size());
-    const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
-    const int64_t n_units = (int64_t)units.size();
-    const int grid = (int)std::min<int64_t>(gmax, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
-    const uint64_t words = fast ? (trace ? pcf_scratch_words_trace(mmax, cls) : 1)
-                                : (trace ? pcb_scratch_words_trace(mmax, smax) : pcb_scratch_words_scan(mmax, smax));
-    if ((rc = ensure_scratch(c, words, grid))) return rc;
-    PcbLaunch L; fill_launch_common(c, L, true);
-    L.src.units = c->d_units.p; L.src.tasks = c->d_tasks.p; L.src.n_units = n_units;
-    L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
-    rc = launch_dp(c, L, trace, cells, cls);
-    if (rc) return rc;
-    // the host vectors are about to go out of scope: the copies above must have completed
-    PCB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return PCB_OK;
-}
+    pcb_context::TaskPlan &P = c->plan;
+    P.launches.clear(); P.n_long = 0; P.n_chunks = 0; P.win_task0 = 0; P.scratch_words = 0; P.valid = false;
+    const int64_t nt = c->n_tasks;
+    if (nt == 0) { P.valid = true; P.stamp = c->stamp; return PCB_OK; }
+    const bool fast_sc = fast_scheme(c->sc) && !getenv("PCB_NO_FAST");
+    const int A = c->n_adapters;
 
-namespace {
-struct TaskList {                       // tasks of one launch, in adapter order
-    std::vector<PcbTask> tasks;
-    std::vector<int32_t> ad;
-    int64_t cells = 0;
-    void add(const PcbTask &t, int32_t adapter, int64_t ncells) { tasks.push_back(t); ad.push_back(adapter); cells += ncells; }
-};
+    // per adapter: length, class, margins
+    std::vector<PcbAdInfo> ad((size_t)A);
+    const int direct_default = 960;
+    for (int a = 0; a < A; ++a) {
+        PcbAdInfo &x = ad[(size_t)a];
+        x.n = (int)(c->ad_off[(size_t)a + 1] - c->ad_off[(size_t)a]);
+        x.cls = fast_sc ? c->ad_fast[(size_t)a] : PCF_NCLS;
+        const WindowBounds wb = window_bounds(c->sc, x.n);
+        x.warm = wb.warm; x.span = wb.span; x.chunked = wb.ok ? 1 : 0;
+        x.direct_max = std::max(direct_default, wb.ok ? wb.warm + wb.span + 8 : 0);
+    }
+    // chunk length: enough chunks to fill the machine, but long enough to amortise the warm-up margin
+    const int chunk = (int)std::min<int64_t>(4096, std::max<int64_t>(1024, c->task_long_cols / (2 * 64 * (int64_t)std::max(1, c->grid_fscan[0]) * (PCB_BLOCK / 32))));
+
+    // pass 1 on the device: items per (kind, adapter, length bucket), widest item per (kind, class)
+    const size_t nb = (size_t)PCB_KINDS * A * PCB_LB, nm = (size_t)PCB_KINDS * (PCF_NCLS + 1);
+    PCB_CUDA(c, c->d_plan_i32.reserve(2 * nb + nm));
+    PCB_CUDA(c, c->d_plan_i64.reserve(nb));
+    PCB_CUDA(c, c->d_adinfo.reserve((size_t)A));
+    PCB_CUDA(c, cudaMemsetAsync(c->d_plan_i32.p, 0, sizeof(int32_t) * (2 * nb + nm), c->stream));
+    PCB_CUDA(c, cudaMemcpyAsync(c->d_adinfo.p, ad.data(), sizeof(PcbAdInfo) * A, cudaMemcpyHostToDevice, c->stream));
+    PcbPlanArgs pa{};
+    pa.seg_off = c->d_seg_off.p; pa.seg_len = c->d_seg_len.p; pa.seg_ad = c->d_seg_ad.p; pa.n_tasks = nt;
+    pa.ad = c->d_adinfo.p; pa.n_adapters = A; pa.chunk = chunk;
+    pa.count = c->d_plan_i32.p; pa.cursor = c->d_plan_i32.p + nb; pa.mmax = c->d_plan_i32.p + 2 * nb; pa.base = c->d_plan_i64.p;
+    PCB_CUDA(c, pcb_launch_plan(pa, false, c->stream));
+    std::vector<int32_t> count(nb), mmax(nm);
+    PCB_CUDA(c, cudaMemcpyAsync(count.data(), pa.count, sizeof(int32_t) * nb, cudaMemcpyDeviceToHost, c->stream));
+    PCB_CUDA(c, cudaMemcpyAsync(mmax.data(), pa.mmax, sizeof(int32_t) * nm, cudaMemcpyDeviceToHost, c->stream));
+    PCB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->cnt.kernel_launches += 2;
+
+    // layout: kind by kind, class by class (the launch order), adapter by adapter, bucket by bucket
+    std::vector<int64_t> base(nb, 0);
+    std::vector<PcbUnit> all_units;
+    int64_t run = 0;
+    int rc;
+    for (int kind = 0; kind < PCB_KINDS; ++kind) {
+        if (kind == 1) pa.scan_task0 = run;
+        if (kind == 2) pa.win_task0 = run;
+        const bool trace = kind != 1;
+        for (int q = PCF_NCLS; q >= 0; --q) {
+            // class of an adapter's items of this kind: windows wider than the fast trace kernel takes go to the general one
+            auto cls_of = [&](int a) { const PcbAdInfo &x = ad[(size_t)a]; return (kind == 2 && x.warm + x.span > PCF_MAX_TRACE_M) ? PCF_NCLS : x.cls; };
+            int64_t total = 0; int nmax = 1, wmax = 1;
+            for (int a = 0; a < A; ++a) {
+                if (cls_of(a) != q) continue;
+                int64_t na = 0;
+                for (int lb = 0; lb < PCB_LB; ++lb) na += count[((size_t)kind * A + a) * PCB_LB + lb];
+                if (na) { nmax = std::max(nmax, ad[(size_t)a].n); wmax = std::max(wmax, ad[(size_t)a].warm + ad[(size_t)a].span); }
+                total += na;
+            }
+            if (total == 0) continue;
+            const bool fast = q < PCF_NCLS;
+            const int lmax = kind == 2 ? wmax : std::max(1, kind == 0 ? mmax[(size_t)q] : mmax[(size_t)(PCF_NCLS + 1) + q]);
+            if (!fast && (rc = check_range(c, nmax, lmax))) return rc;
+            if (fast && lmax > (trace ? PCF_MAX_TRACE_M : PCF_MAX_SCAN_M)) return c->fail(PCB_ERR_RANGE, "internal: segment of %d columns sent to the fast kernels", lmax);
+            const int gmax = fast ? (trace ? c->grid_ftrace[q] : c->grid_fscan[q]) : (trace ? c->grid_trace : c->grid_scan);
+            // fewer tasks per warp when there is not enough work to fill the machine (a warp's time does not depend on its lanes)
+            const int64_t warps = (int64_t)gmax * (PCB_BLOCK / 32);
+            const int per_unit = (int)std::min<int64_t>(64, std::max<int64_t>(2, (total + warps - 1) / warps));
+            pcb_context::TaskPlan::Launch pl{};
+            pl.trace = trace; pl.cls = q; pl.kind = kind; pl.cells = 0;
+            pl.task0 = run; pl.unit0 = (int64_t)all_units.size();
+            for (int a = 0; a < A; ++a) {
+                if (cls_of(a) != q) continue;
+                int64_t na = 0;
+                for (int lb = 0; lb < PCB_LB; ++lb) {
+                    const size_t b = ((size_t)kind * A + a) * PCB_LB + lb;
+                    base[b] = run + na; na += count[b];
+                }
+                for (int64_t u = 0; u < na; u += per_unit) {
+                    PcbUnit un; un.adapter = a; un.ntask = (int32_t)std::min<int64_t>(per_unit, na - u); un.task0 = run - pl.task0 + u;
+                    all_units.push_back(un);
+                }
+                run += na;
+            }
+            pl.n_units = (int64_t)all_units.size() - pl.unit0;
+            pl.mmax = lmax; pl.nmax = nmax; pl.smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
+            pl.grid = (int)std::min<int64_t>(gmax, (pl.n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
+            const uint64_t words = fast ? (trace ? pcf_scratch_words_trace(lmax, q) : 1)
+                                        : (trace ? pcb_scratch_words_trace(lmax, pl.smax) : pcb_scratch_words_scan(lmax, pl.smax));
+            P.scratch_words = std::max<uint64_t>(P.scratch_words, words * (uint64_t)pl.grid * PCB_BLOCK);
+            P.launches.push_back(pl);
+        }
+    }
+    if (!P.launches.empty()) P.launches[0].cells = c->task_cells;      // algorithmic cell updates of the whole run
+    P.n_chunks = pa.win_task0 - pa.scan_task0;
+    P.n_long = run - pa.win_task0;
+    P.win_task0 = pa.win_task0;
+
+    // pass 2 on the device: write the tasks into their buckets
+    PCB_CUDA(c, c->d_tasks.reserve((size_t)run + 1));
+    PCB_CUDA(c, c->d_units.reserve(all_units.size() + 1));
+    PCB_CUDA(c, c->d_longs.reserve((size_t)P.n_long + 1));
+    PCB_CUDA(c, c->d_scan.reserve((size_t)P.n_chunks + 1));
+    PCB_CUDA(c, cudaMemcpyAsync(c->d_plan_i64.p, base.data(), sizeof(int64_t) * nb, cudaMemcpyHostToDevice, c->stream));
+    PCB_CUDA(c, cudaMemcpyAsync(c->d_units.p, all_units.data(), sizeof(PcbUnit) * all_units.size(), cudaMemcpyHostToDevice, c->stream));
+    pa.tasks = c->d_tasks.p; pa.longs = c->d_longs.p;
+    PCB_CUDA(c, pcb_launch_plan(pa, true, c->stream));
+    c->cnt.h2d_bytes += (int64_t)(sizeof(int64_t) * nb + sizeof(PcbUnit) * all_units.size() + sizeof(PcbAdInfo) * A);
+    c->cnt.d2h_bytes += (int64_t)(sizeof(int32_t) * (nb + nm));
+    cudaError_t e = c->d_scratch.reserve((size_t)P.scratch_words);
+    if (e != cudaSuccess) { cudaGetLastError(); return c->fail(PCB_ERR_NOMEM, "scratch of %.1f MB: %s", P.scratch_words * 4 / 1e6, cudaGetErrorString(e)); }
+    PCB_CUDA(c, cudaStreamSynchronize(c->stream));       // the host vectors go out of scope
+    P.valid = true; P.stamp = c->stamp;
+    return PCB_OK;
 }
 
 extern "C" int pcb_run_tasks_resident(pcb_context *c)
 {
     if (!c) return PCB_ERR_ARG;
     cudaSetDevice(c->device);
-    const size_t nt = c->h_tasks.size();
+    const size_t nt = (size_t)c->n_tasks;
     c->S().n_results = (int64_t)nt;
     if (nt == 0) return PCB_OK;
-    PCB_CUDA(c, c->S().d_out.reserve(nt));
-    PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
-    const bool fast_sc = fast_scheme(c->sc) && !getenv("PCB_NO_FAST");
-
-    // order tasks by (adapter, length / 16): two counting sorts, stable, so equal keys keep the input order.
-    // Tasks of one warp share the adapter and run in lockstep over the longest of their segments.
-    std::vector<int64_t> order(nt);
-    {
-        const int LB = 64;                                   // length buckets (only short segments are bucketed finely)
-        auto lbucket = [](int32_t len) { return std::min<int32_t>(len >> 4, 63); };
-        std::vector<int64_t> tmp(nt), cnt((size_t)std::max<int64_t>(LB, c->n_adapters) + 1, 0);
-        for (auto &t : c->h_tasks) cnt[(size_t)lbucket(t.len) + 1]++;
-        for (int k = 0; k < LB; ++k) cnt[(size_t)k + 1] += cnt[(size_t)k];
-        for (size_t t = 0; t < nt; ++t) tmp[(size_t)cnt[(size_t)lbucket(c->h_tasks[t].len)]++] = (int64_t)t;
-        std::fill(cnt.begin(), cnt.end(), 0);
-        for (auto &t : c->h_tasks) cnt[(size_t)t.adapter + 1]++;
-        for (int a = 0; a < c->n_adapters; ++a) cnt[(size_t)a + 1] += cnt[(size_t)a];
-        for (size_t k = 0; k < nt; ++k) order[(size_t)cnt[(size_t)c->h_tasks[(size_t)tmp[k]].adapter]++] = tmp[k];
-    }
-
-    const int direct_default = 960;
-    TaskList direct[3], scan[3];             // by kernel class: 0 / 1 fast kernels, 2 general kernels
-    std::vector<PcbTask> chunks;             // all scan chunks, out_idx = index here
-    struct LongTask { int64_t task; int64_t chunk0; int32_t nchunks; };
-    std::vector<LongTask> longs;
-
-    // chunk length: enough chunks to fill the machine, but long enough to amortise the warm-up margin
-    int64_t long_cols = 0;
-    for (auto &t : c->h_tasks) if (t.len > direct_default) long_cols += t.len;
-    int chunk = (int)std::min<int64_t>(4096, std::max<int64_t>(1024, long_cols / (2 * 64 * (int64_t)std::max(1, c->grid_fscan[0]) * (PCB_BLOCK / 32))));
-
-    for (size_t k = 0; k < nt; ++k) {
-        const int64_t ti = order[k];
-        const auto &t = c->h_tasks[(size_t)ti];
-        const int n = (int)(c->ad_off[(size_t)t.adapter + 1] - c->ad_off[(size_t)t.adapter]);
-        const int cls = fast_sc ? c->ad_fast[(size_t)t.adapter] : 2;
-        const WindowBounds wb = window_bounds(c->sc, n);
-        const int direct_max = std::max(direct_default, wb.ok ? wb.warm + wb.span + 8 : 0);
-        if (t.len <= direct_max || !wb.ok || n == 0) {
-            PcbTask d{}; d.off = (uint64_t)t.off; d.len = t.len; d.col0 = 0; d.m_true = t.len; d.forced_ord = -1;
-            d.out_idx = (int32_t)ti; d.own0 = 0;
-            direct[t.len <= PCF_MAX_TRACE_M ? cls : 2].add(d, t.adapter, (int64_t)t.len * n);
-        } else {
-            LongTask lt{ ti, (int64_t)chunks.size(), 0 };
-            for (int64_t c0 = 0; c0 < t.len; c0 += chunk) {
-                const int64_t col0 = std::max<int64_t>(0, c0 - wb.warm);
-                const int64_t cend = std::min<int64_t>(t.len, c0 + chunk);
-                PcbTask d{}; d.off = (uint64_t)(t.off + col0); d.len = (int32_t)(cend - col0); d.col0 = (int32_t)col0;
-                d.m_true = t.len; d.forced_ord = -1; d.out_idx = (int32_t)chunks.size(); d.own0 = (int32_t)(c0 - col0);
-                chunks.push_back(d);
-                scan[cls].add(d, t.adapter, 0);
-                lt.nchunks++;
-            }
-            scan[cls].cells += (int64_t)t.len * n;
-            longs.push_back(lt);
-        }
-    }
-
     int rc;
-    for (int q = 2; q >= 0; --q)
-        if ((rc = run_explicit(c, direct[q].tasks, direct[q].ad, true, q, direct[q].cells))) return rc;
-    if (!chunks.empty()) {
-        PCB_CUDA(c, c->d_scan.reserve(chunks.size()));
-        for (int q = 2; q >= 0; --q)
-            if ((rc = run_explicit(c, scan[q].tasks, scan[q].ad, false, q, scan[q].cells))) return rc;
-        std::vector<int32_t> keys(chunks.size());
-        PCB_CUDA(c, cudaMemcpyAsync(keys.data(), c->d_scan.p, sizeof(int32_t) * keys.size(), cudaMemcpyDeviceToHost, c->stream));
-        PCB_CUDA(c, cudaStreamSynchronize(c->stream));
-        c->cnt.d2h_bytes += (int64_t)(sizeof(int32_t) * keys.size());
-        // best end cell per long task: highest score, then SeqAn's visiting order (dp_scout.h:167-180)
-        TaskList wins[3];
-        for (auto &lt : longs) {
-            const auto &t = c->h_tasks[(size_t)lt.task];
-            const int n = (int)(c->ad_off[(size_t)t.adapter + 1] - c->ad_off[(size_t)t.adapter]);
-            const int cls = fast_sc ? c->ad_fast[(size_t)t.adapter] : 2;
-            const WindowBounds wb = window_bounds(c->sc, n);
-            int best_score = INT32_MIN; int64_t best_ord = 0; bool have = false;
-            for (int q = 0; q < lt.nchunks; ++q) {
-                const PcbTask &ch = chunks[(size_t)(lt.chunk0 + q)];
-                const int32_t key = keys[(size_t)(lt.chunk0 + q)];
-                if (key == INT32_MIN) continue;
-                const int score = key >> 16;
-                const int ord_l = 0x3FFF - ((key >> 2) & 0x3FFF);
-                // global order: column for last-row cells, m + row for final-column cells
-                const int64_t ord_g = ord_l <= ch.len ? (int64_t)ch.col0 + ord_l : (int64_t)t.len + (ord_l - ch.len);
-                if (!have || score > best_score || (score == best_score && ord_g < best_ord)) { best_score = score; best_ord = ord_g; have = true; }
-            }
-            if (!have) return c->fail(PCB_ERR_RANGE, "scan produced no candidate for task %lld", (long long)lt.task);
-            const bool rowclass = best_ord < t.len;
-            const int64_t cj = rowclass ? best_ord : t.len;
-            const int64_t ws = std::max<int64_t>(0, cj - (wb.warm + wb.span));
-            PcbTask d{};
-            d.col0 = (int32_t)ws; d.len = (int32_t)std::max<int64_t>(1, cj - ws); d.off = (uint64_t)(t.off + ws);
-            d.m_true = t.len; d.own0 = 0; d.out_idx = (int32_t)lt.task;
-            d.forced_ord = rowclass ? (int32_t)(cj - ws) : (int32_t)(d.len + (best_ord - t.len));
-            wins[d.len <= PCF_MAX_TRACE_M ? cls : 2].add(d, t.adapter, 0);   // re-computed cells are not algorithmic work
+    if ((!c->plan.valid || c->plan.stamp != c->stamp) && (rc = build_task_plan(c))) return rc;
+    const pcb_context::TaskPlan &P = c->plan;
+    PCB_CUDA(c, c->S().d_out.reserve(nt));
+    PCB_CUDA(c, c->d_scratch.reserve((size_t)P.scratch_words));     // another slot's run may have shrunk nothing, but be safe
+    PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
+    bool merged = false;
+    for (const auto &pl : P.launches) {
+        if (pl.kind == 2 && !merged) {
+            PCB_CUDA(c, pcb_launch_merge(c->d_longs.p, P.n_long, c->d_scan.p, c->d_tasks.p + P.win_task0, c->d_err.p, c->stream));
+            c->cnt.kernel_launches++;
+            merged = true;
         }
-        for (int q = 2; q >= 0; --q)
-            if ((rc = run_explicit(c, wins[q].tasks, wins[q].ad, true, q, 0))) return rc;
+        PcbLaunch L; fill_launch_common(c, L, true);
+        L.src.units = c->d_units.p + pl.unit0; L.src.tasks = c->d_tasks.p + pl.task0; L.src.n_units = pl.n_units;
+        L.ad.max_len = pl.nmax; L.mmax = pl.mmax; L.smax = pl.smax; L.grid = pl.grid;
+        if ((rc = launch_dp(c, L, pl.trace, pl.cells, pl.cls))) return rc;
     }
     return PCB_OK;
 }
@@ -693,12 +699,22 @@ extern "C" int pcb_stats_from_path(const char *ops, int64_t n_ops, int64_t head_
     if (!out || n_ops < 0 || (n_ops > 0 && (!ops || !match_flags))) return PCB_ERR_ARG;
     PathAcc acc; path_acc_init(acc);
     int64_t m = head_h + tail_h, n = head_v + tail_v;
+    int ei = 0, ej = 0;                                      // core path size: rows / columns it covers
+    for (int64_t k = 0; k < n_ops; ++k) { if (ops[k] != 'H') ++ei; if (ops[k] != 'V') ++ej; }
+    WalkAcc wa; walk_acc_init(wa);
+    int i = ei, j = ej;
     for (int64_t k = n_ops - 1; k >= 0; --k) {              // the kernels walk the path back to front
         const int op = ops[k] == 'D' ? 0 : (ops[k] == 'V' ? 1 : 2);
         path_acc_step(acc, op, match_flags[k]);
+        if (op == 0) { walk_acc_D(wa, i, j, match_flags[k] ? 1 : 0); --i; --j; }
+        else if (op == 1) { walk_acc_V(wa, i, j); --i; }
+        else { walk_acc_H(wa, i, j); --j; }
         if (op != 2) ++n;
         if (op != 1) ++m;
     }
+    // both accumulators (general kernels: PathAcc; fast kernels: WalkAcc) must describe the same path
+    PathAcc acc2; walk_acc_finish(wa, ei, ej, 0, 0, acc2);
+    if (memcmp(&acc, &acc2, sizeof acc) != 0) return PCB_ERR_RANGE;
     PathStats st; path_finalize(acc, head_h, head_v, tail_h, tail_v, m, n, st);
     out->read_start = st.read_start; out->read_end = st.read_end; out->adapter_start = st.adapter_start;
     out->adapter_end = st.adapter_end; out->raw_score = raw_score; out->matches = st.matches;

@@ -40,14 +40,13 @@ namespace {
 #ifdef PCF_FORCE_MINB
 #define PCF_MINB(TRACE, NR) PCF_FORCE_MINB
 #else
-#define PCF_MINB(TRACE, NR) (((TRACE) && (NR) > 24) ? 3 : 4)
+#define PCF_MINB(TRACE, NR) ((TRACE) ? ((NR) <= 24 ? 4 : ((NR) <= 32 ? 3 : 2)) : ((NR) <= 32 ? 4 : ((NR) <= 40 ? 3 : 2)))
 #endif
 #ifndef PCF_UNROLL
 #define PCF_UNROLL 4
 #endif
 constexpr int UNR = PCF_UNROLL;
 constexpr int RT = PCB_RT;            // 32 adapter rows in registers
-constexpr int C = PCF_C;              // checkpoint distance / flag block width (columns)
 constexpr int B0 = 64;                // base bias: keeps every stored value > 0
 constexpr int OFF = 2048;             // offset of un-biased scores in the best-cell comparison (true score + OFF > 0)
 constexpr int REBASE = 1024;          // scan: columns between two re-basings of the anti-diagonal bias
@@ -211,20 +210,45 @@ __device__ __forceinline__ uint32_t join4(const Raw4 &r) { return __funnelshift_
 // offset (in words) into a row of the score table for the two code bytes (Dna5 code * 8) of a column
 __device__ __forceinline__ uint32_t pair_index(uint32_t c8_0, uint32_t c8_1) { return (c8_0 * 5u + c8_1) >> 3; }
 
+// One op of the reverse walk for half h of this thread (dp_traceback_impl.h:379-451).  Flag word layout as col_flags writes
+// it; the block's read bases sit behind the C*FW flag words.  State 0 = M, 1 = V, 2 = H.  In state M a cell whose diagonal
+// flag is off hands over to V or H and that state's step is taken at once, from the same cell's flags, as SeqAn does.
+template <int FW, int C>
+__device__ __forceinline__ void walk_step(const uint32_t *s_fl, const uint32_t *s_code, const int h, const int base,
+                                          int &i, int &j, int &s, WalkAcc &a)
+{
+    const int ar = i - 1, jc = j - base - 1;
+    const uint32_t f = s_fl[(jc * FW + (ar >> 2)) * PCB_BLOCK] >> (8 * h + 2 * (ar & 3));
+    const bool fh = f & 1u, fg = f & 2u, fv = f & 0x10000u, fd = f & 0x20000u;
+    if (s == 0 && fd) {
+        const uint32_t code8 = (s_fl[(C * FW + h * (C / 4) + (jc >> 2)) * PCB_BLOCK] >> (8 * (jc & 3))) & 0xFFu;
+        walk_acc_D(a, i, j, code8 == s_code[ar] * PCB_CODE_SCALE);
+        --i; --j;
+    } else if (s == 1 || (s == 0 && fg)) {
+        walk_acc_V(a, i, j);
+        --i; s = fv ? 1 : 0;
+    } else {
+        walk_acc_H(a, i, j);
+        --j; s = fh ? 2 : 0;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // k_fast<TRACE, NR, EXACT>
 //   TRACE=true  -> pass 1 (score only + checkpoints + end cell), pass 2 (flags for the blocks the traceback crosses,
 //                  traceback, statistics) -> pcb_result
 //   TRACE=false -> pass 1 only -> order key per task (scan chunks of long reads)
 //   NR / EXACT  -> adapter rows in registers; EXACT: every adapter of the launch has exactly NR bases
+//   C           -> checkpoint distance = width of a flag block (columns; a multiple of 4, >= 8)
 // grid: persistent, blockDim = PCB_BLOCK.  Cross-product launches are walked adapter-major in contiguous per-warp ranges
 // (a warp re-builds its score table only when the adapter changes); explicit task lists are walked strided.
 // dynamic smem: [W][NR*25] score tables, [W][NR] adapter codes, then a per-thread area strided by PCB_BLOCK
 //               (TRACE: C*NR/4 flag words + 2*C/4 words of block bases; always >= 2*NR words for the final-column dump).
 // ------------------------------------------------------------------------------------------------
-template <bool TRACE, int NR, bool EXACT>
+template <bool TRACE, int NR, bool EXACT, int C>
 __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const PcbLaunch L)
 {
+    static_assert(C % 4 == 0 && C >= 8, "flag block width");
     extern __shared__ uint32_t smem[];
     constexpr int FW = NR / 4;                           // flag words per column
     constexpr int W = PCB_BLOCK / 32;
@@ -323,6 +347,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
         uint32_t rowT = pk2(B0);                                 // biased M(0, j) = bias of row 0 at the current column
         const uint32_t candK = pk2(OFF - b * n);                 // candidate = M(n, j) + candK - rowT = score + OFF
         uint32_t *ckp = ck;
+        int ckc = 0;                                             // columns since the last checkpoint
         Raw4 nx0 = load4(seq0, 0, lim0), nx1 = load4(seq1, 0, lim1);
 
         // one column; `general` (compile-time after inlining): candidate masks and final-column handling
@@ -369,11 +394,12 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
         for (int j0 = 1; j0 <= mw; j0 += 4) {
             uint32_t cur0 = join4(nx0), cur1 = join4(nx1);
             nx0 = load4(seq0, j0 + 3, lim0); nx1 = load4(seq1, j0 + 3, lim1);       // used one group later
-            if (TRACE && ((j0 - 1) & (C - 1)) == 0) {            // checkpoint = state after column j0-1 (a multiple of C)
+            if (TRACE && ckc == 0) {                             // checkpoint = state after column j0-1 (a multiple of C)
 #pragma unroll
                 for (int r = 0; r < NR; ++r) { ckp[(2 * r) * T] = Mo[r]; ckp[(2 * r + 1) * T] = Hl[r]; }
                 ckp += 2ull * NR * T;
             }
+            if (TRACE) { ckc += 4; if (ckc == C) ckc = 0; }
             if (!TRACE && ((j0 - 1) & (REBASE - 1)) == 0 && j0 > 1) {   // keep the growing bias inside 15 bits
                 const uint32_t d = pk2(b * REBASE);
 #pragma unroll
@@ -409,7 +435,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
         // =========================== pass 2: flags for the blocks the traceback crosses ===========================
         int ci[2], cj[2], endi[2], endj[2], state[2], score[2];
         bool done[2], rowcls[2];
-        PathAcc acc[2];
+        WalkAcc acc[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const HalfTask &t = tk[h];
@@ -417,7 +443,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             const bool fc = h ? fc1 : fc0;
             done[h] = true; rowcls[h] = !fc; state[h] = 0; score[h] = sc - OFF;
             ci[h] = cj[h] = endi[h] = endj[h] = 0;
-            path_acc_init(acc[h]);
+            walk_acc_init(acc[h]);
             if (t.out_idx < 0) continue;
             if (t.len <= 0) { write_failed(L.out, t.out_idx); continue; }
             if (sc <= 0) { atomicOr(L.err_flag, 2); write_failed(L.out, t.out_idx); continue; }   // forced cell not found
@@ -434,8 +460,9 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
                 if (done[h] || (ci[h] > 0 && cj[h] > 0)) continue;
                 const HalfTask &t = tk[h];
                 if (cj[h] == 0 && ci[h] > 0 && t.col0 > 0) atomicOr(L.err_flag, 1);   // window too narrow for this path
+                PathAcc pa; walk_acc_finish(acc[h], endi[h], endj[h], ci[h], cj[h], pa);
                 PathStats st;
-                path_finalize(acc[h], (int64_t)t.col0 + cj[h], ci[h], (int64_t)t.m_true - (t.col0 + endj[h]), n - endi[h],
+                path_finalize(pa, (int64_t)t.col0 + cj[h], ci[h], (int64_t)t.m_true - (t.col0 + endj[h]), n - endi[h],
                               t.m_true, n, st);
                 pcb_result res;
                 res.read_start = st.read_start; res.read_end = st.read_end;
@@ -452,7 +479,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             const int need = max(done[0] ? 0 : cj[0] - k0 * C, done[1] ? 0 : cj[1] - k1 * C);
             const int tmax = __reduce_max_sync(0xffffffffu, need);
             const int jb0 = k0 * C, jb1 = k1 * C;
-            // the block's read bases (16 per half), then the checkpointed column the block starts from
+            // the block's read bases (C per half), then the checkpointed column the block starts from
             uint32_t q0[C / 4], q1[C / 4];
 #pragma unroll
             for (int g = 0; g < C / 4; ++g) {
@@ -488,37 +515,18 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
                 }
             }
             __syncwarp();
-            // walk (dp_traceback_impl.h:379-451, :498-545) inside the block
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                if (done[h]) continue;
-                const int base = h ? jb1 : jb0;
-                const uint32_t *const sb = s_fl + (C * FW + h * (C / 4)) * PCB_BLOCK;     // the block's bases
-                int i = ci[h], j = cj[h], s = state[h];
-                PathAcc a = acc[h];
-                while (i > 0 && j > base) {
-                    const int ar = i - 1;
-                    const uint32_t w = s_fl[((j - base - 1) * FW + (ar >> 2)) * PCB_BLOCK];
-                    const int sh = 8 * h + 2 * (ar & 3);
-                    if (s == 0) {
-                        if ((w >> (17 + sh)) & 1) {
-                            const uint32_t code8 = (sb[((j - base - 1) >> 2) * PCB_BLOCK] >> (8 * ((j - base - 1) & 3))) & 0xFFu;
-                            path_acc_step(a, 0, code8 == s_code[ar] * PCB_CODE_SCALE);
-                            --i; --j;
-                        } else {
-                            s = ((w >> (sh + 1)) & 1) ? 1 : 2;
-                        }
-                    } else if (s == 1) {
-                        path_acc_step(a, 1, 0);
-                        --i;
-                        s = ((w >> (16 + sh)) & 1) ? 1 : 0;
-                    } else {
-                        path_acc_step(a, 2, 0);
-                        --j;
-                        s = ((w >> sh) & 1) ? 2 : 0;
-                    }
+            // walk (dp_traceback_impl.h:379-451, :498-545) inside the block: both halves together, one path op per half
+            // and trip, so that a warp waits for the longest walk of its 64 tasks once, not once per half
+            {
+                int i0 = ci[0], j0 = cj[0], s0 = state[0], i1 = ci[1], j1 = cj[1], s1 = state[1];
+                WalkAcc a0 = acc[0], a1 = acc[1];
+                bool act0 = !done[0] && i0 > 0 && j0 > jb0, act1 = !done[1] && i1 > 0 && j1 > jb1;
+                while (act0 || act1) {
+                    if (act0) { walk_step<FW, C>(s_fl, s_code, 0, jb0, i0, j0, s0, a0); act0 = i0 > 0 && j0 > jb0; }
+                    if (act1) { walk_step<FW, C>(s_fl, s_code, 1, jb1, i1, j1, s1, a1); act1 = i1 > 0 && j1 > jb1; }
                 }
-                ci[h] = i; cj[h] = j; state[h] = s; acc[h] = a;
+                ci[0] = i0; cj[0] = j0; state[0] = s0; acc[0] = a0;
+                ci[1] = i1; cj[1] = j1; state[1] = s1; acc[1] = a1;
             }
             __syncwarp();
         }
@@ -528,43 +536,64 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
-// host-side launchers.  cls 0: every adapter of the launch has exactly 24 bases; cls 1: adapters of 1..32 bases.
+// host-side launchers, by kernel class
 // ------------------------------------------------------------------------------------------------
-static size_t fast_smem(bool trace, int nr)
+static size_t fast_smem(bool trace, int nr, int c)
 {
-    const size_t per_thread = trace ? (size_t)C * (nr / 4) + 2 * (C / 4) : (size_t)2 * nr;   // flags + block bases | column dump
+    const size_t per_thread = trace ? (size_t)c * (nr / 4) + 2 * (c / 4) : (size_t)2 * nr;   // flags + block bases | column dump
     return ((size_t)(PCB_BLOCK / 32) * (nr * TP + nr) + (size_t)PCB_BLOCK * per_thread) * sizeof(uint32_t);
 }
 
-template <bool TRACE, int NR, bool EXACT>
+template <bool TRACE, int NR, bool EXACT, int C>
 static cudaError_t launch_one(const PcbLaunch &L, cudaStream_t st)
 {
     static bool attr = false;
-    const size_t sm = fast_smem(TRACE, NR);
+    const size_t sm = fast_smem(TRACE, NR, C);
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(k_fast<TRACE, NR, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cudaError_t e = cudaFuncSetAttribute(k_fast<TRACE, NR, EXACT, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         if (e != cudaSuccess) return e;
         attr = true;
     }
-    k_fast<TRACE, NR, EXACT><<<L.grid, PCB_BLOCK, sm, st>>>(L);
+    k_fast<TRACE, NR, EXACT, C><<<L.grid, PCB_BLOCK, sm, st>>>(L);
     return cudaGetLastError();
+}
+
+template <bool TRACE, int NR, bool EXACT, int C>
+static int occ_one()
+{
+    int per = 0;
+    const size_t sm = fast_smem(TRACE, NR, C);
+    cudaFuncSetAttribute(k_fast<TRACE, NR, EXACT, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_fast<TRACE, NR, EXACT, C>, PCB_BLOCK, sm);
+    return per < 1 ? 1 : per;
+}
+
+// kernel classes: see pcb_kernels.h
+#define PCF_DISPATCH(FN, TRACE)                                                            \
+    switch (cls) {                                                                         \
+    case 0:  return FN<TRACE, 24, true,  PCF_C_SMALL>;                                     \
+    case 1:  return FN<TRACE, 24, false, PCF_C_SMALL>;                                     \
+    case 2:  return FN<TRACE, 32, false, PCF_C_SMALL>;                                     \
+    case 3:  return FN<TRACE, 40, false, PCF_C_LARGE>;                                     \
+    default: return FN<TRACE, 52, false, PCF_C_LARGE>;                                     \
+    }
+
+typedef cudaError_t (*launch_fn)(const PcbLaunch &, cudaStream_t);
+typedef int (*occ_fn)();
+static launch_fn pick_launch(bool trace, int cls)
+{
+    if (trace) { PCF_DISPATCH(launch_one, true) } else { PCF_DISPATCH(launch_one, false) }
+}
+static occ_fn pick_occ(bool trace, int cls)
+{
+    if (trace) { PCF_DISPATCH(occ_one, true) } else { PCF_DISPATCH(occ_one, false) }
 }
 
 cudaError_t pcf_launch(const PcbLaunch &L, bool trace, int cls, cudaStream_t st)
 {
     if (L.src.n_units == 0) return cudaSuccess;
-    if (cls == 0) return trace ? launch_one<true, 24, true>(L, st) : launch_one<false, 24, true>(L, st);
-    return trace ? launch_one<true, 32, false>(L, st) : launch_one<false, 32, false>(L, st);
-}
-
-template <bool TRACE, int NR, bool EXACT>
-static int occ_one()
-{
-    int per = 0;
-    const size_t sm = fast_smem(TRACE, NR);
-    cudaFuncSetAttribute(k_fast<TRACE, NR, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_fast<TRACE, NR, EXACT>, PCB_BLOCK, sm);
-    return per < 1 ? 1 : per;
+    if (cls < 0 || cls >= PCF_NCLS) return cudaErrorInvalidValue;
+    return pick_launch(trace, cls)(L, st);
 }
 
 int pcf_occupancy_grid(bool trace, int cls)
@@ -572,7 +601,5 @@ int pcf_occupancy_grid(bool trace, int cls)
     int dev = 0, sms = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int per = cls == 0 ? (trace ? occ_one<true, 24, true>() : occ_one<false, 24, true>())
-                             : (trace ? occ_one<true, 32, false>() : occ_one<false, 32, false>());
-    return sms * per;
+    return sms * pick_occ(trace, cls)();
 }

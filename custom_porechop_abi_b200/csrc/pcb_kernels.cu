@@ -392,9 +392,122 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCB_MIN_BLOCKS) k_align(const PcbLa
 
 }  // namespace
 
+namespace {
+
+// One thread per long read.  Chunk q owns columns (q*chunk, min(len, (q+1)*chunk)] and starts `warm` columns early;
+// its key holds the best owned cell as (score << 16) | ((0x3FFF - local order) << 2).  Global visiting order
+// (dp_scout.h:167-180, dp_meta_info.h:205-216): the column for last-row cells, len + row for final-column cells.
+__global__ void k_merge_scan(const PcbLong *__restrict__ longs, int64_t n_long, const int32_t *__restrict__ keys,
+                             PcbTask *__restrict__ wins, int32_t *err_flag)
+{
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_long) return;
+    const PcbLong lt = longs[t];
+    int best_score = 0; int64_t best_ord = 0; bool have = false;
+    for (int q = 0; q < lt.nchunks; ++q) {
+        const int32_t key = keys[lt.chunk0 + q];
+        if (key == (int32_t)0x80000000) continue;
+        const int64_t c0 = (int64_t)q * lt.chunk;
+        const int64_t col0 = c0 > lt.warm ? c0 - lt.warm : 0;
+        const int64_t cend = c0 + lt.chunk < lt.len ? c0 + lt.chunk : lt.len;
+        const int64_t chlen = cend - col0;
+        const int score = key >> 16;
+        const int ord_l = 0x3FFF - ((key >> 2) & 0x3FFF);
+        const int64_t ord_g = ord_l <= chlen ? col0 + ord_l : (int64_t)lt.len + (ord_l - chlen);
+        if (!have || score > best_score || (score == best_score && ord_g < best_ord)) { best_score = score; best_ord = ord_g; have = true; }
+    }
+    PcbTask d;
+    d.own0 = 0; d.out_idx = lt.out_idx; d.m_true = lt.len;
+    if (!have) {                       // cannot happen (cell (n, 0) always scores 0); reported, never silent
+        atomicOr(err_flag, 8);
+        d.off = (uint64_t)lt.off; d.len = 1; d.col0 = 0; d.forced_ord = 0x3FFF;
+    } else {
+        const bool rowclass = best_ord < lt.len;
+        const int64_t cj = rowclass ? best_ord : lt.len;
+        const int64_t ws = cj > (int64_t)lt.warm + lt.span ? cj - ((int64_t)lt.warm + lt.span) : 0;
+        d.col0 = (int32_t)ws; d.len = (int32_t)(cj - ws > 1 ? cj - ws : 1); d.off = (uint64_t)(lt.off + ws);
+        d.forced_ord = rowclass ? (int32_t)(cj - ws) : (int32_t)(d.len + (best_ord - lt.len));
+    }
+    wins[lt.win_slot] = d;
+}
+
+// Planner, two passes over the caller's task list (one thread per task): FILL=false counts items per bucket,
+// FILL=true writes them at base[bucket] + (atomic cursor).  Which slot inside a bucket a task gets varies from run
+// to run; results do not (tasks are independent and carry their own result slot).
+__device__ __forceinline__ void plan_classify(const PcbPlanArgs &a, int32_t len, const PcbAdInfo &x, bool &is_long,
+                                              int &nchunks, int &chunk_r, int &lb)
+{
+    is_long = x.chunked && len > x.direct_max && x.n > 0;
+    if (!is_long) { nchunks = 0; chunk_r = 0; lb = min(len >> 4, PCB_LB - 1); return; }
+    nchunks = (len + a.chunk - 1) / a.chunk;
+    chunk_r = ((len + nchunks - 1) / nchunks + 3) & ~3;          // near-equal chunks: a warp's lanes stay busy together
+    nchunks = (len + chunk_r - 1) / chunk_r;
+    lb = min((chunk_r + x.warm) >> 7, PCB_LB - 1);
+}
+
+template <bool FILL>
+__global__ void k_plan(const PcbPlanArgs a)
+{
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= a.n_tasks) return;
+    const int32_t len = a.seg_len[t], ad = a.seg_ad[t];
+    const int64_t off = a.seg_off[t];
+    const PcbAdInfo x = a.ad[ad];
+    bool is_long; int nchunks, chunk_r, lb;
+    plan_classify(a, len, x, is_long, nchunks, chunk_r, lb);
+    const int64_t per_kind = (int64_t)a.n_adapters * PCB_LB;
+    if (!is_long) {
+        const int64_t bkt = (int64_t)ad * PCB_LB + lb;
+        if (!FILL) { atomicAdd(a.count + bkt, 1); atomicMax(a.mmax + x.cls, len); return; }
+        const int64_t slot = a.base[bkt] + atomicAdd(a.cursor + bkt, 1);
+        PcbTask d; d.off = (uint64_t)off; d.len = len; d.col0 = 0; d.m_true = len; d.forced_ord = -1;
+        d.out_idx = (int32_t)t; d.own0 = 0;
+        a.tasks[slot] = d;
+        return;
+    }
+    const int64_t bs = per_kind + (int64_t)ad * PCB_LB + lb, bw = 2 * per_kind + (int64_t)ad * PCB_LB;
+    if (!FILL) {
+        atomicAdd(a.count + bs, nchunks); atomicAdd(a.count + bw, 1);
+        atomicMax(a.mmax + (PCF_NCLS + 1) + x.cls, min(len, chunk_r + x.warm));
+        return;
+    }
+    const int64_t s0 = a.base[bs] + atomicAdd(a.cursor + bs, nchunks);
+    const int64_t w = a.base[bw] + atomicAdd(a.cursor + bw, 1);
+    for (int q = 0; q < nchunks; ++q) {
+        const int64_t c0 = (int64_t)q * chunk_r;
+        const int64_t col0 = c0 > x.warm ? c0 - x.warm : 0;
+        const int64_t cend = c0 + chunk_r < len ? c0 + chunk_r : len;
+        PcbTask d; d.off = (uint64_t)(off + col0); d.len = (int32_t)(cend - col0); d.col0 = (int32_t)col0;
+        d.m_true = len; d.forced_ord = -1; d.out_idx = (int32_t)(s0 + q - a.scan_task0); d.own0 = (int32_t)(c0 - col0);
+        a.tasks[s0 + q] = d;
+    }
+    PcbLong lt; lt.off = off; lt.len = len; lt.warm = x.warm; lt.span = x.span; lt.chunk = chunk_r;
+    lt.chunk0 = (int32_t)(s0 - a.scan_task0); lt.nchunks = nchunks; lt.out_idx = (int32_t)t;
+    lt.win_slot = (int32_t)(w - a.win_task0);
+    a.longs[w - a.win_task0] = lt;
+}
+
+}  // namespace
+
 // ------------------------------------------------------------------------------------------------
 // host-side launchers
 // ------------------------------------------------------------------------------------------------
+cudaError_t pcb_launch_plan(const PcbPlanArgs &a, bool fill, cudaStream_t st)
+{
+    if (a.n_tasks == 0) return cudaSuccess;
+    const unsigned grid = (unsigned)((a.n_tasks + 255) / 256);
+    if (fill) k_plan<true><<<grid, 256, 0, st>>>(a); else k_plan<false><<<grid, 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t pcb_launch_merge(const PcbLong *longs, int64_t n_long, const int32_t *keys, PcbTask *wins, int32_t *err_flag,
+                             cudaStream_t st)
+{
+    if (n_long == 0) return cudaSuccess;
+    k_merge_scan<<<(unsigned)((n_long + 127) / 128), 128, 0, st>>>(longs, n_long, keys, wins, err_flag);
+    return cudaGetLastError();
+}
+
 cudaError_t pcb_launch_encode(const char *ascii, uint8_t *codes, uint64_t n, cudaStream_t st)
 {
     if (n == 0) return cudaSuccess;

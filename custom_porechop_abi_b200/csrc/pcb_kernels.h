@@ -17,10 +17,29 @@
 #define PCB_NEG_INF     (-8192)   /* "minus infinity" in a signed 16-bit lane                     */
 #define PCB_MAX_TRACE_M 8000      /* widest segment the trace kernel takes (order key is 14 bit)  */
 
-/* fast kernels (pcb_fast.cu): affine schemes, adapters of <= PCB_RT bases */
-#define PCF_C             16      /* checkpoint distance = width of a flag block (columns)        */
+/* fast kernels (pcb_fast.cu): affine schemes, adapters of <= 52 bases.  An adapter's kernel class picks the number of
+ * adapter rows the kernel holds in registers (NR) and the checkpoint distance / flag-block width of the two-pass trace (C):
+ *   class 0: exactly 24 bases (almost every Porechop adapter and barcode)   NR 24, exact
+ *   class 1: 1..23 bases      NR 24      class 2: 25..32 bases   NR 32
+ *   class 3: 33..40 bases     NR 40      class 4: 41..52 bases   NR 52
+ *   class PCF_NCLS: everything else -> general kernels (pcb_kernels.cu) */
+#define PCF_NCLS          5
+#define PCF_MAX_N         52
 #define PCF_MAX_TRACE_M   1000    /* widest segment of the two-pass trace kernel (no bias re-basing) */
 #define PCF_MAX_SCAN_M    12000   /* widest scan chunk (order key is 14 bit)                      */
+#ifndef PCF_C_SMALL
+#define PCF_C_SMALL       16      /* C for NR <= 32 */
+#endif
+#ifndef PCF_C_LARGE
+#define PCF_C_LARGE       8       /* C for NR > 32  */
+#endif
+static inline int pcf_class_nr(int cls) { return cls <= 1 ? 24 : (cls == 2 ? 32 : (cls == 3 ? 40 : 52)); }
+static inline int pcf_class_c(int cls) { return pcf_class_nr(cls) <= 32 ? PCF_C_SMALL : PCF_C_LARGE; }
+static inline int pcf_class_of_len(long len)
+{
+    if (len < 1 || len > PCF_MAX_N) return PCF_NCLS;
+    return len == 24 ? 0 : (len < 24 ? 1 : (len <= 32 ? 2 : (len <= 40 ? 3 : 4)));
+}
 
 /* One alignment task as the kernels see it. 32 bytes. */
 struct PcbTask {
@@ -100,18 +119,60 @@ static inline uint64_t pcb_scratch_words_scan(int mmax, int smax)
     return 2ull * (mmax + 1) + 4ull * smax * PCB_RT;
 }
 
+/* A long read of the explicit-task path: scanned in column chunks, then traced on one window. */
+struct PcbLong {
+    int64_t off;         /* first base of the read in the task arena                               */
+    int32_t len;         /* read length                                                            */
+    int32_t warm, span;  /* margins for this adapter length and scoring scheme                     */
+    int32_t chunk;       /* owned columns per scan chunk                                           */
+    int32_t chunk0;      /* index of its first chunk key in scan_out                               */
+    int32_t nchunks;
+    int32_t out_idx;     /* result slot                                                            */
+    int32_t win_slot;    /* index of its trace-window task in the launch's task array              */
+};
+/* Picks each long read's best end cell from its chunk keys (score, then SeqAn's visiting order) and writes the
+ * trace-window task for it. */
+cudaError_t pcb_launch_merge(const PcbLong *longs, int64_t n_long, const int32_t *keys, PcbTask *wins, int32_t *err_flag,
+                             cudaStream_t st);
+
+/* ---- device-side planner of the explicit-task path ---------------------------------------------------------------
+ * The caller's task list (segment offset, length, adapter id) is turned into kernel task arrays ON THE DEVICE: the host
+ * only sees a histogram.  A task is `direct` (short segment: one trace task) or `long` (column chunks for the scan kernel
+ * + one trace-window task, filled in after the scan by the merge kernel).  Items are bucketed by (kind, adapter,
+ * length bucket) so that a warp's 64 tasks share the adapter and have similar lengths. */
+#define PCB_LB        64                /* length buckets per adapter                                 */
+#define PCB_KINDS     3                 /* 0 direct, 1 scan chunk, 2 trace window                     */
+struct PcbAdInfo {
+    int32_t n;            /* adapter length                                                          */
+    int32_t cls;          /* kernel class of direct tasks and scan chunks                            */
+    int32_t warm, span;   /* margins; valid when chunked != 0                  */
+    int32_t direct_max;   /* segments up to this length are direct tasks                             */
+    int32_t chunked;      /* 0: every segment is a direct task (margins not available)               */
+};
+struct PcbPlanArgs {
+    const int64_t *seg_off; const int32_t *seg_len; const int32_t *seg_ad; int64_t n_tasks;
+    const PcbAdInfo *ad; int32_t n_adapters; int32_t chunk;       /* chunk: target owned columns per scan chunk */
+    int32_t *count;             /* [PCB_KINDS][n_adapters][PCB_LB] items per bucket (count pass)          */
+    int32_t *mmax;              /* [PCB_KINDS][PCF_NCLS + 1] widest item per (kind, class)  (count pass)  */
+    const int64_t *base;        /* [PCB_KINDS][n_adapters][PCB_LB] first slot of a bucket in `tasks`      */
+    int32_t *cursor;            /* same shape, zeroed: next free slot of a bucket                          */
+    PcbTask *tasks; PcbLong *longs;
+    int64_t scan_task0, win_task0;   /* where the scan chunks / window tasks start in `tasks`              */
+};
+cudaError_t pcb_launch_plan(const PcbPlanArgs &a, bool fill, cudaStream_t st);
+
 cudaError_t pcb_launch_encode(const char *ascii, uint8_t *codes, uint64_t n, cudaStream_t st);
 cudaError_t pcb_launch_trace(const PcbLaunch &L, cudaStream_t st);
 cudaError_t pcb_launch_scan(const PcbLaunch &L, cudaStream_t st);
 int pcb_occupancy_grid(int which /*0 trace, 1 scan*/);
 
-/* fast kernels: cls 0 = adapters of exactly 24 bases, cls 1 = adapters of 1..32 bases */
-#define PCF_EXACT_N 24
+/* fast kernels, by class (see above) */
 cudaError_t pcf_launch(const PcbLaunch &L, bool trace, int cls, cudaStream_t st);
 int pcf_occupancy_grid(bool trace, int cls);
 static inline uint64_t pcf_scratch_words_trace(int mmax, int cls)
 {
-    return (uint64_t)((mmax + PCF_C - 1) / PCF_C + 1) * 2ull * (cls == 0 ? PCF_EXACT_N : PCB_RT);     /* checkpoints */
+    const int C = pcf_class_c(cls);
+    return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * pcf_class_nr(cls);     /* checkpoints */
 }
 
 #endif

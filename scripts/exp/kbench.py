@@ -12,7 +12,7 @@ sbuf, ebuf, lens = synthetic.end_windows(blob, off)
 eng = AlignmentEngine(0)
 eng.set_adapters(adapters)
 ad_len = np.array([len(a) for a in adapters])
-for name, ids in (('all start ids', s_ids), ('24-mers only', [i for i in s_ids if ad_len[i] == 24]), ('non-24 <=32', [i for i in s_ids if ad_len[i] != 24 and ad_len[i] <= 32])):
+for name, ids in (('all start ids', s_ids), ('24-mers only', [i for i in s_ids if ad_len[i] == 24]), ('<24', [i for i in s_ids if ad_len[i] < 24]), ('25..32', [i for i in s_ids if 24 < ad_len[i] <= 32]), ('33..40', [i for i in s_ids if 32 < ad_len[i] <= 40]), ('41..52', [i for i in s_ids if 40 < ad_len[i] <= 52])):
     eng.stage_windows(sbuf, lens, ids)
     eng.run_windows_resident(); eng.synchronize()
     eng.timer_start()

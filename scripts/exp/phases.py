@@ -1,0 +1,57 @@
+"""Where a bench step spends its time: per-submit resident time, summed DP-kernel time, and the host-buffer calls.
+python scripts/exp/phases.py [n_reads]"""
+import os, sys, time
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+import bench
+from custom_porechop_abi_b200.engine import AlignmentEngine
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 32768
+wl = bench.workload(n, 1)
+eng = AlignmentEngine(0)
+eng.set_adapters(wl['adapters'])
+eng.select_slot(0); eng.stage_windows(wl['sbuf'], wl['wlen'], wl['start_ids'])
+eng.select_slot(1); eng.stage_windows(wl['ebuf'], wl['wlen'], wl['end_ids'])
+eng.select_slot(2); eng.stage_tasks(wl['blob'], wl['seg_off'], wl['seg_len'], wl['task_ad'])
+runs = [('start windows', 0, eng.run_windows_resident), ('end windows', 1, eng.run_windows_resident), ('full reads', 2, eng.run_tasks_resident)]
+for name, slot, fn in runs:
+    eng.select_slot(slot); fn(); eng.synchronize()
+for timing in (0, 1):
+    eng.set_kernel_timing(timing)
+    for name, slot, fn in runs:
+        eng.select_slot(slot)
+        eng.reset_counters()
+        t0 = time.perf_counter()
+        eng.timer_start()
+        for _ in range(3):
+            fn()
+        ms = eng.timer_stop() / 3
+        wall = (time.perf_counter() - t0) / 3 * 1e3
+        c = eng.counters()
+        print('%-14s ktiming=%d  device %8.2f ms  wall %8.2f ms  dp kernels %8.2f ms in %d launches  %7.1f GCUPS' % (
+            name, timing, ms, wall, c['dp_kernel_ms'] / 3, c['dp_kernel_launches'] // 3, c['dp_cells'] / 3 / ms / 1e6), flush=True)
+eng.set_kernel_timing(0)
+# host-buffer path split into its parts, pinned buffers (as bench.py)
+import torch
+def pin(a):
+    t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory(); return t, t.numpy()
+keep = []
+def P(a):
+    t, v = pin(a); keep.append(t); return v
+sbuf, wlen, blob = P(wl['sbuf']), P(wl['wlen']), P(wl['blob'])
+seg_off, seg_len, task_ad = P(wl['seg_off']), P(wl['seg_len']), P(wl['task_ad'])
+def timed(name, fn):
+    eng.synchronize(); t0 = time.perf_counter(); r = fn(); eng.synchronize()
+    print('   %-28s %8.2f ms' % (name, (time.perf_counter() - t0) * 1e3), flush=True); return r
+for rep in range(2):
+    print('rep', rep)
+    eng.select_slot(0)
+    timed('stage_windows (start)', lambda: eng.stage_windows(sbuf, wlen, wl['start_ids']))
+    timed('run_windows', eng.run_windows_resident)
+    timed('fetch (pageable dst)', eng.fetch)
+    eng.select_slot(2)
+    timed('stage_tasks', lambda: eng.stage_tasks(blob, seg_off, seg_len, task_ad))
+    timed('run_tasks (plan + kernels)', eng.run_tasks_resident)
+    timed('run_tasks (kernels)', eng.run_tasks_resident)
+    timed('fetch', eng.fetch)
