@@ -44,6 +44,8 @@ struct DevBuf {
 struct pcb_context {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t cstream = nullptr;       // copies that run beside the kernels of `stream`
+    cudaEvent_t pipe_ev[8] = {};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, kev0 = nullptr, kev1 = nullptr;
     std::string err;
     PcbScores sc{3, -6, -5, -2, 0};
@@ -79,17 +81,27 @@ struct pcb_context {
     DevBuf<int64_t> d_seg_off, d_plan_i64;
     DevBuf<int32_t> d_seg_len, d_seg_ad, d_plan_i32;
     DevBuf<PcbAdInfo> d_adinfo;
-    DevBuf<PcbTask> d_tasks;
-    DevBuf<PcbUnit> d_units;
-    DevBuf<int32_t> d_scan;
-    DevBuf<PcbLong> d_longs;
     struct TaskPlan {
+        DevBuf<PcbTask> d_tasks;
+        DevBuf<PcbUnit> d_units;
+        DevBuf<int32_t> d_scan;
+        DevBuf<PcbLong> d_longs;
+        int64_t b0 = 0, b1 = 0;              // byte range of the piece
+        int64_t end_lo = -1, end_hi = 0;     // the piece of the blob this plan covers: tasks whose segment ends in (end_lo, end_hi]
+        cudaEvent_t ready = nullptr;         // recorded on the copy stream once that piece is in the arena
+        bool has_ready = false;
+        void release() { d_tasks.release(); d_units.release(); d_scan.release(); d_longs.release(); }
         struct Launch { bool trace; int cls, kind /*0 direct, 1 scan, 2 window*/; int64_t cells, task0, unit0, n_units; int mmax, nmax, smax, grid; };
         std::vector<Launch> launches;
         int64_t n_long = 0, n_chunks = 0, win_task0 = 0;
         uint64_t scratch_words = 0, stamp = 0;
         bool valid = false;
-    } plan;
+    };
+    enum { MAX_PIECES = 4 };
+    TaskPlan plans[MAX_PIECES];
+    int n_pieces = 1, pieces_sent = 0;
+    const char *pending_blob = nullptr;  // host blob whose later pieces are sent once the plans exist (small planning copies
+                                         // would otherwise queue behind the whole blob on the copy engine)
     // outputs / scratch
     DevBuf<uint32_t> d_scratch;
     DevBuf<int32_t> d_err;
@@ -137,12 +149,14 @@ extern "C" int pcb_create(int device, pcb_context **out)
     pcb_context *c = new pcb_context();
     c->device = device;
     if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&c->cstream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
         (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
         g_global_err = std::string("context setup failed: ") + cudaGetErrorString(e);
         delete c;
         return PCB_ERR_CUDA;
     }
+    for (auto &ev : c->pipe_ev) if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { g_global_err = "event creation failed"; delete c; return PCB_ERR_CUDA; }
     c->grid_trace = pcb_occupancy_grid(0);
     c->grid_scan = pcb_occupancy_grid(1);
     for (int cls = 0; cls < PCF_NCLS; ++cls) { c->grid_ftrace[cls] = pcf_occupancy_grid(true, cls); c->grid_fscan[cls] = pcf_occupancy_grid(false, cls); }
@@ -155,13 +169,15 @@ extern "C" void pcb_destroy(pcb_context *c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->cstream);
     c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_arena_t.release();
     for (auto &sl : c->slots) { sl.d_arena.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release(); }
-    c->d_tasks.release(); c->d_units.release(); c->d_scan.release(); c->d_longs.release();
+    for (auto &pl : c->plans) { pl.release(); if (pl.ready) cudaEventDestroy(pl.ready); }
     c->d_seg_off.release(); c->d_plan_i64.release(); c->d_seg_len.release(); c->d_seg_ad.release(); c->d_plan_i32.release(); c->d_adinfo.release();
     c->d_scratch.release(); c->d_err.release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->kev0); cudaEventDestroy(c->kev1);
+    for (auto &ev : c->pipe_ev) if (ev) cudaEventDestroy(ev);
+    cudaStreamDestroy(c->cstream);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -265,7 +281,7 @@ static void fill_launch_common(pcb_context *c, PcbLaunch &L, bool task_arena = f
     L.ad.codes = c->d_ad_codes.p; L.ad.off = c->d_ad_off.p;
     L.sc = c->sc;
     L.arena = task_arena ? c->d_arena_t.p : c->S().d_arena.p; L.arena_len = task_arena ? c->arena_t_len : c->S().arena_len;
-    L.out = c->S().d_out.p; L.scan_out = c->d_scan.p;
+    L.out = c->S().d_out.p; L.scan_out = nullptr;
     L.scratch = c->d_scratch.p; L.err_flag = c->d_err.p;
 }
 
@@ -361,10 +377,10 @@ static int split_ids(pcb_context *c, bool fast_ok)
     return PCB_OK;
 }
 
-extern "C" int pcb_run_windows_resident(pcb_context *c)
+// Cross product of the selected slot.  host_out == NULL: results stay in HBM.  Otherwise the biggest launch is cut
+// into window ranges and each range's records travel to host_out on the copy stream while the next range computes.
+static int run_windows(pcb_context *c, pcb_result *host_out)
 {
-    if (!c) return PCB_ERR_ARG;
-    cudaSetDevice(c->device);
     pcb_context::Slot &S = c->S();
     const int64_t n_res = S.n_windows * S.n_ids;
     S.n_results = n_res;
@@ -376,37 +392,72 @@ extern "C" int pcb_run_windows_resident(pcb_context *c)
     PCB_CUDA(c, S.d_out.reserve((size_t)n_res));
     PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
     const int n = S.n_ids;
-    const int64_t groups = (S.n_windows + 63) / 64;
-    // the small launches first: their tails then overlap nothing bigger than themselves
-    int first = 0;
-    for (int cls = PCF_NCLS; cls >= 0; --cls) {
+    // classes in ascending order of work: the small launches first (their tails then overlap nothing bigger than
+    // themselves), the biggest last (it is the one that is pipelined against the copies)
+    int order[PCF_NCLS + 1], n_used = 0;
+    int64_t work[PCF_NCLS + 1];
+    for (int cls = 0; cls <= PCF_NCLS; ++cls) {
+        if (S.n_cls[cls] == 0) continue;
+        work[cls] = (int64_t)S.n_cls[cls] * (cls < PCF_NCLS ? pcf_class_nr(cls) : 4 * PCB_RT);
+        order[n_used++] = cls;
+    }
+    std::sort(order, order + n_used, [&](int x, int y) { return work[x] < work[y]; });
+    for (int oi = 0; oi < n_used; ++oi) {
+        const int cls = order[oi];
         const int cnt = S.n_cls[cls];
-        if (cnt == 0) continue;
         int start = 0;
         for (int q = 0; q < cls; ++q) start += S.n_cls[q];
         const int32_t *h_list = S.h_split.data() + start;
         const int nmax = max_adapter_len(c, h_list, cnt);
         const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
         if (cls == PCF_NCLS && (rc = check_range(c, nmax, mmax))) return rc;
-        const int64_t n_units = groups * cnt;
         const int gmax = cls < PCF_NCLS ? c->grid_ftrace[cls] : c->grid_trace;
-        const int grid = (int)std::min<int64_t>(gmax, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
-        rc = ensure_scratch(c, cls < PCF_NCLS ? pcf_scratch_words_trace(mmax, cls) : pcb_scratch_words_trace(mmax, smax), grid);
-        if (rc) return rc;
-        PcbLaunch L; fill_launch_common(c, L);
-        L.src.units = nullptr; L.src.tasks = nullptr;
-        L.src.n_windows = S.n_windows; L.src.stride = S.stride; L.src.win_len = S.d_winlen.p;
-        L.src.ids = S.d_ids.p + start; L.src.n_ids = cnt;
-        L.src.id_pos = S.d_ids.p + n + start; L.src.n_ids_total = n;
-        L.src.n_units = n_units;
-        L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
-        // algorithmic cell count: sum over windows of len x sum over ids of adapter length
-        int64_t sum_n = 0;
+        const int64_t warps = (int64_t)gmax * (PCB_BLOCK / 32);
+        int64_t sum_n = 0;                 // algorithmic cell count: sum over windows of len x sum over ids of adapter length
         for (int i = 0; i < cnt; ++i) sum_n += c->ad_off[h_list[i] + 1] - c->ad_off[h_list[i]];
-        if ((rc = launch_dp(c, L, true, S.sum_winlen * sum_n, cls))) return rc;
-        (void)first;
+        // window ranges of this launch (multiples of 64 windows; each range keeps every warp busy for >= 8 units)
+        const int64_t groups_all = (S.n_windows + 63) / 64;
+        int64_t n_ranges = 1;
+        if (host_out && oi == n_used - 1) n_ranges = std::max<int64_t>(1, std::min<int64_t>(8, groups_all * cnt / (8 * warps)));
+        const int64_t groups_per = (groups_all + n_ranges - 1) / n_ranges;
+        for (int64_t r = 0; r < n_ranges; ++r) {
+            const int64_t w0 = r * groups_per * 64, w1 = std::min<int64_t>(S.n_windows, (r + 1) * groups_per * 64);
+            if (w0 >= w1) break;
+            const int64_t n_units = ((w1 - w0 + 63) / 64) * cnt;
+            const int grid = (int)std::min<int64_t>(gmax, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
+            rc = ensure_scratch(c, cls < PCF_NCLS ? pcf_scratch_words_trace(mmax, cls) : pcb_scratch_words_trace(mmax, smax), grid);
+            if (rc) return rc;
+            PcbLaunch L; fill_launch_common(c, L);
+            L.arena = S.d_arena.p + (uint64_t)w0 * S.stride;
+            L.out = S.d_out.p + w0 * n;
+            L.src.units = nullptr; L.src.tasks = nullptr;
+            L.src.n_windows = w1 - w0; L.src.stride = S.stride; L.src.win_len = S.d_winlen.p + w0;
+            L.src.ids = S.d_ids.p + start; L.src.n_ids = cnt;
+            L.src.id_pos = S.d_ids.p + n + start; L.src.n_ids_total = n;
+            L.src.n_units = n_units;
+            L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
+            if ((rc = launch_dp(c, L, true, r == 0 ? S.sum_winlen * sum_n : 0, cls))) return rc;
+            if (host_out && oi == n_used - 1) {
+                cudaEvent_t ev = c->pipe_ev[r % 8];
+                PCB_CUDA(c, cudaEventRecord(ev, c->stream));
+                PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, ev, 0));
+                PCB_CUDA(c, cudaMemcpyAsync(host_out + w0 * n, S.d_out.p + w0 * n, sizeof(pcb_result) * (size_t)((w1 - w0) * n),
+                                            cudaMemcpyDeviceToHost, c->cstream));
+            }
+        }
+    }
+    if (host_out) {
+        c->cnt.d2h_bytes += (int64_t)sizeof(pcb_result) * n_res;
+        PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
     }
     return PCB_OK;
+}
+
+extern "C" int pcb_run_windows_resident(pcb_context *c)
+{
+    if (!c) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    return run_windows(c, nullptr);
 }
 
 extern "C" int pcb_fetch_results(pcb_context *c, pcb_result *out, int64_t n_results)
@@ -425,8 +476,9 @@ extern "C" int pcb_align_windows(pcb_context *c, const char *windows, int64_t n_
     int rc;
     if ((rc = pcb_stage_windows(c, windows, n_windows, stride, win_len))) return rc;
     if ((rc = pcb_stage_ids(c, adapter_ids, n_ids))) return rc;
-    if ((rc = pcb_run_windows_resident(c))) return rc;
-    return pcb_fetch_results(c, out, n_windows * n_ids);
+    if (n_windows * (int64_t)n_ids > 0 && !out) return PCB_ERR_ARG;
+    if ((rc = run_windows(c, out))) return rc;
+    return check_err_flag(c);
 }
 
 extern "C" int pcb_timer_start(pcb_context *c) { if (!c) return PCB_ERR_ARG; cudaSetDevice(c->device); PCB_CUDA(c, cudaEventRecord(c->ev0, c->stream)); return PCB_OK; }
@@ -472,30 +524,72 @@ WindowBounds window_bounds(const PcbScores &s, int n)
 
 }  // namespace
 
-extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, const int64_t *seg_off,
-                               const int32_t *seg_len, const int32_t *task_adapter, int64_t n_tasks)
+// Puts pieces [pieces_sent, upto) of the pending blob on the copy stream: H2D, encode, `ready` event.
+static int send_pieces(pcb_context *c, int upto)
+{
+    if (!c->pending_blob) return PCB_OK;
+    for (int p = c->pieces_sent; p < upto && p < c->n_pieces; ++p) {
+        pcb_context::TaskPlan &P = c->plans[p];
+        if (P.b1 > P.b0) {
+            PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p + P.b0, c->pending_blob + P.b0, (size_t)(P.b1 - P.b0), cudaMemcpyHostToDevice, c->cstream));
+            PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p + P.b0, c->d_arena_t.p + P.b0, (uint64_t)(P.b1 - P.b0), c->cstream));
+            c->cnt.kernel_launches++;
+        }
+        PCB_CUDA(c, cudaEventRecord(P.ready, c->cstream));
+        c->pieces_sent = p + 1;
+    }
+    if (c->pieces_sent >= c->n_pieces) c->pending_blob = nullptr;
+    return PCB_OK;
+}
+
+// n_pieces > 1: the blob travels in pieces on the copy stream and each piece gets its own plan (the tasks whose segment
+// ends inside it), so that the kernels of piece p run while piece p + 1 is still on the PCIe bus.
+static int stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, const int64_t *seg_off,
+                       const int32_t *seg_len, const int32_t *task_adapter, int64_t n_tasks, int n_pieces)
 {
     if (!c || blob_len < 0 || n_tasks < 0 || (n_tasks > 0 && (!seg_off || !seg_len || !task_adapter)) || (blob_len > 0 && !seq_blob))
         return PCB_ERR_ARG;
     cudaSetDevice(c->device);
-    c->plan.valid = false; c->n_tasks = 0;
+    for (auto &pl : c->plans) pl.valid = false;
+    c->n_tasks = 0;
     // copies first (asynchronous from pinned memory), so that the host-side checks below run under them
     PCB_CUDA(c, c->d_ascii.reserve((size_t)blob_len + 16));
     PCB_CUDA(c, c->d_arena_t.reserve((size_t)blob_len + 16));
     PCB_CUDA(c, c->d_seg_off.reserve((size_t)n_tasks + 1));
     PCB_CUDA(c, c->d_seg_len.reserve((size_t)n_tasks + 1));
     PCB_CUDA(c, c->d_seg_ad.reserve((size_t)n_tasks + 1));
-    if (blob_len) {
-        PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, seq_blob, (size_t)blob_len, cudaMemcpyHostToDevice, c->stream));
-        PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena_t.p, (uint64_t)blob_len, c->stream));
-        c->cnt.kernel_launches++;
-    }
-    PCB_CUDA(c, cudaMemsetAsync(c->d_arena_t.p + blob_len, 0, 16, c->stream));   // valid codes past the last segment
     if (n_tasks) {
         PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_off.p, seg_off, sizeof(int64_t) * n_tasks, cudaMemcpyHostToDevice, c->stream));
         PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_len.p, seg_len, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->stream));
         PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_ad.p, task_adapter, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->stream));
     }
+    n_pieces = std::max(1, std::min<int>(n_pieces, pcb_context::MAX_PIECES));
+    c->n_pieces = n_pieces;
+    c->pending_blob = nullptr;
+    PCB_CUDA(c, cudaMemsetAsync(c->d_arena_t.p + blob_len, 0, 16, c->stream));   // valid codes past the last segment
+    if (n_pieces == 1) {
+        if (blob_len) {
+            PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, seq_blob, (size_t)blob_len, cudaMemcpyHostToDevice, c->stream));
+            PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena_t.p, (uint64_t)blob_len, c->stream));
+            c->cnt.kernel_launches++;
+        }
+        c->plans[0].end_lo = -1; c->plans[0].end_hi = blob_len; c->plans[0].has_ready = false;
+    } else {
+        // the copy stream starts after whatever the main stream still does with the two staging buffers
+        PCB_CUDA(c, cudaEventRecord(c->pipe_ev[0], c->stream));
+        PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, c->pipe_ev[0], 0));
+        const int64_t per = ((blob_len + n_pieces - 1) / n_pieces + 15) & ~(int64_t)15;
+        for (int p = 0; p < n_pieces; ++p) {
+            pcb_context::TaskPlan &P = c->plans[p];
+            P.b0 = std::min<int64_t>(blob_len, p * per); P.b1 = p == n_pieces - 1 ? blob_len : std::min<int64_t>(blob_len, (p + 1) * per);
+            if (!P.ready) PCB_CUDA(c, cudaEventCreateWithFlags(&P.ready, cudaEventDisableTiming));
+            P.has_ready = true;
+            // the kernels fetch bases up to 8 bytes past a segment's end: a task waits for the piece that holds those too
+            P.end_lo = p == 0 ? -1 : P.b0 - 16; P.end_hi = p == n_pieces - 1 ? blob_len : P.b1 - 16;
+        }
+        c->pending_blob = seq_blob; c->pieces_sent = 0;
+    }
+    { int rc0 = send_pieces(c, 1); if (rc0) return rc0; }      // piece 0 now; the rest once the plans are built
     int64_t long_cols = 0, cells = 0;
     for (int64_t t = 0; t < n_tasks; ++t) {
         const bool bad_seg = seg_len[t] < 0 || seg_off[t] < 0 || seg_off[t] + seg_len[t] > blob_len;
@@ -515,6 +609,12 @@ extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blo
     return PCB_OK;
 }
 
+extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, const int64_t *seg_off,
+                               const int32_t *seg_len, const int32_t *task_adapter, int64_t n_tasks)
+{
+    return stage_tasks(c, seq_blob, blob_len, seg_off, seg_len, task_adapter, n_tasks, 1);
+}
+
 // ------------------------------------------------------------------------------------------------
 // The plan of a staged task list: every launch the run needs, with its task / unit arrays already in HBM.  It depends
 // only on the staged segments, the adapter set and the scoring scheme, so it is built once per staging (or when one
@@ -522,9 +622,8 @@ extern "C" int pcb_stage_tasks(pcb_context *c, const char *seq_blob, int64_t blo
 // chunk scans, one merge kernel (best end cell per long read -> its trace-window task), window traces.  No host
 // round trip inside a run.
 // ------------------------------------------------------------------------------------------------
-static int build_task_plan(pcb_context *c)
+static int build_task_plan(pcb_context *c, pcb_context::TaskPlan &P, bool first_piece)
 {
-    pcb_context::TaskPlan &P = c->plan;
     P.launches.clear(); P.n_long = 0; P.n_chunks = 0; P.win_task0 = 0; P.scratch_words = 0; P.valid = false;
     const int64_t nt = c->n_tasks;
     if (nt == 0) { P.valid = true; P.stamp = c->stamp; return PCB_OK; }
@@ -554,7 +653,7 @@ static int build_task_plan(pcb_context *c)
     PCB_CUDA(c, cudaMemcpyAsync(c->d_adinfo.p, ad.data(), sizeof(PcbAdInfo) * A, cudaMemcpyHostToDevice, c->stream));
     PcbPlanArgs pa{};
     pa.seg_off = c->d_seg_off.p; pa.seg_len = c->d_seg_len.p; pa.seg_ad = c->d_seg_ad.p; pa.n_tasks = nt;
-    pa.ad = c->d_adinfo.p; pa.n_adapters = A; pa.chunk = chunk;
+    pa.ad = c->d_adinfo.p; pa.n_adapters = A; pa.chunk = chunk; pa.end_lo = P.end_lo; pa.end_hi = P.end_hi;
     pa.count = c->d_plan_i32.p; pa.cursor = c->d_plan_i32.p + nb; pa.mmax = c->d_plan_i32.p + 2 * nb; pa.base = c->d_plan_i64.p;
     PCB_CUDA(c, pcb_launch_plan(pa, false, c->stream));
     std::vector<int32_t> count(nb), mmax(nm);
@@ -617,19 +716,19 @@ static int build_task_plan(pcb_context *c)
             P.launches.push_back(pl);
         }
     }
-    if (!P.launches.empty()) P.launches[0].cells = c->task_cells;      // algorithmic cell updates of the whole run
+    if (!P.launches.empty() && first_piece) P.launches[0].cells = c->task_cells;      // algorithmic cell updates of the whole run
     P.n_chunks = pa.win_task0 - pa.scan_task0;
     P.n_long = run - pa.win_task0;
     P.win_task0 = pa.win_task0;
 
     // pass 2 on the device: write the tasks into their buckets
-    PCB_CUDA(c, c->d_tasks.reserve((size_t)run + 1));
-    PCB_CUDA(c, c->d_units.reserve(all_units.size() + 1));
-    PCB_CUDA(c, c->d_longs.reserve((size_t)P.n_long + 1));
-    PCB_CUDA(c, c->d_scan.reserve((size_t)P.n_chunks + 1));
+    PCB_CUDA(c, P.d_tasks.reserve((size_t)run + 1));
+    PCB_CUDA(c, P.d_units.reserve(all_units.size() + 1));
+    PCB_CUDA(c, P.d_longs.reserve((size_t)P.n_long + 1));
+    PCB_CUDA(c, P.d_scan.reserve((size_t)P.n_chunks + 1));
     PCB_CUDA(c, cudaMemcpyAsync(c->d_plan_i64.p, base.data(), sizeof(int64_t) * nb, cudaMemcpyHostToDevice, c->stream));
-    PCB_CUDA(c, cudaMemcpyAsync(c->d_units.p, all_units.data(), sizeof(PcbUnit) * all_units.size(), cudaMemcpyHostToDevice, c->stream));
-    pa.tasks = c->d_tasks.p; pa.longs = c->d_longs.p;
+    PCB_CUDA(c, cudaMemcpyAsync(P.d_units.p, all_units.data(), sizeof(PcbUnit) * all_units.size(), cudaMemcpyHostToDevice, c->stream));
+    pa.tasks = P.d_tasks.p; pa.longs = P.d_longs.p;
     PCB_CUDA(c, pcb_launch_plan(pa, true, c->stream));
     c->cnt.h2d_bytes += (int64_t)(sizeof(int64_t) * nb + sizeof(PcbUnit) * all_units.size() + sizeof(PcbAdInfo) * A);
     c->cnt.d2h_bytes += (int64_t)(sizeof(int32_t) * (nb + nm));
@@ -648,22 +747,30 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
     c->S().n_results = (int64_t)nt;
     if (nt == 0) return PCB_OK;
     int rc;
-    if ((!c->plan.valid || c->plan.stamp != c->stamp) && (rc = build_task_plan(c))) return rc;
-    const pcb_context::TaskPlan &P = c->plan;
+    for (int p = 0; p < c->n_pieces; ++p)
+        if ((!c->plans[p].valid || c->plans[p].stamp != c->stamp) && (rc = build_task_plan(c, c->plans[p], p == 0))) return rc;
+    if ((rc = send_pieces(c, c->n_pieces))) return rc;
     PCB_CUDA(c, c->S().d_out.reserve(nt));
-    PCB_CUDA(c, c->d_scratch.reserve((size_t)P.scratch_words));     // another slot's run may have shrunk nothing, but be safe
+    uint64_t scratch = 0;
+    for (int p = 0; p < c->n_pieces; ++p) scratch = std::max(scratch, c->plans[p].scratch_words);
+    PCB_CUDA(c, c->d_scratch.reserve((size_t)scratch));
     PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
-    bool merged = false;
-    for (const auto &pl : P.launches) {
-        if (pl.kind == 2 && !merged) {
-            PCB_CUDA(c, pcb_launch_merge(c->d_longs.p, P.n_long, c->d_scan.p, c->d_tasks.p + P.win_task0, c->d_err.p, c->stream));
-            c->cnt.kernel_launches++;
-            merged = true;
+    for (int p = 0; p < c->n_pieces; ++p) {
+        pcb_context::TaskPlan &P = c->plans[p];
+        if (P.has_ready) PCB_CUDA(c, cudaStreamWaitEvent(c->stream, P.ready, 0));     // this piece of the blob has arrived
+        bool merged = false;
+        for (const auto &pl : P.launches) {
+            if (pl.kind == 2 && !merged) {
+                PCB_CUDA(c, pcb_launch_merge(P.d_longs.p, P.n_long, P.d_scan.p, P.d_tasks.p + P.win_task0, c->d_err.p, c->stream));
+                c->cnt.kernel_launches++;
+                merged = true;
+            }
+            PcbLaunch L; fill_launch_common(c, L, true);
+            L.scan_out = P.d_scan.p;
+            L.src.units = P.d_units.p + pl.unit0; L.src.tasks = P.d_tasks.p + pl.task0; L.src.n_units = pl.n_units;
+            L.ad.max_len = pl.nmax; L.mmax = pl.mmax; L.smax = pl.smax; L.grid = pl.grid;
+            if ((rc = launch_dp(c, L, pl.trace, pl.cells, pl.cls))) return rc;
         }
-        PcbLaunch L; fill_launch_common(c, L, true);
-        L.src.units = c->d_units.p + pl.unit0; L.src.tasks = c->d_tasks.p + pl.task0; L.src.n_units = pl.n_units;
-        L.ad.max_len = pl.nmax; L.mmax = pl.mmax; L.smax = pl.smax; L.grid = pl.grid;
-        if ((rc = launch_dp(c, L, pl.trace, pl.cells, pl.cls))) return rc;
     }
     return PCB_OK;
 }
@@ -672,7 +779,11 @@ extern "C" int pcb_align_tasks(pcb_context *c, const char *seq_blob, int64_t blo
                                const int32_t *seg_len, const int32_t *task_adapter, int64_t n_tasks, pcb_result *out)
 {
     int rc;
-    if ((rc = pcb_stage_tasks(c, seq_blob, blob_len, seg_off, seg_len, task_adapter, n_tasks))) return rc;
+    // big blobs travel in pieces, each piece's kernels running under the next piece's copy
+    const char *pm = getenv("PCB_PIECE_MIN_BYTES");           // tests lower it to reach the pieced path with small inputs
+    const int64_t piece_min = pm ? atoll(pm) : (64ll << 20);
+    const int pieces = blob_len >= piece_min && blob_len >= 4096 ? pcb_context::MAX_PIECES : 1;
+    if ((rc = stage_tasks(c, seq_blob, blob_len, seg_off, seg_len, task_adapter, n_tasks, pieces))) return rc;
     if ((rc = pcb_run_tasks_resident(c))) return rc;
     return pcb_fetch_results(c, out, n_tasks);
 }

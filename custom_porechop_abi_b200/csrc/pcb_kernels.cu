@@ -452,6 +452,7 @@ __global__ void k_plan(const PcbPlanArgs a)
     if (t >= a.n_tasks) return;
     const int32_t len = a.seg_len[t], ad = a.seg_ad[t];
     const int64_t off = a.seg_off[t];
+    if (off + len <= a.end_lo || off + len > a.end_hi) return;      // another piece's task
     const PcbAdInfo x = a.ad[ad];
     bool is_long; int nchunks, chunk_r, lb;
     plan_classify(a, len, x, is_long, nchunks, chunk_r, lb);

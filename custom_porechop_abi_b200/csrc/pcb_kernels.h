@@ -158,6 +158,7 @@ struct PcbPlanArgs {
     int32_t *cursor;            /* same shape, zeroed: next free slot of a bucket                          */
     PcbTask *tasks; PcbLong *longs;
     int64_t scan_task0, win_task0;   /* where the scan chunks / window tasks start in `tasks`              */
+    int64_t end_lo, end_hi;          /* only tasks whose segment ends in (end_lo, end_hi] (one piece of the blob) */
 };
 cudaError_t pcb_launch_plan(const PcbPlanArgs &a, bool fill, cudaStream_t st);
 

@@ -55,3 +55,21 @@ for rep in range(2):
     timed('run_tasks (plan + kernels)', eng.run_tasks_resident)
     timed('run_tasks (kernels)', eng.run_tasks_resident)
     timed('fetch', eng.fetch)
+
+# the three host-buffer calls of a bench step, pinned in and out
+from custom_porechop_abi_b200.engine import RESULT_DTYPE, _ptr
+from custom_porechop_abi_b200 import cpp_function_wrappers as w
+def pinned_out(shape):
+    t = torch.empty(tuple(shape) + (8,), dtype=torch.int32).pin_memory(); keep.append(t)
+    return t.numpy().view(RESULT_DTYPE).reshape(shape)
+ebuf = P(wl['ebuf'])
+out_s = pinned_out((n, len(wl['start_ids']))); out_e = pinned_out((n, len(wl['end_ids']))); out_m = pinned_out((len(task_ad),))
+sid = np.ascontiguousarray(wl['start_ids']); eid = np.ascontiguousarray(wl['end_ids'])
+for rep in range(3):
+    print('e2e rep', rep)
+    eng.select_slot(0)
+    timed('align_windows start', lambda: eng._check(w.C_LIB.pcb_align_windows(eng._h, _ptr(sbuf), n, 160, _ptr(wlen), _ptr(sid), len(sid), _ptr(out_s)), 'x'))
+    eng.select_slot(1)
+    timed('align_windows end', lambda: eng._check(w.C_LIB.pcb_align_windows(eng._h, _ptr(ebuf), n, 160, _ptr(wlen), _ptr(eid), len(eid), _ptr(out_e)), 'x'))
+    eng.select_slot(2)
+    timed('align_tasks', lambda: eng._check(w.C_LIB.pcb_align_tasks(eng._h, _ptr(blob), blob.size, _ptr(seg_off), _ptr(seg_len), _ptr(task_ad), len(task_ad), _ptr(out_m)), 'x'))

@@ -171,3 +171,39 @@ def test_full_size_windows_properties(engine):
     recs = engine.align_pairs(pairs)
     for (w, k), rec in zip(sample[:500], recs):
         assert rec.tobytes() == a[w, k].tobytes()
+
+
+def test_pipelined_host_buffer_paths_equal_resident(engine):
+    """The host-buffer calls overlap copies with kernels (window ranges on the copy stream; the read blob in pieces,
+    each with its own plan).  Same records as the plain stage / run / fetch sequence, and as the oracle on a sample."""
+    import os
+    from custom_porechop_abi_b200 import synthetic
+    adapters, s_ids, e_ids = synthetic.adapter_set()
+    engine.set_scoring(DEFAULT)
+    engine.set_adapters(adapters)
+    n = 49152
+    blob, off = synthetic.make_reads(n, adapters, s_ids, e_ids, seed=13, lengths=np.full(n, 220))
+    sbuf, ebuf, lens = synthetic.end_windows(blob, off)
+    piped = engine.align_windows(ebuf, lens, e_ids)
+    engine.stage_windows(ebuf, lens, e_ids)
+    engine.run_windows_resident()
+    plain = engine.fetch()
+    assert piped.tobytes() == plain.tobytes()
+    # blob in pieces: ragged reads, some straddling the piece boundaries, long and short
+    rng = np.random.default_rng(5)
+    lengths = np.clip(rng.lognormal(7.5, 1.0, 3000), 1, 60000).astype(np.int64)
+    blob, off = synthetic.make_reads(len(lengths), adapters, s_ids, e_ids, seed=17, lengths=lengths, middle_rate=0.2)
+    ids = np.array([s_ids[0], e_ids[0], s_ids[-1]], dtype=np.int32)
+    seg_off = np.repeat(off[:-1], len(ids)); seg_len = np.repeat(lengths.astype(np.int32), len(ids))
+    ad = np.tile(ids, len(lengths))
+    one = engine.align_tasks(blob, seg_off, seg_len, ad)
+    os.environ['PCB_PIECE_MIN_BYTES'] = '4096'
+    try:
+        pieced = engine.align_tasks(blob, seg_off, seg_len, ad)
+    finally:
+        del os.environ['PCB_PIECE_MIN_BYTES']
+    assert pieced.tobytes() == one.tobytes()
+    rs = random.Random(8)
+    for t in rs.sample(range(len(ad)), 300):
+        r = bytes(blob[seg_off[t]:seg_off[t] + seg_len[t]])
+        assert rec_matches_oracle(pieced[t], oracle_align(r, adapters[ad[t]], DEFAULT)), t
