@@ -14,7 +14,7 @@ Every (window|read, adapter) pair is one adapterAlignment of the reference (src/
 
 value   : reads/s, whole job over all ranks, inputs already resident in HBM (CUDA events, max over ranks)
 e2e     : reads/s through the host-buffer C-ABI calls (pinned host buffers, H2D + D2H inside the timed region)
-roofline: the dominant kernel (k_align<true> on the end windows), timed alone with CUDA events
+roofline: the dominant kernel (k_fast<TRACE,24,EXACT> on the end windows), timed alone with CUDA events
 """
 import argparse
 import json
@@ -295,19 +295,30 @@ def run_gpu_arm(args):
     e2e_s = max_over_ranks(e2e_s)
     checksum = int(out_s['raw_score'].astype(np.int64).sum() + out_e['raw_score'].astype(np.int64).sum() + out_m['raw_score'].astype(np.int64).sum())
 
-    # ---- dominant kernel alone (k_align<true> over the end windows of slot 1), CUDA events on the launching stream
-    eng.select_slot(1)
+    # ---- dominant kernel alone: k_fast<TRACE, NR=24, EXACT> = the end windows against the 24-base end sequences (one launch;
+    #      55% of the step in the ncu launch list), CUDA events on the library's own stream
+    ad_len = np.array([len(a) for a in wl['adapters']], dtype=np.int64)
+    ids24 = np.array([i for i in wl['end_ids'] if ad_len[i] == 24], dtype=np.int32)
+    eng.select_slot(3); eng.stage_windows(ebuf, wlen, ids24)
     eng.run_windows_resident(); eng.synchronize()
     reps = 5
+    c_k0 = eng.counters()
     eng.timer_start()
     for _ in range(reps):
         eng.run_windows_resident()
     k_ms = eng.timer_stop() / reps
-    ad_len = np.array([len(a) for a in wl['adapters']], dtype=np.int64)
-    k_cells = int(wlen.astype(np.int64).sum()) * int(ad_len[wl['end_ids']].sum())
-    k_tasks = n * len(wl['end_ids'])
+    k_launches = (eng.counters()['dp_kernel_launches'] - c_k0['dp_kernel_launches']) // reps
+    k_cells = int(wlen.astype(np.int64).sum()) * int(ad_len[ids24].sum())
+    k_tasks = n * len(ids24)
     # algorithmic bytes of that launch: window bases read once + adapters + one 32-byte record per pair
-    k_bytes = int(wlen.astype(np.int64).sum()) + int(ad_len[wl['end_ids']].sum()) + 32 * k_tasks
+    k_bytes = int(wlen.astype(np.int64).sum()) + int(ad_len[ids24].sum()) + 32 * k_tasks
+    # the scan kernel of the full-length search (k_fast<SCAN>), timed with its planner / merge / window-trace launches
+    eng.select_slot(2)
+    eng.timer_start()
+    for _ in range(reps):
+        eng.run_tasks_resident()
+    t_ms = eng.timer_stop() / reps
+    t_cells = int((off_lens := (wl['off'][1:] - wl['off'][:-1])).astype(np.int64).sum()) * int(ad_len[wl['mid_ids']].sum())
 
     if rank == 0:
         peaks = {}
@@ -320,8 +331,11 @@ def run_gpu_arm(args):
         clocks = sampler.summary()
         sm_mhz = clocks.get('sm_mhz') or 1965
         # integer-issue model: 148 SMs x 4 sub-partitions x 32 lanes x 1 instr/clk, 2 cells per lane-op
-        ops_per_cell_pair = float(os.environ.get('PCB_OPS_PER_CELL_PAIR', '27'))
-        int_peak_gcups = 148 * 4 * 32 * sm_mhz * 1e6 * 2 / ops_per_cell_pair / 1e9
+        # integer-issue roofline: a DP cell pair (two tasks packed in one register) needs at least 4
+        # integer warp instructions (diagonal add, H, V, max3); profiles/pipes_r1e.txt measures 1.8 clk per integer warp
+        # instruction and sub-partition at best (ALU + FMA pipes alternating) -> 64 cells per 7.2 clk per sub-partition
+        instr_per_pair, clk_per_instr = 4.0, 1.8
+        int_peak_gcups = 148 * 4 * 64 / (instr_per_pair * clk_per_instr) * sm_mhz * 1e6 / 1e9
         line = {
             'metric': METRIC, 'value': world * n / (ms_step / 1000.0), 'unit': 'reads/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_step, 'higher_is_better': True,
@@ -334,12 +348,14 @@ def run_gpu_arm(args):
                     'gcups': world * wl['cells'] * args.steps / e2e_s / 1e9, 'checksum': checksum},
             'gpu_launches': int(cnt['kernel_launches']),
             'clocks': clocks,
-            'roofline': {'bound': 'hbm', 'kernel': 'k_align<true> (end windows x 117 adapters)', 'achieved': k_bytes / (k_ms / 1000.0) / 1e9,
+            'roofline': {'bound': 'hbm', 'kernel': 'k_fast<TRACE,24,EXACT,16> (end windows x %d 24-base end sequences, %d launch)' % (len(ids24), k_launches), 'achieved': k_bytes / (k_ms / 1000.0) / 1e9,
                          'peak': hbm_peak, 'unit': 'GB/s', 'frac': k_bytes / (k_ms / 1000.0) / 1e9 / hbm_peak, 'traffic': None,
                          'peak_source': peak_src, 'launch_ms': k_ms,
                          'note': 'integer-issue bound kernel: see int_dp; HBM figures are the algorithmic bytes only'},
             'int_dp': {'kernel_gcups': k_cells / (k_ms / 1000.0) / 1e9, 'model_peak_gcups': int_peak_gcups,
-                       'frac': k_cells / (k_ms / 1000.0) / 1e9 / int_peak_gcups, 'ops_per_cell_pair': ops_per_cell_pair,
+                       'frac': k_cells / (k_ms / 1000.0) / 1e9 / int_peak_gcups,
+                       'model': '148 SM x 4 sub-partitions x 64 cells / (4 integer instr x 1.8 clk) x SM clock',
+                       'scan_phase_gcups': t_cells / (t_ms / 1000.0) / 1e9, 'scan_phase_frac': t_cells / (t_ms / 1000.0) / 1e9 / int_peak_gcups,
                        'sm_mhz': sm_mhz},
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -1,15 +1,15 @@
-# usage (under gpurun): bash scripts/gpu_ncu.sh <tag> [kernel regex] [skip]  -- launch list + one full capture of the dominant kernel
+# usage (under gpurun): bash scripts/gpu_ncu.sh <tag>  -- launch list + full captures of the trace kernel (24 exact) and the scan kernel
 set -x
 TAG=${1:-r1}
-KRE=${2:-k_fast}
-SKIP=${3:-2}
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
 CMD="python bench.py --steps 1 --warmup 1 --reads-per-gpu 8192 --no-cpu-baseline"
 $CMD > gpurun_out/ncu_plain_$TAG.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_list_$TAG.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_list_$TAG.log 2>&1
 echo "ncu list rc=$?"
 $CMD > gpurun_out/ncu_plain2_$TAG.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:$KRE -s $SKIP -c 2 -f -o gpurun_out/prof_$TAG $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k 'regex:k_fast<\(bool\)1, \(int\)24, \(bool\)1' -s 2 -c 1 -f -o gpurun_out/prof_$TAG $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
 echo "ncu full rc=$?"
-ls -la gpurun_out
+ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k 'regex:k_fast<\(bool\)0' -s 1 -c 1 -f -o gpurun_out/prof_${TAG}_scan $CMD > gpurun_out/ncu_full2_$TAG.log 2>&1
+echo "ncu scan rc=$?"
+ls -la gpurun_out | tail -5

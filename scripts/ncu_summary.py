@@ -63,6 +63,14 @@ def kernel(tag):
     rep = os.path.join(OUT, 'prof_%s.ncu-rep' % tag)
     if not os.path.isfile(rep):
         return None
+    text = kernel_one(rep, tag)
+    rep2 = os.path.join(OUT, 'prof_%s_scan.ncu-rep' % tag)
+    if os.path.isfile(rep2):
+        text += '\n' + kernel_one(rep2, tag + ' (scan)')
+    return text
+
+
+def kernel_one(rep, tag):
     raw = ncu_csv(rep, 'raw')
     h, units, data = raw[0], raw[1], raw[2:]
     ni = h.index('Kernel Name')
