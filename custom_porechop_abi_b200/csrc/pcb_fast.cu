@@ -22,8 +22,8 @@
  *   3. the scan kernel for long reads (middle-adapter search) is pass 1 alone, with the bias re-based every 1024 columns.
  *
  *   4. no copies, no waits.  The column body is straight-line code over NR rows (template parameter: 24 = the length of
- *      almost every Porechop adapter and barcode, exact; 32 = any shorter-or-equal adapter, top-aligned, the rows below the
- *      adapter compute harmless garbage), so ptxas updates the DP registers in place; read bases are fetched four columns
+ *      almost every Porechop adapter and barcode, exact; 24 / 32 / 40 / 52 = any shorter-or-equal adapter, bottom-aligned, the
+ *      rows above the adapter being exact copies of DP row 0), so ptxas updates the DP registers in place; read bases are fetched four columns
  *      at a time, one group ahead of their use, so that no column waits on a global load.
  *
  * One thread = two tasks (the halves of each 32-bit register), one warp = 64 tasks sharing an adapter, as in pcb_kernels.cu.
@@ -143,10 +143,10 @@ constexpr int TP = 25;
 // updated in place.  rowTp / rowT: biased M(0, j-1) / M(0, j).  tp = tbl + p of this column.  The diagonal term of the
 // NEXT row (old Mo[r] + score) is formed before Mo[r] is overwritten.  Per row: LDS, IADD, VIADDMNMX (H),
 // VIADDMNMX (V), VIMNMX3 (M).  Recurrence: seqan/align/dp_formula_affine.h:65-124.
-// Ml / Vl / Hlast: M, V, H of the adapter's last row (row nm1; with EXACT that is row NR-1).
+// Ml / Vl / Hlast: M, V, H of the adapter's last row = register row NR-1 (adapters are bottom-aligned, see k_fast).
 template <int NR, bool EXACT>
 __device__ __forceinline__ void col_score(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *tp,
-                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, int nm1, uint32_t &Ml)
+                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, uint32_t &Ml)
 {
     uint32_t Dn = rowTp + tp[0];
     uint32_t Vu = rowT;                              // V(1, j) = M(0, j) + gapOpen  (row 0: V = -inf)
@@ -157,9 +157,8 @@ __device__ __forceinline__ void col_score(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR]
         const uint32_t D = Dn;
         if (r < NR - 1) Dn = Mo[r] + tp[(r + 1) * TP];
         Mo[r] = __vimax3_s16x2(D, Vu, Hn); Hl[r] = Hn;
-        if (!EXACT && r == nm1) Ml = Mo[r];
     }
-    if (EXACT) Ml = Mo[NR - 1];
+    Ml = Mo[NR - 1];
 }
 
 // The same column with trace flags (pass 2).  Flag bits of row r, half h, in flag word r >> 2 with q = r & 3:
@@ -170,7 +169,7 @@ __device__ __forceinline__ void col_score(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR]
 // column, stride PCB_BLOCK.
 template <int NR, bool EXACT>
 __device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *tp,
-                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, int nm1, uint32_t *fp,
+                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, uint32_t *fp,
                                           uint32_t &Ml, uint32_t &Vl, uint32_t &Hlast)
 {
     uint32_t Dn = rowTp + tp[0];
@@ -191,9 +190,8 @@ __device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR]
         if ((r & 3) == 3 || r == NR - 1) fp[(r >> 2) * PCB_BLOCK] = Wacc;
         if (r < NR - 1) Dn = Mo[r] + tp[(r + 1) * TP];
         Vu = Vn; Mo[r] = __vmaxs2(D, G); Hl[r] = Hn;
-        if (!EXACT && r == nm1) { Ml = Mo[r]; Vl = Vn; Hlast = Hn; }
     }
-    if (EXACT) { Ml = Mo[NR - 1]; Vl = Vu; Hlast = Hl[NR - 1]; }
+    Ml = Mo[NR - 1]; Vl = Vu; Hlast = Hl[NR - 1];
 }
 
 // Four consecutive sequence bytes starting at seq[pos] (pos clamped to lim) come from two aligned words; the funnel shift
@@ -214,10 +212,10 @@ __device__ __forceinline__ uint32_t pair_index(uint32_t c8_0, uint32_t c8_1) { r
 // it; the block's read bases sit behind the C*FW flag words.  State 0 = M, 1 = V, 2 = H.  In state M a cell whose diagonal
 // flag is off hands over to V or H and that state's step is taken at once, from the same cell's flags, as SeqAn does.
 template <int FW, int C>
-__device__ __forceinline__ void walk_step(const uint32_t *s_fl, const uint32_t *s_code, const int h, const int base,
+__device__ __forceinline__ void walk_step(const uint32_t *s_fl, const uint32_t *s_code, const int h, const int base, const int r0,
                                           int &i, int &j, int &s, WalkAcc &a)
 {
-    const int ar = i - 1, jc = j - base - 1;
+    const int ar = r0 + i - 1, jc = j - base - 1;         // register row of adapter row i
     const uint32_t f = s_fl[(jc * FW + (ar >> 2)) * PCB_BLOCK] >> (8 * h + 2 * (ar & 3));
     const bool fh = f & 1u, fg = f & 2u, fv = f & 0x10000u, fd = f & 0x20000u;
     if (s == 0 && fd) {
@@ -303,15 +301,19 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             }
             continue;
         }
-        const int nm1 = n - 1;
+        // The adapter is bottom-aligned in the NR register rows: adapter row i lives in register row r0 + i - 1 and the
+        // last adapter row is always row NR-1.  The r0 rows above it score 0 against every base, which makes each of them
+        // an exact copy of DP row 0 (M = 0 by the diagonal, H and V never above gapOpen), so adapter row 1 sees the same
+        // neighbours as under row 0 itself and no row of the column loop needs a bounds test.
+        const int r0 = EXACT ? 0 : NR - n;
         if (adapter != tbl_adapter) {
             __syncwarp();
-            for (int i = lane; i < NR; i += 32) s_code[i] = i < n ? (uint32_t)(L.ad.codes[aoff + i] / PCB_CODE_SCALE) : 0u;
+            for (int i = lane; i < NR; i += 32) s_code[i] = i >= r0 ? (uint32_t)(L.ad.codes[aoff + i - r0] / PCB_CODE_SCALE) : 0u;
             __syncwarp();
             for (int e = lane; e < NR * TP; e += 32) {
                 const int r = e / TP, p = e - r * TP;
                 const uint32_t a = s_code[r], c0 = (uint32_t)(p / 5), c1 = (uint32_t)(p % 5);
-                tbl[e] = pk(c0 == a ? s_match : s_mis, c1 == a ? s_match : s_mis);
+                tbl[e] = r >= r0 ? pk(c0 == a ? s_match : s_mis, c1 == a ? s_match : s_mis) : pk(2 * b, 2 * b);
             }
             __syncwarp();
             tbl_adapter = adapter;
@@ -345,7 +347,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
 #pragma unroll
         for (int r = 0; r < NR; ++r) { Mo[r] = pk2(B0 + b * (r + 1)); Hl[r] = 0; }   // column 0: M = 0, H = -inf
         uint32_t rowT = pk2(B0);                                 // biased M(0, j) = bias of row 0 at the current column
-        const uint32_t candK = pk2(OFF - b * n);                 // candidate = M(n, j) + candK - rowT = score + OFF
+        const uint32_t candK = pk2(OFF - b * NR);                // candidate = M(n, j) + candK - rowT = score + OFF
         uint32_t *ckp = ck;
         int ckc = 0;                                             // columns since the last checkpoint
         Raw4 nx0 = load4(seq0, 0, lim0), nx1 = load4(seq1, 0, lim1);
@@ -356,7 +358,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             const uint32_t rowTp = rowT;
             rowT += Bp;
             uint32_t Ml;
-            col_score<NR, EXACT>(Mo, Hl, tp, rowTp, rowT, GEB, nm1, Ml);
+            col_score<NR, EXACT>(Mo, Hl, tp, rowTp, rowT, GEB, Ml);
             uint32_t cand = Ml + candK - rowT;                    // scout, row class: strict '>' in visiting order (dp_scout.h:167-180)
             if (general)
                 cand &= ((j >= lo0 && j <= hi0) ? 0x0000FFFFu : 0u) | ((j >= lo1 && j <= hi1) ? 0xFFFF0000u : 0u);
@@ -375,9 +377,9 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
                     for (int h = 0; h < 2; ++h) {
                         if (!(h ? d1 : d0)) continue;
                         const int forced = tk[h].forced, len = tk[h].len;
-                        int Tn = half16(rowT, h), Vp = 0, Mp = Tn, best = 0, bi = 0, be = 0;
+                        int Tn = half16(rowT, h) + b * r0, Vp = 0, Mp = Tn, best = 0, bi = 0, be = 0;     // the row above adapter row 1
                         for (int i = 1; i <= n; ++i) {
-                            const int M = half16(s_fl[(2 * (i - 1)) * PCB_BLOCK], h), H = half16(s_fl[(2 * (i - 1) + 1) * PCB_BLOCK], h);
+                            const int M = half16(s_fl[(2 * (r0 + i - 1)) * PCB_BLOCK], h), H = half16(s_fl[(2 * (r0 + i - 1) + 1) * PCB_BLOCK], h);
                             const int V = max(Vp + geb, Mp);
                             Tn += b;
                             const int c = M + OFF - Tn;
@@ -505,7 +507,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
                 const uint32_t rowTp = rT;
                 rT += Bp;
                 uint32_t Ml, Vl, Hlast;
-                col_flags<NR, EXACT>(Mo, Hl, tp, rowTp, rT, GEB, nm1, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
+                col_flags<NR, EXACT>(Mo, Hl, tp, rowTp, rT, GEB, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
                 if (iter == 0) {
                     // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
                     // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
@@ -522,8 +524,8 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
                 WalkAcc a0 = acc[0], a1 = acc[1];
                 bool act0 = !done[0] && i0 > 0 && j0 > jb0, act1 = !done[1] && i1 > 0 && j1 > jb1;
                 while (act0 || act1) {
-                    if (act0) { walk_step<FW, C>(s_fl, s_code, 0, jb0, i0, j0, s0, a0); act0 = i0 > 0 && j0 > jb0; }
-                    if (act1) { walk_step<FW, C>(s_fl, s_code, 1, jb1, i1, j1, s1, a1); act1 = i1 > 0 && j1 > jb1; }
+                    if (act0) { walk_step<FW, C>(s_fl, s_code, 0, jb0, r0, i0, j0, s0, a0); act0 = i0 > 0 && j0 > jb0; }
+                    if (act1) { walk_step<FW, C>(s_fl, s_code, 1, jb1, r0, i1, j1, s1, a1); act1 = i1 > 0 && j1 > jb1; }
                 }
                 ci[0] = i0; cj[0] = j0; state[0] = s0; acc[0] = a0;
                 ci[1] = i1; cj[1] = j1; state[1] = s1; acc[1] = a1;
