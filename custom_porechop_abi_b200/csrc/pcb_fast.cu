@@ -40,12 +40,18 @@ namespace {
 #ifdef PCF_FORCE_MINB
 #define PCF_MINB(TRACE, NR) PCF_FORCE_MINB
 #else
-#define PCF_MINB(TRACE, NR) ((TRACE) ? ((NR) <= 24 ? 4 : ((NR) <= 32 ? 3 : 2)) : ((NR) <= 32 ? 4 : ((NR) <= 40 ? 3 : 2)))
+// measured on B200 (scripts/exp/kbench.py, phases.py): the kernels issue integer instructions at the pipes' limit with 2-3
+// CTAs per SM already; a larger register budget (no spills, fewer register moves) beats more resident warps
+#define PCF_MINB(TRACE, NR) (((TRACE) && (NR) <= 24) ? 3 : 2)
 #endif
 #ifndef PCF_UNROLL
-#define PCF_UNROLL 4
+#define PCF_UNROLL 2
 #endif
 constexpr int UNR = PCF_UNROLL;
+#ifndef PCF_UNROLL2
+#define PCF_UNROLL2 1
+#endif
+constexpr int UNR2 = PCF_UNROLL2;
 constexpr int RT = PCB_RT;            // 32 adapter rows in registers
 constexpr int B0 = 64;                // base bias: keeps every stored value > 0
 constexpr int OFF = 2048;             // offset of un-biased scores in the best-cell comparison (true score + OFF > 0)
@@ -497,6 +503,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
                 }
             }
             uint32_t rT = pk(B0 + b * jb0, B0 + b * jb1);
+#pragma unroll UNR2
             for (int t = 1; t <= tmax; ++t) {
                 const uint32_t *tp = tbl + pair_index(q0[0] & 0xFFu, q1[0] & 0xFFu);
 #pragma unroll

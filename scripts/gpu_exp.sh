@@ -6,6 +6,6 @@ mkdir -p gpurun_out
 make -C oracle libporechop_oracle.so > /dev/null
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_$TAG.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/pytest_$TAG.log
 ( echo "== main"; timeout 300 python scripts/exp/kbench.py 16384
-  for so in scratch_dbg/*.so; do [ -f "$so" ] && { echo "== $so"; PCB_SO=$PWD/$so timeout 300 python scripts/exp/kbench.py 16384; }; done
+  for so in scratch_dbg/*.so; do [ -f "$so" ] && { echo "== $so"; PCB_SO=$PWD/$so timeout 300 python scripts/exp/kbench.py 16384; PCB_SO=$PWD/$so timeout 300 python scripts/exp/phases.py 32768 | head -3; }; done
   echo "== phases"; timeout 600 python scripts/exp/phases.py 32768 ) > gpurun_out/exp_$TAG.log 2>&1
 cat gpurun_out/exp_$TAG.log
