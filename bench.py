@@ -373,6 +373,10 @@ def run_gpu_arm(args):
 
 
 def main():
+    # the contract is ONE JSON line on stdout: libraries that print there (NCCL's version banner ...) go to stderr instead
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, 'w')
     args = parse_args()
     if args.impl == 'reference':
         run_reference_arm(args)
