@@ -1,0 +1,102 @@
+#!/usr/bin/env python3
+"""
+Generates tests/golden/phases_golden.json with the REFERENCE ITSELF: the reference's own Python
+(porechop_abi/porechop_abi.py: find_matching_adapter_sets, find_adapters_at_read_ends,
+find_adapters_in_read_middles, driving nanopore_read.NanoporeRead) on top of the reference's own C++ library
+(oracle/_ref/cpp_functions_ref.so, built by oracle/Makefile), run single-threaded on the reference's own test reads.
+The package is imported from a scratch copy (the reference tree is read-only and has no built library); nothing of
+it is copied into the repo -- only inputs (reads, adapter sets) and the resulting per-read / per-set state, as JSON.
+Run in the build container only:  python tests/golden/make_phase_golden.py
+"""
+import json
+import os
+import shutil
+import sys
+import tempfile
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = '/root/reference'
+REF_SO = os.path.join(ROOT, 'oracle', '_ref', 'cpp_functions_ref.so')
+
+DEFAULTS = dict(end_size=150, scoring=[3, -6, -5, -2], adapter_threshold=90.0, end_threshold=75.0, extra_end_trim=2,
+                min_trim_size=4, middle_threshold=90.0, good_side=10, bad_side=100, barcode_threshold=75.0,
+                barcode_diff=5.0)
+
+
+def load_fastq(path):
+    out = []
+    lines = open(path).read().split('\n')
+    for i in range(0, len(lines) - 3, 4):
+        out.append((lines[i][1:], lines[i + 1].strip(), lines[i + 3].strip()))
+    return out
+
+
+def adapter_dict(a):
+    return {'name': a.name, 'start_sequence': list(a.start_sequence) if a.start_sequence else None,
+            'end_sequence': list(a.end_sequence) if a.end_sequence else None}
+
+
+def main():
+    tmp = tempfile.mkdtemp(prefix='pc_ref_')
+    shutil.copytree(os.path.join(REF, 'porechop_abi'), os.path.join(tmp, 'porechop_abi'),
+                    ignore=shutil.ignore_patterns('include', 'src', '*.so', '__pycache__'))
+    shutil.copy(REF_SO, os.path.join(tmp, 'porechop_abi', 'cpp_functions.so'))
+    sys.path.insert(0, tmp)
+    import warnings
+    warnings.simplefilter('ignore')
+    from porechop_abi import porechop_abi as pc
+    from porechop_abi import adapters as ad
+    from porechop_abi.nanopore_read import NanoporeRead
+
+    devnull = open(os.devnull, 'w')
+    P = DEFAULTS
+    cases = []
+    for fastq, check_barcodes, variants in (
+            ('test_one_adapter_set.fastq', False, [dict(), dict(min_trim_size=7, end_size=100), dict(middle_threshold=80.0, extra_end_trim=0)]),
+            ('test_two_adapter_sets.fastq', False, [dict()]),
+            ('test_barcodes.fastq', True, [dict(), dict(require_two=True)])):
+        for var in variants:
+            p = dict(P); p.update({k: v for k, v in var.items() if k != 'require_two'})
+            require_two = var.get('require_two', False)
+            records = load_fastq(os.path.join(REF, 'test', fastq))
+            reads = [NanoporeRead(n, s, q) for n, s, q in records]
+            for a in ad.ADAPTERS:                          # the reference keeps scores on module-level objects
+                a.best_start_score, a.best_end_score = 0.0, 0.0
+            search = [a for a in ad.ADAPTERS if '(full sequence)' not in a.name]
+            matching = pc.find_matching_adapter_sets(reads, 0, p['end_size'], p['scoring'], devnull, p['adapter_threshold'], 1)
+            phase_a = {'best': [[a.best_start_score, a.best_end_score] for a in search],
+                       'matching': [a.name for a in matching]}
+            # the reference's own order between the phases (porechop_abi.py:78-88)
+            matching = pc.fix_up_1d2_sets(matching)
+            forward_or_reverse = pc.choose_barcoding_kit(matching, 0, devnull) if check_barcodes else None
+            matching = pc.add_full_barcode_adapter_sets(matching)
+            pc.find_adapters_at_read_ends(reads, matching, 0, p['end_size'], p['extra_end_trim'], p['end_threshold'],
+                                          p['scoring'], devnull, p['min_trim_size'], 1, check_barcodes,
+                                          p['barcode_threshold'], p['barcode_diff'], require_two, forward_or_reverse)
+            phase_b = [{'start_trim_amount': r.start_trim_amount, 'end_trim_amount': r.end_trim_amount,
+                        'start_alignments': [[a.name, f, pa, s, e] for a, f, pa, s, e in r.start_adapter_alignments],
+                        'end_alignments': [[a.name, f, pa, s, e] for a, f, pa, s, e in r.end_adapter_alignments],
+                        'start_barcode_scores': r.start_barcode_scores, 'end_barcode_scores': r.end_barcode_scores,
+                        'barcode_call': r.barcode_call} for r in reads]
+            pc.find_adapters_in_read_middles(reads, matching, 0, p['middle_threshold'], p['good_side'], p['bad_side'],
+                                             p['scoring'], devnull, 1, False)
+            phase_c = [{'middle_adapter_positions': sorted(r.middle_adapter_positions),
+                        'middle_trim_positions': sorted(r.middle_trim_positions),
+                        'middle_hit_str': r.middle_hit_str} for r in reads]
+            cases.append({'fastq': fastq, 'params': p, 'check_barcodes': check_barcodes, 'require_two_barcodes': require_two,
+                          'forward_or_reverse': forward_or_reverse,
+                          'reads': [[n, s] for n, s, _ in records],
+                          'search_adapters': [adapter_dict(a) for a in search],
+                          'matching_used': [adapter_dict(a) for a in matching],
+                          'phase_a': phase_a, 'phase_b': phase_b, 'phase_c': phase_c})
+    out = os.path.join(HERE, 'phases_golden.json')
+    with open(out, 'w') as f:
+        json.dump({'generator': 'tests/golden/make_phase_golden.py', 'cases': cases}, f, separators=(',', ':'))
+    shutil.rmtree(tmp)
+    n_hits = sum(len(r['middle_adapter_positions']) > 0 for c in cases for r in c['phase_c'])
+    print('wrote %s: %d cases, %d reads with middle hits, %.0f KB' % (out, len(cases), n_hits, os.path.getsize(out) / 1e3))
+
+
+if __name__ == '__main__':
+    main()

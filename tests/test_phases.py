@@ -1,0 +1,148 @@
+"""The batched phase functions (custom_porechop_abi_b200/porechop_batch.py) against the state the reference's own
+Python + C++ left on its reads and adapter sets (tests/golden/phases_golden.json, made by make_phase_golden.py).
+CPU: the host logic over a stand-in engine that answers with the oracle.  GPU: the same through the CUDA library."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle_lib import oracle_align
+
+GOLDEN = os.path.join(os.path.dirname(__file__), 'golden', 'phases_golden.json')
+
+
+class Read(object):
+    """The attributes of the reference's NanoporeRead that the three phases touch (nanopore_read.py:32-75)."""
+
+    def __init__(self, name, seq):
+        self.name = name
+        self.seq = seq.upper()
+        if self.seq.count('U') > self.seq.count('T'):
+            self.seq = self.seq.replace('U', 'T')
+        self.start_trim_amount = 0
+        self.end_trim_amount = 0
+        self.start_adapter_alignments = []
+        self.end_adapter_alignments = []
+        self.middle_adapter_positions = set()
+        self.middle_trim_positions = set()
+        self.middle_hit_str = ''
+        self.start_barcode_scores = {}
+        self.end_barcode_scores = {}
+
+    def get_seq_with_start_end_adapters_trimmed(self):
+        if not self.start_trim_amount and not self.end_trim_amount:
+            return self.seq
+        return self.seq[self.start_trim_amount:len(self.seq) - self.end_trim_amount]
+
+    def determine_barcode(self, *args):
+        pass                                    # pure host logic of the reference, not on the alignment path
+
+
+class AdapterSet(object):
+    """The attributes of the reference's Adapter (adapters.py:18-53) the phases touch."""
+
+    def __init__(self, d):
+        self.name = d['name']
+        self.start_sequence = tuple(d['start_sequence']) if d['start_sequence'] else None
+        self.end_sequence = tuple(d['end_sequence']) if d['end_sequence'] else None
+        self.best_start_score, self.best_end_score = 0.0, 0.0
+
+    def best_start_or_end_score(self):
+        return max(self.best_start_score, self.best_end_score)
+
+    def is_barcode(self):
+        return self.name.startswith('Barcode ')
+
+    def barcode_direction(self):
+        return 'reverse' if '_rev' in self.start_sequence[0] else 'forward'
+
+    def get_barcode_name(self):
+        names = [self.name] + ([self.start_sequence[0]] if self.start_sequence else []) + \
+            ([self.end_sequence[0]] if self.end_sequence else [])
+        return sorted(names, key=lambda x: len(x))[0].replace(' ', '_')
+
+
+class OracleEngine(object):
+    """Same calls as AlignmentEngine, answered by the CPU oracle (test infrastructure: checks the host logic only)."""
+
+    def __init__(self):
+        from custom_porechop_abi_b200.engine import RESULT_DTYPE
+        self.dtype = RESULT_DTYPE
+        self.scoring = (3, -6, -5, -2)
+        self.adapters = []
+
+    def set_scoring(self, vals):
+        self.scoring = tuple(int(v) for v in vals)
+
+    def set_adapters(self, seqs):
+        self.adapters = [s.encode() if isinstance(s, str) else bytes(s) for s in seqs]
+
+    def _one(self, seq, aid):
+        o = oracle_align(seq, self.adapters[aid], self.scoring)
+        return (o.read_start, o.read_end, o.adapter_start, o.adapter_end, o.raw_score, o.full_matches, o.aligned_len, o.full_len)
+
+    def align_windows(self, buf, lens, ids):
+        out = np.empty((len(lens), len(ids)), dtype=self.dtype)
+        for i in range(len(lens)):
+            w = bytes(buf[i, :lens[i]])
+            for k, aid in enumerate(ids):
+                out[i, k] = self._one(w, int(aid))
+        return out
+
+    def align_tasks(self, blob, seg_off, seg_len, seg_ad):
+        out = np.empty(len(seg_ad), dtype=self.dtype)
+        for t in range(len(seg_ad)):
+            out[t] = self._one(bytes(blob[seg_off[t]:seg_off[t] + seg_len[t]]), int(seg_ad[t]))
+        return out
+
+
+def cases():
+    with open(GOLDEN) as f:
+        return json.load(f)['cases']
+
+
+def run_case(c, eng):
+    from custom_porechop_abi_b200 import porechop_batch as pb
+    p = c['params']
+    reads = [Read(n, s) for n, s in c['reads']]
+    search = [AdapterSet(d) for d in c['search_adapters']]
+    # phase A
+    matching = pb.find_matching_adapter_sets(reads, 0, p['end_size'], p['scoring'], None, p['adapter_threshold'], 1, search, engine=eng)
+    assert [[a.best_start_score, a.best_end_score] for a in search] == c['phase_a']['best']
+    assert [a.name for a in matching] == c['phase_a']['matching']
+    # phases B and C on the sets the reference went on with (its 1D^2 / full-barcode rewrites are host logic)
+    used = [AdapterSet(d) for d in c['matching_used']]
+    pb.find_adapters_at_read_ends(reads, used, 0, p['end_size'], p['extra_end_trim'], p['end_threshold'], p['scoring'], None,
+                                  p['min_trim_size'], 1, c['check_barcodes'], p['barcode_threshold'], p['barcode_diff'],
+                                  c['require_two_barcodes'], c['forward_or_reverse'], engine=eng)
+    for r, g in zip(reads, c['phase_b']):
+        assert r.start_trim_amount == g['start_trim_amount'] and r.end_trim_amount == g['end_trim_amount'], r.name
+        assert [[a.name, f, pa, s, e] for a, f, pa, s, e in r.start_adapter_alignments] == g['start_alignments'], r.name
+        assert [[a.name, f, pa, s, e] for a, f, pa, s, e in r.end_adapter_alignments] == g['end_alignments'], r.name
+        assert r.start_barcode_scores == g['start_barcode_scores'] and r.end_barcode_scores == g['end_barcode_scores'], r.name
+    pb.find_adapters_in_read_middles(reads, used, 0, p['middle_threshold'], p['good_side'], p['bad_side'], p['scoring'], None, 1,
+                                     False, engine=eng)
+    for r, g in zip(reads, c['phase_c']):
+        assert sorted(r.middle_adapter_positions) == g['middle_adapter_positions'], r.name
+        assert sorted(r.middle_trim_positions) == g['middle_trim_positions'], r.name
+        assert r.middle_hit_str == g['middle_hit_str'], r.name
+
+
+def test_golden_has_hits():
+    cs = cases()
+    assert len(cs) >= 6
+    assert sum(len(r['middle_adapter_positions']) > 0 for c in cs for r in c['phase_c']) >= 10
+    assert sum(r['start_trim_amount'] > 0 for c in cs for r in c['phase_b']) >= 10
+    assert any(r['start_barcode_scores'] for c in cs for r in c['phase_b'])
+
+
+@pytest.mark.parametrize('idx', [0, 1, 2, 3, 4, 5])
+def test_phase_logic_with_oracle_engine(idx):
+    run_case(cases()[idx], OracleEngine())
+
+
+@pytest.mark.gpu
+def test_phases_on_gpu(engine):
+    for c in cases():
+        run_case(c, engine)
