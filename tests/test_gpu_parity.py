@@ -207,3 +207,44 @@ def test_pipelined_host_buffer_paths_equal_resident(engine):
     for t in rs.sample(range(len(ad)), 300):
         r = bytes(blob[seg_off[t]:seg_off[t] + seg_len[t]])
         assert rec_matches_oracle(pieced[t], oracle_align(r, adapters[ad[t]], DEFAULT)), t
+
+
+def test_ultra_long_reads_and_barcode_sets(engine):
+    """BASELINE configs[3] and [4] in miniature: 50-200 kb reads through the chunked scan (dozens of chunks per read,
+    hits planted near chunk boundaries and at both read ends), and a 96-barcode set (forward + reverse, 24-mers with
+    flanks of 20-40 bases -> kernel classes 2-4) against end windows, all against the oracle."""
+    from oracle_lib import mutate
+    rng = random.Random(31)
+    ad = ['AATGTACTTCGTTCAGTTACGTATTGCT', 'GCAATACGTAACTGAACGAAGT', 'ACTTGCCTGTCGCTCTATCTTC',
+          'GGCGTCTGCTTGGGTGTTTAACCTTTTTTTTTTAATGTACTTCGTTCAGTTACGTATTGCT'[:50]]
+    pairs = []
+    for m in (50000, 81234, 120000, 200000):
+        r = [rng.choice('ACGT') for _ in range(m)]
+        for aid, a in enumerate(ad):
+            for p in (0, 4096 - 10, 8192 + 3, m // 2, m - len(a) - 1, m - 9):
+                if rng.random() < 0.5:
+                    ins = mutate(rng, a, rng.choice([0, 0.05, 0.12]))
+                    r[p:p + len(ins)] = list(ins)[:max(0, m - p)]
+        r = ''.join(r)[:m]
+        for aid in range(len(ad)):
+            pairs.append((r, aid))
+    _check_pairs(engine, pairs, ad, DEFAULT)
+    # barcodes
+    bar = [''.join(rng.choice('ACGT') for _ in range(24)) for _ in range(48)]
+    comp = {'A': 'T', 'C': 'G', 'G': 'C', 'T': 'A'}
+    seqs = bar + [''.join(comp[c] for c in reversed(b)) for b in bar]
+    seqs += [''.join(rng.choice('ACGT') for _ in range(k)) + b + ''.join(rng.choice('ACGT') for _ in range(8)) for b, k in zip(bar[:12], (4, 8, 12, 16, 20, 4, 8, 12, 16, 20, 3, 9))]
+    windows = []
+    for _ in range(400):
+        w = ''.join(rng.choice('ACGT') for _ in range(150))
+        b = rng.choice(seqs)
+        p = rng.randrange(0, 110)
+        w = (w[:p] + mutate(rng, b, rng.choice([0, 0.08, 0.2])) + w[p:])[:150]
+        windows.append(w)
+    engine.set_scoring(DEFAULT)
+    engine.set_adapters(seqs)
+    buf, lens = engine.pack_windows(windows, stride=160)
+    out = engine.align_windows(buf, lens, list(range(len(seqs))))
+    for w in range(0, len(windows), 3):
+        for k in range(len(seqs)):
+            assert rec_matches_oracle(out[w, k], oracle_align(windows[w], seqs[k], DEFAULT)), (windows[w], seqs[k])
