@@ -64,6 +64,9 @@ C_LIB.pcb_set_scoring.argtypes = [_P, c_int, c_int, c_int, c_int]
 C_LIB.pcb_set_adapters.argtypes = [_P, c_char_p, POINTER(c_int64), c_int32]
 C_LIB.pcb_align_windows.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, c_void_p]
 C_LIB.pcb_align_tasks.argtypes = [_P, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
+C_LIB.pcb_upload_reads.argtypes = [_P, c_void_p, c_int64]
+C_LIB.pcb_set_deferred.argtypes = [_P, c_int]
+C_LIB.pcb_wait.argtypes = [_P]
 C_LIB.pcb_stage_windows.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p]
 C_LIB.pcb_stage_ids.argtypes = [_P, c_void_p, c_int32]
 C_LIB.pcb_run_windows_resident.argtypes = [_P]

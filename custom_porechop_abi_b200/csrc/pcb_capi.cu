@@ -44,7 +44,14 @@ struct DevBuf {
 struct pcb_context {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaStream_t cstream = nullptr;       // copies that run beside the kernels of `stream`
+    cudaStream_t cstream = nullptr;       // result copies (D2H) that run beside the kernels of `stream`
+    cudaStream_t ustream = nullptr;       // read-blob uploads (H2D + encode) that run beside them
+    int64_t uploaded_len = -1;            // pcb_upload_reads announced a blob of this length
+    cudaStream_t pstream = nullptr;       // deferred mode: task staging + planning, beside the kernels of earlier calls
+    cudaEvent_t tasks_done = nullptr;     // the task kernels of the last run no longer read the plan / segment arrays
+    bool deferred = false;                // pcb_set_deferred: host-buffer calls only enqueue; pcb_wait collects
+    cudaStream_t in_stream() const { return deferred ? ustream : stream; }     // window / id staging copies
+    cudaStream_t plan_stream() const { return deferred ? pstream : stream; }   // segment copies + planner kernels
     cudaEvent_t pipe_ev[8] = {};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, kev0 = nullptr, kev1 = nullptr;
     std::string err;
@@ -58,12 +65,15 @@ struct pcb_context {
     DevBuf<int64_t> d_ad_off;
     // staged inputs
     DevBuf<char> d_ascii;
+    DevBuf<char> d_ascii_t;           // ASCII staging of the read blob (its own buffer: uploads run beside window staging)
     DevBuf<uint8_t> d_arena_t;        // explicit-task arena (kept apart so both inputs can stay resident)
     uint64_t arena_t_len = 0;
     // staged window sets + their results: a context holds PCB_SLOTS independent sets so that several inputs
     // (start windows, end windows, full-length tasks) can be resident at once; pcb_select_slot picks one
     struct Slot {
         DevBuf<uint8_t> d_arena;          // window arena
+        DevBuf<char> d_ascii;             // its ASCII staging (per slot: in deferred mode the next call's copy runs beside this one's kernels)
+        cudaEvent_t staged = nullptr;     // deferred mode: the slot's staging copies have arrived
         uint64_t arena_len = 0;
         int64_t sum_winlen = 0;
         DevBuf<int32_t> d_winlen, d_ids;      // d_ids: [fast ids | other ids | fast positions | other positions]
@@ -90,6 +100,7 @@ struct pcb_context {
         int64_t end_lo = -1, end_hi = 0;     // the piece of the blob this plan covers: tasks whose segment ends in (end_lo, end_hi]
         cudaEvent_t ready = nullptr;         // recorded on the copy stream once that piece is in the arena
         bool has_ready = false;
+        bool encoded = true;          // false: the ASCII of [b0, b1) has been sent but not yet turned into codes
         void release() { d_tasks.release(); d_units.release(); d_scan.release(); d_longs.release(); }
         struct Launch { bool trace; int cls, kind /*0 direct, 1 scan, 2 window*/; int64_t cells, task0, unit0, n_units; int mmax, nmax, smax, grid; };
         std::vector<Launch> launches;
@@ -150,6 +161,9 @@ extern "C" int pcb_create(int device, pcb_context **out)
     c->device = device;
     if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&c->cstream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&c->ustream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithPriority(&c->pstream, cudaStreamNonBlocking, -1)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&c->tasks_done, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
         (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
         g_global_err = std::string("context setup failed: ") + cudaGetErrorString(e);
@@ -157,6 +171,7 @@ extern "C" int pcb_create(int device, pcb_context **out)
         return PCB_ERR_CUDA;
     }
     for (auto &ev : c->pipe_ev) if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { g_global_err = "event creation failed"; delete c; return PCB_ERR_CUDA; }
+    for (auto &sl : c->slots) if (cudaEventCreateWithFlags(&sl.staged, cudaEventDisableTiming) != cudaSuccess) { g_global_err = "event creation failed"; delete c; return PCB_ERR_CUDA; }
     c->grid_trace = pcb_occupancy_grid(0);
     c->grid_scan = pcb_occupancy_grid(1);
     for (int cls = 0; cls < PCF_NCLS; ++cls) { c->grid_ftrace[cls] = pcf_occupancy_grid(true, cls); c->grid_fscan[cls] = pcf_occupancy_grid(false, cls); }
@@ -169,15 +184,18 @@ extern "C" void pcb_destroy(pcb_context *c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->cstream);
-    c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_arena_t.release();
-    for (auto &sl : c->slots) { sl.d_arena.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release(); }
+    cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->cstream); cudaStreamSynchronize(c->ustream); cudaStreamSynchronize(c->pstream);
+    c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_ascii_t.release(); c->d_arena_t.release();
+    for (auto &sl : c->slots) { sl.d_arena.release(); sl.d_ascii.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release(); if (sl.staged) cudaEventDestroy(sl.staged); }
     for (auto &pl : c->plans) { pl.release(); if (pl.ready) cudaEventDestroy(pl.ready); }
     c->d_seg_off.release(); c->d_plan_i64.release(); c->d_seg_len.release(); c->d_seg_ad.release(); c->d_plan_i32.release(); c->d_adinfo.release();
     c->d_scratch.release(); c->d_err.release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->kev0); cudaEventDestroy(c->kev1);
     for (auto &ev : c->pipe_ev) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(c->cstream);
+    cudaStreamDestroy(c->ustream);
+    cudaStreamDestroy(c->pstream);
+    if (c->tasks_done) cudaEventDestroy(c->tasks_done);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -325,13 +343,17 @@ extern "C" int pcb_stage_windows(pcb_context *c, const char *windows, int64_t n_
     }
     c->S().sum_winlen = sumlen;
     const uint64_t bytes = (uint64_t)n_windows * stride;
-    PCB_CUDA(c, c->d_ascii.reserve((size_t)bytes + 16));
+    PCB_CUDA(c, c->S().d_ascii.reserve((size_t)bytes + 16));
     PCB_CUDA(c, c->S().d_arena.reserve((size_t)bytes + 16));
     PCB_CUDA(c, c->S().d_winlen.reserve((size_t)n_windows + 1));
     if (bytes) {
-        PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, windows, bytes, cudaMemcpyHostToDevice, c->stream));
-        PCB_CUDA(c, cudaMemcpyAsync(c->S().d_winlen.p, win_len, sizeof(int32_t) * n_windows, cudaMemcpyHostToDevice, c->stream));
-        PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->S().d_arena.p, bytes, c->stream));
+        PCB_CUDA(c, cudaMemcpyAsync(c->S().d_ascii.p, windows, bytes, cudaMemcpyHostToDevice, c->in_stream()));
+        PCB_CUDA(c, cudaMemcpyAsync(c->S().d_winlen.p, win_len, sizeof(int32_t) * n_windows, cudaMemcpyHostToDevice, c->in_stream()));
+        if (c->deferred) {               // the copies run beside the kernels of earlier calls; the encode waits for them
+            PCB_CUDA(c, cudaEventRecord(c->S().staged, c->ustream));
+            PCB_CUDA(c, cudaStreamWaitEvent(c->stream, c->S().staged, 0));
+        }
+        PCB_CUDA(c, pcb_launch_encode(c->S().d_ascii.p, c->S().d_arena.p, bytes, c->stream));
         c->cnt.kernel_launches++;
     }
     // the kernels fetch bases a few bytes past a segment's end: keep valid codes there
@@ -355,6 +377,8 @@ extern "C" int pcb_stage_ids(pcb_context *c, const int32_t *ids, int32_t n_ids)
 
 // Splits the slot's id list by kernel class and uploads [ids of class 0 | class 1 | class 2 | their positions in the same
 // order] (position = index in the caller's list).
+static int send_pieces(pcb_context *c, int upto);
+
 static int split_ids(pcb_context *c, bool fast_ok)
 {
     pcb_context::Slot &S = c->S();
@@ -371,7 +395,13 @@ static int split_ids(pcb_context *c, bool fast_ok)
     for (int q = 0; q <= PCF_NCLS; ++q) S.h_split.insert(S.h_split.end(), pos[q].begin(), pos[q].end());
     PCB_CUDA(c, S.d_ids.reserve((size_t)2 * n + 1));
     // h_split lives in the slot until the next split, so the asynchronous copy may read it later
-    if (n) PCB_CUDA(c, cudaMemcpyAsync(S.d_ids.p, S.h_split.data(), sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, c->stream));
+    if (n) {
+        PCB_CUDA(c, cudaMemcpyAsync(S.d_ids.p, S.h_split.data(), sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, c->in_stream()));
+        if (c->deferred) {
+            PCB_CUDA(c, cudaEventRecord(S.staged, c->ustream));
+            PCB_CUDA(c, cudaStreamWaitEvent(c->stream, S.staged, 0));
+        }
+    }
     c->cnt.h2d_bytes += (int64_t)sizeof(int32_t) * 2 * n;
     S.split_stamp = c->stamp;
     return PCB_OK;
@@ -390,7 +420,10 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
     int rc = split_ids(c, fast_ok);
     if (rc) return rc;
     PCB_CUDA(c, S.d_out.reserve((size_t)n_res));
-    PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
+    if (!c->deferred) PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
+    // an announced read blob (pcb_upload_reads) travels under this call's kernels: its pieces go out now, behind this
+    // call's own copies on the copy engine
+    if ((host_out || c->deferred) && c->uploaded_len >= 0 && c->pending_blob && (rc = send_pieces(c, c->pieces_sent + (c->n_pieces + 1) / 2))) return rc;
     const int n = S.n_ids;
     // classes in ascending order of work: the small launches first (their tails then overlap nothing bigger than
     // themselves), the biggest last (it is the one that is pipelined against the copies)
@@ -448,7 +481,7 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
     }
     if (host_out) {
         c->cnt.d2h_bytes += (int64_t)sizeof(pcb_result) * n_res;
-        PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
+        if (!c->deferred) PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
     }
     return PCB_OK;
 }
@@ -478,7 +511,7 @@ extern "C" int pcb_align_windows(pcb_context *c, const char *windows, int64_t n_
     if ((rc = pcb_stage_ids(c, adapter_ids, n_ids))) return rc;
     if (n_windows * (int64_t)n_ids > 0 && !out) return PCB_ERR_ARG;
     if ((rc = run_windows(c, out))) return rc;
-    return check_err_flag(c);
+    return c->deferred ? PCB_OK : check_err_flag(c);        // deferred: pcb_wait reports
 }
 
 extern "C" int pcb_timer_start(pcb_context *c) { if (!c) return PCB_ERR_ARG; cudaSetDevice(c->device); PCB_CUDA(c, cudaEventRecord(c->ev0, c->stream)); return PCB_OK; }
@@ -491,7 +524,13 @@ extern "C" int pcb_timer_stop(pcb_context *c, float *ms)
     PCB_CUDA(c, cudaEventElapsedTime(ms, c->ev0, c->ev1));
     return PCB_OK;
 }
-extern "C" int pcb_synchronize(pcb_context *c) { if (!c) return PCB_ERR_ARG; cudaSetDevice(c->device); PCB_CUDA(c, cudaStreamSynchronize(c->stream)); return PCB_OK; }
+extern "C" int pcb_synchronize(pcb_context *c)
+{
+    if (!c) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    for (cudaStream_t st : {c->pstream, c->ustream, c->stream, c->cstream}) PCB_CUDA(c, cudaStreamSynchronize(st));
+    return PCB_OK;
+}
 extern "C" int pcb_get_counters(pcb_context *c, pcb_counters *out) { if (!c || !out) return PCB_ERR_ARG; *out = c->cnt; return PCB_OK; }
 extern "C" int pcb_reset_counters(pcb_context *c) { if (!c) return PCB_ERR_ARG; memset(&c->cnt, 0, sizeof c->cnt); return PCB_OK; }
 extern "C" int pcb_set_kernel_timing(pcb_context *c, int on) { if (!c) return PCB_ERR_ARG; c->ktiming = on != 0; return PCB_OK; }
@@ -531,53 +570,41 @@ static int send_pieces(pcb_context *c, int upto)
     for (int p = c->pieces_sent; p < upto && p < c->n_pieces; ++p) {
         pcb_context::TaskPlan &P = c->plans[p];
         if (P.b1 > P.b0) {
-            PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p + P.b0, c->pending_blob + P.b0, (size_t)(P.b1 - P.b0), cudaMemcpyHostToDevice, c->cstream));
-            PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p + P.b0, c->d_arena_t.p + P.b0, (uint64_t)(P.b1 - P.b0), c->cstream));
-            c->cnt.kernel_launches++;
+            PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii_t.p + P.b0, c->pending_blob + P.b0, (size_t)(P.b1 - P.b0), cudaMemcpyHostToDevice, c->ustream));
         }
-        PCB_CUDA(c, cudaEventRecord(P.ready, c->cstream));
+        P.encoded = false;            // the encode runs on the main stream, ahead of the piece's kernels (pcb_run_tasks_resident)
+        PCB_CUDA(c, cudaEventRecord(P.ready, c->ustream));
         c->pieces_sent = p + 1;
     }
     if (c->pieces_sent >= c->n_pieces) c->pending_blob = nullptr;
     return PCB_OK;
 }
 
-// n_pieces > 1: the blob travels in pieces on the copy stream and each piece gets its own plan (the tasks whose segment
-// ends inside it), so that the kernels of piece p run while piece p + 1 is still on the PCIe bus.
-static int stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, const int64_t *seg_off,
-                       const int32_t *seg_len, const int32_t *task_adapter, int64_t n_tasks, int n_pieces)
+// The read blob of the explicit-task path.  n_pieces > 1: it travels in pieces on the upload stream and each piece gets
+// its own plan (the tasks whose segment ends inside it), so that the kernels of piece p run while piece p + 1 is still
+// on the PCIe bus.  Only piece 0 is sent here; the rest follows from send_pieces (after the plans exist, or pumped by
+// the window calls of the same step: small copies issued later would otherwise queue behind the whole blob).
+static int setup_blob(pcb_context *c, const char *seq_blob, int64_t blob_len, int n_pieces, int send_now)
 {
-    if (!c || blob_len < 0 || n_tasks < 0 || (n_tasks > 0 && (!seg_off || !seg_len || !task_adapter)) || (blob_len > 0 && !seq_blob))
-        return PCB_ERR_ARG;
-    cudaSetDevice(c->device);
     for (auto &pl : c->plans) pl.valid = false;
-    c->n_tasks = 0;
-    // copies first (asynchronous from pinned memory), so that the host-side checks below run under them
-    PCB_CUDA(c, c->d_ascii.reserve((size_t)blob_len + 16));
+    PCB_CUDA(c, c->d_ascii_t.reserve((size_t)blob_len + 16));
     PCB_CUDA(c, c->d_arena_t.reserve((size_t)blob_len + 16));
-    PCB_CUDA(c, c->d_seg_off.reserve((size_t)n_tasks + 1));
-    PCB_CUDA(c, c->d_seg_len.reserve((size_t)n_tasks + 1));
-    PCB_CUDA(c, c->d_seg_ad.reserve((size_t)n_tasks + 1));
-    if (n_tasks) {
-        PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_off.p, seg_off, sizeof(int64_t) * n_tasks, cudaMemcpyHostToDevice, c->stream));
-        PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_len.p, seg_len, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->stream));
-        PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_ad.p, task_adapter, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->stream));
-    }
     n_pieces = std::max(1, std::min<int>(n_pieces, pcb_context::MAX_PIECES));
     c->n_pieces = n_pieces;
     c->pending_blob = nullptr;
     PCB_CUDA(c, cudaMemsetAsync(c->d_arena_t.p + blob_len, 0, 16, c->stream));   // valid codes past the last segment
     if (n_pieces == 1) {
         if (blob_len) {
-            PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii.p, seq_blob, (size_t)blob_len, cudaMemcpyHostToDevice, c->stream));
-            PCB_CUDA(c, pcb_launch_encode(c->d_ascii.p, c->d_arena_t.p, (uint64_t)blob_len, c->stream));
+            PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii_t.p, seq_blob, (size_t)blob_len, cudaMemcpyHostToDevice, c->stream));
+            PCB_CUDA(c, pcb_launch_encode(c->d_ascii_t.p, c->d_arena_t.p, (uint64_t)blob_len, c->stream));
             c->cnt.kernel_launches++;
         }
-        c->plans[0].end_lo = -1; c->plans[0].end_hi = blob_len; c->plans[0].has_ready = false;
+        c->plans[0].b0 = 0; c->plans[0].b1 = blob_len;
+        c->plans[0].end_lo = -1; c->plans[0].end_hi = blob_len; c->plans[0].has_ready = false; c->plans[0].encoded = true;
     } else {
-        // the copy stream starts after whatever the main stream still does with the two staging buffers
+        // the upload stream starts after whatever the main stream still does with the arena
         PCB_CUDA(c, cudaEventRecord(c->pipe_ev[0], c->stream));
-        PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, c->pipe_ev[0], 0));
+        PCB_CUDA(c, cudaStreamWaitEvent(c->ustream, c->pipe_ev[0], 0));
         const int64_t per = ((blob_len + n_pieces - 1) / n_pieces + 15) & ~(int64_t)15;
         for (int p = 0; p < n_pieces; ++p) {
             pcb_context::TaskPlan &P = c->plans[p];
@@ -589,13 +616,33 @@ static int stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, c
         }
         c->pending_blob = seq_blob; c->pieces_sent = 0;
     }
-    { int rc0 = send_pieces(c, 1); if (rc0) return rc0; }      // piece 0 now; the rest once the plans are built
+    c->cnt.h2d_bytes += blob_len;
+    c->arena_t_len = (uint64_t)blob_len;
+    return send_pieces(c, send_now);
+}
+
+// The task list over the blob that setup_blob put (or is putting) into the arena.
+static int stage_segments(pcb_context *c, int64_t blob_len, const int64_t *seg_off, const int32_t *seg_len,
+                          const int32_t *task_adapter, int64_t n_tasks)
+{
+    for (auto &pl : c->plans) pl.valid = false;
+    c->n_tasks = 0;
+    PCB_CUDA(c, c->d_seg_off.reserve((size_t)n_tasks + 1));
+    PCB_CUDA(c, c->d_seg_len.reserve((size_t)n_tasks + 1));
+    PCB_CUDA(c, c->d_seg_ad.reserve((size_t)n_tasks + 1));
+    // deferred mode: the copies and the planner run on their own stream, beside the kernels of earlier calls
+    if (c->deferred) PCB_CUDA(c, cudaStreamWaitEvent(c->pstream, c->tasks_done, 0));
+    if (n_tasks) {          // asynchronous from pinned memory: the host-side checks below run under the copies
+        PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_off.p, seg_off, sizeof(int64_t) * n_tasks, cudaMemcpyHostToDevice, c->plan_stream()));
+        PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_len.p, seg_len, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->plan_stream()));
+        PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_ad.p, task_adapter, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->plan_stream()));
+    }
     int64_t long_cols = 0, cells = 0;
     for (int64_t t = 0; t < n_tasks; ++t) {
         const bool bad_seg = seg_len[t] < 0 || seg_off[t] < 0 || seg_off[t] + seg_len[t] > blob_len;
         const bool bad_ad = task_adapter[t] < 0 || task_adapter[t] >= c->n_adapters;
         if (bad_seg || bad_ad) {
-            cudaStreamSynchronize(c->stream);               // the caller's buffers are still being read
+            cudaStreamSynchronize(c->plan_stream());               // the caller's buffers are still being read
             if (bad_seg) return c->fail(PCB_ERR_ARG, "task %lld: segment [%lld, +%d) outside the blob", (long long)t, (long long)seg_off[t], seg_len[t]);
             return c->fail(PCB_ERR_ARG, "task %lld: adapter id %d out of range", (long long)t, task_adapter[t]);
         }
@@ -604,8 +651,38 @@ static int stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, c
     }
     c->n_tasks = n_tasks; c->task_long_cols = long_cols; c->task_cells = cells;
     c->cnt.h2d_bytes += 16 * n_tasks;
-    c->cnt.h2d_bytes += blob_len;
-    c->arena_t_len = (uint64_t)blob_len;
+    return PCB_OK;
+}
+
+static int blob_pieces(int64_t blob_len)
+{
+    const char *pm = getenv("PCB_PIECE_MIN_BYTES");           // tests lower it to reach the pieced path with small inputs
+    const int64_t piece_min = pm ? atoll(pm) : (64ll << 20);
+    return blob_len >= piece_min && blob_len >= 4096 ? pcb_context::MAX_PIECES : 1;
+}
+
+static int stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, const int64_t *seg_off,
+                       const int32_t *seg_len, const int32_t *task_adapter, int64_t n_tasks, int n_pieces)
+{
+    if (!c || blob_len < 0 || n_tasks < 0 || (n_tasks > 0 && (!seg_off || !seg_len || !task_adapter)) || (blob_len > 0 && !seq_blob))
+        return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    c->uploaded_len = -1;
+    int rc = setup_blob(c, seq_blob, blob_len, n_pieces, 1);
+    if (rc) return rc;
+    return stage_segments(c, blob_len, seg_off, seg_len, task_adapter, n_tasks);
+}
+
+extern "C" int pcb_upload_reads(pcb_context *c, const char *seq_blob, int64_t blob_len)
+{
+    if (!c || blob_len < 0 || (blob_len > 0 && !seq_blob)) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    c->n_tasks = 0;
+    // nothing is sent yet: the window calls that follow pump the pieces AFTER their own (small) copies, so that those
+    // do not wait behind the blob on the copy engine; pcb_align_tasks sends whatever is left
+    int rc = setup_blob(c, seq_blob, blob_len, blob_pieces(blob_len), 0);
+    if (rc) return rc;
+    c->uploaded_len = blob_len;
     return PCB_OK;
 }
 
@@ -649,17 +726,17 @@ static int build_task_plan(pcb_context *c, pcb_context::TaskPlan &P, bool first_
     PCB_CUDA(c, c->d_plan_i32.reserve(2 * nb + nm));
     PCB_CUDA(c, c->d_plan_i64.reserve(nb));
     PCB_CUDA(c, c->d_adinfo.reserve((size_t)A));
-    PCB_CUDA(c, cudaMemsetAsync(c->d_plan_i32.p, 0, sizeof(int32_t) * (2 * nb + nm), c->stream));
-    PCB_CUDA(c, cudaMemcpyAsync(c->d_adinfo.p, ad.data(), sizeof(PcbAdInfo) * A, cudaMemcpyHostToDevice, c->stream));
+    PCB_CUDA(c, cudaMemsetAsync(c->d_plan_i32.p, 0, sizeof(int32_t) * (2 * nb + nm), c->plan_stream()));
+    PCB_CUDA(c, cudaMemcpyAsync(c->d_adinfo.p, ad.data(), sizeof(PcbAdInfo) * A, cudaMemcpyHostToDevice, c->plan_stream()));
     PcbPlanArgs pa{};
     pa.seg_off = c->d_seg_off.p; pa.seg_len = c->d_seg_len.p; pa.seg_ad = c->d_seg_ad.p; pa.n_tasks = nt;
     pa.ad = c->d_adinfo.p; pa.n_adapters = A; pa.chunk = chunk; pa.end_lo = P.end_lo; pa.end_hi = P.end_hi;
     pa.count = c->d_plan_i32.p; pa.cursor = c->d_plan_i32.p + nb; pa.mmax = c->d_plan_i32.p + 2 * nb; pa.base = c->d_plan_i64.p;
-    PCB_CUDA(c, pcb_launch_plan(pa, false, c->stream));
+    PCB_CUDA(c, pcb_launch_plan(pa, false, c->plan_stream()));
     std::vector<int32_t> count(nb), mmax(nm);
-    PCB_CUDA(c, cudaMemcpyAsync(count.data(), pa.count, sizeof(int32_t) * nb, cudaMemcpyDeviceToHost, c->stream));
-    PCB_CUDA(c, cudaMemcpyAsync(mmax.data(), pa.mmax, sizeof(int32_t) * nm, cudaMemcpyDeviceToHost, c->stream));
-    PCB_CUDA(c, cudaStreamSynchronize(c->stream));
+    PCB_CUDA(c, cudaMemcpyAsync(count.data(), pa.count, sizeof(int32_t) * nb, cudaMemcpyDeviceToHost, c->plan_stream()));
+    PCB_CUDA(c, cudaMemcpyAsync(mmax.data(), pa.mmax, sizeof(int32_t) * nm, cudaMemcpyDeviceToHost, c->plan_stream()));
+    PCB_CUDA(c, cudaStreamSynchronize(c->plan_stream()));
     c->cnt.kernel_launches += 2;
 
     // layout: kind by kind, class by class (the launch order), adapter by adapter, bucket by bucket
@@ -726,15 +803,15 @@ static int build_task_plan(pcb_context *c, pcb_context::TaskPlan &P, bool first_
     PCB_CUDA(c, P.d_units.reserve(all_units.size() + 1));
     PCB_CUDA(c, P.d_longs.reserve((size_t)P.n_long + 1));
     PCB_CUDA(c, P.d_scan.reserve((size_t)P.n_chunks + 1));
-    PCB_CUDA(c, cudaMemcpyAsync(c->d_plan_i64.p, base.data(), sizeof(int64_t) * nb, cudaMemcpyHostToDevice, c->stream));
-    PCB_CUDA(c, cudaMemcpyAsync(P.d_units.p, all_units.data(), sizeof(PcbUnit) * all_units.size(), cudaMemcpyHostToDevice, c->stream));
+    PCB_CUDA(c, cudaMemcpyAsync(c->d_plan_i64.p, base.data(), sizeof(int64_t) * nb, cudaMemcpyHostToDevice, c->plan_stream()));
+    PCB_CUDA(c, cudaMemcpyAsync(P.d_units.p, all_units.data(), sizeof(PcbUnit) * all_units.size(), cudaMemcpyHostToDevice, c->plan_stream()));
     pa.tasks = P.d_tasks.p; pa.longs = P.d_longs.p;
-    PCB_CUDA(c, pcb_launch_plan(pa, true, c->stream));
+    PCB_CUDA(c, pcb_launch_plan(pa, true, c->plan_stream()));
     c->cnt.h2d_bytes += (int64_t)(sizeof(int64_t) * nb + sizeof(PcbUnit) * all_units.size() + sizeof(PcbAdInfo) * A);
     c->cnt.d2h_bytes += (int64_t)(sizeof(int32_t) * (nb + nm));
     cudaError_t e = c->d_scratch.reserve((size_t)P.scratch_words);
     if (e != cudaSuccess) { cudaGetLastError(); return c->fail(PCB_ERR_NOMEM, "scratch of %.1f MB: %s", P.scratch_words * 4 / 1e6, cudaGetErrorString(e)); }
-    PCB_CUDA(c, cudaStreamSynchronize(c->stream));       // the host vectors go out of scope
+    PCB_CUDA(c, cudaStreamSynchronize(c->plan_stream()));       // the host vectors go out of scope
     P.valid = true; P.stamp = c->stamp;
     return PCB_OK;
 }
@@ -754,10 +831,17 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
     uint64_t scratch = 0;
     for (int p = 0; p < c->n_pieces; ++p) scratch = std::max(scratch, c->plans[p].scratch_words);
     PCB_CUDA(c, c->d_scratch.reserve((size_t)scratch));
-    PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
+    if (!c->deferred) PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
     for (int p = 0; p < c->n_pieces; ++p) {
         pcb_context::TaskPlan &P = c->plans[p];
         if (P.has_ready) PCB_CUDA(c, cudaStreamWaitEvent(c->stream, P.ready, 0));     // this piece of the blob has arrived
+        if (!P.encoded) {
+            if (P.b1 > P.b0) {
+                PCB_CUDA(c, pcb_launch_encode(c->d_ascii_t.p + P.b0, c->d_arena_t.p + P.b0, (uint64_t)(P.b1 - P.b0), c->stream));
+                c->cnt.kernel_launches++;
+            }
+            P.encoded = true;
+        }
         bool merged = false;
         for (const auto &pl : P.launches) {
             if (pl.kind == 2 && !merged) {
@@ -772,6 +856,7 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
             if ((rc = launch_dp(c, L, pl.trace, pl.cells, pl.cls))) return rc;
         }
     }
+    PCB_CUDA(c, cudaEventRecord(c->tasks_done, c->stream));
     return PCB_OK;
 }
 
@@ -779,13 +864,46 @@ extern "C" int pcb_align_tasks(pcb_context *c, const char *seq_blob, int64_t blo
                                const int32_t *seg_len, const int32_t *task_adapter, int64_t n_tasks, pcb_result *out)
 {
     int rc;
-    // big blobs travel in pieces, each piece's kernels running under the next piece's copy
-    const char *pm = getenv("PCB_PIECE_MIN_BYTES");           // tests lower it to reach the pieced path with small inputs
-    const int64_t piece_min = pm ? atoll(pm) : (64ll << 20);
-    const int pieces = blob_len >= piece_min && blob_len >= 4096 ? pcb_context::MAX_PIECES : 1;
-    if ((rc = stage_tasks(c, seq_blob, blob_len, seg_off, seg_len, task_adapter, n_tasks, pieces))) return rc;
+    if (!seq_blob && c && c->uploaded_len >= 0) {
+        // the blob was announced with pcb_upload_reads and is in the arena, or on its way there
+        if (blob_len != c->uploaded_len) return c->fail(PCB_ERR_ARG, "blob_len %lld differs from the uploaded blob (%lld)", (long long)blob_len, (long long)c->uploaded_len);
+        if (n_tasks < 0 || (n_tasks > 0 && (!seg_off || !seg_len || !task_adapter))) return PCB_ERR_ARG;
+        cudaSetDevice(c->device);
+        if ((rc = stage_segments(c, blob_len, seg_off, seg_len, task_adapter, n_tasks))) return rc;
+    } else {
+        // big blobs travel in pieces, each piece's kernels running under the next piece's copy
+        if ((rc = stage_tasks(c, seq_blob, blob_len, seg_off, seg_len, task_adapter, n_tasks, blob_pieces(blob_len)))) return rc;
+    }
     if ((rc = pcb_run_tasks_resident(c))) return rc;
-    return pcb_fetch_results(c, out, n_tasks);
+    if (!c->deferred) return pcb_fetch_results(c, out, n_tasks);
+    if (n_tasks > 0 && !out) return PCB_ERR_ARG;
+    if (n_tasks) PCB_CUDA(c, cudaMemcpyAsync(out, c->S().d_out.p, sizeof(pcb_result) * n_tasks, cudaMemcpyDeviceToHost, c->stream));
+    c->cnt.d2h_bytes += (int64_t)sizeof(pcb_result) * n_tasks;
+    return PCB_OK;                      // pcb_wait reports
+}
+
+extern "C" int pcb_set_deferred(pcb_context *c, int on)
+{
+    if (!c) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    for (cudaStream_t st : {c->stream, c->cstream, c->ustream, c->pstream}) PCB_CUDA(c, cudaStreamSynchronize(st));
+    PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
+    PCB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->deferred = on != 0;
+    return PCB_OK;
+}
+
+extern "C" int pcb_wait(pcb_context *c)
+{
+    if (!c) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    for (cudaStream_t st : {c->pstream, c->ustream, c->stream, c->cstream}) PCB_CUDA(c, cudaStreamSynchronize(st));
+    int32_t f = 0;
+    PCB_CUDA(c, cudaMemcpyAsync(&f, c->d_err.p, sizeof f, cudaMemcpyDeviceToHost, c->stream));
+    PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
+    PCB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (f) return c->fail(PCB_ERR_RANGE, "device reported alignment-window violation (flag %d)", f);
+    return PCB_OK;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -9,6 +9,7 @@ printed from; ``identities()`` evaluates the two percent identities in double ex
 src/alignment.cpp:81,89 does, and ``to_align_adapter_tuple`` reproduces what nanopore_read.align_adapter
 returns from the string.
 """
+import contextlib
 import ctypes
 from ctypes import byref, c_float, c_void_p
 
@@ -98,6 +99,8 @@ class AlignmentEngine(object):
         out = np.empty((n, len(ids)), dtype=RESULT_DTYPE)
         self._check(w.C_LIB.pcb_align_windows(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids),
                                               _ptr(out)), 'pcb_align_windows')
+        if getattr(self, '_deferred', False):
+            self._held.append((win_buf, win_len, out))
         return out
 
     def stage_windows(self, win_buf, win_len, adapter_ids):
@@ -120,8 +123,30 @@ class AlignmentEngine(object):
         return out
 
     # -- explicit tasks (phase C and anything irregular) ------------------------------------------------
+    def upload_reads(self, blob):
+        """Announces the blob of a later align_tasks(None, ...): it travels to the GPU under the window calls made in
+        between (pcb_upload_reads).  The array is kept alive here until that call."""
+        blob = np.frombuffer(blob, dtype=np.uint8) if isinstance(blob, (bytes, bytearray)) else np.ascontiguousarray(blob, dtype=np.uint8)
+        self._check(w.C_LIB.pcb_upload_reads(self._h, _ptr(blob), blob.size), 'pcb_upload_reads')
+        self._uploaded = blob
+
     def align_tasks(self, blob, seg_off, seg_len, task_adapter):
-        """task t = blob[seg_off[t] : seg_off[t] + seg_len[t]] vs adapter task_adapter[t]; any length."""
+        """task t = blob[seg_off[t] : seg_off[t] + seg_len[t]] vs adapter task_adapter[t]; any length.
+        blob None: the blob announced with upload_reads."""
+        if blob is None:
+            if getattr(self, '_uploaded', None) is None:
+                raise w.AlignmentError('align_tasks(None, ...) without upload_reads')
+            held, self._uploaded = self._uploaded, None
+            seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+            seg_len = np.ascontiguousarray(seg_len, dtype=np.int32)
+            ad = np.ascontiguousarray(task_adapter, dtype=np.int32)
+            out = np.empty(len(ad), dtype=RESULT_DTYPE)
+            self._check(w.C_LIB.pcb_align_tasks(self._h, None, held.size, _ptr(seg_off), _ptr(seg_len), _ptr(ad),
+                                                len(ad), _ptr(out)), 'pcb_align_tasks')
+            if getattr(self, '_deferred', False):
+                self._held.append((held, seg_off, seg_len, ad, out))
+            return out
+        self._uploaded = None
         blob = np.frombuffer(blob, dtype=np.uint8) if isinstance(blob, (bytes, bytearray)) else np.ascontiguousarray(blob, dtype=np.uint8)
         seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
         seg_len = np.ascontiguousarray(seg_len, dtype=np.int32)
@@ -129,6 +154,8 @@ class AlignmentEngine(object):
         out = np.empty(len(ad), dtype=RESULT_DTYPE)
         self._check(w.C_LIB.pcb_align_tasks(self._h, _ptr(blob), blob.size, _ptr(seg_off), _ptr(seg_len), _ptr(ad),
                                             len(ad), _ptr(out)), 'pcb_align_tasks')
+        if getattr(self, '_deferred', False):
+            self._held.append((blob, seg_off, seg_len, ad, out))
         return out
 
     def stage_tasks(self, blob, seg_off, seg_len, task_adapter):
@@ -161,6 +188,29 @@ class AlignmentEngine(object):
         ms = c_float()
         self._check(w.C_LIB.pcb_timer_stop(self._h, byref(ms)), 'pcb_timer_stop')
         return ms.value
+
+    # -- submit / collect (pcb_set_deferred, pcb_wait) ----------------------------------------------------
+    def set_deferred(self, on):
+        self._check(w.C_LIB.pcb_set_deferred(self._h, 1 if on else 0), 'pcb_set_deferred')
+        self._deferred = bool(on)
+        self._held = []
+
+    def wait(self):
+        """Completes every queued call; the arrays the align_* calls returned are valid after it."""
+        try:
+            self._check(w.C_LIB.pcb_wait(self._h), 'pcb_wait')
+        finally:
+            self._held = []
+
+    @contextlib.contextmanager
+    def deferred(self):
+        """with eng.deferred(): a = eng.align_windows(...); b = eng.align_windows(...)   # a, b valid after the block"""
+        self.set_deferred(True)
+        try:
+            yield self
+            self.wait()
+        finally:
+            self.set_deferred(False)
 
     def synchronize(self):
         self._check(w.C_LIB.pcb_synchronize(self._h), 'pcb_synchronize')

@@ -89,6 +89,24 @@ int pcb_align_tasks(pcb_context *ctx, const char *seq_blob, int64_t blob_len,
                     const int64_t *seg_off, const int32_t *seg_len, const int32_t *task_adapter,
                     int64_t n_tasks, pcb_result *out);
 
+/* Announces the read blob of a later pcb_align_tasks call (the reference holds all reads in memory before the
+ * first alignment, porechop_abi.py:61-71, so the blob is known while phases A and B still run).  Returns at
+ * once; the pcb_align_windows calls that follow send the blob to the device, in pieces, under their own
+ * kernels.  The matching call is pcb_align_tasks(ctx, NULL, blob_len, ...): a NULL seq_blob means "the
+ * announced blob".  The host buffer (pinned, for the copies to overlap) must stay untouched until that call
+ * returns.  A pcb_align_tasks / pcb_stage_tasks call with its own blob cancels the announcement. */
+int pcb_upload_reads(pcb_context *ctx, const char *seq_blob, int64_t blob_len);
+
+/* Submit / collect.  The reference queues its alignments on a thread pool and collects them when the pool has
+ * drained (porechop_abi.py:225-231, :395-407, :489-499).  pcb_set_deferred(ctx, 1) gives the host-buffer calls the
+ * same shape: pcb_align_windows / pcb_align_tasks return once their copies and kernels are queued, so the copies of
+ * one call run under the kernels of the one before, and pcb_wait(ctx) returns when every queued call is complete,
+ * its results are in the callers' buffers, and reports the first device-side error of the batch.  Between two
+ * pcb_wait calls: input and output buffers stay untouched, every call uses its own slot (pcb_select_slot), and at
+ * most one pcb_align_tasks is queued.  pcb_set_deferred waits for queued work before it switches. */
+int pcb_set_deferred(pcb_context *ctx, int on);
+int pcb_wait(pcb_context *ctx);
+
 /* ---- 3. device-resident form (same kernels; used to time the kernels without PCIe) ---------- */
 
 /* A context holds 4 independent staging slots (inputs + results); all stage/run/fetch calls, and the host-buffer

@@ -73,3 +73,17 @@ for rep in range(3):
     timed('align_windows end', lambda: eng._check(w.C_LIB.pcb_align_windows(eng._h, _ptr(ebuf), n, 160, _ptr(wlen), _ptr(eid), len(eid), _ptr(out_e)), 'x'))
     eng.select_slot(2)
     timed('align_tasks', lambda: eng._check(w.C_LIB.pcb_align_tasks(eng._h, _ptr(blob), blob.size, _ptr(seg_off), _ptr(seg_len), _ptr(task_ad), len(task_ad), _ptr(out_m)), 'x'))
+def timed_ns(name, fn):
+    t0 = time.perf_counter(); r = fn()
+    print('   %-28s %8.2f ms (no sync)' % (name, (time.perf_counter() - t0) * 1e3), flush=True); return r
+for rep in range(3):
+    print('e2e announced rep', rep)
+    eng.synchronize(); t00 = time.perf_counter()
+    timed_ns('upload_reads', lambda: eng._check(w.C_LIB.pcb_upload_reads(eng._h, _ptr(blob), blob.size), 'x'))
+    eng.select_slot(0)
+    timed_ns('align_windows start', lambda: eng._check(w.C_LIB.pcb_align_windows(eng._h, _ptr(sbuf), n, 160, _ptr(wlen), _ptr(sid), len(sid), _ptr(out_s)), 'x'))
+    eng.select_slot(1)
+    timed_ns('align_windows end', lambda: eng._check(w.C_LIB.pcb_align_windows(eng._h, _ptr(ebuf), n, 160, _ptr(wlen), _ptr(eid), len(eid), _ptr(out_e)), 'x'))
+    eng.select_slot(2)
+    timed_ns('align_tasks (announced)', lambda: eng._check(w.C_LIB.pcb_align_tasks(eng._h, None, blob.size, _ptr(seg_off), _ptr(seg_len), _ptr(task_ad), len(task_ad), _ptr(out_m)), 'x'))
+    eng.synchronize(); print('   step total %8.2f ms' % ((time.perf_counter() - t00) * 1e3), flush=True)

@@ -203,6 +203,49 @@ def test_pipelined_host_buffer_paths_equal_resident(engine):
     finally:
         del os.environ['PCB_PIECE_MIN_BYTES']
     assert pieced.tobytes() == one.tobytes()
+    # announced blob (pcb_upload_reads): it travels under the window calls made in between; NULL blob in the task call
+    for env in (None, '4096'):
+        if env:
+            os.environ['PCB_PIECE_MIN_BYTES'] = env
+        try:
+            engine.upload_reads(blob)
+            w1 = engine.align_windows(ebuf, lens, e_ids)
+            w2 = engine.align_windows(sbuf, lens, s_ids[:2])
+            up = engine.align_tasks(None, seg_off, seg_len, ad)
+        finally:
+            os.environ.pop('PCB_PIECE_MIN_BYTES', None)
+        assert up.tobytes() == one.tobytes()
+        assert w1.tobytes() == plain.tobytes() and w2.shape == (n, 2)
+    # an announcement with no window call in between, then trimmed segments of the same blob (phase C after phase B)
+    os.environ['PCB_PIECE_MIN_BYTES'] = '4096'
+    try:
+        engine.upload_reads(blob)
+        cut = np.minimum(seg_len // 3, 70).astype(np.int32)
+        up = engine.align_tasks(None, seg_off + cut, seg_len - 2 * cut, ad)
+    finally:
+        del os.environ['PCB_PIECE_MIN_BYTES']
+    assert up.tobytes() == engine.align_tasks(blob, seg_off + cut, seg_len - 2 * cut, ad).tobytes()
+    with pytest.raises(Exception):
+        engine.align_tasks(None, seg_off, seg_len, ad)          # nothing announced any more
+    # submit / collect (pcb_set_deferred + pcb_wait): the calls only queue, each in its own slot; same records
+    for env in (None, '4096'):
+        if env:
+            os.environ['PCB_PIECE_MIN_BYTES'] = env
+        try:
+            with engine.deferred():
+                engine.upload_reads(blob)
+                engine.select_slot(0); d1 = engine.align_windows(ebuf, lens, e_ids)
+                engine.select_slot(1); d2 = engine.align_windows(sbuf, lens, s_ids)
+                engine.select_slot(2); d3 = engine.align_tasks(None, seg_off, seg_len, ad)
+            with engine.deferred():                             # a second batch reuses the slots and the plan buffers
+                engine.select_slot(1); d4 = engine.align_windows(ebuf, lens, e_ids)
+                engine.select_slot(2); d5 = engine.align_tasks(blob, seg_off + cut, seg_len - 2 * cut, ad)
+        finally:
+            os.environ.pop('PCB_PIECE_MIN_BYTES', None)
+            engine.select_slot(0)
+        assert d1.tobytes() == plain.tobytes() and d4.tobytes() == plain.tobytes()
+        assert d3.tobytes() == one.tobytes() and d5.tobytes() == up.tobytes()
+        assert d2.tobytes() == engine.align_windows(sbuf, lens, s_ids).tobytes()
     rs = random.Random(8)
     for t in rs.sample(range(len(ad)), 300):
         r = bytes(blob[seg_off[t]:seg_off[t] + seg_len[t]])
