@@ -451,7 +451,9 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
         // window ranges of this launch (multiples of 64 windows; each range keeps every warp busy for >= 8 units)
         const int64_t groups_all = (S.n_windows + 63) / 64;
         int64_t n_ranges = 1;
-        if (host_out && oi == n_used - 1) n_ranges = std::max<int64_t>(1, std::min<int64_t>(8, groups_all * cnt / (8 * warps)));
+        // deferred mode: the copy of a call's results runs under the next call's kernels anyway, and every extra launch costs a tail
+        const int max_ranges = c->deferred ? 2 : 8;
+        if (host_out && oi == n_used - 1) n_ranges = std::max<int64_t>(1, std::min<int64_t>(max_ranges, groups_all * cnt / (8 * warps)));
         const int64_t groups_per = (groups_all + n_ranges - 1) / n_ranges;
         for (int64_t r = 0; r < n_ranges; ++r) {
             const int64_t w0 = r * groups_per * 64, w1 = std::min<int64_t>(S.n_windows, (r + 1) * groups_per * 64);
