@@ -24,6 +24,8 @@ Exactness notes
 * Verbosity-dependent printing is the reference's business and is left to the caller (the alignments are stored on the
   reads exactly as the reference stores them, so its formatting methods work unchanged).
 """
+import contextlib
+
 import numpy as np
 
 from .engine import AlignmentEngine
@@ -65,6 +67,11 @@ def _windows(reads, end_size, at_end):
     return buf, lens
 
 
+def _collect_after(eng):
+    """Submit / collect around a group of engine calls (AlignmentEngine.deferred); a plain engine collects per call."""
+    return eng.deferred() if hasattr(eng, 'deferred') else contextlib.nullcontext()
+
+
 def _engine(engine, scoring_scheme_vals):
     eng = engine if engine is not None else AlignmentEngine(0)
     eng.set_scoring(scoring_scheme_vals)
@@ -84,11 +91,21 @@ def find_matching_adapter_sets(check_reads, verbosity, end_size, scoring_scheme_
     seqs = [a.start_sequence[1] for a in with_start] + [a.end_sequence[1] for a in with_end]
     if check_reads and seqs:
         eng.set_adapters(seqs)
-        for at_end, sets, id0 in ((False, with_start, 0), (True, with_end, len(with_start))):
-            if not sets:
+        submitted = {}
+        with _collect_after(eng):                          # both submits queued, then collected together
+            for slot, (at_end, sets, id0) in enumerate(((False, with_start, 0), (True, with_end, len(with_start)))):
+                if not sets:
+                    continue
+                if hasattr(eng, 'select_slot'):
+                    eng.select_slot(slot)
+                buf, lens = _windows(check_reads, end_size, at_end)
+                submitted[at_end] = eng.align_windows(buf, lens, np.arange(id0, id0 + len(sets), dtype=np.int32))
+        if hasattr(eng, 'select_slot'):
+            eng.select_slot(0)
+        for at_end, sets in ((False, with_start), (True, with_end)):
+            if at_end not in submitted:
                 continue
-            buf, lens = _windows(check_reads, end_size, at_end)
-            rec = eng.align_windows(buf, lens, np.arange(id0, id0 + len(sets), dtype=np.int32))
+            rec = submitted[at_end]
             _, full = _parsed_identities(rec)
             best = full.max(axis=0)                       # no NaN here: full_len >= 1 whenever the alignment exists
             for a, score in zip(sets, best):
@@ -113,11 +130,23 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
     seqs = [a.start_sequence[1] for a in starts] + [a.end_sequence[1] for a in ends]
     if reads and seqs:
         eng.set_adapters(seqs)
+    # both submits are queued before either is collected (submit / collect: the copies of the second run under the
+    # kernels of the first), as the reference queues all reads on its pool before it collects (porechop_abi.py:395-407)
+    submitted = {}
+    with _collect_after(eng):
+        for slot, (at_end, sets, id0) in enumerate(((False, starts, 0), (True, ends, len(starts)))):
+            if not reads or not sets:
+                continue
+            if hasattr(eng, 'select_slot'):
+                eng.select_slot(slot)
+            buf, lens = _windows(reads, end_size, at_end)
+            submitted[at_end] = eng.align_windows(buf, lens, np.arange(id0, id0 + len(sets), dtype=np.int32))
+    if hasattr(eng, 'select_slot'):
+        eng.select_slot(0)
     for at_end, sets, id0 in ((False, starts, 0), (True, ends, len(starts))):
-        if not reads or not sets:
+        if at_end not in submitted:
             continue
-        buf, lens = _windows(reads, end_size, at_end)
-        rec = eng.align_windows(buf, lens, np.arange(id0, id0 + len(sets), dtype=np.int32))
+        rec = submitted[at_end]
         partial, full = _parsed_identities(rec)
         r_start, r_end = rec['read_start'], _read_ends(rec)
         with np.errstate(invalid='ignore'):
