@@ -178,12 +178,18 @@ __device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR]
                                           uint32_t rowTp, uint32_t rowT, uint32_t GEB, uint32_t *fp,
                                           uint32_t &Ml, uint32_t &Vl, uint32_t &Hlast)
 {
-    uint32_t Dn = rowTp + tp[0];
+    // the substitution scores of the column come from shared memory PF rows ahead of their use
+    constexpr int PF = 8;
+    uint32_t tv[PF];
+#pragma unroll
+    for (int d = 0; d < PF; ++d) tv[d] = tp[d * TP];
+    uint32_t Dn = rowTp + tv[0];
     uint32_t Vu = 0, Wacc = 0;
     const uint32_t GEBG = GEB + GUARD;
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
         const uint32_t D = Dn;
+        if (r + PF < NR) tv[r % PF] = tp[(r + PF) * TP];
         const uint32_t Mup = (r == 0) ? rowT : Mo[(r > 0) ? r - 1 : 0];
         const uint32_t ch = Hl[r] + GEBG - Mo[r], cv = Vu + GEBG - Mup;
         const uint32_t Hn = __viaddmax_s16x2(Hl[r], GEB, Mo[r]), Vn = __viaddmax_s16x2(Vu, GEB, Mup);
@@ -194,7 +200,7 @@ __device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR]
         else if ((r & 3) == 2) Wacc = (Wacc & 0x0F0F0F0Fu) | (W & 0xF0F0F0F0u);
         else Wacc = (Wacc & 0x3F3F3F3Fu) | (W & 0xC0C0C0C0u);
         if ((r & 3) == 3 || r == NR - 1) fp[(r >> 2) * PCB_BLOCK] = Wacc;
-        if (r < NR - 1) Dn = Mo[r] + tp[(r + 1) * TP];
+        if (r < NR - 1) Dn = Mo[r] + tv[(r + 1) % PF];
         Vu = Vn; Mo[r] = __vmaxs2(D, G); Hl[r] = Hn;
     }
     Ml = Mo[NR - 1]; Vl = Vu; Hlast = Hl[NR - 1];
@@ -213,6 +219,8 @@ __device__ __forceinline__ Raw4 load4(const uint8_t *seq, int pos, int lim)
 __device__ __forceinline__ uint32_t join4(const Raw4 &r) { return __funnelshift_r(r.w0, r.w1, r.sh); }
 // offset (in words) into a row of the score table for the two code bytes (Dna5 code * 8) of a column
 __device__ __forceinline__ uint32_t pair_index(uint32_t c8_0, uint32_t c8_1) { return (c8_0 * 5u + c8_1) >> 3; }
+
+__device__ __forceinline__ uint64_t ckw_of(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * NR; }   // = pcf_ck_words (pcb_kernels.h)
 
 // One op of the reverse walk for half h of this thread (dp_traceback_impl.h:379-451).  Flag word layout as col_flags writes
 // it; the block's read bases sit behind the C*FW flag words.  State 0 = M, 1 = V, 2 = H.  In state M a cell whose diagonal
@@ -235,6 +243,186 @@ __device__ __forceinline__ void walk_step(const uint32_t *s_fl, const uint32_t *
         walk_acc_H(a, i, j);
         --j; s = fh ? 2 : 0;
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Pass 2 as a per-warp work queue.  A task's traceback crosses 1.8 flag blocks on average but the longest of 64 crosses 3+,
+// so a warp that takes its 64 tasks through pass 2 in lockstep spends a third of its rounds on a few lanes.  Instead every
+// task that still has blocks to go is an ENTRY of a ring in global memory (L2-resident: PCF_QCAP entries of PCF_QF words
+// per warp), and a ROUND pops 64 entries -- from whatever units they come, the adapter is the same --, rebuilds one flag
+// block for each, walks it, writes the results of the paths that ended and pushes the others back.  Rounds run when the
+// ring holds 64 entries, so every lane of a round works; the ring is drained when the warp's adapter changes and at the
+// end.  Checkpoints live in a ring of PCF_RING per-unit slots; s_live[slot] counts the entries that still need a slot.
+// ------------------------------------------------------------------------------------------------
+constexpr int PCF_QF = 20;
+enum { QF_OFFLO, QF_OFFHI, QF_LEN, QF_COL0, QF_MTRUE, QF_OUTLO, QF_OUTHI, QF_CI, QF_CJ, QF_ENDI, QF_ENDJ, QF_ST, QF_SCORE,
+       QF_ACC, QF_CKREF = QF_ACC + 6 };
+static_assert(QF_CKREF + 1 == PCF_QF, "queue entry layout");
+
+struct RoundCtx {
+    uint32_t *queue;                 // [PCF_QF][PCF_QCAP] of this warp
+    int head, count;                 // warp-uniform
+    int tbl_off, code_off, fl_off, live_off;   // word offsets into the CTA's dynamic shared memory (pointers through this struct
+                                     // would lose their address space and turn every LDS / STS into a generic access)
+    const uint32_t *ck_warp;         // checkpoint area of the warp's lane 0, ring slot 0
+    uint64_t ckw, T;                 // checkpoint words per thread and ring slot; threads in the grid
+    const uint8_t *arena;
+    pcb_result *out;
+    int32_t *err_flag;
+    int n, r0, b, lane;
+    uint32_t GEB, Bp;
+};
+
+template <int NR, bool EXACT, int C>
+__device__ __noinline__ void trace_round(RoundCtx &q)
+{
+    constexpr int FW = NR / 4;
+    // the context lives in local memory: take what the loops use into registers once
+    const int lane = q.lane, n = q.n, r0 = q.r0, b = q.b;
+    const uint64_t T = q.T, ckw = q.ckw;
+    extern __shared__ uint32_t smem[];
+    const uint32_t *const tbl = smem + q.tbl_off, *const s_code = smem + q.code_off, *const ck_warp = q.ck_warp;
+    uint32_t *const s_fl = smem + q.fl_off;
+    volatile int *const s_live = reinterpret_cast<volatile int *>(smem + q.live_off);
+    const uint32_t GEB = q.GEB, Bp = q.Bp;
+    const int take = min(q.count, 64);
+    uint64_t off[2]; int64_t oidx[2];
+    int len[2], col0[2], mtrue[2], ci[2], cj[2], endi[2], endj[2], st[2], score[2], ckref[2];
+    WalkAcc acc[2];
+    bool valid[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int e = 2 * lane + h;
+        valid[h] = e < take;
+        const uint32_t *p = q.queue + ((q.head + e) & (PCF_QCAP - 1));
+        off[h] = 0; oidx[h] = -1; len[h] = col0[h] = mtrue[h] = ci[h] = cj[h] = endi[h] = endj[h] = st[h] = score[h] = ckref[h] = 0;
+        walk_acc_init(acc[h]);
+        if (valid[h]) {
+            off[h] = (uint64_t)p[QF_OFFLO * PCF_QCAP] | ((uint64_t)p[QF_OFFHI * PCF_QCAP] << 32);
+            oidx[h] = (int64_t)((uint64_t)p[QF_OUTLO * PCF_QCAP] | ((uint64_t)p[QF_OUTHI * PCF_QCAP] << 32));
+            len[h] = (int)p[QF_LEN * PCF_QCAP]; col0[h] = (int)p[QF_COL0 * PCF_QCAP]; mtrue[h] = (int)p[QF_MTRUE * PCF_QCAP];
+            ci[h] = (int)p[QF_CI * PCF_QCAP]; cj[h] = (int)p[QF_CJ * PCF_QCAP];
+            endi[h] = (int)p[QF_ENDI * PCF_QCAP]; endj[h] = (int)p[QF_ENDJ * PCF_QCAP];
+            st[h] = (int)p[QF_ST * PCF_QCAP]; score[h] = (int)p[QF_SCORE * PCF_QCAP]; ckref[h] = (int)p[QF_CKREF * PCF_QCAP];
+            acc[h].nD = (int)p[(QF_ACC + 0) * PCF_QCAP]; acc[h].matches = (int)p[(QF_ACC + 1) * PCF_QCAP];
+            acc[h].kA = (int)p[(QF_ACC + 2) * PCF_QCAP]; acc[h].kR = (int)p[(QF_ACC + 3) * PCF_QCAP];
+            acc[h].jA = (int)p[(QF_ACC + 4) * PCF_QCAP]; acc[h].iR = (int)p[(QF_ACC + 5) * PCF_QCAP];
+        }
+    }
+    q.head = (q.head + take) & (PCF_QCAP - 1); q.count -= take;
+
+    // block of each half: columns k*C+1 .. k*C+C, holding its current column
+    const bool go0 = valid[0] && ci[0] > 0 && cj[0] > 0, go1 = valid[1] && ci[1] > 0 && cj[1] > 0;
+    const int k0 = go0 ? (cj[0] - 1) / C : 0, k1 = go1 ? (cj[1] - 1) / C : 0;
+    const int jb0 = k0 * C, jb1 = k1 * C;
+    const int tmax = __reduce_max_sync(0xffffffffu, max(go0 ? cj[0] - jb0 : 0, go1 ? cj[1] - jb1 : 0));
+    if (tmax > 0) {
+        const uint8_t *const seq0 = q.arena + off[0], *const seq1 = q.arena + off[1];
+        const int lim0 = max(len[0] - 1, 0), lim1 = max(len[1] - 1, 0);
+        // the block's read bases (C per half), then the checkpointed column the block starts from
+        uint32_t q0[C / 4], q1[C / 4];
+#pragma unroll
+        for (int g = 0; g < C / 4; ++g) {
+            q0[g] = join4(load4(seq0, jb0 + 4 * g, lim0)); q1[g] = join4(load4(seq1, jb1 + 4 * g, lim1));
+            s_fl[(C * FW + g) * PCB_BLOCK] = q0[g]; s_fl[(C * FW + C / 4 + g) * PCB_BLOCK] = q1[g];   // for the walk
+        }
+        uint32_t Mo[NR], Hl[NR];
+        {
+            // an entry's checkpoints were written by the (lane, half) that ran its pass 1, in that unit's ring slot
+            // (a checkpoint is 2*NR contiguous words: any lane can fetch any entry's with full sectors)
+            const uint4 *p0 = reinterpret_cast<const uint4 *>(ck_warp + (((uint64_t)(ckref[0] >> 8) * T + ((ckref[0] >> 1) & 31)) * ckw + (uint64_t)k0 * 2ull * NR));
+            const uint4 *p1 = reinterpret_cast<const uint4 *>(ck_warp + (((uint64_t)(ckref[1] >> 8) * T + ((ckref[1] >> 1) & 31)) * ckw + (uint64_t)k1 * 2ull * NR));
+            const uint32_t sel = ((ckref[0] & 1) ? 0x0032u : 0x0010u) | ((ckref[1] & 1) ? 0x7600u : 0x5400u);
+#pragma unroll
+            for (int g = 0; g < NR / 2; ++g) {
+                const uint4 a = p0[g], c = p1[g];
+                Mo[2 * g] = prmt(a.x, c.x, sel); Hl[2 * g] = prmt(a.y, c.y, sel);
+                Mo[2 * g + 1] = prmt(a.z, c.z, sel); Hl[2 * g + 1] = prmt(a.w, c.w, sel);
+            }
+        }
+        uint32_t rT = pk(B0 + b * jb0, B0 + b * jb1);
+        const bool pend0 = go0 && (st[0] & 4), pend1 = go1 && (st[1] & 4);
+        const bool anypend = __any_sync(0xffffffffu, pend0 || pend1);
+        int s0 = st[0] & 3, s1 = st[1] & 3;
+#pragma unroll UNR2
+        for (int t = 1; t <= tmax; ++t) {
+            const uint32_t *tp = tbl + pair_index(q0[0] & 0xFFu, q1[0] & 0xFFu);
+#pragma unroll
+            for (int g = 0; g < C / 4; ++g) {                  // shift the base queues by one byte
+                q0[g] = __funnelshift_r(q0[g], g + 1 < C / 4 ? q0[(g + 1) % (C / 4)] : 0u, 8);
+                q1[g] = __funnelshift_r(q1[g], g + 1 < C / 4 ? q1[(g + 1) % (C / 4)] : 0u, 8);
+            }
+            const uint32_t rowTp = rT;
+            rT += Bp;
+            uint32_t Ml, Vl, Hlast;
+            col_flags<NR, EXACT>(Mo, Hl, tp, rowTp, rT, GEB, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
+            if (anypend) {
+                // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
+                // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
+                const uint32_t xv = Ml ^ Vl, xh = Ml ^ Hlast;
+                if (pend0 && jb0 + t == cj[0]) s0 = ((xv & 0xFFFFu) == 0) ? 1 : (((xh & 0xFFFFu) == 0) ? 2 : 0);
+                if (pend1 && jb1 + t == cj[1]) s1 = ((xv >> 16) == 0) ? 1 : (((xh >> 16) == 0) ? 2 : 0);
+            }
+        }
+        __syncwarp();
+        // walk (dp_traceback_impl.h:379-451, :498-545) inside the block: both halves together, one path op per half and trip
+        {
+            int i0 = ci[0], j0 = cj[0], i1 = ci[1], j1 = cj[1];
+            WalkAcc a0 = acc[0], a1 = acc[1];
+            bool act0 = go0 && j0 > jb0, act1 = go1 && j1 > jb1;
+            while (act0 || act1) {
+                if (act0) { walk_step<FW, C>(s_fl, s_code, 0, jb0, r0, i0, j0, s0, a0); act0 = i0 > 0 && j0 > jb0; }
+                if (act1) { walk_step<FW, C>(s_fl, s_code, 1, jb1, r0, i1, j1, s1, a1); act1 = i1 > 0 && j1 > jb1; }
+            }
+            ci[0] = i0; cj[0] = j0; acc[0] = a0; ci[1] = i1; cj[1] = j1; acc[1] = a1;
+        }
+        st[0] = s0; st[1] = s1;                                  // the pending bit is spent
+        __syncwarp();
+    }
+
+    // paths that reached row 0 / column 0 are complete (this also covers the empty path); the others go back into the ring
+    bool keep[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        keep[h] = valid[h] && ci[h] > 0 && cj[h] > 0;
+        if (!valid[h] || keep[h]) continue;
+        if (cj[h] == 0 && ci[h] > 0 && col0[h] > 0) atomicOr(q.err_flag, 1);      // window too narrow for this path
+        PathAcc pa; walk_acc_finish(acc[h], endi[h], endj[h], ci[h], cj[h], pa);
+        PathStats ps;
+        path_finalize(pa, (int64_t)col0[h] + cj[h], ci[h], (int64_t)mtrue[h] - (col0[h] + endj[h]), n - endi[h], mtrue[h], n, ps);
+        pcb_result res;
+        res.read_start = ps.read_start; res.read_end = ps.read_end;
+        res.adapter_start = ps.adapter_start; res.adapter_end = ps.adapter_end;
+        res.raw_score = score[h]; res.matches = ps.matches;
+        res.aligned_len = ps.aligned_len; res.full_len = ps.full_len;
+        q.out[oidx[h]] = res;
+    }
+#pragma unroll
+    for (int s = 0; s < PCF_RING; ++s) {
+        const int gone = __popc(__ballot_sync(0xffffffffu, valid[0] && !keep[0] && (ckref[0] >> 8) == s)) +
+                         __popc(__ballot_sync(0xffffffffu, valid[1] && !keep[1] && (ckref[1] >> 8) == s));
+        if (lane == 0 && gone) s_live[s] -= gone;
+    }
+    const uint32_t m0 = __ballot_sync(0xffffffffu, keep[0]), m1 = __ballot_sync(0xffffffffu, keep[1]);
+    const uint32_t lt = (1u << lane) - 1u;
+    const int tail = q.head + q.count;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        if (!keep[h]) continue;
+        const int pos = h ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
+        uint32_t *p = q.queue + ((tail + pos) & (PCF_QCAP - 1));
+        p[QF_OFFLO * PCF_QCAP] = (uint32_t)off[h]; p[QF_OFFHI * PCF_QCAP] = (uint32_t)(off[h] >> 32);
+        p[QF_OUTLO * PCF_QCAP] = (uint32_t)(uint64_t)oidx[h]; p[QF_OUTHI * PCF_QCAP] = (uint32_t)((uint64_t)oidx[h] >> 32);
+        p[QF_LEN * PCF_QCAP] = (uint32_t)len[h]; p[QF_COL0 * PCF_QCAP] = (uint32_t)col0[h]; p[QF_MTRUE * PCF_QCAP] = (uint32_t)mtrue[h];
+        p[QF_CI * PCF_QCAP] = (uint32_t)ci[h]; p[QF_CJ * PCF_QCAP] = (uint32_t)cj[h];
+        p[QF_ENDI * PCF_QCAP] = (uint32_t)endi[h]; p[QF_ENDJ * PCF_QCAP] = (uint32_t)endj[h];
+        p[QF_ST * PCF_QCAP] = (uint32_t)st[h]; p[QF_SCORE * PCF_QCAP] = (uint32_t)score[h]; p[QF_CKREF * PCF_QCAP] = (uint32_t)ckref[h];
+        p[(QF_ACC + 0) * PCF_QCAP] = (uint32_t)acc[h].nD; p[(QF_ACC + 1) * PCF_QCAP] = (uint32_t)acc[h].matches;
+        p[(QF_ACC + 2) * PCF_QCAP] = (uint32_t)acc[h].kA; p[(QF_ACC + 3) * PCF_QCAP] = (uint32_t)acc[h].kR;
+        p[(QF_ACC + 4) * PCF_QCAP] = (uint32_t)acc[h].jA; p[(QF_ACC + 5) * PCF_QCAP] = (uint32_t)acc[h].iR;
+    }
+    q.count += __popc(m0) + __popc(m1);
+    __syncwarp();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -261,8 +449,10 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
     const uint64_t slot = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t *const tbl = smem + warp * (NR * TP);
     uint32_t *const s_code = smem + W * (NR * TP) + warp * NR;
-    uint32_t *const s_fl = smem + W * (NR * TP + NR) + threadIdx.x;
-    uint32_t *const ck = L.scratch + slot;               // checkpoints [k][2*NR], element stride T
+    volatile int *const s_live = reinterpret_cast<volatile int *>(smem + W * (NR * TP + NR) + warp * PCF_RING);
+    uint32_t *const s_fl = smem + W * (NR * TP + NR + PCF_RING) + threadIdx.x;
+    uint32_t *const ck = L.scratch + slot * ckw_of(L.mmax, C, NR);     // checkpoints [ring slot][thread][k][2*NR]
+    const uint64_t ckw = ckw_of(L.mmax, C, NR);
 
     const int b = -L.sc.gap_open;
     const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b);
@@ -276,6 +466,20 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
     if (cross) { u_begin = gw * L.src.n_units / nwarps; u_end = (gw + 1) * L.src.n_units / nwarps; u_step = 1; }
     else       { u_begin = gw; u_end = L.src.n_units; u_step = nwarps; }
     int32_t tbl_adapter = -1;
+    RoundCtx q;
+    int useq = 0;                                        // units this warp has taken through pass 1
+    if (TRACE) {
+        q.queue = L.scratch + PCF_RING * ckw * T + (uint64_t)gw * (PCF_QCAP * PCF_QF);
+        q.head = 0; q.count = 0;
+        q.tbl_off = (int)(tbl - smem); q.code_off = (int)(s_code - smem); q.fl_off = (int)(s_fl - smem);
+        q.live_off = W * (NR * TP + NR) + warp * PCF_RING;
+        q.ck_warp = L.scratch + (slot - lane) * ckw; q.ckw = ckw; q.T = T;
+        q.arena = L.arena; q.out = L.out; q.err_flag = L.err_flag;
+        q.n = 0; q.r0 = 0; q.b = -L.sc.gap_open; q.lane = lane;
+        q.GEB = pk2(L.sc.gap_extend - L.sc.gap_open); q.Bp = pk2(-L.sc.gap_open);
+        if (lane < PCF_RING) s_live[lane] = 0;
+        __syncwarp();
+    }
 
     for (int64_t unit = u_begin; unit < u_end; unit += u_step) {
         int32_t adapter = 0;
@@ -313,6 +517,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
         // neighbours as under row 0 itself and no row of the column loop needs a bounds test.
         const int r0 = EXACT ? 0 : NR - n;
         if (adapter != tbl_adapter) {
+            if (TRACE) { while (q.count > 0) trace_round<NR, EXACT, C>(q); q.n = n; q.r0 = r0; }   // the ring's entries use the old table
             __syncwarp();
             for (int i = lane; i < NR; i += 32) s_code[i] = i >= r0 ? (uint32_t)(L.ad.codes[aoff + i - r0] / PCB_CODE_SCALE) : 0u;
             __syncwarp();
@@ -354,7 +559,10 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
         for (int r = 0; r < NR; ++r) { Mo[r] = pk2(B0 + b * (r + 1)); Hl[r] = 0; }   // column 0: M = 0, H = -inf
         uint32_t rowT = pk2(B0);                                 // biased M(0, j) = bias of row 0 at the current column
         const uint32_t candK = pk2(OFF - b * NR);                // candidate = M(n, j) + candK - rowT = score + OFF
-        uint32_t *ckp = ck;
+        // ring slot of this unit's checkpoints: free once every entry of the unit that used it last has completed
+        const int rs = TRACE ? useq % PCF_RING : 0;
+        if (TRACE) while (s_live[rs] > 0 && q.count > 0) trace_round<NR, EXACT, C>(q);
+        uint32_t *ckp = ck + (uint64_t)rs * ckw * T;
         int ckc = 0;                                             // columns since the last checkpoint
         Raw4 nx0 = load4(seq0, 0, lim0), nx1 = load4(seq1, 0, lim1);
 
@@ -404,8 +612,8 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             nx0 = load4(seq0, j0 + 3, lim0); nx1 = load4(seq1, j0 + 3, lim1);       // used one group later
             if (TRACE && ckc == 0) {                             // checkpoint = state after column j0-1 (a multiple of C)
 #pragma unroll
-                for (int r = 0; r < NR; ++r) { ckp[(2 * r) * T] = Mo[r]; ckp[(2 * r + 1) * T] = Hl[r]; }
-                ckp += 2ull * NR * T;
+                for (int g = 0; g < NR / 2; ++g) reinterpret_cast<uint4 *>(ckp)[g] = make_uint4(Mo[2 * g], Hl[2 * g], Mo[2 * g + 1], Hl[2 * g + 1]);
+                ckp += 2 * NR;
             }
             if (TRACE) { ckc += 4; if (ckc == C) ckc = 0; }
             if (!TRACE && ((j0 - 1) & (REBASE - 1)) == 0 && j0 > 1) {   // keep the growing bias inside 15 bits
@@ -435,111 +643,51 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             if (tk[1].out_idx >= 0) L.scan_out[tk[1].out_idx] = (len1 > 0 && sc1 > 0) ? (int)(((uint32_t)(sc1 - OFF) << 16) | ((uint32_t)(0x3FFF - ord1) << 2)) : (int)0x80000000;
             continue;
         }
-#ifdef PCF_SKIP_PASS2
-        { pcb_result r{}; r.raw_score = sc0 - OFF; r.read_end = ord0; if (tk[0].out_idx >= 0) L.out[tk[0].out_idx] = r;
-          r.raw_score = sc1 - OFF; r.read_end = ord1; if (tk[1].out_idx >= 0) L.out[tk[1].out_idx] = r; continue; }
-#endif
-
-        // =========================== pass 2: flags for the blocks the traceback crosses ===========================
-        int ci[2], cj[2], endi[2], endj[2], state[2], score[2];
-        bool done[2], rowcls[2];
-        WalkAcc acc[2];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const HalfTask &t = tk[h];
-            const int sc = h ? sc1 : sc0, ord = h ? ord1 : ord0;
-            const bool fc = h ? fc1 : fc0;
-            done[h] = true; rowcls[h] = !fc; state[h] = 0; score[h] = sc - OFF;
-            ci[h] = cj[h] = endi[h] = endj[h] = 0;
-            walk_acc_init(acc[h]);
-            if (t.out_idx < 0) continue;
-            if (t.len <= 0) { write_failed(L.out, t.out_idx); continue; }
-            if (sc <= 0) { atomicOr(L.err_flag, 2); write_failed(L.out, t.out_idx); continue; }   // forced cell not found
-            if (fc) { ci[h] = ord - t.len; cj[h] = t.len; const int e = h ? finE1 : finE0; state[h] = (e & 2) ? 1 : ((e & 1) ? 2 : 0); }
-            else    { ci[h] = n; cj[h] = ord; }
-            endi[h] = ci[h]; endj[h] = cj[h];
-            done[h] = false;
-        }
-
-        for (int iter = 0;; ++iter) {
-            // a half whose walk already stands on row 0 / column 0 is finished (this also covers the empty path)
+        // =========================== pass 2: every task becomes an entry of the warp's ring ===========================
+        {
+            bool pv[2]; int pci[2], pcj[2], pst[2];
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                if (done[h] || (ci[h] > 0 && cj[h] > 0)) continue;
                 const HalfTask &t = tk[h];
-                if (cj[h] == 0 && ci[h] > 0 && t.col0 > 0) atomicOr(L.err_flag, 1);   // window too narrow for this path
-                PathAcc pa; walk_acc_finish(acc[h], endi[h], endj[h], ci[h], cj[h], pa);
-                PathStats st;
-                path_finalize(pa, (int64_t)t.col0 + cj[h], ci[h], (int64_t)t.m_true - (t.col0 + endj[h]), n - endi[h],
-                              t.m_true, n, st);
-                pcb_result res;
-                res.read_start = st.read_start; res.read_end = st.read_end;
-                res.adapter_start = st.adapter_start; res.adapter_end = st.adapter_end;
-                res.raw_score = score[h]; res.matches = st.matches;
-                res.aligned_len = st.aligned_len; res.full_len = st.full_len;
-                L.out[t.out_idx] = res;
-                done[h] = true;
+                const int sc = h ? sc1 : sc0, ord = h ? ord1 : ord0;
+                const bool fc = h ? fc1 : fc0;
+                pv[h] = false; pci[h] = pcj[h] = pst[h] = 0;
+                if (t.out_idx < 0) continue;
+                if (t.len <= 0) { write_failed(L.out, t.out_idx); continue; }
+                if (sc <= 0) { atomicOr(L.err_flag, 2); write_failed(L.out, t.out_idx); continue; }   // forced cell not found
+                if (fc) { pci[h] = ord - t.len; pcj[h] = t.len; const int e = h ? finE1 : finE0; pst[h] = (e & 2) ? 1 : ((e & 1) ? 2 : 0); }
+                else    { pci[h] = n; pcj[h] = ord; pst[h] = 4; }      // 4: the end cell's V == M / H == M still decide the start state
+                pv[h] = true;
             }
-            if (!__any_sync(0xffffffffu, !done[0] || !done[1])) break;
-
-            // block of each half: columns k*C+1 .. k*C+C, holding its current column
-            const int k0 = done[0] ? 0 : (cj[0] - 1) / C, k1 = done[1] ? 0 : (cj[1] - 1) / C;
-            const int need = max(done[0] ? 0 : cj[0] - k0 * C, done[1] ? 0 : cj[1] - k1 * C);
-            const int tmax = __reduce_max_sync(0xffffffffu, need);
-            const int jb0 = k0 * C, jb1 = k1 * C;
-            // the block's read bases (C per half), then the checkpointed column the block starts from
-            uint32_t q0[C / 4], q1[C / 4];
+            const uint32_t m0 = __ballot_sync(0xffffffffu, pv[0]), m1 = __ballot_sync(0xffffffffu, pv[1]);
+            const uint32_t lt = (1u << lane) - 1u;
+            const int tail = q.head + q.count;
 #pragma unroll
-            for (int g = 0; g < C / 4; ++g) {
-                q0[g] = join4(load4(seq0, jb0 + 4 * g, lim0)); q1[g] = join4(load4(seq1, jb1 + 4 * g, lim1));
-                s_fl[(C * FW + g) * PCB_BLOCK] = q0[g]; s_fl[(C * FW + C / 4 + g) * PCB_BLOCK] = q1[g];   // for the walk
+            for (int h = 0; h < 2; ++h) {
+                if (!pv[h]) continue;
+                const HalfTask &t = tk[h];
+                const int pos = h ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
+                uint32_t *p = q.queue + ((tail + pos) & (PCF_QCAP - 1));
+                p[QF_OFFLO * PCF_QCAP] = (uint32_t)t.off; p[QF_OFFHI * PCF_QCAP] = (uint32_t)(t.off >> 32);
+                p[QF_OUTLO * PCF_QCAP] = (uint32_t)(uint64_t)t.out_idx; p[QF_OUTHI * PCF_QCAP] = (uint32_t)((uint64_t)t.out_idx >> 32);
+                p[QF_LEN * PCF_QCAP] = (uint32_t)t.len; p[QF_COL0 * PCF_QCAP] = (uint32_t)t.col0; p[QF_MTRUE * PCF_QCAP] = (uint32_t)t.m_true;
+                p[QF_CI * PCF_QCAP] = (uint32_t)pci[h]; p[QF_CJ * PCF_QCAP] = (uint32_t)pcj[h];
+                p[QF_ENDI * PCF_QCAP] = (uint32_t)pci[h]; p[QF_ENDJ * PCF_QCAP] = (uint32_t)pcj[h];
+                p[QF_ST * PCF_QCAP] = (uint32_t)pst[h]; p[QF_SCORE * PCF_QCAP] = (uint32_t)((h ? sc1 : sc0) - OFF);
+                p[QF_CKREF * PCF_QCAP] = (uint32_t)((rs << 8) | (lane << 1) | h);
+                p[(QF_ACC + 0) * PCF_QCAP] = 0u; p[(QF_ACC + 1) * PCF_QCAP] = 0u;
+                p[(QF_ACC + 2) * PCF_QCAP] = 0xFFFFFFFFu; p[(QF_ACC + 3) * PCF_QCAP] = 0xFFFFFFFFu;        // walk_acc_init
+                p[(QF_ACC + 4) * PCF_QCAP] = 0u; p[(QF_ACC + 5) * PCF_QCAP] = 0u;
             }
-            {
-                const uint32_t *p0 = ck + (uint64_t)k0 * 2ull * NR * T, *p1 = ck + (uint64_t)k1 * 2ull * NR * T;
-#pragma unroll
-                for (int r = 0; r < NR; ++r) {
-                    Mo[r] = prmt(p0[(2 * r) * T], p1[(2 * r) * T], 0x7610);
-                    Hl[r] = prmt(p0[(2 * r + 1) * T], p1[(2 * r + 1) * T], 0x7610);
-                }
-            }
-            uint32_t rT = pk(B0 + b * jb0, B0 + b * jb1);
-#pragma unroll UNR2
-            for (int t = 1; t <= tmax; ++t) {
-                const uint32_t *tp = tbl + pair_index(q0[0] & 0xFFu, q1[0] & 0xFFu);
-#pragma unroll
-                for (int g = 0; g < C / 4; ++g) {                  // shift the base queues by one byte
-                    q0[g] = __funnelshift_r(q0[g], g + 1 < C / 4 ? q0[(g + 1) % (C / 4)] : 0u, 8);
-                    q1[g] = __funnelshift_r(q1[g], g + 1 < C / 4 ? q1[(g + 1) % (C / 4)] : 0u, 8);
-                }
-                const uint32_t rowTp = rT;
-                rT += Bp;
-                uint32_t Ml, Vl, Hlast;
-                col_flags<NR, EXACT>(Mo, Hl, tp, rowTp, rT, GEB, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
-                if (iter == 0) {
-                    // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
-                    // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
-                    const uint32_t xv = Ml ^ Vl, xh = Ml ^ Hlast;
-                    if (!done[0] && rowcls[0] && jb0 + t == cj[0]) state[0] = ((xv & 0xFFFFu) == 0) ? 1 : (((xh & 0xFFFFu) == 0) ? 2 : 0);
-                    if (!done[1] && rowcls[1] && jb1 + t == cj[1]) state[1] = ((xv >> 16) == 0) ? 1 : (((xh >> 16) == 0) ? 2 : 0);
-                }
-            }
+            const int total = __popc(m0) + __popc(m1);
+            if (lane == 0 && total) s_live[rs] += total;
+            q.count += total;
+            ++useq;
             __syncwarp();
-            // walk (dp_traceback_impl.h:379-451, :498-545) inside the block: both halves together, one path op per half
-            // and trip, so that a warp waits for the longest walk of its 64 tasks once, not once per half
-            {
-                int i0 = ci[0], j0 = cj[0], s0 = state[0], i1 = ci[1], j1 = cj[1], s1 = state[1];
-                WalkAcc a0 = acc[0], a1 = acc[1];
-                bool act0 = !done[0] && i0 > 0 && j0 > jb0, act1 = !done[1] && i1 > 0 && j1 > jb1;
-                while (act0 || act1) {
-                    if (act0) { walk_step<FW, C>(s_fl, s_code, 0, jb0, r0, i0, j0, s0, a0); act0 = i0 > 0 && j0 > jb0; }
-                    if (act1) { walk_step<FW, C>(s_fl, s_code, 1, jb1, r0, i1, j1, s1, a1); act1 = i1 > 0 && j1 > jb1; }
-                }
-                ci[0] = i0; cj[0] = j0; state[0] = s0; acc[0] = a0;
-                ci[1] = i1; cj[1] = j1; state[1] = s1; acc[1] = a1;
-            }
-            __syncwarp();
+            while (q.count >= 64) trace_round<NR, EXACT, C>(q);
         }
     }
+    if (TRACE) while (q.count > 0) trace_round<NR, EXACT, C>(q);
 }
 
 }  // namespace
@@ -550,7 +698,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
 static size_t fast_smem(bool trace, int nr, int c)
 {
     const size_t per_thread = trace ? (size_t)c * (nr / 4) + 2 * (c / 4) : (size_t)2 * nr;   // flags + block bases | column dump
-    return ((size_t)(PCB_BLOCK / 32) * (nr * TP + nr) + (size_t)PCB_BLOCK * per_thread) * sizeof(uint32_t);
+    return ((size_t)(PCB_BLOCK / 32) * (nr * TP + nr + PCF_RING) + (size_t)PCB_BLOCK * per_thread) * sizeof(uint32_t);
 }
 
 template <bool TRACE, int NR, bool EXACT, int C>

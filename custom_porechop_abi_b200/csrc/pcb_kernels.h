@@ -170,10 +170,14 @@ int pcb_occupancy_grid(int which /*0 trace, 1 scan*/);
 /* fast kernels, by class (see above) */
 cudaError_t pcf_launch(const PcbLaunch &L, bool trace, int cls, cudaStream_t st);
 int pcf_occupancy_grid(bool trace, int cls);
+/* Trace scratch per thread: PCF_RING per-unit slots of checkpoints, then the warp's pass-2 ring (PCF_QCAP entries of 20 words
+ * per warp = 80 words per thread); see trace_round in pcb_fast.cu. */
+#define PCF_RING 8
+#define PCF_QCAP 128
+static inline uint64_t pcf_ck_words(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * NR; }
 static inline uint64_t pcf_scratch_words_trace(int mmax, int cls)
 {
-    const int C = pcf_class_c(cls);
-    return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * pcf_class_nr(cls);     /* checkpoints */
+    return pcf_ck_words(mmax, pcf_class_c(cls), pcf_class_nr(cls)) * PCF_RING + (PCF_QCAP * 20) / 32;
 }
 
 #endif
