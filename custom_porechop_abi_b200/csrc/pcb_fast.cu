@@ -286,29 +286,38 @@ __device__ __noinline__ void trace_round(RoundCtx &q)
     volatile int *const s_live = reinterpret_cast<volatile int *>(smem + q.live_off);
     const uint32_t GEB = q.GEB, Bp = q.Bp;
     const int take = min(q.count, 64);
+    // An entry's fields are fetched where they are needed (what the flag columns need now, the walk's accumulators before
+    // the walk, the rest before the result is written or the entry goes back): the column loop wants the registers.
     uint64_t off[2]; int64_t oidx[2];
     int len[2], col0[2], mtrue[2], ci[2], cj[2], endi[2], endj[2], st[2], score[2], ckref[2];
     WalkAcc acc[2];
     bool valid[2];
+    const uint32_t *const qp0 = q.queue + ((q.head + 2 * lane) & (PCF_QCAP - 1));
+    const uint32_t *const qp1 = q.queue + ((q.head + 2 * lane + 1) & (PCF_QCAP - 1));
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-        const int e = 2 * lane + h;
-        valid[h] = e < take;
-        const uint32_t *p = q.queue + ((q.head + e) & (PCF_QCAP - 1));
-        off[h] = 0; oidx[h] = -1; len[h] = col0[h] = mtrue[h] = ci[h] = cj[h] = endi[h] = endj[h] = st[h] = score[h] = ckref[h] = 0;
-        walk_acc_init(acc[h]);
+        valid[h] = 2 * lane + h < take;
+        const uint32_t *p = h ? qp1 : qp0;
+        off[h] = 0; len[h] = ci[h] = cj[h] = st[h] = ckref[h] = 0;
         if (valid[h]) {
             off[h] = (uint64_t)p[QF_OFFLO * PCF_QCAP] | ((uint64_t)p[QF_OFFHI * PCF_QCAP] << 32);
-            oidx[h] = (int64_t)((uint64_t)p[QF_OUTLO * PCF_QCAP] | ((uint64_t)p[QF_OUTHI * PCF_QCAP] << 32));
-            len[h] = (int)p[QF_LEN * PCF_QCAP]; col0[h] = (int)p[QF_COL0 * PCF_QCAP]; mtrue[h] = (int)p[QF_MTRUE * PCF_QCAP];
+            len[h] = (int)p[QF_LEN * PCF_QCAP];
             ci[h] = (int)p[QF_CI * PCF_QCAP]; cj[h] = (int)p[QF_CJ * PCF_QCAP];
-            endi[h] = (int)p[QF_ENDI * PCF_QCAP]; endj[h] = (int)p[QF_ENDJ * PCF_QCAP];
-            st[h] = (int)p[QF_ST * PCF_QCAP]; score[h] = (int)p[QF_SCORE * PCF_QCAP]; ckref[h] = (int)p[QF_CKREF * PCF_QCAP];
-            acc[h].nD = (int)p[(QF_ACC + 0) * PCF_QCAP]; acc[h].matches = (int)p[(QF_ACC + 1) * PCF_QCAP];
-            acc[h].kA = (int)p[(QF_ACC + 2) * PCF_QCAP]; acc[h].kR = (int)p[(QF_ACC + 3) * PCF_QCAP];
-            acc[h].jA = (int)p[(QF_ACC + 4) * PCF_QCAP]; acc[h].iR = (int)p[(QF_ACC + 5) * PCF_QCAP];
+            st[h] = (int)p[QF_ST * PCF_QCAP]; ckref[h] = (int)p[QF_CKREF * PCF_QCAP];
         }
     }
+    auto load_acc = [&]() {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint32_t *p = h ? qp1 : qp0;
+            walk_acc_init(acc[h]);
+            if (valid[h]) {
+                acc[h].nD = (int)p[(QF_ACC + 0) * PCF_QCAP]; acc[h].matches = (int)p[(QF_ACC + 1) * PCF_QCAP];
+                acc[h].kA = (int)p[(QF_ACC + 2) * PCF_QCAP]; acc[h].kR = (int)p[(QF_ACC + 3) * PCF_QCAP];
+                acc[h].jA = (int)p[(QF_ACC + 4) * PCF_QCAP]; acc[h].iR = (int)p[(QF_ACC + 5) * PCF_QCAP];
+            }
+        }
+    };
     q.head = (q.head + take) & (PCF_QCAP - 1); q.count -= take;
 
     // block of each half: columns k*C+1 .. k*C+C, holding its current column
@@ -365,6 +374,7 @@ __device__ __noinline__ void trace_round(RoundCtx &q)
             }
         }
         __syncwarp();
+        load_acc();
         // walk (dp_traceback_impl.h:379-451, :498-545) inside the block: both halves together, one path op per half and trip
         {
             int i0 = ci[0], j0 = cj[0], i1 = ci[1], j1 = cj[1];
@@ -378,7 +388,21 @@ __device__ __noinline__ void trace_round(RoundCtx &q)
         }
         st[0] = s0; st[1] = s1;                                  // the pending bit is spent
         __syncwarp();
+    } else {
+        load_acc();
     }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t *p = h ? qp1 : qp0;
+        oidx[h] = -1; col0[h] = mtrue[h] = endi[h] = endj[h] = score[h] = 0;
+        if (valid[h]) {
+            oidx[h] = (int64_t)((uint64_t)p[QF_OUTLO * PCF_QCAP] | ((uint64_t)p[QF_OUTHI * PCF_QCAP] << 32));
+            col0[h] = (int)p[QF_COL0 * PCF_QCAP]; mtrue[h] = (int)p[QF_MTRUE * PCF_QCAP];
+            endi[h] = (int)p[QF_ENDI * PCF_QCAP]; endj[h] = (int)p[QF_ENDJ * PCF_QCAP];
+            score[h] = (int)p[QF_SCORE * PCF_QCAP];
+        }
+    }
+    __syncwarp();                                                // every lane has its entry before a slot can be written again
 
     // paths that reached row 0 / column 0 are complete (this also covers the empty path); the others go back into the ring
     bool keep[2];
