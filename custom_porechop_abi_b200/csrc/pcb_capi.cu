@@ -175,6 +175,11 @@ extern "C" int pcb_create(int device, pcb_context **out)
     c->grid_trace = pcb_occupancy_grid(0);
     c->grid_scan = pcb_occupancy_grid(1);
     for (int cls = 0; cls < PCF_NCLS; ++cls) { c->grid_ftrace[cls] = pcf_occupancy_grid(true, cls); c->grid_fscan[cls] = pcf_occupancy_grid(false, cls); }
+    if (const char *gl = getenv("PCB_GRID_LIMIT")) {       // tests: few CTAs, so that a small input gives every warp many units
+        const int lim = std::max(1, atoi(gl));
+        c->grid_trace = std::min(c->grid_trace, lim); c->grid_scan = std::min(c->grid_scan, lim);
+        for (int cls = 0; cls < PCF_NCLS; ++cls) { c->grid_ftrace[cls] = std::min(c->grid_ftrace[cls], lim); c->grid_fscan[cls] = std::min(c->grid_fscan[cls], lim); }
+    }
     if (c->d_err.reserve(1) != cudaSuccess) { g_global_err = "cudaMalloc failed"; delete c; return PCB_ERR_NOMEM; }
     *out = c;
     return PCB_OK;

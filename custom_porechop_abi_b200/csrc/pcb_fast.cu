@@ -179,7 +179,10 @@ __device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR]
                                           uint32_t &Ml, uint32_t &Vl, uint32_t &Hlast)
 {
     // the substitution scores of the column come from shared memory PF rows ahead of their use
-    constexpr int PF = 8;
+#ifndef PCF_PF
+#define PCF_PF 8
+#endif
+    constexpr int PF = PCF_PF;
     uint32_t tv[PF];
 #pragma unroll
     for (int d = 0; d < PF; ++d) tv[d] = tp[d * TP];

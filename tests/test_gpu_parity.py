@@ -291,3 +291,55 @@ def test_ultra_long_reads_and_barcode_sets(engine):
     for w in range(0, len(windows), 3):
         for k in range(len(seqs)):
             assert rec_matches_oracle(out[w, k], oracle_align(windows[w], seqs[k], DEFAULT)), (windows[w], seqs[k])
+
+
+def test_trace_queue_many_units_per_warp_and_long_paths():
+    """The trace kernels take pass 2 through a per-warp ring of entries (pcb_fast.cu: trace_round).  A context limited to
+    two CTAs gives every warp dozens of units, so the ring runs full rounds across unit boundaries, wraps, and re-uses its
+    checkpoint slots; cheap gaps make paths that cross up to ten flag blocks (entries that stay in the ring for many rounds
+    and force a slot to be drained); adapters of several classes alternate.  Every record against the oracle."""
+    import os
+    from custom_porechop_abi_b200.engine import AlignmentEngine
+    rng = random.Random(77)
+    ads = [''.join(rng.choice('ACGT') for _ in range(n)) for n in (24, 24, 19, 30, 24, 37, 24, 50)]
+    wins = []
+    for w in range(1536):
+        a = rng.choice(ads)
+        kind = rng.randrange(4)
+        if kind == 0:       # the two halves of an adapter far apart: one long path when gaps are cheap
+            gap = ''.join(rng.choice('ACGT') for _ in range(rng.randrange(40, 115)))
+            s = a[:len(a) // 2] + gap + a[len(a) // 2:]
+        elif kind == 1:     # adapter overhanging either window end
+            s = a[rng.randrange(1, len(a)):] + ''.join(rng.choice('ACGT') for _ in range(rng.randrange(60, 130)))
+            if rng.random() < 0.5:
+                s = s[::-1]
+        elif kind == 2:
+            s = ''.join(rng.choice('ACGT') for _ in range(rng.randrange(1, 150)))
+        else:
+            pos = rng.randrange(0, 100)
+            s = ''.join(rng.choice('ACGT') for _ in range(pos)) + a + ''.join(rng.choice('ACGTN') for _ in range(rng.randrange(0, 40)))
+        wins.append(s[:150].encode())
+    os.environ['PCB_GRID_LIMIT'] = '2'
+    try:
+        eng = AlignmentEngine(0)
+    finally:
+        del os.environ['PCB_GRID_LIMIT']
+    try:
+        eng.set_adapters(ads)
+        buf, lens = eng.pack_windows(wins, stride=160)
+        ids = np.arange(len(ads), dtype=np.int32)
+        for scoring in ((20, -4, -2, -1), DEFAULT):
+            eng.set_scoring(scoring)
+            out = eng.align_windows(buf, lens, ids)
+            for w in range(len(wins)):
+                for k in range(len(ads)):
+                    assert rec_matches_oracle(out[w, k], oracle_align(wins[w], ads[k].encode(), scoring)), (scoring, w, k)
+            # explicit tasks through the same kernels, adapters alternating from unit to unit
+            blob = b''.join(wins[:512])
+            off = np.concatenate([[0], np.cumsum([len(x) for x in wins[:512]])]).astype(np.int64)
+            seg_off = np.repeat(off[:-1], len(ads)); seg_len = np.repeat(np.diff(off).astype(np.int32), len(ads))
+            ad = np.tile(ids, 512)
+            t = eng.align_tasks(blob, seg_off, seg_len, ad)
+            assert t.tobytes() == out[:512].reshape(-1).tobytes()
+    finally:
+        eng.close()
