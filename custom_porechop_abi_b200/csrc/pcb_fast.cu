@@ -589,7 +589,8 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
         // ring slot of this unit's checkpoints: free once every entry of the unit that used it last has completed
         const int rs = TRACE ? useq % PCF_RING : 0;
         if (TRACE) while (s_live[rs] > 0 && q.count > 0) trace_round<NR, EXACT, C>(q);
-        uint32_t *ckp = ck + (uint64_t)rs * ckw * T;
+        uint32_t *const ckp = ck + (uint64_t)rs * ckw * T;
+        uint32_t ckoff = 0;
         int ckc = 0;                                             // columns since the last checkpoint
         Raw4 nx0 = load4(seq0, 0, lim0), nx1 = load4(seq1, 0, lim1);
 
@@ -639,8 +640,10 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             nx0 = load4(seq0, j0 + 3, lim0); nx1 = load4(seq1, j0 + 3, lim1);       // used one group later
             if (TRACE && ckc == 0) {                             // checkpoint = state after column j0-1 (a multiple of C)
 #pragma unroll
-                for (int g = 0; g < NR / 2; ++g) reinterpret_cast<uint4 *>(ckp)[g] = make_uint4(Mo[2 * g], Hl[2 * g], Mo[2 * g + 1], Hl[2 * g + 1]);
-                ckp += 2 * NR;
+                // (address from base + running offset: a pointer bumped after the stores waits for all 12 of them to read it)
+                uint4 *const cq = reinterpret_cast<uint4 *>(ckp + ckoff);
+                for (int g = 0; g < NR / 2; ++g) cq[g] = make_uint4(Mo[2 * g], Hl[2 * g], Mo[2 * g + 1], Hl[2 * g + 1]);
+                ckoff += 2 * NR;
             }
             if (TRACE) { ckc += 4; if (ckc == C) ckc = 0; }
             if (!TRACE && ((j0 - 1) & (REBASE - 1)) == 0 && j0 > 1) {   // keep the growing bias inside 15 bits
