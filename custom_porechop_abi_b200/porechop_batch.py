@@ -31,23 +31,45 @@ import numpy as np
 from .engine import AlignmentEngine
 
 
-def _parsed_identities(rec):
+def _percent_table(matches, length):
+    """float('%f' % (100.0 * m / l)) for every element, through a table over the distinct (m, l) pairs: the C++ side prints
+    the double with std::to_string and the reference parses it back (alignment.cpp:112-120, nanopore_read.py:487-498), so
+    the identities the thresholds see carry six decimals.  0 / 0 prints "-nan" there: NaN here."""
+    m = matches.astype(np.int64)
+    length = length.astype(np.int64)
+    if m.size == 0:
+        return np.zeros(m.shape, dtype=np.float64)
+    width = int(length.max()) + 1
+    key = m * width + length
+    n_keys = int(key.max()) + 1
+    if n_keys <= (1 << 22):                                 # the usual case: a few thousand distinct pairs in a small range
+        present = np.zeros(n_keys, dtype=bool)
+        present[key.ravel()] = True
+        table = np.zeros(n_keys, dtype=np.float64)
+        for u in np.nonzero(present)[0]:
+            mm, ll = divmod(int(u), width)
+            table[u] = float('%f' % (100.0 * mm / ll)) if ll else float('nan')
+        return table[key]
+    uniq, inv = np.unique(key, return_inverse=True)
+    table = np.empty(len(uniq), dtype=np.float64)
+    for k, u in enumerate(uniq):
+        mm, ll = divmod(int(u), width)
+        table[k] = float('%f' % (100.0 * mm / ll)) if ll else float('nan')
+    return table[inv].reshape(key.shape)
+
+
+def _parsed_identities(rec, aligned=True):
     """(aligned_region_percent_identity, full_adapter_percent_identity) as nanopore_read.align_adapter sees them
-    (nanopore_read.py:485-500): the doubles of src/alignment.cpp:81,89 printed with %f and parsed back."""
-    m = rec['matches'].astype(np.int64)
-    out = []
-    for length in (rec['aligned_len'].astype(np.int64), rec['full_len'].astype(np.int64)):
-        key = (m << 32) | length
-        uniq, inv = np.unique(key, return_inverse=True)
-        table = np.empty(len(uniq), dtype=np.float64)
-        for k, u in enumerate(uniq):
-            mm, ll = int(u >> 32), int(u & 0xFFFFFFFF)
-            table[k] = float('%f' % (100.0 * mm / ll)) if ll else float('nan')     # the C++ prints "-nan" for 0.0 / 0
-        out.append(table[inv].reshape(key.shape))
+    (nanopore_read.py:485-500): the doubles of src/alignment.cpp:81,89 printed with %f and parsed back.
+    aligned=False skips the first one (phases A and C only look at the full-adapter identity)."""
     failed = rec['read_start'] == -1
-    out[0][failed] = 0.0
-    out[1][failed] = 0.0
-    return out[0], out[1]
+    full = _percent_table(rec['matches'], rec['full_len'])
+    full[failed] = 0.0
+    part = None
+    if aligned:
+        part = _percent_table(rec['matches'], rec['aligned_len'])
+        part[failed] = 0.0
+    return part, full
 
 
 def _read_ends(rec):
@@ -58,13 +80,21 @@ def _read_ends(rec):
 def _windows(reads, end_size, at_end):
     """The reference's seq[:end_size] / seq[-end_size:] (nanopore_read.py:164,170,181,203) as a fixed-stride buffer."""
     stride = max(16, -(-end_size // 16) * 16)
+    parts = [r.seq[-end_size:] for r in reads] if at_end else [r.seq[:end_size] for r in reads]
+    lens = np.fromiter((len(w) for w in parts), dtype=np.int32, count=len(parts))
     buf = np.zeros((len(reads), stride), dtype=np.uint8)
-    lens = np.empty(len(reads), dtype=np.int32)
-    for i, r in enumerate(reads):
-        w = (r.seq[-end_size:] if at_end else r.seq[:end_size]).encode()
-        lens[i] = len(w)
-        buf[i, :len(w)] = np.frombuffer(w, dtype=np.uint8)
+    if len(parts):
+        flat = np.frombuffer(''.join(parts).encode(), dtype=np.uint8)     # windows back to back, row-major like the mask
+        buf[np.arange(stride, dtype=np.int32)[None, :] < lens[:, None]] = flat
     return buf, lens
+
+
+def _trimmed_bounds(r):
+    """[lo, hi) of get_seq_with_start_end_adapters_trimmed() inside r.seq (nanopore_read.py:77-81), Python slice rules included."""
+    if not r.start_trim_amount and not r.end_trim_amount:
+        return 0, len(r.seq)
+    lo, hi, _ = slice(r.start_trim_amount, len(r.seq) - r.end_trim_amount).indices(len(r.seq))
+    return lo, max(lo, hi)
 
 
 def _collect_after(eng):
@@ -106,7 +136,7 @@ def find_matching_adapter_sets(check_reads, verbosity, end_size, scoring_scheme_
             if at_end not in submitted:
                 continue
             rec = submitted[at_end]
-            _, full = _parsed_identities(rec)
+            _, full = _parsed_identities(rec, aligned=False)
             best = full.max(axis=0)                       # no NaN here: full_len >= 1 whenever the alignment exists
             for a, score in zip(sets, best):
                 if at_end:
@@ -194,44 +224,64 @@ def find_adapters_in_read_middles(reads, matching_sets, verbosity, middle_thresh
     eng.set_adapters([seq for _, seq in adapters])
     n_ad = len(adapters)
 
-    masked = [bytearray(r.get_seq_with_start_end_adapters_trimmed().encode()) for r in reads]
-    queue = [(i, 0) for i in range(len(reads))]             # (read, first adapter still to be aligned)
-    while queue:
+    # A read's sequence as the reference's loop sees it: get_seq_with_start_end_adapters_trimmed() (nanopore_read.py:77-81),
+    # with every hit so far overwritten by '-'.  Round 0 does not slice a billion bases in Python: the untrimmed reads go
+    # up as one blob and the trimmed sequence is a segment of it, with Python's own slice arithmetic (a trim longer than
+    # the read makes the reference's stop index negative, which Python counts from the end).  A read becomes a bytearray
+    # of its trimmed sequence once it has a hit.
+    current = [None] * len(reads)                           # bytearray of the masked trimmed sequence, once a read has a hit
+    q_read = np.arange(len(reads), dtype=np.int64)          # queued reads and, per read, the first adapter still to align
+    q_k0 = np.zeros(len(reads), dtype=np.int64)
+    first_round = True
+    while len(q_read):
         # one submit: every queued read against its remaining adapters
-        lens = np.array([len(masked[i]) for i, _ in queue], dtype=np.int64)
-        offs = np.zeros(len(queue) + 1, dtype=np.int64)
-        np.cumsum(lens, out=offs[1:])
-        blob = np.empty(int(offs[-1]), dtype=np.uint8)
-        seg_off, seg_len, seg_ad, first = [], [], [], []
-        for q, (i, k0) in enumerate(queue):
-            blob[offs[q]:offs[q + 1]] = np.frombuffer(bytes(masked[i]), dtype=np.uint8)
-            first.append(len(seg_ad))
-            for k in range(k0, n_ad):
-                seg_off.append(offs[q]); seg_len.append(lens[q]); seg_ad.append(k)
-        rec = eng.align_tasks(blob, np.array(seg_off, dtype=np.int64), np.array(seg_len, dtype=np.int32),
-                              np.array(seg_ad, dtype=np.int32))
-        _, full = _parsed_identities(rec)
+        if first_round:
+            bounds = np.array([_trimmed_bounds(r) for r in reads], dtype=np.int64).reshape(len(reads), 2)
+            full_lens = np.fromiter((len(r.seq) for r in reads), dtype=np.int64, count=len(reads))
+            base = np.zeros(len(reads) + 1, dtype=np.int64)
+            np.cumsum(full_lens, out=base[1:])
+            blob = np.frombuffer(''.join(r.seq for r in reads).encode(), dtype=np.uint8)
+            offs = base[:-1] + bounds[:, 0]
+            lens = bounds[:, 1] - bounds[:, 0]
+            first_round = False
+        else:
+            parts = [bytes(current[i]) for i in q_read]
+            lens = np.fromiter((len(x) for x in parts), dtype=np.int64, count=len(parts))
+            offs = np.zeros(len(parts) + 1, dtype=np.int64)
+            np.cumsum(lens, out=offs[1:])
+            offs = offs[:-1]
+            blob = np.frombuffer(b''.join(parts), dtype=np.uint8)
+        counts = n_ad - q_k0                                 # tasks per queued read
+        first = np.zeros(len(q_read) + 1, dtype=np.int64)
+        np.cumsum(counts, out=first[1:])
+        entry = np.repeat(np.arange(len(q_read), dtype=np.int64), counts)    # queue entry of every task
+        seg_ad = np.arange(int(first[-1]), dtype=np.int64) - first[entry] + q_k0[entry]
+        rec = eng.align_tasks(blob, offs[entry], lens[entry].astype(np.int32), seg_ad.astype(np.int32))
+        _, full = _parsed_identities(rec, aligned=False)
         r_start, r_end = rec['read_start'], _read_ends(rec)
-        requeue = []
-        for q, (i, k0) in enumerate(queue):
-            t0 = first[q]
-            for k in range(k0, n_ad):
-                t = t0 + (k - k0)
-                if full[t] >= middle_threshold:             # a hit: record, mask, align the same adapter again
-                    read = reads[i]
-                    adapter_name = adapters[k][0]
-                    read_start, read_end = int(r_start[t]), int(r_end[t])
-                    masked[i][read_start:read_end] = b'-' * (read_end - read_start)
-                    read.middle_adapter_positions.update(range(read_start, read_end))
-                    read.middle_hit_str += '  ' + adapter_name + ' (read coords: ' + str(read_start) + '-' + \
-                        str(read_end) + ', ' + 'identity: ' + '%.1f' % full[t] + '%)\n'
-                    trim_start = read_start - extra_trim_good_side
-                    if adapter_name in start_sequence_names:
-                        trim_start = read_start - extra_trim_bad_side
-                    trim_end = read_end + extra_trim_good_side
-                    if adapter_name in end_sequence_names:
-                        trim_end = read_end + extra_trim_bad_side
-                    read.middle_trim_positions.update(range(trim_start, trim_end))
-                    requeue.append((i, k))
-                    break                                   # later adapters were aligned on the old mask: redo them
-        queue = requeue
+        # first hit of every queued read (tasks are in adapter order per read); NaN compares False, as in the reference
+        with np.errstate(invalid='ignore'):
+            hits = np.nonzero(full >= middle_threshold)[0]
+        hit_entry, pos = np.unique(entry[hits], return_index=True)
+        next_read, next_k0 = [], []
+        for q, t in zip(hit_entry, hits[pos]):               # a hit: record, mask, align the same adapter again
+            i, k = int(q_read[q]), int(seg_ad[t])
+            read = reads[i]
+            adapter_name = adapters[k][0]
+            read_start, read_end = int(r_start[t]), int(r_end[t])
+            if current[i] is None:
+                current[i] = bytearray(read.get_seq_with_start_end_adapters_trimmed().encode())
+            current[i][read_start:read_end] = b'-' * (read_end - read_start)
+            read.middle_adapter_positions.update(range(read_start, read_end))
+            read.middle_hit_str += '  ' + adapter_name + ' (read coords: ' + str(read_start) + '-' + \
+                str(read_end) + ', ' + 'identity: ' + '%.1f' % full[t] + '%)\n'
+            trim_start = read_start - extra_trim_good_side
+            if adapter_name in start_sequence_names:
+                trim_start = read_start - extra_trim_bad_side
+            trim_end = read_end + extra_trim_good_side
+            if adapter_name in end_sequence_names:
+                trim_end = read_end + extra_trim_bad_side
+            read.middle_trim_positions.update(range(trim_start, trim_end))
+            next_read.append(i); next_k0.append(k)           # later adapters were aligned on the old mask: redo them
+        q_read = np.array(next_read, dtype=np.int64)
+        q_k0 = np.array(next_k0, dtype=np.int64)

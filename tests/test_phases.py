@@ -142,6 +142,19 @@ def test_phase_logic_with_oracle_engine(idx):
     run_case(cases()[idx], OracleEngine())
 
 
+def test_trimmed_bounds_follow_python_slicing():
+    """Phase C addresses the trimmed read as a segment of the untrimmed one: same bases as the reference's slice, also
+    when a trim exceeds the read (its stop index goes negative and Python counts it from the end)."""
+    import random
+    from custom_porechop_abi_b200.porechop_batch import _trimmed_bounds
+    rng = random.Random(4)
+    for _ in range(3000):
+        r = Read('x', ''.join(rng.choice('ACGT') for _ in range(rng.randrange(0, 30))))
+        r.start_trim_amount, r.end_trim_amount = rng.randrange(0, 40), rng.randrange(0, 40)
+        lo, hi = _trimmed_bounds(r)
+        assert r.seq[lo:hi] == r.get_seq_with_start_end_adapters_trimmed(), (r.seq, r.start_trim_amount, r.end_trim_amount)
+
+
 @pytest.mark.gpu
 def test_phases_on_gpu(engine):
     for c in cases():
