@@ -149,10 +149,12 @@ def find_matching_adapter_sets(check_reads, verbosity, end_size, scoring_scheme_
 def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_trim_size, end_threshold,
                                scoring_scheme_vals, print_dest, min_trim_size, threads, check_barcodes,
                                barcode_threshold, barcode_diff, require_two_barcodes, forward_or_reverse_barcodes,
-                               engine=None):
+                               engine=None, read_blob=None):
     """
     Phase B (porechop_abi.py:359-438): find_start_trim + find_end_trim (nanopore_read.py:175-217) for every read, then
     determine_barcode.  Start windows x start sequences and end windows x end sequences are two GPU submits.
+    read_blob: the same reads as a read_blob.ReadBlob (same order); the windows then come out of its buffer with one
+    numpy gather instead of a Python slice per read.
     """
     eng = _engine(engine, scoring_scheme_vals)
     starts = [a for a in matching_sets if a.start_sequence]
@@ -169,7 +171,7 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
                 continue
             if hasattr(eng, 'select_slot'):
                 eng.select_slot(slot)
-            buf, lens = _windows(reads, end_size, at_end)
+            buf, lens = read_blob.windows(end_size, at_end) if read_blob is not None else _windows(reads, end_size, at_end)
             submitted[at_end] = eng.align_windows(buf, lens, np.arange(id0, id0 + len(sets), dtype=np.int32))
     if hasattr(eng, 'select_slot'):
         eng.select_slot(0)
@@ -204,7 +206,7 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
 
 def find_adapters_in_read_middles(reads, matching_sets, verbosity, middle_threshold, extra_trim_good_side,
                                   extra_trim_bad_side, scoring_scheme_vals, print_dest, threads, discard_middle,
-                                  engine=None):
+                                  engine=None, read_blob=None):
     """
     Phase C (porechop_abi.py:457-522): NanoporeRead.find_middle_adapters (nanopore_read.py:219-252) for every read, in
     rounds (see the module docstring).  Updates middle_adapter_positions, middle_trim_positions and middle_hit_str.
@@ -221,6 +223,8 @@ def find_adapters_in_read_middles(reads, matching_sets, verbosity, middle_thresh
     end_sequence_names = set(m.end_sequence[0] for m in matching_sets if m.end_sequence)
     if not reads or not adapters:
         return
+    if read_blob is not None and len(read_blob) != len(reads):
+        raise ValueError('read_blob holds %d reads, the read list %d' % (len(read_blob), len(reads)))
     eng.set_adapters([seq for _, seq in adapters])
     n_ad = len(adapters)
 
@@ -235,7 +239,13 @@ def find_adapters_in_read_middles(reads, matching_sets, verbosity, middle_thresh
     first_round = True
     while len(q_read):
         # one submit: every queued read against its remaining adapters
-        if first_round:
+        if first_round and read_blob is not None:           # the file's own bytes are the blob: nothing to join or encode
+            blob = read_blob.buf
+            offs, lens = read_blob.trimmed_segments(
+                np.fromiter((r.start_trim_amount for r in reads), dtype=np.int64, count=len(reads)),
+                np.fromiter((r.end_trim_amount for r in reads), dtype=np.int64, count=len(reads)))
+            first_round = False
+        elif first_round:
             bounds = np.array([_trimmed_bounds(r) for r in reads], dtype=np.int64).reshape(len(reads), 2)
             full_lens = np.fromiter((len(r.seq) for r in reads), dtype=np.int64, count=len(reads))
             base = np.zeros(len(reads) + 1, dtype=np.int64)

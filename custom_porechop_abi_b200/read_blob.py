@@ -1,0 +1,145 @@
+"""
+Reads as one byte buffer plus per-read segments, for the batched phases (porechop_batch.py).
+
+The reference loads every record into Python strings (misc.py:109-168: load_fasta_or_fastq -> load_fastq / load_fasta) and
+NanoporeRead keeps seq.upper() (nanopore_read.py:32-44).  The alignment path only needs the bases: the C ABI takes a blob
+and (offset, length) segments, and the device-side encoder maps a/c/g/t/u in either case like SeqAn's own table
+(alphabet_residue_tabs.h:113-140), so the bytes of the file can go to the GPU as they are.  Joining and encoding a
+million Python strings per phase costs more than the alignments (scripts/exp/batch_phases.py); a ReadBlob does that work
+once, with numpy, at load time.
+
+FASTQ: four-line records as the reference parses them (line.strip() of lines 4k .. 4k+3).  FASTA: sequences may span
+lines, so they are compacted into a fresh buffer.  gzip is read through gzip.open, as in the reference.
+"""
+import gzip
+
+import numpy as np
+
+_WS = (9, 10, 11, 12, 13, 32)                     # what str.strip() removes from ASCII text
+
+
+def _open_bytes(filename):
+    with open(filename, 'rb') as f:
+        magic = f.read(3)
+    opener = gzip.open if magic == b'\x1f\x8b\x08' else open          # misc.py:60-81
+    with opener(filename, 'rb') as f:
+        return f.read()
+
+
+def _strip(buf, start, end):
+    """Vectorised line.strip(): move start / end inwards over ASCII whitespace."""
+    start, end = start.copy(), end.copy()
+    ws = np.zeros(256, dtype=bool)
+    ws[list(_WS)] = True
+    while True:
+        m = (end > start) & ws[buf[np.maximum(end - 1, 0)]]
+        if not m.any():
+            break
+        end[m] -= 1
+    while True:
+        m = (end > start) & ws[buf[np.minimum(start, len(buf) - 1)]]
+        if not m.any():
+            break
+        start[m] += 1
+    return start, end
+
+
+class ReadBlob(object):
+    """buf: uint8 buffer; read i is buf[seq_off[i] : seq_off[i] + seq_len[i]]; names / qualities likewise (FASTQ)."""
+
+    def __init__(self, buf, seq_off, seq_len, name_off, name_len, qual_off=None, qual_len=None, file_type='FASTQ'):
+        self.buf = buf
+        self.seq_off = np.ascontiguousarray(seq_off, dtype=np.int64)
+        self.seq_len = np.ascontiguousarray(seq_len, dtype=np.int64)
+        self.name_off, self.name_len = name_off, name_len
+        self.qual_off, self.qual_len = qual_off, qual_len
+        self.file_type = file_type
+
+    def __len__(self):
+        return len(self.seq_off)
+
+    def seq(self, i):
+        """The sequence as NanoporeRead stores it (nanopore_read.py:36-39): upper case, U -> T when U outnumbers T."""
+        s = self.buf[self.seq_off[i]:self.seq_off[i] + self.seq_len[i]].tobytes().decode().upper()
+        if s.count('U') > s.count('T'):
+            s = s.replace('U', 'T')
+        return s
+
+    def full_name(self, i):
+        return self.buf[self.name_off[i]:self.name_off[i] + self.name_len[i]].tobytes().decode()
+
+    def name(self, i):
+        return self.full_name(i).split()[0]
+
+    def quals(self, i):
+        if self.qual_off is None:
+            return ''
+        return self.buf[self.qual_off[i]:self.qual_off[i] + self.qual_len[i]].tobytes().decode()
+
+    def windows(self, end_size, at_end):
+        """seq[:end_size] / seq[-end_size:] of every read (nanopore_read.py:164,170,181,203) as a fixed-stride buffer."""
+        stride = max(16, -(-end_size // 16) * 16)
+        lens = np.minimum(self.seq_len, end_size)
+        first = self.seq_off + (self.seq_len - lens if at_end else 0)
+        col = np.arange(stride, dtype=np.int64)[None, :]
+        idx = np.minimum(first[:, None] + col, max(len(self.buf) - 1, 0))
+        out = self.buf[idx] if len(self.buf) else np.zeros((len(self), stride), dtype=np.uint8)
+        out[col >= lens[:, None]] = 0
+        return np.ascontiguousarray(out, dtype=np.uint8), lens.astype(np.int32)
+
+    def trimmed_segments(self, start_trim, end_trim):
+        """(offset, length) in buf of seq[start_trim : len - end_trim] for every read, with Python's slice rules (a stop
+        index below zero counts from the end), and the whole read where both trims are 0 (nanopore_read.py:77-81)."""
+        n = self.seq_len
+        start_trim = np.asarray(start_trim, dtype=np.int64)
+        end_trim = np.asarray(end_trim, dtype=np.int64)
+        lo = np.minimum(start_trim, n)
+        stop = n - end_trim
+        stop = np.where(stop < 0, np.maximum(stop + n, 0), np.minimum(stop, n))
+        hi = np.maximum(lo, stop)
+        return self.seq_off + lo, hi - lo
+
+
+def load_read_blob(filename):
+    """The records of a FASTQ or FASTA file (plain or gzip) as a ReadBlob; record order = file order."""
+    raw = _open_bytes(filename)
+    buf = np.frombuffer(raw, dtype=np.uint8)
+    if len(buf) == 0:
+        raise ValueError('File is neither FASTA or FASTQ')
+    nl = np.flatnonzero(buf == 10)
+    starts = np.concatenate(([0], nl + 1))
+    ends = np.concatenate((nl, [len(buf)]))
+    if starts[-1] >= len(buf):                               # the file ends with a newline: no line after it
+        starts, ends = starts[:-1], ends[:-1]
+    first = chr(buf[0])
+    if first == '@':
+        n = len(starts) // 4                                 # a truncated last record: the reference stops with an error there
+        if len(starts) % 4:
+            tail_s, tail_e = _strip(buf, starts[4 * n:], ends[4 * n:])
+            if (tail_e > tail_s).any():
+                raise IndexError('FASTQ record count is not a multiple of four lines')
+        s, e = _strip(buf, starts[:4 * n], ends[:4 * n])
+        s, e = s.reshape(n, 4), e.reshape(n, 4)
+        name_off = np.minimum(s[:, 0] + 1, e[:, 0])          # line.strip()[1:]
+        return ReadBlob(buf, s[:, 1], e[:, 1] - s[:, 1], name_off, e[:, 0] - name_off, s[:, 3], e[:, 3] - s[:, 3], 'FASTQ')
+    if first == '>':
+        s, e = _strip(buf, starts, ends)
+        keep = e > s                                          # blank lines are skipped (misc.py:136-138)
+        s, e = s[keep], e[keep]
+        header = buf[s] == ord('>')
+        rec = np.cumsum(header) - 1                           # record of every line
+        n = int(header.sum())
+        body = ~header & (rec >= 0)
+        line_len = (e - s)[body]
+        seq_len = np.bincount(rec[body], weights=line_len, minlength=n).astype(np.int64)
+        seq_off = np.zeros(n + 1, dtype=np.int64)
+        np.cumsum(seq_len, out=seq_off[1:])
+        # compact the sequence lines: one gather over the bytes that belong to them
+        pos = np.repeat(s[body] - np.concatenate(([0], np.cumsum(line_len)[:-1])), line_len) + np.arange(int(line_len.sum()), dtype=np.int64)
+        names = buf[np.repeat(s[header] + 1, (e - s)[header] - 1) + (np.arange(int(((e - s)[header] - 1).sum()), dtype=np.int64)
+                                                                    - np.repeat(np.concatenate(([0], np.cumsum((e - s)[header] - 1)[:-1])), (e - s)[header] - 1))]
+        name_len = (e - s)[header] - 1
+        name_off = np.concatenate(([0], np.cumsum(name_len)[:-1])) + int(seq_off[-1])
+        out = np.concatenate((buf[pos], names)) if n else np.zeros(0, dtype=np.uint8)
+        return ReadBlob(out, seq_off[:-1], seq_len, name_off, name_len, None, None, 'FASTA')
+    raise ValueError('File is neither FASTA or FASTQ')

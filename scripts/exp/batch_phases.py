@@ -64,6 +64,29 @@ for rep in range(2):
     print('rep %d  n=%d  matching sets %d | phase A (10000 reads x %d sets) %.3f s | phase B %.3f s | phase C %.3f s | trimmed starts %d ends %d middles %d' % (
         rep, n, len(matching), len(sets), t1 - t0, t2 - t1, t3 - t2, sum(r.start_trim_amount > 0 for r in reads),
         sum(r.end_trim_amount > 0 for r in reads), sum(bool(r.middle_adapter_positions) for r in reads)), flush=True)
+# the same with the reads as a ReadBlob of a FASTQ file (no Python string handling per phase)
+import tempfile
+from custom_porechop_abi_b200.read_blob import load_read_blob
+with tempfile.TemporaryDirectory() as tmp:
+    path = os.path.join(tmp, 'reads.fastq')
+    with open(path, 'w') as f:
+        for r in reads:
+            f.write('@%s\n%s\n+\n%s\n' % (r.name, r.seq, 'I' * len(r.seq)))
+    t0 = time.perf_counter()
+    rb = load_read_blob(path)
+    t_load = time.perf_counter() - t0
+for rep in range(2):
+    for r in reads:
+        r.__init__(r.name, r.seq)
+    t1 = time.perf_counter()
+    pb.find_adapters_at_read_ends(reads, matching, 0, 150, 2, 75.0, vals, None, 4, 1, False, 75.0, 5.0, False, None, engine=eng, read_blob=rb)
+    t2 = time.perf_counter()
+    pb.find_adapters_in_read_middles(reads, matching, 0, 90.0, 10, 100, vals, None, 1, False, engine=eng, read_blob=rb)
+    t3 = time.perf_counter()
+    print('read_blob rep %d  load %.3f s | phase B %.3f s | phase C %.3f s | trimmed starts %d ends %d middles %d' % (
+        rep, t_load, t2 - t1, t3 - t2, sum(r.start_trim_amount > 0 for r in reads), sum(r.end_trim_amount > 0 for r in reads),
+        sum(bool(r.middle_adapter_positions) for r in reads)), flush=True)
+
 if os.environ.get('PROFILE_C'):
     import cProfile, pstats
     for r in reads:

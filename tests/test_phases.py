@@ -102,7 +102,7 @@ def cases():
         return json.load(f)['cases']
 
 
-def run_case(c, eng):
+def run_case(c, eng, read_blob=None):
     from custom_porechop_abi_b200 import porechop_batch as pb
     p = c['params']
     reads = [Read(n, s) for n, s in c['reads']]
@@ -115,14 +115,14 @@ def run_case(c, eng):
     used = [AdapterSet(d) for d in c['matching_used']]
     pb.find_adapters_at_read_ends(reads, used, 0, p['end_size'], p['extra_end_trim'], p['end_threshold'], p['scoring'], None,
                                   p['min_trim_size'], 1, c['check_barcodes'], p['barcode_threshold'], p['barcode_diff'],
-                                  c['require_two_barcodes'], c['forward_or_reverse'], engine=eng)
+                                  c['require_two_barcodes'], c['forward_or_reverse'], engine=eng, read_blob=read_blob)
     for r, g in zip(reads, c['phase_b']):
         assert r.start_trim_amount == g['start_trim_amount'] and r.end_trim_amount == g['end_trim_amount'], r.name
         assert [[a.name, f, pa, s, e] for a, f, pa, s, e in r.start_adapter_alignments] == g['start_alignments'], r.name
         assert [[a.name, f, pa, s, e] for a, f, pa, s, e in r.end_adapter_alignments] == g['end_alignments'], r.name
         assert r.start_barcode_scores == g['start_barcode_scores'] and r.end_barcode_scores == g['end_barcode_scores'], r.name
     pb.find_adapters_in_read_middles(reads, used, 0, p['middle_threshold'], p['good_side'], p['bad_side'], p['scoring'], None, 1,
-                                     False, engine=eng)
+                                     False, engine=eng, read_blob=read_blob)
     for r, g in zip(reads, c['phase_c']):
         assert sorted(r.middle_adapter_positions) == g['middle_adapter_positions'], r.name
         assert sorted(r.middle_trim_positions) == g['middle_trim_positions'], r.name
@@ -155,7 +155,77 @@ def test_trimmed_bounds_follow_python_slicing():
         assert r.seq[lo:hi] == r.get_seq_with_start_end_adapters_trimmed(), (r.seq, r.start_trim_amount, r.end_trim_amount)
 
 
+def _write_fastq(path, records, lower=False, crlf=False):
+    eol = '\r\n' if crlf else '\n'
+    with open(path, 'w', newline='') as f:
+        for name, seq in records:
+            f.write('@' + name + ' extra words' + eol + (seq.lower() if lower else seq) + eol + '+' + eol + 'I' * len(seq) + eol)
+
+
+def test_read_blob_matches_the_reference_loader_semantics(tmp_path):
+    """ReadBlob (read_blob.py): the records of a FASTQ / FASTA file as one buffer + segments.  Names and sequences as the
+    reference's loader + NanoporeRead give them (misc.py:123-168, nanopore_read.py:36-39), windows as _windows packs them,
+    trimmed segments as Python slices them."""
+    import gzip
+    import random
+    from custom_porechop_abi_b200 import porechop_batch as pb
+    from custom_porechop_abi_b200.read_blob import load_read_blob
+    records = cases()[0]['reads'] + [['empty', ''], ['rna', 'ACGUUUUACG'], ['n', 'ACGTNNNACGT']]
+    reads = [Read(n, s) for n, s in records]
+    for variant, kw in (('plain', {}), ('lower', {'lower': True}), ('crlf', {'crlf': True})):
+        path = str(tmp_path / (variant + '.fastq'))
+        _write_fastq(path, records, **kw)
+        if variant == 'plain':                               # gzip goes through the same parser
+            with open(path, 'rb') as f, gzip.open(path + '.gz', 'wb') as g:
+                g.write(f.read())
+            path = path + '.gz'
+        blob = load_read_blob(path)
+        assert len(blob) == len(reads) and blob.file_type == 'FASTQ'
+        for i, r in enumerate(reads):
+            assert blob.seq(i) == r.seq and blob.name(i) == r.name and blob.full_name(i) == r.name + ' extra words'
+            assert blob.quals(i) == 'I' * len(r.seq)
+        for at_end in (False, True):
+            for end_size in (150, 100, 7):
+                b1, l1 = blob.windows(end_size, at_end)
+                b2, l2 = pb._windows(reads, end_size, at_end)
+                assert (l1 == l2).all() and bytes(b1).upper().replace(b'U', b'T') == bytes(b2).replace(b'U', b'T')
+    rng = random.Random(9)
+    st = [rng.randrange(0, 300) if rng.random() < 0.7 else 0 for _ in reads]
+    en = [rng.randrange(0, 300) if rng.random() < 0.7 else 0 for _ in reads]
+    off, ln = blob.trimmed_segments(st, en)
+    for i, r in enumerate(reads):
+        r.start_trim_amount, r.end_trim_amount = st[i], en[i]
+        got = blob.buf[off[i]:off[i] + ln[i]].tobytes().decode().upper()
+        assert got.replace('U', 'T') == r.get_seq_with_start_end_adapters_trimmed().replace('U', 'T'), i
+    # FASTA, sequences over several lines, blank lines in between
+    path = str(tmp_path / 'x.fasta')
+    with open(path, 'w') as f:
+        for name, seq in records:
+            f.write('>' + name + ' more\n')
+            for k in range(0, len(seq), 60):
+                f.write(seq[k:k + 60] + '\n')
+            f.write('\n')
+    blob = load_read_blob(path)
+    assert len(blob) == len(reads) and blob.file_type == 'FASTA'
+    for i, r in enumerate(reads):
+        assert blob.seq(i) == r.seq and blob.name(i) == r.name
+
+
+@pytest.mark.parametrize('idx', [0, 3, 5])
+def test_phase_logic_with_read_blob(idx, tmp_path):
+    """Phases B and C fed from a ReadBlob (windows gathered from the file buffer, phase C's blob = the file's bytes)."""
+    from custom_porechop_abi_b200.read_blob import load_read_blob
+    c = cases()[idx]
+    path = str(tmp_path / 'reads.fastq')
+    _write_fastq(path, c['reads'], lower=(idx == 3))
+    run_case(c, OracleEngine(), read_blob=load_read_blob(path))
+
+
 @pytest.mark.gpu
-def test_phases_on_gpu(engine):
-    for c in cases():
+def test_phases_on_gpu(engine, tmp_path):
+    from custom_porechop_abi_b200.read_blob import load_read_blob
+    for k, c in enumerate(cases()):
         run_case(c, engine)
+        path = str(tmp_path / ('reads%d.fastq' % k))
+        _write_fastq(path, c['reads'], lower=(k % 2 == 1))
+        run_case(c, engine, read_blob=load_read_blob(path))
