@@ -184,14 +184,17 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
         with np.errstate(invalid='ignore'):
             edge_ok = (r_start != 0) if at_end else (r_end != end_size)
             hit = (partial > end_threshold) & edge_ok & (r_end - r_start >= min_trim_size)
-        for i, k in zip(*np.nonzero(hit)):                 # row-major: per read, in adapter order, as the reference appends
-            read, adapter = reads[i], sets[k]
-            entry = (adapter, float(full[i, k]), float(partial[i, k]), int(r_start[i, k]), int(r_end[i, k]))
+        ii, kk = np.nonzero(hit)                           # row-major: per read, in adapter order, as the reference appends
+        fulls, parts = full[ii, kk].tolist(), partial[ii, kk].tolist()
+        starts_, ends_ = r_start[ii, kk].tolist(), r_end[ii, kk].tolist()
+        for i, k, f, pa, rs_, re_ in zip(ii.tolist(), kk.tolist(), fulls, parts, starts_, ends_):
+            read = reads[i]
+            entry = (sets[k], f, pa, rs_, re_)
             if at_end:
-                read.end_trim_amount = max(read.end_trim_amount, (end_size - int(r_start[i, k])) + extra_trim_size)
+                read.end_trim_amount = max(read.end_trim_amount, (end_size - rs_) + extra_trim_size)
                 read.end_adapter_alignments.append(entry)
             else:
-                read.start_trim_amount = max(read.start_trim_amount, int(r_end[i, k]) + extra_trim_size)
+                read.start_trim_amount = max(read.start_trim_amount, re_ + extra_trim_size)
                 read.start_adapter_alignments.append(entry)
         if check_barcodes:
             for k, adapter in enumerate(sets):

@@ -95,3 +95,11 @@ if os.environ.get('PROFILE_C'):
     pb.find_adapters_in_read_middles(reads, matching, 0, 90.0, 10, 100, vals, None, 1, False, engine=eng)
     pr.disable()
     pstats.Stats(pr).sort_stats('tottime').print_stats(14)
+if os.environ.get('PROFILE_B'):
+    import cProfile, pstats
+    for r in reads:
+        r.__init__(r.name, r.seq)
+    pr = cProfile.Profile(); pr.enable()
+    pb.find_adapters_at_read_ends(reads, matching, 0, 150, 2, 75.0, vals, None, 4, 1, False, 75.0, 5.0, False, None, engine=eng, read_blob=rb)
+    pr.disable()
+    pstats.Stats(pr).sort_stats('tottime').print_stats(12)
