@@ -81,10 +81,15 @@ class ReadBlob(object):
         stride = max(16, -(-end_size // 16) * 16)
         lens = np.minimum(self.seq_len, end_size)
         first = self.seq_off + (self.seq_len - lens if at_end else 0)
-        col = np.arange(stride, dtype=np.int64)[None, :]
-        idx = np.minimum(first[:, None] + col, max(len(self.buf) - 1, 0))
-        out = self.buf[idx] if len(self.buf) else np.zeros((len(self), stride), dtype=np.uint8)
-        out[col >= lens[:, None]] = 0
+        out = np.zeros((len(self), stride), dtype=np.uint8)
+        # rows of `stride` contiguous bytes out of a sliding-window view (a row copy each, no index matrix); the few windows
+        # that start within `stride` bytes of the buffer's end are copied one by one
+        fits = first <= len(self.buf) - stride
+        if len(self.buf) >= stride and fits.any():
+            out[fits] = np.lib.stride_tricks.sliding_window_view(self.buf, stride)[first[fits]]
+        for i in np.flatnonzero(~fits):
+            out[i, :lens[i]] = self.buf[first[i]:first[i] + lens[i]]
+        out[np.arange(stride, dtype=np.int32)[None, :] >= lens[:, None]] = 0
         return np.ascontiguousarray(out, dtype=np.uint8), lens.astype(np.int32)
 
     def trimmed_segments(self, start_trim, end_trim):
