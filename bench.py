@@ -207,6 +207,10 @@ def run_gpu_arm(args):
     if not torch.cuda.is_available():
         raise SystemExit('bench.py: no CUDA device; the hot path has no CPU fallback')
     torch.cuda.set_device(local)
+    numa_cpus = None
+    if world > 1:                                # pinned buffers and the submitting thread next to this rank's GPU
+        from custom_porechop_abi_b200.sharding import bind_to_gpu_cpus
+        numa_cpus = bind_to_gpu_cpus(local)
 
     from custom_porechop_abi_b200.engine import AlignmentEngine, RESULT_DTYPE, _ptr
     from custom_porechop_abi_b200 import cpp_function_wrappers as w
@@ -350,7 +354,7 @@ def run_gpu_arm(args):
             'metric': METRIC, 'value': world * n / (ms_step / 1000.0), 'unit': 'reads/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_step, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'int16x2', 'data': 'synthetic',
-            'config': bench_config(args, wl),
+            'config': dict(bench_config(args, wl), host_binding=('rank bound to the %d CPUs next to its GPU (NVML affinity)' % len(numa_cpus)) if numa_cpus else 'none'),
             'gcups': world * wl['cells'] / (ms_step / 1000.0) / 1e9,
             'e2e': {'value': world * n * args.steps / e2e_s, 'unit': 'reads/s',
                     'h2d_bytes_per_step': int((c1['h2d_bytes'] - c0['h2d_bytes']) / args.steps),
