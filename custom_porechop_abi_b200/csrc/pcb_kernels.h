@@ -172,7 +172,9 @@ cudaError_t pcf_launch(const PcbLaunch &L, bool trace, int cls, cudaStream_t st)
 int pcf_occupancy_grid(bool trace, int cls);
 /* Trace scratch per thread: PCF_RING per-unit slots of checkpoints, then the warp's pass-2 ring (PCF_QCAP entries of 20 words
  * per warp = 80 words per thread); see trace_round in pcb_fast.cu. */
-#define PCF_RING 8
+#ifndef PCF_RING
+#define PCF_RING 4
+#endif
 #define PCF_QCAP 128
 static inline uint64_t pcf_ck_words(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * NR; }
 static inline uint64_t pcf_scratch_words_trace(int mmax, int cls)
