@@ -111,6 +111,8 @@ struct pcb_context {
     enum { MAX_PIECES = 4 };
     TaskPlan plans[MAX_PIECES];
     int n_pieces = 1, pieces_sent = 0;
+    int plan_pieces = 1;                 // plans over the blob: one per piece (kernels of piece p under the copy of piece p+1), or one for
+                                         // the whole blob when it was announced early and is on the device before its tasks are (pcb_upload_reads)
     const char *pending_blob = nullptr;  // host blob whose later pieces are sent once the plans exist (small planning copies
                                          // would otherwise queue behind the whole blob on the copy engine)
     // outputs / scratch
@@ -591,13 +593,14 @@ static int send_pieces(pcb_context *c, int upto)
 // its own plan (the tasks whose segment ends inside it), so that the kernels of piece p run while piece p + 1 is still
 // on the PCIe bus.  Only piece 0 is sent here; the rest follows from send_pieces (after the plans exist, or pumped by
 // the window calls of the same step: small copies issued later would otherwise queue behind the whole blob).
-static int setup_blob(pcb_context *c, const char *seq_blob, int64_t blob_len, int n_pieces, int send_now)
+static int setup_blob(pcb_context *c, const char *seq_blob, int64_t blob_len, int n_pieces, int send_now, bool one_plan)
 {
     for (auto &pl : c->plans) pl.valid = false;
     PCB_CUDA(c, c->d_ascii_t.reserve((size_t)blob_len + 16));
     PCB_CUDA(c, c->d_arena_t.reserve((size_t)blob_len + 16));
     n_pieces = std::max(1, std::min<int>(n_pieces, pcb_context::MAX_PIECES));
     c->n_pieces = n_pieces;
+    c->plan_pieces = one_plan ? 1 : n_pieces;
     c->pending_blob = nullptr;
     PCB_CUDA(c, cudaMemsetAsync(c->d_arena_t.p + blob_len, 0, 16, c->stream));   // valid codes past the last segment
     if (n_pieces == 1) {
@@ -620,6 +623,7 @@ static int setup_blob(pcb_context *c, const char *seq_blob, int64_t blob_len, in
             P.has_ready = true;
             // the kernels fetch bases up to 8 bytes past a segment's end: a task waits for the piece that holds those too
             P.end_lo = p == 0 ? -1 : P.b0 - 16; P.end_hi = p == n_pieces - 1 ? blob_len : P.b1 - 16;
+            if (one_plan) { P.end_lo = p == 0 ? -1 : blob_len; P.end_hi = blob_len; }      // plan 0 takes every task
         }
         c->pending_blob = seq_blob; c->pieces_sent = 0;
     }
@@ -675,7 +679,7 @@ static int stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, c
         return PCB_ERR_ARG;
     cudaSetDevice(c->device);
     c->uploaded_len = -1;
-    int rc = setup_blob(c, seq_blob, blob_len, n_pieces, 1);
+    int rc = setup_blob(c, seq_blob, blob_len, n_pieces, 1, false);
     if (rc) return rc;
     return stage_segments(c, blob_len, seg_off, seg_len, task_adapter, n_tasks);
 }
@@ -687,7 +691,7 @@ extern "C" int pcb_upload_reads(pcb_context *c, const char *seq_blob, int64_t bl
     c->n_tasks = 0;
     // nothing is sent yet: the window calls that follow pump the pieces AFTER their own (small) copies, so that those
     // do not wait behind the blob on the copy engine; pcb_align_tasks sends whatever is left
-    int rc = setup_blob(c, seq_blob, blob_len, blob_pieces(blob_len), 0);
+    int rc = setup_blob(c, seq_blob, blob_len, blob_pieces(blob_len), 0, true);
     if (rc) return rc;
     c->uploaded_len = blob_len;
     return PCB_OK;
@@ -831,17 +835,16 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
     c->S().n_results = (int64_t)nt;
     if (nt == 0) return PCB_OK;
     int rc;
-    for (int p = 0; p < c->n_pieces; ++p)
+    for (int p = 0; p < c->plan_pieces; ++p)
         if ((!c->plans[p].valid || c->plans[p].stamp != c->stamp) && (rc = build_task_plan(c, c->plans[p], p == 0))) return rc;
     if ((rc = send_pieces(c, c->n_pieces))) return rc;
     PCB_CUDA(c, c->S().d_out.reserve(nt));
     uint64_t scratch = 0;
-    for (int p = 0; p < c->n_pieces; ++p) scratch = std::max(scratch, c->plans[p].scratch_words);
+    for (int p = 0; p < c->plan_pieces; ++p) scratch = std::max(scratch, c->plans[p].scratch_words);
     PCB_CUDA(c, c->d_scratch.reserve((size_t)scratch));
     if (!c->deferred) PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
-    for (int p = 0; p < c->n_pieces; ++p) {
-        pcb_context::TaskPlan &P = c->plans[p];
-        if (P.has_ready) PCB_CUDA(c, cudaStreamWaitEvent(c->stream, P.ready, 0));     // this piece of the blob has arrived
+    auto arrive = [&](pcb_context::TaskPlan &P) -> int {   // this piece of the blob is on the device, as codes
+        if (P.has_ready) PCB_CUDA(c, cudaStreamWaitEvent(c->stream, P.ready, 0));
         if (!P.encoded) {
             if (P.b1 > P.b0) {
                 PCB_CUDA(c, pcb_launch_encode(c->d_ascii_t.p + P.b0, c->d_arena_t.p + P.b0, (uint64_t)(P.b1 - P.b0), c->stream));
@@ -849,6 +852,12 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
             }
             P.encoded = true;
         }
+        return PCB_OK;
+    };
+    if (c->plan_pieces == 1) for (int p = 1; p < c->n_pieces; ++p) if ((rc = arrive(c->plans[p]))) return rc;
+    for (int p = 0; p < c->plan_pieces; ++p) {
+        pcb_context::TaskPlan &P = c->plans[p];
+        if ((rc = arrive(P))) return rc;
         bool merged = false;
         for (const auto &pl : P.launches) {
             if (pl.kind == 2 && !merged) {
