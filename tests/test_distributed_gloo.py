@@ -48,3 +48,15 @@ def test_world_size_two_gloo(tmp_path):
                          capture_output=True, text=True, timeout=300, env=env)
     assert out.returncode == 0, out.stderr[-2000:]
     assert 'GLOO_OK' in out.stdout
+
+
+def test_bind_to_gpu_cpus_changes_nothing_without_nvml():
+    """Without a GPU / NVML the binding helper leaves the process where it is and says so."""
+    import os
+    from custom_porechop_abi_b200.sharding import bind_to_gpu_cpus
+    before = os.sched_getaffinity(0)
+    got = bind_to_gpu_cpus(0)
+    assert got is None or set(got) <= before
+    if got is None:
+        assert os.sched_getaffinity(0) == before
+    os.sched_setaffinity(0, before)
