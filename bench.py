@@ -323,9 +323,9 @@ def run_gpu_arm(args):
     k_tasks = n * len(ids24)
     # algorithmic bytes of that launch: window bases read once + adapters + one 32-byte record per pair
     k_bytes = int(wlen.astype(np.int64).sum()) + int(ad_len[ids24].sum()) + 32 * k_tasks
-    # DRAM traffic of the same kernel from the ncu --set full capture (profiles/kernel_r1v.md: 1.251 GB read + 3.942 GB
+    # DRAM traffic of the same kernel from the ncu --set full capture (profiles/kernel_r1y.md: 1.251 GB read + 3.942 GB
     # written for 32768 windows x 109 adapters = 1454 B per pair, almost all of it the checkpoint ring), per launch
-    k_traffic = int(round((1.251098e9 + 3.942171e9) / (32768 * 109) * k_tasks))
+    k_traffic = int(round((1.251407e9 + 3.941954e9) / (32768 * 109) * k_tasks))
     # the scan kernel of the full-length search (k_fast<SCAN>), timed with its planner / merge / window-trace launches
     eng.select_slot(2)
     eng.timer_start()
@@ -364,7 +364,7 @@ def run_gpu_arm(args):
             'clocks': clocks,
             'roofline': {'bound': 'hbm', 'kernel': 'k_fast<TRACE,24,EXACT,16> (end windows x %d 24-base end sequences, %d launch)' % (len(ids24), k_launches), 'achieved': k_bytes / (k_ms / 1000.0) / 1e9,
                          'peak': hbm_peak, 'unit': 'GB/s', 'frac': k_bytes / (k_ms / 1000.0) / 1e9 / hbm_peak, 'traffic': k_traffic,
-                         'traffic_source': 'ncu dram__bytes_read.sum + dram__bytes_write.sum per (window, adapter) pair of profiles/kernel_r1v.md x the pairs of this launch',
+                         'traffic_source': 'ncu dram__bytes_read.sum + dram__bytes_write.sum per (window, adapter) pair of profiles/kernel_r1y.md x the pairs of this launch',
                          'peak_source': peak_src, 'launch_ms': k_ms,
                          'note': 'integer-issue bound kernel: see int_dp; achieved counts the algorithmic bytes only, the traffic above them is the trace checkpoints (written once in pass 1, a sixth read back in pass 2)'},
             'int_dp': {'kernel_gcups': k_cells / (k_ms / 1000.0) / 1e9, 'model_peak_gcups': int_peak_gcups,
