@@ -354,7 +354,8 @@ def run_gpu_arm(args):
             'metric': METRIC, 'value': world * n / (ms_step / 1000.0), 'unit': 'reads/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_step, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'int16x2', 'data': 'synthetic',
-            'config': dict(bench_config(args, wl), host_binding=('rank bound to the %d CPUs next to its GPU (NVML affinity)' % len(numa_cpus)) if numa_cpus else 'none'),
+            'config': bench_config(args, wl),
+            'host_binding': ('rank bound to the %d CPUs next to its GPU (NVML affinity)' % len(numa_cpus)) if numa_cpus else 'none',
             'gcups': world * wl['cells'] / (ms_step / 1000.0) / 1e9,
             'e2e': {'value': world * n * args.steps / e2e_s, 'unit': 'reads/s',
                     'h2d_bytes_per_step': int((c1['h2d_bytes'] - c0['h2d_bytes']) / args.steps),
