@@ -118,7 +118,8 @@ struct pcb_context {
     // outputs / scratch
     DevBuf<uint32_t> d_scratch;
     DevBuf<int32_t> d_err;
-    int grid_trace = 0, grid_scan = 0, grid_ftrace[PCF_NCLS] = {}, grid_fscan[PCF_NCLS] = {};
+    int grid_trace = 0, grid_scan = 0, grid_fp1[PCF_NCLS] = {}, grid_fp2[PCF_NCLS] = {}, grid_fscan[PCF_NCLS] = {};   // fast kernels: pass 1, rounds, scan
+    uint64_t scratch_budget = 6144ull << 18;   // words of checkpoint scratch a batch of the fast trace may use (PCB_SCRATCH_MB)
     pcb_counters cnt{};
     bool ktiming = false;
 
@@ -176,12 +177,17 @@ extern "C" int pcb_create(int device, pcb_context **out)
     for (auto &sl : c->slots) if (cudaEventCreateWithFlags(&sl.staged, cudaEventDisableTiming) != cudaSuccess) { g_global_err = "event creation failed"; delete c; return PCB_ERR_CUDA; }
     c->grid_trace = pcb_occupancy_grid(0);
     c->grid_scan = pcb_occupancy_grid(1);
-    for (int cls = 0; cls < PCF_NCLS; ++cls) { c->grid_ftrace[cls] = pcf_occupancy_grid(true, cls); c->grid_fscan[cls] = pcf_occupancy_grid(false, cls); }
+    for (int cls = 0; cls < PCF_NCLS; ++cls) {
+        c->grid_fscan[cls] = pcf_occupancy_grid(0, cls); c->grid_fp1[cls] = pcf_occupancy_grid(1, cls); c->grid_fp2[cls] = pcf_occupancy_grid(2, cls);
+    }
     if (const char *gl = getenv("PCB_GRID_LIMIT")) {       // tests: few CTAs, so that a small input gives every warp many units
         const int lim = std::max(1, atoi(gl));
         c->grid_trace = std::min(c->grid_trace, lim); c->grid_scan = std::min(c->grid_scan, lim);
-        for (int cls = 0; cls < PCF_NCLS; ++cls) { c->grid_ftrace[cls] = std::min(c->grid_ftrace[cls], lim); c->grid_fscan[cls] = std::min(c->grid_fscan[cls], lim); }
+        for (int cls = 0; cls < PCF_NCLS; ++cls) {
+            c->grid_fscan[cls] = std::min(c->grid_fscan[cls], lim); c->grid_fp1[cls] = std::min(c->grid_fp1[cls], lim); c->grid_fp2[cls] = std::min(c->grid_fp2[cls], lim);
+        }
     }
+    if (const char *mb = getenv("PCB_SCRATCH_MB")) c->scratch_budget = (uint64_t)std::max(1, atoi(mb)) << 18;   // tests: many batches from a small input
     if (c->d_err.reserve(1) != cudaSuccess) { g_global_err = "cudaMalloc failed"; delete c; return PCB_ERR_NOMEM; }
     *out = c;
     return PCB_OK;
@@ -312,18 +318,42 @@ static void fill_launch_common(pcb_context *c, PcbLaunch &L, bool task_arena = f
 
 // launch with optional per-kernel event timing
 // cls: 0 .. PCF_NCLS-1 = fast kernels (pcb_fast.cu), PCF_NCLS = general kernels (pcb_kernels.cu)
-static int launch_dp(pcb_context *c, const PcbLaunch &L, bool trace, int64_t cells, int cls = PCF_NCLS)
+// A fast trace is two kernels per batch of units (pass 1 -> checkpoints + end cells in scratch, then the rounds); a batch is
+// as many units as the scratch budget holds.
+static int launch_dp(pcb_context *c, PcbLaunch &L, bool trace, int64_t cells, int cls = PCF_NCLS)
 {
+    const int64_t n_units = L.src.n_units;
+    if (n_units == 0) return PCB_OK;
     if (c->ktiming) PCB_CUDA(c, cudaEventRecord(c->kev0, c->stream));
-    if (cls < PCF_NCLS) PCB_CUDA(c, pcf_launch(L, trace, cls, c->stream));
-    else         PCB_CUDA(c, trace ? pcb_launch_trace(L, c->stream) : pcb_launch_scan(L, c->stream));
+    int launches = 1;
+    if (cls < PCF_NCLS && trace) {
+        const uint64_t per_unit = pcf_unit_words_trace(L.mmax, cls);
+        const int64_t per_batch = (int64_t)std::max<uint64_t>(1, std::min<uint64_t>({(uint64_t)n_units, c->scratch_budget / per_unit, 1ull << 25}));
+        cudaError_t e = c->d_scratch.reserve((size_t)(per_unit * (uint64_t)per_batch));
+        if (e != cudaSuccess) { cudaGetLastError(); return c->fail(PCB_ERR_NOMEM, "trace scratch of %.1f MB: %s", per_unit * per_batch * 4 / 1e6, cudaGetErrorString(e)); }
+        L.scratch = c->d_scratch.p;
+        L.entries = reinterpret_cast<uint4 *>(c->d_scratch.p + (per_unit - 128) * (uint64_t)per_batch);
+        const int W = PCB_BLOCK / 32;
+        launches = 0;
+        for (int64_t u0 = 0; u0 < n_units; u0 += per_batch) {
+            L.unit0 = u0; L.unit1 = std::min(n_units, u0 + per_batch);
+            const int64_t ctas = (L.unit1 - L.unit0 + W - 1) / W;
+            L.grid = (int)std::min<int64_t>(c->grid_fp1[cls], ctas);
+            PCB_CUDA(c, pcf_launch_trace(L, cls, (int)std::min<int64_t>(c->grid_fp2[cls], ctas), c->stream));
+            launches += 2;
+        }
+    } else {
+        L.unit0 = 0; L.unit1 = n_units;
+        if (cls < PCF_NCLS) PCB_CUDA(c, pcf_launch_scan(L, cls, c->stream));
+        else         PCB_CUDA(c, trace ? pcb_launch_trace(L, c->stream) : pcb_launch_scan(L, c->stream));
+    }
     if (c->ktiming) {
         PCB_CUDA(c, cudaEventRecord(c->kev1, c->stream));
         PCB_CUDA(c, cudaEventSynchronize(c->kev1));
         float ms = 0; PCB_CUDA(c, cudaEventElapsedTime(&ms, c->kev0, c->kev1));
         c->cnt.dp_kernel_ms += ms;
     }
-    c->cnt.kernel_launches++; c->cnt.dp_kernel_launches++; c->cnt.dp_cells += cells;
+    c->cnt.kernel_launches += launches; c->cnt.dp_kernel_launches += launches; c->cnt.dp_cells += cells;
     return PCB_OK;
 }
 
@@ -451,7 +481,7 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
         const int nmax = max_adapter_len(c, h_list, cnt);
         const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
         if (cls == PCF_NCLS && (rc = check_range(c, nmax, mmax))) return rc;
-        const int gmax = cls < PCF_NCLS ? c->grid_ftrace[cls] : c->grid_trace;
+        const int gmax = cls < PCF_NCLS ? c->grid_fp1[cls] : c->grid_trace;
         const int64_t warps = (int64_t)gmax * (PCB_BLOCK / 32);
         int64_t sum_n = 0;                 // algorithmic cell count: sum over windows of len x sum over ids of adapter length
         for (int i = 0; i < cnt; ++i) sum_n += c->ad_off[h_list[i] + 1] - c->ad_off[h_list[i]];
@@ -467,8 +497,7 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
             if (w0 >= w1) break;
             const int64_t n_units = ((w1 - w0 + 63) / 64) * cnt;
             const int grid = (int)std::min<int64_t>(gmax, (n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
-            rc = ensure_scratch(c, cls < PCF_NCLS ? pcf_scratch_words_trace(mmax, cls) : pcb_scratch_words_trace(mmax, smax), grid);
-            if (rc) return rc;
+            if (cls == PCF_NCLS && (rc = ensure_scratch(c, pcb_scratch_words_trace(mmax, smax), grid))) return rc;
             PcbLaunch L; fill_launch_common(c, L);
             L.arena = S.d_arena.p + (uint64_t)w0 * S.stride;
             L.out = S.d_out.p + w0 * n;
@@ -638,6 +667,8 @@ static int stage_segments(pcb_context *c, int64_t blob_len, const int64_t *seg_o
 {
     for (auto &pl : c->plans) pl.valid = false;
     c->n_tasks = 0;
+    // result slots, task and chunk indices are 32-bit on the device (PcbTask.out_idx, PcbLong.chunk0 / win_slot)
+    if (n_tasks >= (1ll << 31) - 64) return c->fail(PCB_ERR_RANGE, "%lld tasks in one call: the task path indexes with 32 bits", (long long)n_tasks);
     PCB_CUDA(c, c->d_seg_off.reserve((size_t)n_tasks + 1));
     PCB_CUDA(c, c->d_seg_len.reserve((size_t)n_tasks + 1));
     PCB_CUDA(c, c->d_seg_ad.reserve((size_t)n_tasks + 1));
@@ -728,6 +759,11 @@ static int build_task_plan(pcb_context *c, pcb_context::TaskPlan &P, bool first_
         const WindowBounds wb = window_bounds(c->sc, x.n);
         x.warm = wb.warm; x.span = wb.span; x.chunked = wb.ok ? 1 : 0;
         x.direct_max = std::max(direct_default, wb.ok ? wb.warm + wb.span + 8 : 0);
+        // what the fast kernels take: direct tasks of <= PCF_MAX_TRACE_M columns (longer segments are scanned in chunks and
+        // traced on a window; a window wider than that goes to the general kernel, cls_of below) and scan chunks of
+        // <= PCF_MAX_SCAN_M columns including their warm-up margin
+        if (x.cls < PCF_NCLS && wb.ok && wb.warm + 4100 > PCF_MAX_SCAN_M) x.cls = PCF_NCLS;
+        if (x.cls < PCF_NCLS) x.direct_max = std::min(x.direct_max, PCF_MAX_TRACE_M);
     }
     // chunk length: enough chunks to fill the machine, but long enough to amortise the warm-up margin
     const int chunk = (int)std::min<int64_t>(4096, std::max<int64_t>(1024, c->task_long_cols / (2 * 64 * (int64_t)std::max(1, c->grid_fscan[0]) * (PCB_BLOCK / 32))));
@@ -775,7 +811,7 @@ static int build_task_plan(pcb_context *c, pcb_context::TaskPlan &P, bool first_
             const int lmax = kind == 2 ? wmax : std::max(1, kind == 0 ? mmax[(size_t)q] : mmax[(size_t)(PCF_NCLS + 1) + q]);
             if (!fast && (rc = check_range(c, nmax, lmax))) return rc;
             if (fast && lmax > (trace ? PCF_MAX_TRACE_M : PCF_MAX_SCAN_M)) return c->fail(PCB_ERR_RANGE, "internal: segment of %d columns sent to the fast kernels", lmax);
-            const int gmax = fast ? (trace ? c->grid_ftrace[q] : c->grid_fscan[q]) : (trace ? c->grid_trace : c->grid_scan);
+            const int gmax = fast ? (trace ? c->grid_fp1[q] : c->grid_fscan[q]) : (trace ? c->grid_trace : c->grid_scan);
             // fewer tasks per warp when there is not enough work to fill the machine (a warp's time does not depend on its lanes)
             const int64_t warps = (int64_t)gmax * (PCB_BLOCK / 32);
             const int per_unit = (int)std::min<int64_t>(64, std::max<int64_t>(2, (total + warps - 1) / warps));
@@ -798,13 +834,14 @@ static int build_task_plan(pcb_context *c, pcb_context::TaskPlan &P, bool first_
             pl.n_units = (int64_t)all_units.size() - pl.unit0;
             pl.mmax = lmax; pl.nmax = nmax; pl.smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
             pl.grid = (int)std::min<int64_t>(gmax, (pl.n_units + PCB_BLOCK / 32 - 1) / (PCB_BLOCK / 32));
-            const uint64_t words = fast ? (trace ? pcf_scratch_words_trace(lmax, q) : 1)
-                                        : (trace ? pcb_scratch_words_trace(lmax, pl.smax) : pcb_scratch_words_scan(lmax, pl.smax));
+            // (the fast trace sizes its own scratch, batch by batch: launch_dp)
+            const uint64_t words = fast ? 1 : (trace ? pcb_scratch_words_trace(lmax, pl.smax) : pcb_scratch_words_scan(lmax, pl.smax));
             P.scratch_words = std::max<uint64_t>(P.scratch_words, words * (uint64_t)pl.grid * PCB_BLOCK);
             P.launches.push_back(pl);
         }
     }
     if (!P.launches.empty() && first_piece) P.launches[0].cells = c->task_cells;      // algorithmic cell updates of the whole run
+    if (run >= (1ll << 31) - 64) return c->fail(PCB_ERR_RANGE, "%lld kernel tasks (direct + scan chunks + windows) in one plan: the task path indexes with 32 bits", (long long)run);
     P.n_chunks = pa.win_task0 - pa.scan_task0;
     P.n_long = run - pa.win_task0;
     P.win_task0 = pa.win_task0;

@@ -1,30 +1,34 @@
 /*
- * pcb_fast.cu -- the fast sm_100a kernels of the adapter-alignment hot path (affine schemes, adapters of <= 32 bases).
+ * pcb_fast.cu -- the fast sm_100a kernels of the adapter-alignment hot path (affine schemes, ACGT adapters of <= 52 bases).
  *
  * Same result contract as pcb_kernels.cu (reference: porechop_abi/src/adapter_align.cpp:11-31 = SeqAn 2.4.0 globalAlignment
  * with all four end gaps free, Gotoh recursion seqan/align/dp_formula_affine.h:65-124, single trace, then
  * porechop_abi/src/alignment.cpp:5-110), but organised around what the B200 integer pipes cost (measured with
- * scripts/microbench/pipes.cu: every packed 16x2 / DPX / PRMT / LOP3 instruction is 2 clk per warp on the ALU pipe,
- * 32-bit adds about 1.4 clk, and FMA-pipe work does not hide under ALU work), i.e. around the instruction count per cell:
+ * scripts/microbench/pipes.cu: every packed 16x2 / DPX / PRMT / LOP3 / IMAD instruction is 2 clk per warp and sub-partition,
+ * 32-bit adds about 1.4 clk, and FMA-pipe work hides only a little under ALU work), i.e. around the instruction count per cell:
  *
  *   1. anti-diagonal bias.  Every DP value is stored as  x + b*(i+j) + B0  with b = -gapOpen.  All four candidates of a
  *      cell share the bias, so every comparison (and therefore every tie-break) is unchanged, but
  *        - M + gapOpen needs no instruction (gapOpen + b == 0),
  *        - all stored values and the substitution scores (s + 2b) are non-negative, so the diagonal add is a plain
  *          32-bit add on the packed pair (no carry can cross the halves).
- *      Score-only cell for two tasks: PRMT (score of this read base against the adapter base, by byte select from a
- *      per-column profile word), 32-bit add, 2 x VIADDMNMX.S16x2 (H and V), VIMNMX3.S16x2 (M) = 5 instructions.
- *   2. two passes instead of a trace matrix.  Pass 1 is score-only: it finds SeqAn's end cell (dp_scout.h:167-180) and
- *      checkpoints the DP column every PCF_C columns (a few hundred bytes per task pair, L2 resident).  Pass 2 recomputes,
- *      with trace flags, only the PCF_C-column blocks the traceback actually walks through (usually 1-2 of them), keeps the
- *      flags in shared memory and walks them.  Values are 15-bit non-negative, so "a >= b" is bit 15 of
- *      (a + 0x8000 - b): one IADD3 per flag, extracted four at a time with PRMT in sign-replicate mode.
- *   3. the scan kernel for long reads (middle-adapter search) is pass 1 alone, with the bias re-based every 1024 columns.
- *
+ *      Score-only cell for two tasks: LDS (substitution scores of the two read bases against the adapter base, from a
+ *      per-warp table in shared memory), 32-bit add, 2 x VIADDMNMX.S16x2 (H and V), VIMNMX3.S16x2 (M): 4 integer
+ *      instructions; the lean column loop of the built library runs at 5.75 instructions per cell pair.
+ *   2. two passes, two kernels, instead of a trace matrix.  k_fast<1> (pass 1) is score-only: it finds SeqAn's end cell
+ *      (dp_scout.h:167-180) and leaves the DP column of every C-th column in HBM (one 2*NR-word record per thread and
+ *      checkpoint, streaming stores).  k_rounds (pass 2) recomputes, with trace flags, only the C-column blocks a traceback
+ *      actually walks through (1.8 of them on average), keeps the flags in shared memory and walks them.  Values are
+ *      15-bit non-negative, so "a >= b" is bit 15 of (a + 0x8000 - b): one IADD3 per flag, extracted four at a time with
+ *      PRMT in sign-replicate mode.  Two kernels because the passes want different things: pass 1 is a register-bound
+ *      integer stream with no memory stalls, the rounds are short latency-bound phases (checkpoint fetch, flag walk) that
+ *      need flag memory and resident warps; fused into one kernel (round 1) each held the other back.
+ *   3. the scan kernel for long reads (middle-adapter search) is pass 1 without checkpoints (k_fast<0>), with the bias
+ *      re-based every 1024 columns.
  *   4. no copies, no waits.  The column body is straight-line code over NR rows (template parameter: 24 = the length of
- *      almost every Porechop adapter and barcode, exact; 24 / 32 / 40 / 52 = any shorter-or-equal adapter, bottom-aligned, the
- *      rows above the adapter being exact copies of DP row 0), so ptxas updates the DP registers in place; read bases are fetched four columns
- *      at a time, one group ahead of their use, so that no column waits on a global load.
+ *      almost every Porechop adapter and barcode, exact; 24 / 32 / 40 / 52 = any shorter-or-equal adapter, bottom-aligned,
+ *      the rows above the adapter being exact copies of DP row 0), so ptxas updates the DP registers in place; read bases
+ *      are fetched four columns at a time, one group ahead of their use, so that no column waits on a global load.
  *
  * One thread = two tasks (the halves of each 32-bit register), one warp = 64 tasks sharing an adapter, as in pcb_kernels.cu.
  * Sequence codes in the arenas are Dna5 code * 8 (0, 8, 16, 24, 32 = N), so that a code is directly a byte shift.
@@ -37,13 +41,18 @@
 
 namespace {
 
-#ifdef PCF_FORCE_MINB
-#define PCF_MINB(TRACE, NR) PCF_FORCE_MINB
-#else
-// measured on B200 (scripts/exp/kbench.py, phases.py): the kernels issue integer instructions at the pipes' limit with 2-3
-// CTAs per SM already; a larger register budget (no spills, fewer register moves) beats more resident warps
-#define PCF_MINB(TRACE, NR) (((TRACE) && (NR) <= 24) ? 3 : 2)
+// CTAs per SM the register allocation is held to.  Measured on B200: the score-only kernels issue integer instructions at the
+// pipes' limit with 2-3 CTAs per SM already; a larger register budget (no spills, fewer register moves) beats more warps.
+#ifndef PCF_MINB_SCAN
+#define PCF_MINB_SCAN 2
 #endif
+#ifndef PCF_MINB_P1
+#define PCF_MINB_P1(NR) ((NR) <= 32 ? 3 : 2)
+#endif
+#ifndef PCF_MINB_P2
+#define PCF_MINB_P2(NR) ((NR) <= 24 ? 3 : 2)      /* shared memory (flags + queue) allows no more */
+#endif
+#define PCF_MINB(MODE, NR) ((MODE) ? PCF_MINB_P1(NR) : PCF_MINB_SCAN)
 #ifndef PCF_UNROLL
 #define PCF_UNROLL 2
 #endif
@@ -52,7 +61,6 @@ constexpr int UNR = PCF_UNROLL;
 #define PCF_UNROLL2 1
 #endif
 constexpr int UNR2 = PCF_UNROLL2;
-constexpr int RT = PCB_RT;            // 32 adapter rows in registers
 constexpr int B0 = 64;                // base bias: keeps every stored value > 0
 constexpr int OFF = 2048;             // offset of un-biased scores in the best-cell comparison (true score + OFF > 0)
 constexpr int REBASE = 1024;          // scan: columns between two re-basings of the anti-diagonal bias
@@ -249,236 +257,31 @@ __device__ __forceinline__ void walk_step(const uint32_t *s_fl, const uint32_t *
 }
 
 // ------------------------------------------------------------------------------------------------
-// Pass 2 as a per-warp work queue.  A task's traceback crosses 1.8 flag blocks on average but the longest of 64 crosses 3+,
-// so a warp that takes its 64 tasks through pass 2 in lockstep spends a third of its rounds on a few lanes.  Instead every
-// task that still has blocks to go is an ENTRY of a ring in global memory (L2-resident: PCF_QCAP entries of PCF_QF words
-// per warp), and a ROUND pops 64 entries -- from whatever units they come, the adapter is the same --, rebuilds one flag
-// block for each, walks it, writes the results of the paths that ended and pushes the others back.  Rounds run when the
-// ring holds 64 entries, so every lane of a round works; the ring is drained when the warp's adapter changes and at the
-// end.  Checkpoints live in a ring of PCF_RING per-unit slots; s_live[slot] counts the entries that still need a slot.
-// ------------------------------------------------------------------------------------------------
-constexpr int PCF_QF = 20;
-enum { QF_OFFLO, QF_OFFHI, QF_LEN, QF_COL0, QF_MTRUE, QF_OUTLO, QF_OUTHI, QF_CI, QF_CJ, QF_ENDI, QF_ENDJ, QF_ST, QF_SCORE,
-       QF_ACC, QF_CKREF = QF_ACC + 6 };
-static_assert(QF_CKREF + 1 == PCF_QF, "queue entry layout");
-
-struct RoundCtx {
-    uint32_t *queue;                 // [PCF_QF][PCF_QCAP] of this warp
-    int head, count;                 // warp-uniform
-    int tbl_off, code_off, fl_off, live_off;   // word offsets into the CTA's dynamic shared memory (pointers through this struct
-                                     // would lose their address space and turn every LDS / STS into a generic access)
-    const uint32_t *ck_warp;         // checkpoint area of the warp's lane 0, ring slot 0
-    uint64_t ckw, T;                 // checkpoint words per thread and ring slot; threads in the grid
-    const uint8_t *arena;
-    pcb_result *out;
-    int32_t *err_flag;
-    int n, r0, b, lane;
-    uint32_t GEB, Bp;
-};
-
-template <int NR, bool EXACT, int C>
-__device__ __noinline__ void trace_round(RoundCtx &q)
-{
-    constexpr int FW = NR / 4;
-    // the context lives in local memory: take what the loops use into registers once
-    const int lane = q.lane, n = q.n, r0 = q.r0, b = q.b;
-    const uint64_t T = q.T, ckw = q.ckw;
-    extern __shared__ uint32_t smem[];
-    const uint32_t *const tbl = smem + q.tbl_off, *const s_code = smem + q.code_off, *const ck_warp = q.ck_warp;
-    uint32_t *const s_fl = smem + q.fl_off;
-    volatile int *const s_live = reinterpret_cast<volatile int *>(smem + q.live_off);
-    const uint32_t GEB = q.GEB, Bp = q.Bp;
-    const int take = min(q.count, 64);
-    // An entry's fields are fetched where they are needed (what the flag columns need now, the walk's accumulators before
-    // the walk, the rest before the result is written or the entry goes back): the column loop wants the registers.
-    uint64_t off[2]; int64_t oidx[2];
-    int len[2], col0[2], mtrue[2], ci[2], cj[2], endi[2], endj[2], st[2], score[2], ckref[2];
-    WalkAcc acc[2];
-    bool valid[2];
-    const uint32_t *const qp0 = q.queue + ((q.head + 2 * lane) & (PCF_QCAP - 1));
-    const uint32_t *const qp1 = q.queue + ((q.head + 2 * lane + 1) & (PCF_QCAP - 1));
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        valid[h] = 2 * lane + h < take;
-        const uint32_t *p = h ? qp1 : qp0;
-        off[h] = 0; len[h] = ci[h] = cj[h] = st[h] = ckref[h] = 0;
-        if (valid[h]) {
-            off[h] = (uint64_t)p[QF_OFFLO * PCF_QCAP] | ((uint64_t)p[QF_OFFHI * PCF_QCAP] << 32);
-            len[h] = (int)p[QF_LEN * PCF_QCAP];
-            ci[h] = (int)p[QF_CI * PCF_QCAP]; cj[h] = (int)p[QF_CJ * PCF_QCAP];
-            st[h] = (int)p[QF_ST * PCF_QCAP]; ckref[h] = (int)p[QF_CKREF * PCF_QCAP];
-        }
-    }
-    auto load_acc = [&]() {
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const uint32_t *p = h ? qp1 : qp0;
-            walk_acc_init(acc[h]);
-            if (valid[h]) {
-                acc[h].nD = (int)p[(QF_ACC + 0) * PCF_QCAP]; acc[h].matches = (int)p[(QF_ACC + 1) * PCF_QCAP];
-                acc[h].kA = (int)p[(QF_ACC + 2) * PCF_QCAP]; acc[h].kR = (int)p[(QF_ACC + 3) * PCF_QCAP];
-                acc[h].jA = (int)p[(QF_ACC + 4) * PCF_QCAP]; acc[h].iR = (int)p[(QF_ACC + 5) * PCF_QCAP];
-            }
-        }
-    };
-    q.head = (q.head + take) & (PCF_QCAP - 1); q.count -= take;
-
-    // block of each half: columns k*C+1 .. k*C+C, holding its current column
-    const bool go0 = valid[0] && ci[0] > 0 && cj[0] > 0, go1 = valid[1] && ci[1] > 0 && cj[1] > 0;
-    const int k0 = go0 ? (cj[0] - 1) / C : 0, k1 = go1 ? (cj[1] - 1) / C : 0;
-    const int jb0 = k0 * C, jb1 = k1 * C;
-    const int tmax = __reduce_max_sync(0xffffffffu, max(go0 ? cj[0] - jb0 : 0, go1 ? cj[1] - jb1 : 0));
-    if (tmax > 0) {
-        const uint8_t *const seq0 = q.arena + off[0], *const seq1 = q.arena + off[1];
-        const int lim0 = max(len[0] - 1, 0), lim1 = max(len[1] - 1, 0);
-        // the block's read bases (C per half), then the checkpointed column the block starts from
-        uint32_t q0[C / 4], q1[C / 4];
-#pragma unroll
-        for (int g = 0; g < C / 4; ++g) {
-            q0[g] = join4(load4(seq0, jb0 + 4 * g, lim0)); q1[g] = join4(load4(seq1, jb1 + 4 * g, lim1));
-            s_fl[(C * FW + g) * PCB_BLOCK] = q0[g]; s_fl[(C * FW + C / 4 + g) * PCB_BLOCK] = q1[g];   // for the walk
-        }
-        uint32_t Mo[NR], Hl[NR];
-        {
-            // an entry's checkpoints were written by the (lane, half) that ran its pass 1, in that unit's ring slot
-            // (a checkpoint is 2*NR contiguous words: any lane can fetch any entry's with full sectors)
-            const uint4 *p0 = reinterpret_cast<const uint4 *>(ck_warp + (((uint64_t)(ckref[0] >> 8) * T + ((ckref[0] >> 1) & 31)) * ckw + (uint64_t)k0 * 2ull * NR));
-            const uint4 *p1 = reinterpret_cast<const uint4 *>(ck_warp + (((uint64_t)(ckref[1] >> 8) * T + ((ckref[1] >> 1) & 31)) * ckw + (uint64_t)k1 * 2ull * NR));
-            const uint32_t sel = ((ckref[0] & 1) ? 0x0032u : 0x0010u) | ((ckref[1] & 1) ? 0x7600u : 0x5400u);
-#pragma unroll
-            for (int g = 0; g < NR / 2; ++g) {
-                const uint4 a = p0[g], c = p1[g];
-                Mo[2 * g] = prmt(a.x, c.x, sel); Hl[2 * g] = prmt(a.y, c.y, sel);
-                Mo[2 * g + 1] = prmt(a.z, c.z, sel); Hl[2 * g + 1] = prmt(a.w, c.w, sel);
-            }
-        }
-        uint32_t rT = pk(B0 + b * jb0, B0 + b * jb1);
-        const bool pend0 = go0 && (st[0] & 4), pend1 = go1 && (st[1] & 4);
-        const bool anypend = __any_sync(0xffffffffu, pend0 || pend1);
-        int s0 = st[0] & 3, s1 = st[1] & 3;
-#pragma unroll UNR2
-        for (int t = 1; t <= tmax; ++t) {
-            const uint32_t *tp = tbl + pair_index(q0[0] & 0xFFu, q1[0] & 0xFFu);
-#pragma unroll
-            for (int g = 0; g < C / 4; ++g) {                  // shift the base queues by one byte
-                q0[g] = __funnelshift_r(q0[g], g + 1 < C / 4 ? q0[(g + 1) % (C / 4)] : 0u, 8);
-                q1[g] = __funnelshift_r(q1[g], g + 1 < C / 4 ? q1[(g + 1) % (C / 4)] : 0u, 8);
-            }
-            const uint32_t rowTp = rT;
-            rT += Bp;
-            uint32_t Ml, Vl, Hlast;
-            col_flags<NR, EXACT>(Mo, Hl, tp, rowTp, rT, GEB, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
-            if (anypend) {
-                // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
-                // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
-                const uint32_t xv = Ml ^ Vl, xh = Ml ^ Hlast;
-                if (pend0 && jb0 + t == cj[0]) s0 = ((xv & 0xFFFFu) == 0) ? 1 : (((xh & 0xFFFFu) == 0) ? 2 : 0);
-                if (pend1 && jb1 + t == cj[1]) s1 = ((xv >> 16) == 0) ? 1 : (((xh >> 16) == 0) ? 2 : 0);
-            }
-        }
-        __syncwarp();
-        load_acc();
-        // walk (dp_traceback_impl.h:379-451, :498-545) inside the block: both halves together, one path op per half and trip
-        {
-            int i0 = ci[0], j0 = cj[0], i1 = ci[1], j1 = cj[1];
-            WalkAcc a0 = acc[0], a1 = acc[1];
-            bool act0 = go0 && j0 > jb0, act1 = go1 && j1 > jb1;
-            while (act0 || act1) {
-                if (act0) { walk_step<FW, C>(s_fl, s_code, 0, jb0, r0, i0, j0, s0, a0); act0 = i0 > 0 && j0 > jb0; }
-                if (act1) { walk_step<FW, C>(s_fl, s_code, 1, jb1, r0, i1, j1, s1, a1); act1 = i1 > 0 && j1 > jb1; }
-            }
-            ci[0] = i0; cj[0] = j0; acc[0] = a0; ci[1] = i1; cj[1] = j1; acc[1] = a1;
-        }
-        st[0] = s0; st[1] = s1;                                  // the pending bit is spent
-        __syncwarp();
-    } else {
-        load_acc();
-    }
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        const uint32_t *p = h ? qp1 : qp0;
-        oidx[h] = -1; col0[h] = mtrue[h] = endi[h] = endj[h] = score[h] = 0;
-        if (valid[h]) {
-            oidx[h] = (int64_t)((uint64_t)p[QF_OUTLO * PCF_QCAP] | ((uint64_t)p[QF_OUTHI * PCF_QCAP] << 32));
-            col0[h] = (int)p[QF_COL0 * PCF_QCAP]; mtrue[h] = (int)p[QF_MTRUE * PCF_QCAP];
-            endi[h] = (int)p[QF_ENDI * PCF_QCAP]; endj[h] = (int)p[QF_ENDJ * PCF_QCAP];
-            score[h] = (int)p[QF_SCORE * PCF_QCAP];
-        }
-    }
-    __syncwarp();                                                // every lane has its entry before a slot can be written again
-
-    // paths that reached row 0 / column 0 are complete (this also covers the empty path); the others go back into the ring
-    bool keep[2];
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        keep[h] = valid[h] && ci[h] > 0 && cj[h] > 0;
-        if (!valid[h] || keep[h]) continue;
-        if (cj[h] == 0 && ci[h] > 0 && col0[h] > 0) atomicOr(q.err_flag, 1);      // window too narrow for this path
-        PathAcc pa; walk_acc_finish(acc[h], endi[h], endj[h], ci[h], cj[h], pa);
-        PathStats ps;
-        path_finalize(pa, (int64_t)col0[h] + cj[h], ci[h], (int64_t)mtrue[h] - (col0[h] + endj[h]), n - endi[h], mtrue[h], n, ps);
-        pcb_result res;
-        res.read_start = ps.read_start; res.read_end = ps.read_end;
-        res.adapter_start = ps.adapter_start; res.adapter_end = ps.adapter_end;
-        res.raw_score = score[h]; res.matches = ps.matches;
-        res.aligned_len = ps.aligned_len; res.full_len = ps.full_len;
-        q.out[oidx[h]] = res;
-    }
-#pragma unroll
-    for (int s = 0; s < PCF_RING; ++s) {
-        const int gone = __popc(__ballot_sync(0xffffffffu, valid[0] && !keep[0] && (ckref[0] >> 8) == s)) +
-                         __popc(__ballot_sync(0xffffffffu, valid[1] && !keep[1] && (ckref[1] >> 8) == s));
-        if (lane == 0 && gone) s_live[s] -= gone;
-    }
-    const uint32_t m0 = __ballot_sync(0xffffffffu, keep[0]), m1 = __ballot_sync(0xffffffffu, keep[1]);
-    const uint32_t lt = (1u << lane) - 1u;
-    const int tail = q.head + q.count;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        if (!keep[h]) continue;
-        const int pos = h ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
-        uint32_t *p = q.queue + ((tail + pos) & (PCF_QCAP - 1));
-        p[QF_OFFLO * PCF_QCAP] = (uint32_t)off[h]; p[QF_OFFHI * PCF_QCAP] = (uint32_t)(off[h] >> 32);
-        p[QF_OUTLO * PCF_QCAP] = (uint32_t)(uint64_t)oidx[h]; p[QF_OUTHI * PCF_QCAP] = (uint32_t)((uint64_t)oidx[h] >> 32);
-        p[QF_LEN * PCF_QCAP] = (uint32_t)len[h]; p[QF_COL0 * PCF_QCAP] = (uint32_t)col0[h]; p[QF_MTRUE * PCF_QCAP] = (uint32_t)mtrue[h];
-        p[QF_CI * PCF_QCAP] = (uint32_t)ci[h]; p[QF_CJ * PCF_QCAP] = (uint32_t)cj[h];
-        p[QF_ENDI * PCF_QCAP] = (uint32_t)endi[h]; p[QF_ENDJ * PCF_QCAP] = (uint32_t)endj[h];
-        p[QF_ST * PCF_QCAP] = (uint32_t)st[h]; p[QF_SCORE * PCF_QCAP] = (uint32_t)score[h]; p[QF_CKREF * PCF_QCAP] = (uint32_t)ckref[h];
-        p[(QF_ACC + 0) * PCF_QCAP] = (uint32_t)acc[h].nD; p[(QF_ACC + 1) * PCF_QCAP] = (uint32_t)acc[h].matches;
-        p[(QF_ACC + 2) * PCF_QCAP] = (uint32_t)acc[h].kA; p[(QF_ACC + 3) * PCF_QCAP] = (uint32_t)acc[h].kR;
-        p[(QF_ACC + 4) * PCF_QCAP] = (uint32_t)acc[h].jA; p[(QF_ACC + 5) * PCF_QCAP] = (uint32_t)acc[h].iR;
-    }
-    q.count += __popc(m0) + __popc(m1);
-    __syncwarp();
-}
-
-// ------------------------------------------------------------------------------------------------
-// k_fast<TRACE, NR, EXACT>
-//   TRACE=true  -> pass 1 (score only + checkpoints + end cell), pass 2 (flags for the blocks the traceback crosses,
-//                  traceback, statistics) -> pcb_result
-//   TRACE=false -> pass 1 only -> order key per task (scan chunks of long reads)
+// k_fast<MODE, NR, EXACT, C>: the score-only pass
+//   MODE 0 -> scan: order key per task (chunks of long reads)
+//   MODE 1 -> pass 1 of the trace: the DP column of every C-th column goes to L.scratch (checkpoints), the end cell of
+//             every task (SeqAn's scout, dp_scout.h:167-180) to L.entries; k_rounds takes it from there
 //   NR / EXACT  -> adapter rows in registers; EXACT: every adapter of the launch has exactly NR bases
 //   C           -> checkpoint distance = width of a flag block (columns; a multiple of 4, >= 8)
-// grid: persistent, blockDim = PCB_BLOCK.  Cross-product launches are walked adapter-major in contiguous per-warp ranges
-// (a warp re-builds its score table only when the adapter changes); explicit task lists are walked strided.
-// dynamic smem: [W][NR*25] score tables, [W][NR] adapter codes, then a per-thread area strided by PCB_BLOCK
-//               (TRACE: C*NR/4 flag words + 2*C/4 words of block bases; always >= 2*NR words for the final-column dump).
+// grid: persistent, blockDim = PCB_BLOCK, units [L.unit0, L.unit1).  Cross-product launches are walked adapter-major in
+// contiguous per-warp ranges (a warp re-builds its score table only when the adapter changes); explicit task lists are
+// walked strided.
+// dynamic smem: [W][NR*25] score tables, [W][NR] adapter codes, then 2*NR words per thread (strided by PCB_BLOCK) for the
+//               final-column dump.
+// Entry of a task (two words): x = end row | end column << 6 | start state << 18 | 1 << 31 (0: no entry, the failed record
+// is already written), y = raw score + OFF.  Start state 4 = "decide from V == M / H == M of the end cell".
 // ------------------------------------------------------------------------------------------------
-template <bool TRACE, int NR, bool EXACT, int C>
-__global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const PcbLaunch L)
+template <int MODE, int NR, bool EXACT, int C>
+__global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(MODE, NR)) k_fast(const PcbLaunch L)
 {
     static_assert(C % 4 == 0 && C >= 8, "flag block width");
+    constexpr bool TRACE = MODE != 0;
     extern __shared__ uint32_t smem[];
-    constexpr int FW = NR / 4;                           // flag words per column
     constexpr int W = PCB_BLOCK / 32;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint64_t T = (uint64_t)gridDim.x * blockDim.x;
-    const uint64_t slot = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t *const tbl = smem + warp * (NR * TP);
     uint32_t *const s_code = smem + W * (NR * TP) + warp * NR;
-    volatile int *const s_live = reinterpret_cast<volatile int *>(smem + W * (NR * TP + NR) + warp * PCF_RING);
-    uint32_t *const s_fl = smem + W * (NR * TP + NR + PCF_RING) + threadIdx.x;
-    uint32_t *const ck = L.scratch + slot * ckw_of(L.mmax, C, NR);     // checkpoints [ring slot][thread][k][2*NR]
+    uint32_t *const s_fl = smem + W * (NR * TP + NR) + threadIdx.x;
     const uint64_t ckw = ckw_of(L.mmax, C, NR);
 
     const int b = -L.sc.gap_open;
@@ -489,24 +292,11 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
     const int64_t nwarps = (int64_t)gridDim.x * W, gw = (int64_t)blockIdx.x * W + warp;
     const bool cross = L.src.units == nullptr;
     const int64_t groups = cross ? (L.src.n_windows + 63) / 64 : 0;
+    const int64_t nu = L.unit1 - L.unit0;
     int64_t u_begin, u_end, u_step;
-    if (cross) { u_begin = gw * L.src.n_units / nwarps; u_end = (gw + 1) * L.src.n_units / nwarps; u_step = 1; }
-    else       { u_begin = gw; u_end = L.src.n_units; u_step = nwarps; }
+    if (cross) { u_begin = L.unit0 + gw * nu / nwarps; u_end = L.unit0 + (gw + 1) * nu / nwarps; u_step = 1; }
+    else       { u_begin = L.unit0 + gw; u_end = L.unit1; u_step = nwarps; }
     int32_t tbl_adapter = -1;
-    RoundCtx q;
-    int useq = 0;                                        // units this warp has taken through pass 1
-    if (TRACE) {
-        q.queue = L.scratch + PCF_RING * ckw * T + (uint64_t)gw * (PCF_QCAP * PCF_QF);
-        q.head = 0; q.count = 0;
-        q.tbl_off = (int)(tbl - smem); q.code_off = (int)(s_code - smem); q.fl_off = (int)(s_fl - smem);
-        q.live_off = W * (NR * TP + NR) + warp * PCF_RING;
-        q.ck_warp = L.scratch + (slot - lane) * ckw; q.ckw = ckw; q.T = T;
-        q.arena = L.arena; q.out = L.out; q.err_flag = L.err_flag;
-        q.n = 0; q.r0 = 0; q.b = -L.sc.gap_open; q.lane = lane;
-        q.GEB = pk2(L.sc.gap_extend - L.sc.gap_open); q.Bp = pk2(-L.sc.gap_open);
-        if (lane < PCF_RING) s_live[lane] = 0;
-        __syncwarp();
-    }
 
     for (int64_t unit = u_begin; unit < u_end; unit += u_step) {
         int32_t adapter = 0;
@@ -529,6 +319,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             fetch_task(L.src, unit, 2 * lane, adapter, tk[0]);
             fetch_task(L.src, unit, 2 * lane + 1, adapter, tk[1]);
         }
+        uint4 *const entp = TRACE ? L.entries + (unit - L.unit0) * 32 + lane : nullptr;
         const int64_t aoff = L.ad.off[adapter];
         const int n = (int)(L.ad.off[adapter + 1] - aoff);
         if (n <= 0 || n > NR || (EXACT && n != NR)) {          // the host never sends these here; fail loudly if it does
@@ -536,6 +327,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             for (int h = 0; h < 2; ++h) if (tk[h].out_idx >= 0) {
                 if (TRACE) write_failed(L.out, tk[h].out_idx); else L.scan_out[tk[h].out_idx] = (int)0x80000000;
             }
+            if (TRACE) *entp = make_uint4(0u, 0u, 0u, 0u);
             continue;
         }
         // The adapter is bottom-aligned in the NR register rows: adapter row i lives in register row r0 + i - 1 and the
@@ -544,7 +336,6 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
         // neighbours as under row 0 itself and no row of the column loop needs a bounds test.
         const int r0 = EXACT ? 0 : NR - n;
         if (adapter != tbl_adapter) {
-            if (TRACE) { while (q.count > 0) trace_round<NR, EXACT, C>(q); q.n = n; q.r0 = r0; }   // the ring's entries use the old table
             __syncwarp();
             for (int i = lane; i < NR; i += 32) s_code[i] = i >= r0 ? (uint32_t)(L.ad.codes[aoff + i - r0] / PCB_CODE_SCALE) : 0u;
             __syncwarp();
@@ -586,10 +377,8 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
         for (int r = 0; r < NR; ++r) { Mo[r] = pk2(B0 + b * (r + 1)); Hl[r] = 0; }   // column 0: M = 0, H = -inf
         uint32_t rowT = pk2(B0);                                 // biased M(0, j) = bias of row 0 at the current column
         const uint32_t candK = pk2(OFF - b * NR);                // candidate = M(n, j) + candK - rowT = score + OFF
-        // ring slot of this unit's checkpoints: free once every entry of the unit that used it last has completed
-        const int rs = TRACE ? useq % PCF_RING : 0;
-        if (TRACE) while (s_live[rs] > 0 && q.count > 0) trace_round<NR, EXACT, C>(q);
-        uint32_t *const ckp = ck + (uint64_t)rs * ckw * T;
+        // this thread's checkpoint records of the unit: [unit - unit0][lane][k][2 * NR]
+        uint32_t *const ckp = TRACE ? L.scratch + ((uint64_t)(unit - L.unit0) * 32u + (uint64_t)lane) * ckw : nullptr;
         uint32_t ckoff = 0;
         int ckc = 0;                                             // columns since the last checkpoint
         Raw4 nx0 = load4(seq0, 0, lim0), nx1 = load4(seq1, 0, lim1);
@@ -634,15 +423,15 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             }
         };
 
-        // =========================== pass 1: score only ===========================
         for (int j0 = 1; j0 <= mw; j0 += 4) {
             uint32_t cur0 = join4(nx0), cur1 = join4(nx1);
             nx0 = load4(seq0, j0 + 3, lim0); nx1 = load4(seq1, j0 + 3, lim1);       // used one group later
             if (TRACE && ckc == 0) {                             // checkpoint = state after column j0-1 (a multiple of C)
-#pragma unroll
-                // (address from base + running offset: a pointer bumped after the stores waits for all 12 of them to read it)
+                // (address from base + running offset: a pointer bumped after the stores waits for all of them to read it;
+                //  streaming stores: a record is read back at most once, by another SM, much later)
                 uint4 *const cq = reinterpret_cast<uint4 *>(ckp + ckoff);
-                for (int g = 0; g < NR / 2; ++g) cq[g] = make_uint4(Mo[2 * g], Hl[2 * g], Mo[2 * g + 1], Hl[2 * g + 1]);
+#pragma unroll
+                for (int g = 0; g < NR / 2; ++g) __stcs(cq + g, make_uint4(Mo[2 * g], Hl[2 * g], Mo[2 * g + 1], Hl[2 * g + 1]));
                 ckoff += 2 * NR;
             }
             if (TRACE) { ckc += 4; if (ckc == C) ckc = 0; }
@@ -673,51 +462,307 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
             if (tk[1].out_idx >= 0) L.scan_out[tk[1].out_idx] = (len1 > 0 && sc1 > 0) ? (int)(((uint32_t)(sc1 - OFF) << 16) | ((uint32_t)(0x3FFF - ord1) << 2)) : (int)0x80000000;
             continue;
         }
-        // =========================== pass 2: every task becomes an entry of the warp's ring ===========================
-        {
-            bool pv[2]; int pci[2], pcj[2], pst[2];
+        // every task that has an end cell becomes an entry for k_rounds
+        uint32_t ex[2], ey[2];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const HalfTask &t = tk[h];
-                const int sc = h ? sc1 : sc0, ord = h ? ord1 : ord0;
-                const bool fc = h ? fc1 : fc0;
-                pv[h] = false; pci[h] = pcj[h] = pst[h] = 0;
-                if (t.out_idx < 0) continue;
-                if (t.len <= 0) { write_failed(L.out, t.out_idx); continue; }
-                if (sc <= 0) { atomicOr(L.err_flag, 2); write_failed(L.out, t.out_idx); continue; }   // forced cell not found
-                if (fc) { pci[h] = ord - t.len; pcj[h] = t.len; const int e = h ? finE1 : finE0; pst[h] = (e & 2) ? 1 : ((e & 1) ? 2 : 0); }
-                else    { pci[h] = n; pcj[h] = ord; pst[h] = 4; }      // 4: the end cell's V == M / H == M still decide the start state
-                pv[h] = true;
-            }
-            const uint32_t m0 = __ballot_sync(0xffffffffu, pv[0]), m1 = __ballot_sync(0xffffffffu, pv[1]);
-            const uint32_t lt = (1u << lane) - 1u;
-            const int tail = q.head + q.count;
+        for (int h = 0; h < 2; ++h) {
+            const HalfTask &t = tk[h];
+            const int sc = h ? sc1 : sc0, ord = h ? ord1 : ord0;
+            const bool fc = h ? fc1 : fc0;
+            ex[h] = 0u; ey[h] = 0u;
+            if (t.out_idx < 0) continue;
+            if (t.len <= 0) { write_failed(L.out, t.out_idx); continue; }
+            if (sc <= 0) { atomicOr(L.err_flag, 2); write_failed(L.out, t.out_idx); continue; }   // forced cell not found
+            int pci, pcj, pst;
+            if (fc) { pci = ord - t.len; pcj = t.len; const int e = h ? finE1 : finE0; pst = (e & 2) ? 1 : ((e & 1) ? 2 : 0); }
+            else    { pci = n; pcj = ord; pst = 4; }      // 4: the end cell's V == M / H == M still decide the start state
+            ex[h] = (uint32_t)pci | ((uint32_t)pcj << 6) | ((uint32_t)pst << 18) | 0x80000000u;
+            ey[h] = (uint32_t)sc;
+        }
+        *entp = make_uint4(ex[0], ey[0], ex[1], ey[1]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_rounds<NR, EXACT, C>: pass 2 of the trace.  A task's traceback crosses 1.8 flag blocks on average but the longest of
+// 64 crosses 3+, so a warp that took its 64 tasks through pass 2 in lockstep would spend a third of its time on a few
+// lanes.  Instead a unit gets ONE round: every task's flag block holding its end cell is rebuilt from the checkpoint on
+// its left and walked; the paths that end inside it are finished (statistics, result record), the others become ENTRIES
+// of the warp's continuation queue in shared memory (5 words: which task, where the walk stands, the walk's
+// accumulators).  A continuation round pops 64 entries -- from whatever units, the adapter is the same -- and does the
+// same for each entry's next block; it runs whenever the queue holds 64, so every lane of a round works.  The queue is
+// drained when the warp's adapter changes and at the end.
+// dynamic smem: [W][NR*25] score tables, [W][NR] adapter codes, [W][5][PCF_QCAP] queues, then per thread (strided by
+//               PCB_BLOCK) C*NR/4 flag words + 2*C/4 words of block bases.
+// ------------------------------------------------------------------------------------------------
+constexpr int QW = 5;
+// queue words: 0 task = (unit - unit0) << 6 | slot        1 walk position = row | column << 6 | state << 18
+//              2 end cell = row | column << 6 | (raw score + OFF) << 18
+//              3 nD | matches << 6 | (kA + 1) << 12 | (kR + 1) << 24       4 jA | iR << 12      (WalkAcc, align_stats.h)
+struct RoundCtx {
+    int head, count;                               // queue state, warp-uniform
+    int tbl_off, code_off, fl_off, q_off;          // word offsets into the CTA's dynamic shared memory (pointers through this
+                                                   // struct would lose their address space: every LDS / STS a generic access)
+    const uint32_t *ck;                            // checkpoints of the batch: [unit - unit0][lane][k][2 * NR]
+    const uint4 *entries;
+    uint64_t ckw;                                  // checkpoint words per thread and unit
+    const PcbUnit *units;                          // explicit source: units of the batch (nullptr: cross product)
+    const PcbTask *tasks;
+    const int32_t *win_len;                        // cross product
+    int64_t gbase;                                 // cross product: window group of batch unit u = u + gbase
+    int32_t stride, n_ids_total, out_col;
+    const uint8_t *arena;
+    pcb_result *out;
+    int32_t *err_flag;
+    int n, r0, b, lane;
+    uint32_t GEB, Bp;
+};
+
+template <int NR, bool EXACT, int C>
+__device__ __noinline__ void trace_round(RoundCtx &q, const int64_t fresh_u /* >= 0: the entries of batch unit fresh_u; -1: pop */)
+{
+    constexpr int FW = NR / 4;
+    // the context lives in local memory: take what the loops use into registers once
+    const int lane = q.lane, n = q.n, r0 = q.r0, b = q.b;
+    const uint64_t ckw = q.ckw;
+    extern __shared__ uint32_t smem[];
+    const uint32_t *const tbl = smem + q.tbl_off, *const s_code = smem + q.code_off;
+    uint32_t *const s_fl = smem + q.fl_off, *const s_q = smem + q.q_off;
+    const uint32_t GEB = q.GEB, Bp = q.Bp;
+    const bool cross = q.units == nullptr;
+
+    uint32_t tref[2], w2[2];
+    int ci[2], cj[2], st[2], qpos[2];
+    bool valid[2];
+    if (fresh_u >= 0) {
+        const uint4 e = q.entries[fresh_u * 32 + lane];
+        tref[0] = ((uint32_t)fresh_u << 6) | (uint32_t)(2 * lane); tref[1] = tref[0] | 1u;
+        valid[0] = (e.x >> 31) != 0u; valid[1] = (e.z >> 31) != 0u;
+        ci[0] = (int)(e.x & 63u); cj[0] = (int)((e.x >> 6) & 0xFFFu); st[0] = (int)((e.x >> 18) & 7u);
+        ci[1] = (int)(e.z & 63u); cj[1] = (int)((e.z >> 6) & 0xFFFu); st[1] = (int)((e.z >> 18) & 7u);
+        w2[0] = (e.x & 0x3FFFFu) | (e.y << 18); w2[1] = (e.z & 0x3FFFFu) | (e.w << 18);
+        qpos[0] = qpos[1] = -1;
+    } else {
+        const int take = min(q.count, 64);
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                if (!pv[h]) continue;
-                const HalfTask &t = tk[h];
-                const int pos = h ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
-                uint32_t *p = q.queue + ((tail + pos) & (PCF_QCAP - 1));
-                p[QF_OFFLO * PCF_QCAP] = (uint32_t)t.off; p[QF_OFFHI * PCF_QCAP] = (uint32_t)(t.off >> 32);
-                p[QF_OUTLO * PCF_QCAP] = (uint32_t)(uint64_t)t.out_idx; p[QF_OUTHI * PCF_QCAP] = (uint32_t)((uint64_t)t.out_idx >> 32);
-                p[QF_LEN * PCF_QCAP] = (uint32_t)t.len; p[QF_COL0 * PCF_QCAP] = (uint32_t)t.col0; p[QF_MTRUE * PCF_QCAP] = (uint32_t)t.m_true;
-                p[QF_CI * PCF_QCAP] = (uint32_t)pci[h]; p[QF_CJ * PCF_QCAP] = (uint32_t)pcj[h];
-                p[QF_ENDI * PCF_QCAP] = (uint32_t)pci[h]; p[QF_ENDJ * PCF_QCAP] = (uint32_t)pcj[h];
-                p[QF_ST * PCF_QCAP] = (uint32_t)pst[h]; p[QF_SCORE * PCF_QCAP] = (uint32_t)((h ? sc1 : sc0) - OFF);
-                p[QF_CKREF * PCF_QCAP] = (uint32_t)((rs << 8) | (lane << 1) | h);
-                p[(QF_ACC + 0) * PCF_QCAP] = 0u; p[(QF_ACC + 1) * PCF_QCAP] = 0u;
-                p[(QF_ACC + 2) * PCF_QCAP] = 0xFFFFFFFFu; p[(QF_ACC + 3) * PCF_QCAP] = 0xFFFFFFFFu;        // walk_acc_init
-                p[(QF_ACC + 4) * PCF_QCAP] = 0u; p[(QF_ACC + 5) * PCF_QCAP] = 0u;
+        for (int h = 0; h < 2; ++h) {
+            valid[h] = 2 * lane + h < take;
+            qpos[h] = (q.head + 2 * lane + h) & (PCF_QCAP - 1);
+            tref[h] = 0u; w2[h] = 0u; ci[h] = cj[h] = st[h] = 0;
+            if (valid[h]) {
+                tref[h] = s_q[qpos[h]];
+                const uint32_t w1 = s_q[PCF_QCAP + qpos[h]];
+                ci[h] = (int)(w1 & 63u); cj[h] = (int)((w1 >> 6) & 0xFFFu); st[h] = (int)((w1 >> 18) & 7u);
+                w2[h] = s_q[2 * PCF_QCAP + qpos[h]];
             }
-            const int total = __popc(m0) + __popc(m1);
-            if (lane == 0 && total) s_live[rs] += total;
-            q.count += total;
-            ++useq;
-            __syncwarp();
-            while (q.count >= 64) trace_round<NR, EXACT, C>(q);
+        }
+        q.head = (q.head + take) & (PCF_QCAP - 1); q.count -= take;
+    }
+    // where the task's bases are
+    uint64_t off[2]; int len[2]; int64_t widx[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        off[h] = 0; len[h] = 0; widx[h] = 0;
+        if (!valid[h]) continue;
+        if (cross) {
+            const int64_t w = ((int64_t)(tref[h] >> 6) + q.gbase) * 64 + (int64_t)(tref[h] & 63u);
+            widx[h] = w; off[h] = (uint64_t)w * (uint64_t)q.stride; len[h] = q.win_len[w];
+        } else {
+            const int64_t t = q.units[tref[h] >> 6].task0 + (int64_t)(tref[h] & 63u);
+            widx[h] = t; off[h] = q.tasks[t].off; len[h] = q.tasks[t].len;
         }
     }
-    if (TRACE) while (q.count > 0) trace_round<NR, EXACT, C>(q);
+    WalkAcc acc[2];
+    auto load_acc = [&]() {                        // the walk's accumulators are fetched where the walk starts: the column loop wants the registers
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            walk_acc_init(acc[h]);
+            if (valid[h] && qpos[h] >= 0) {
+                const uint32_t a = s_q[3 * PCF_QCAP + qpos[h]], c = s_q[4 * PCF_QCAP + qpos[h]];
+                acc[h].nD = (int)(a & 63u); acc[h].matches = (int)((a >> 6) & 63u);
+                acc[h].kA = (int)((a >> 12) & 0xFFFu) - 1; acc[h].kR = (int)(a >> 24) - 1;
+                acc[h].jA = (int)(c & 0xFFFu); acc[h].iR = (int)(c >> 12);
+            }
+        }
+    };
+
+    // block of each half: columns k*C+1 .. k*C+C, holding its current column
+    const bool go0 = valid[0] && ci[0] > 0 && cj[0] > 0, go1 = valid[1] && ci[1] > 0 && cj[1] > 0;
+    const int k0 = go0 ? (cj[0] - 1) / C : 0, k1 = go1 ? (cj[1] - 1) / C : 0;
+    const int jb0 = k0 * C, jb1 = k1 * C;
+    const int tmax = __reduce_max_sync(0xffffffffu, max(go0 ? cj[0] - jb0 : 0, go1 ? cj[1] - jb1 : 0));
+    if (tmax > 0) {
+        const uint8_t *const seq0 = q.arena + off[0], *const seq1 = q.arena + off[1];
+        const int lim0 = max(len[0] - 1, 0), lim1 = max(len[1] - 1, 0);
+        // the block's read bases (C per half), then the checkpointed column the block starts from
+        uint32_t q0[C / 4], q1[C / 4];
+#pragma unroll
+        for (int g = 0; g < C / 4; ++g) {
+            q0[g] = join4(load4(seq0, jb0 + 4 * g, lim0)); q1[g] = join4(load4(seq1, jb1 + 4 * g, lim1));
+            s_fl[(C * FW + g) * PCB_BLOCK] = q0[g]; s_fl[(C * FW + C / 4 + g) * PCB_BLOCK] = q1[g];   // for the walk
+        }
+        uint32_t Mo[NR], Hl[NR];
+        {
+            // a task's checkpoints were written by the thread that ran its pass 1 (task >> 1 = batch unit * 32 + lane), two
+            // tasks per word; a record is 2*NR contiguous words, so any lane can fetch any task's with full sectors
+            const uint4 *p0 = reinterpret_cast<const uint4 *>(q.ck + ((uint64_t)(tref[0] >> 1) * ckw + (uint64_t)k0 * 2ull * NR));
+            const uint4 *p1 = reinterpret_cast<const uint4 *>(q.ck + ((uint64_t)(tref[1] >> 1) * ckw + (uint64_t)k1 * 2ull * NR));
+            const uint32_t sel = ((tref[0] & 1u) ? 0x0032u : 0x0010u) | ((tref[1] & 1u) ? 0x7600u : 0x5400u);
+#pragma unroll
+            for (int g = 0; g < NR / 2; ++g) {
+                const uint4 a = __ldcs(p0 + g), c = __ldcs(p1 + g);
+                Mo[2 * g] = prmt(a.x, c.x, sel); Hl[2 * g] = prmt(a.y, c.y, sel);
+                Mo[2 * g + 1] = prmt(a.z, c.z, sel); Hl[2 * g + 1] = prmt(a.w, c.w, sel);
+            }
+        }
+        uint32_t rT = pk(B0 + b * jb0, B0 + b * jb1);
+        const bool pend0 = go0 && (st[0] & 4), pend1 = go1 && (st[1] & 4);
+        const bool anypend = __any_sync(0xffffffffu, pend0 || pend1);
+        int s0 = st[0] & 3, s1 = st[1] & 3;
+#pragma unroll UNR2
+        for (int t = 1; t <= tmax; ++t) {
+            const uint32_t *tp = tbl + pair_index(q0[0] & 0xFFu, q1[0] & 0xFFu);
+#pragma unroll
+            for (int g = 0; g < C / 4; ++g) {                  // shift the base queues by one byte
+                q0[g] = __funnelshift_r(q0[g], g + 1 < C / 4 ? q0[(g + 1) % (C / 4)] : 0u, 8);
+                q1[g] = __funnelshift_r(q1[g], g + 1 < C / 4 ? q1[(g + 1) % (C / 4)] : 0u, 8);
+            }
+            const uint32_t rowTp = rT;
+            rT += Bp;
+            uint32_t Ml, Vl, Hlast;
+            col_flags<NR, EXACT>(Mo, Hl, tp, rowTp, rT, GEB, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
+            if (anypend) {
+                // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
+                // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
+                const uint32_t xv = Ml ^ Vl, xh = Ml ^ Hlast;
+                if (pend0 && jb0 + t == cj[0]) s0 = ((xv & 0xFFFFu) == 0) ? 1 : (((xh & 0xFFFFu) == 0) ? 2 : 0);
+                if (pend1 && jb1 + t == cj[1]) s1 = ((xv >> 16) == 0) ? 1 : (((xh >> 16) == 0) ? 2 : 0);
+            }
+        }
+        __syncwarp();
+        load_acc();
+        // walk (dp_traceback_impl.h:379-451, :498-545) inside the block: both halves together, one path op per half and trip
+        {
+            int i0 = ci[0], j0 = cj[0], i1 = ci[1], j1 = cj[1];
+            WalkAcc a0 = acc[0], a1 = acc[1];
+            bool act0 = go0 && j0 > jb0, act1 = go1 && j1 > jb1;
+            while (act0 || act1) {
+                if (act0) { walk_step<FW, C>(s_fl, s_code, 0, jb0, r0, i0, j0, s0, a0); act0 = i0 > 0 && j0 > jb0; }
+                if (act1) { walk_step<FW, C>(s_fl, s_code, 1, jb1, r0, i1, j1, s1, a1); act1 = i1 > 0 && j1 > jb1; }
+            }
+            ci[0] = i0; cj[0] = j0; acc[0] = a0; ci[1] = i1; cj[1] = j1; acc[1] = a1;
+        }
+        st[0] = s0; st[1] = s1;                                  // the pending bit is spent
+    } else {
+        load_acc();
+    }
+    __syncwarp();                                                // every lane has read its entry before a queue slot is written again
+
+    // paths that reached row 0 / column 0 are complete (this also covers the empty path); the others go (back) into the queue
+    bool keep[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        keep[h] = valid[h] && ci[h] > 0 && cj[h] > 0;
+        if (!valid[h] || keep[h]) continue;
+        int col0 = 0, mtrue = len[h];
+        int64_t oidx;
+        if (cross) oidx = widx[h] * q.n_ids_total + q.out_col;
+        else { const PcbTask &k = q.tasks[widx[h]]; col0 = k.col0; mtrue = k.m_true; oidx = k.out_idx; }
+        const int endi = (int)(w2[h] & 63u), endj = (int)((w2[h] >> 6) & 0xFFFu);
+        if (cj[h] == 0 && ci[h] > 0 && col0 > 0) atomicOr(q.err_flag, 1);      // window too narrow for this path
+        PathAcc pa; walk_acc_finish(acc[h], endi, endj, ci[h], cj[h], pa);
+        PathStats ps;
+        path_finalize(pa, (int64_t)col0 + cj[h], ci[h], (int64_t)mtrue - (col0 + endj), n - endi, mtrue, n, ps);
+        pcb_result res;
+        res.read_start = ps.read_start; res.read_end = ps.read_end;
+        res.adapter_start = ps.adapter_start; res.adapter_end = ps.adapter_end;
+        res.raw_score = (int)(w2[h] >> 18) - OFF; res.matches = ps.matches;
+        res.aligned_len = ps.aligned_len; res.full_len = ps.full_len;
+        q.out[oidx] = res;
+    }
+    const uint32_t m0 = __ballot_sync(0xffffffffu, keep[0]), m1 = __ballot_sync(0xffffffffu, keep[1]);
+    const uint32_t lt = (1u << lane) - 1u;
+    const int tail = q.head + q.count;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        if (!keep[h]) continue;
+        const int pos = (tail + (h ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt))) & (PCF_QCAP - 1);
+        s_q[pos] = tref[h];
+        s_q[PCF_QCAP + pos] = (uint32_t)ci[h] | ((uint32_t)cj[h] << 6) | ((uint32_t)st[h] << 18);
+        s_q[2 * PCF_QCAP + pos] = w2[h];
+        s_q[3 * PCF_QCAP + pos] = (uint32_t)acc[h].nD | ((uint32_t)acc[h].matches << 6) | ((uint32_t)(acc[h].kA + 1) << 12) | ((uint32_t)(acc[h].kR + 1) << 24);
+        s_q[4 * PCF_QCAP + pos] = (uint32_t)acc[h].jA | ((uint32_t)acc[h].iR << 12);
+    }
+    q.count += __popc(m0) + __popc(m1);
+    __syncwarp();
+}
+
+template <int NR, bool EXACT, int C>
+__global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const PcbLaunch L)
+{
+    extern __shared__ uint32_t smem[];
+    constexpr int FW = NR / 4;
+    constexpr int W = PCB_BLOCK / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t *const tbl = smem + warp * (NR * TP);
+    uint32_t *const s_code = smem + W * (NR * TP) + warp * NR;
+
+    const int b = -L.sc.gap_open;
+    const int s_match = L.sc.match + 2 * b, s_mis = L.sc.mismatch + 2 * b;
+    const int64_t nwarps = (int64_t)gridDim.x * W, gw = (int64_t)blockIdx.x * W + warp;
+    const bool cross = L.src.units == nullptr;
+    const int64_t groups = cross ? (L.src.n_windows + 63) / 64 : 0;
+    const int64_t nu = L.unit1 - L.unit0;
+    int64_t u_begin, u_end, u_step;
+    if (cross) { u_begin = L.unit0 + gw * nu / nwarps; u_end = L.unit0 + (gw + 1) * nu / nwarps; u_step = 1; }
+    else       { u_begin = L.unit0 + gw; u_end = L.unit1; u_step = nwarps; }
+
+    RoundCtx q;
+    q.head = 0; q.count = 0;
+    q.tbl_off = (int)(tbl - smem); q.code_off = (int)(s_code - smem);
+    q.q_off = W * (NR * TP + NR) + warp * (QW * PCF_QCAP);
+    q.fl_off = W * (NR * TP + NR + QW * PCF_QCAP) + (int)threadIdx.x;
+    q.ck = L.scratch; q.entries = L.entries; q.ckw = ckw_of(L.mmax, C, NR);
+    q.units = cross ? nullptr : L.src.units + L.unit0; q.tasks = L.src.tasks;
+    q.win_len = L.src.win_len; q.gbase = 0; q.stride = L.src.stride; q.n_ids_total = L.src.n_ids_total; q.out_col = 0;
+    q.arena = L.arena; q.out = L.out; q.err_flag = L.err_flag;
+    q.n = 0; q.r0 = 0; q.b = b; q.lane = lane;
+    q.GEB = pk2(L.sc.gap_extend + b); q.Bp = pk2(b);
+    (void)FW;
+
+    int32_t tbl_adapter = -1;
+    int64_t cur_k = -1;
+    for (int64_t unit = u_begin; unit < u_end; unit += u_step) {
+        int32_t adapter;
+        int64_t k = 0;
+        if (cross) { k = unit / groups; adapter = L.src.ids[k]; }
+        else adapter = L.src.units[unit].adapter;
+        const int64_t aoff = L.ad.off[adapter];
+        const int n = (int)(L.ad.off[adapter + 1] - aoff);
+        if (n <= 0 || n > NR || (EXACT && n != NR)) continue;          // pass 1 wrote the failed records and raised the flag
+        const int r0 = EXACT ? 0 : NR - n;
+        if (adapter != tbl_adapter || k != cur_k) {
+            while (q.count > 0) trace_round<NR, EXACT, C>(q, -1);     // the queue's entries belong to the old adapter / result column
+            if (cross) { q.gbase = L.unit0 - k * groups; q.out_col = L.src.id_pos ? L.src.id_pos[k] : (int32_t)k; }
+            cur_k = k;
+        }
+        if (adapter != tbl_adapter) {
+            q.n = n; q.r0 = r0;
+            __syncwarp();
+            for (int i = lane; i < NR; i += 32) s_code[i] = i >= r0 ? (uint32_t)(L.ad.codes[aoff + i - r0] / PCB_CODE_SCALE) : 0u;
+            __syncwarp();
+            for (int e = lane; e < NR * TP; e += 32) {
+                const int r = e / TP, p = e - r * TP;
+                const uint32_t a = s_code[r], c0 = (uint32_t)(p / 5), c1 = (uint32_t)(p % 5);
+                tbl[e] = r >= r0 ? pk(c0 == a ? s_match : s_mis, c1 == a ? s_match : s_mis) : pk(2 * b, 2 * b);
+            }
+            __syncwarp();
+            tbl_adapter = adapter;
+        }
+        trace_round<NR, EXACT, C>(q, unit - L.unit0);
+        while (q.count >= 64) trace_round<NR, EXACT, C>(q, -1);
+    }
+    while (q.count > 0) trace_round<NR, EXACT, C>(q, -1);
 }
 
 }  // namespace
@@ -725,68 +770,91 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(TRACE, NR)) k_fast(const P
 // ------------------------------------------------------------------------------------------------
 // host-side launchers, by kernel class
 // ------------------------------------------------------------------------------------------------
-static size_t fast_smem(bool trace, int nr, int c)
+static size_t fast_smem(int kind, int nr, int c)
 {
-    const size_t per_thread = trace ? (size_t)c * (nr / 4) + 2 * (c / 4) : (size_t)2 * nr;   // flags + block bases | column dump
-    return ((size_t)(PCB_BLOCK / 32) * (nr * TP + nr + PCF_RING) + (size_t)PCB_BLOCK * per_thread) * sizeof(uint32_t);
+    const size_t W = PCB_BLOCK / 32;
+    if (kind == 2)       // rounds: tables, codes, queues, then flags + block bases per thread
+        return (W * (size_t)(nr * TP + nr + QW * PCF_QCAP) + (size_t)PCB_BLOCK * ((size_t)c * (nr / 4) + 2 * (c / 4))) * sizeof(uint32_t);
+    return (W * (size_t)(nr * TP + nr) + (size_t)PCB_BLOCK * 2 * nr) * sizeof(uint32_t);      // column dump
 }
 
-template <bool TRACE, int NR, bool EXACT, int C>
-static cudaError_t launch_one(const PcbLaunch &L, cudaStream_t st)
+template <int MODE, int NR, bool EXACT, int C>
+static cudaError_t launch_fast(const PcbLaunch &L, int grid, cudaStream_t st)
 {
     static bool attr = false;
-    const size_t sm = fast_smem(TRACE, NR, C);
+    const size_t sm = fast_smem(MODE, NR, C);
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(k_fast<TRACE, NR, EXACT, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cudaError_t e = cudaFuncSetAttribute(k_fast<MODE, NR, EXACT, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         if (e != cudaSuccess) return e;
         attr = true;
     }
-    k_fast<TRACE, NR, EXACT, C><<<L.grid, PCB_BLOCK, sm, st>>>(L);
+    k_fast<MODE, NR, EXACT, C><<<grid, PCB_BLOCK, sm, st>>>(L);
     return cudaGetLastError();
 }
 
-template <bool TRACE, int NR, bool EXACT, int C>
+template <int NR, bool EXACT, int C>
+static cudaError_t launch_rounds(const PcbLaunch &L, int grid, cudaStream_t st)
+{
+    static bool attr = false;
+    const size_t sm = fast_smem(2, NR, C);
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(k_rounds<NR, EXACT, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if (e != cudaSuccess) return e;
+        attr = true;
+    }
+    k_rounds<NR, EXACT, C><<<grid, PCB_BLOCK, sm, st>>>(L);
+    return cudaGetLastError();
+}
+
+template <int KIND, int NR, bool EXACT, int C>
 static int occ_one()
 {
     int per = 0;
-    const size_t sm = fast_smem(TRACE, NR, C);
-    cudaFuncSetAttribute(k_fast<TRACE, NR, EXACT, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_fast<TRACE, NR, EXACT, C>, PCB_BLOCK, sm);
+    const size_t sm = fast_smem(KIND, NR, C);
+    if (KIND == 2) {
+        cudaFuncSetAttribute(k_rounds<NR, EXACT, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_rounds<NR, EXACT, C>, PCB_BLOCK, sm);
+    } else {
+        cudaFuncSetAttribute(k_fast<(KIND == 1), NR, EXACT, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_fast<(KIND == 1), NR, EXACT, C>, PCB_BLOCK, sm);
+    }
     return per < 1 ? 1 : per;
 }
 
 // kernel classes: see pcb_kernels.h
-#define PCF_DISPATCH(FN, TRACE)                                                            \
-    switch (cls) {                                                                         \
-    case 0:  return FN<TRACE, 24, true,  PCF_C_SMALL>;                                     \
-    case 1:  return FN<TRACE, 24, false, PCF_C_SMALL>;                                     \
-    case 2:  return FN<TRACE, 32, false, PCF_C_SMALL>;                                     \
-    case 3:  return FN<TRACE, 40, false, PCF_C_LARGE>;                                     \
-    default: return FN<TRACE, 52, false, PCF_C_LARGE>;                                     \
+#define PCF_BY_CLASS(...)                                                                 \
+    switch (cls) {                                                                          \
+    case 0:  { constexpr int NR = 24; constexpr bool EX = true;  constexpr int C = PCF_C_SMALL; __VA_ARGS__; } break; \
+    case 1:  { constexpr int NR = 24; constexpr bool EX = false; constexpr int C = PCF_C_SMALL; __VA_ARGS__; } break; \
+    case 2:  { constexpr int NR = 32; constexpr bool EX = false; constexpr int C = PCF_C_SMALL; __VA_ARGS__; } break; \
+    case 3:  { constexpr int NR = 40; constexpr bool EX = false; constexpr int C = PCF_C_LARGE; __VA_ARGS__; } break; \
+    default: { constexpr int NR = 52; constexpr bool EX = false; constexpr int C = PCF_C_LARGE; __VA_ARGS__; } break; \
     }
 
-typedef cudaError_t (*launch_fn)(const PcbLaunch &, cudaStream_t);
-typedef int (*occ_fn)();
-static launch_fn pick_launch(bool trace, int cls)
+cudaError_t pcf_launch_scan(const PcbLaunch &L, int cls, cudaStream_t st)
 {
-    if (trace) { PCF_DISPATCH(launch_one, true) } else { PCF_DISPATCH(launch_one, false) }
-}
-static occ_fn pick_occ(bool trace, int cls)
-{
-    if (trace) { PCF_DISPATCH(occ_one, true) } else { PCF_DISPATCH(occ_one, false) }
-}
-
-cudaError_t pcf_launch(const PcbLaunch &L, bool trace, int cls, cudaStream_t st)
-{
-    if (L.src.n_units == 0) return cudaSuccess;
+    if (L.unit1 <= L.unit0) return cudaSuccess;
     if (cls < 0 || cls >= PCF_NCLS) return cudaErrorInvalidValue;
-    return pick_launch(trace, cls)(L, st);
+    PCF_BY_CLASS(return (launch_fast<0, NR, EX, C>(L, L.grid, st)))
+    return cudaSuccess;
 }
 
-int pcf_occupancy_grid(bool trace, int cls)
+cudaError_t pcf_launch_trace(const PcbLaunch &L, int cls, int grid_rounds, cudaStream_t st)
 {
-    int dev = 0, sms = 0;
+    if (L.unit1 <= L.unit0) return cudaSuccess;
+    if (cls < 0 || cls >= PCF_NCLS) return cudaErrorInvalidValue;
+    cudaError_t e = cudaSuccess;
+    PCF_BY_CLASS(e = launch_fast<1, NR, EX, C>(L, L.grid, st); if (e == cudaSuccess) e = launch_rounds<NR, EX, C>(L, grid_rounds, st))
+    return e;
+}
+
+int pcf_occupancy_grid(int kind, int cls)
+{
+    int dev = 0, sms = 0, per = 1;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    return sms * pick_occ(trace, cls)();
+    if (kind == 0)      { PCF_BY_CLASS(per = (occ_one<0, NR, EX, C>())) }
+    else if (kind == 1) { PCF_BY_CLASS(per = (occ_one<1, NR, EX, C>())) }
+    else                { PCF_BY_CLASS(per = (occ_one<2, NR, EX, C>())) }
+    return sms * per;
 }

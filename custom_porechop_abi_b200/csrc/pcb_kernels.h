@@ -104,6 +104,10 @@ struct PcbLaunch {
     int32_t     smax;            /* ... and adapters up to this many stripes                      */
     int32_t    *err_flag;        /* device int: bit0 = a path ran into the window's left edge     */
     int32_t     grid;
+    /* two-kernel trace of the fast classes (pcb_fast.cu): this launch covers units [unit0, unit1) of src; pass 1 leaves
+     * every task's checkpoints in scratch ([unit - unit0][lane][pcf_ck_words]) and its end cell in entries */
+    int64_t     unit0, unit1;
+    uint4      *entries;         /* [unit - unit0][lane]: {end cell, score} of the lane's two tasks */
 };
 
 /* words of scratch per thread slot */
@@ -167,19 +171,20 @@ cudaError_t pcb_launch_trace(const PcbLaunch &L, cudaStream_t st);
 cudaError_t pcb_launch_scan(const PcbLaunch &L, cudaStream_t st);
 int pcb_occupancy_grid(int which /*0 trace, 1 scan*/);
 
-/* fast kernels, by class (see above) */
-cudaError_t pcf_launch(const PcbLaunch &L, bool trace, int cls, cudaStream_t st);
-int pcf_occupancy_grid(bool trace, int cls);
-/* Trace scratch per thread: PCF_RING per-unit slots of checkpoints, then the warp's pass-2 ring (PCF_QCAP entries of 20 words
- * per warp = 80 words per thread); see trace_round in pcb_fast.cu. */
-#ifndef PCF_RING
-#define PCF_RING 4
-#endif
-#define PCF_QCAP 128
+/* fast kernels, by class (see above).  pcf_launch_scan: score-only keys.  pcf_launch_trace: pass 1 + rounds over the units
+ * [L.unit0, L.unit1), whose checkpoints must fit L.scratch (pcf_unit_words_trace per unit) */
+cudaError_t pcf_launch_scan(const PcbLaunch &L, int cls, cudaStream_t st);
+cudaError_t pcf_launch_trace(const PcbLaunch &L, int cls, int grid_rounds, cudaStream_t st);
+int pcf_occupancy_grid(int kind /* 0 scan, 1 pass 1, 2 rounds */, int cls);
+/* Trace of the fast classes = two kernels over a batch of units (pcf_launch_trace): pass 1 (score only) leaves the DP column
+ * of every task at every C-th column in scratch, one record of 2*NR words per (thread, checkpoint), and each task's end
+ * cell in `entries`; the rounds kernel recomputes, with trace flags, only the C-column blocks a path crosses.
+ * Words of scratch per unit (64 tasks = 32 threads): checkpoints, then 4 words of entries per thread. */
+#define PCF_QCAP 128              /* entries in a warp's continuation queue (shared memory) */
 static inline uint64_t pcf_ck_words(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * NR; }
-static inline uint64_t pcf_scratch_words_trace(int mmax, int cls)
+static inline uint64_t pcf_unit_words_trace(int mmax, int cls)
 {
-    return pcf_ck_words(mmax, pcf_class_c(cls), pcf_class_nr(cls)) * PCF_RING + (PCF_QCAP * 20) / 32;
+    return 32ull * (pcf_ck_words(mmax, pcf_class_c(cls), pcf_class_nr(cls)) + 4);
 }
 
 #endif

@@ -6,6 +6,7 @@ sys.path.insert(0, ROOT)
 from custom_porechop_abi_b200 import synthetic
 from custom_porechop_abi_b200.engine import AlignmentEngine
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
+only24 = len(sys.argv) > 2 and sys.argv[2] == '24'
 adapters, s_ids, e_ids = synthetic.adapter_set()
 blob, off = synthetic.make_reads(n, adapters, s_ids, e_ids, seed=5, lengths=np.full(n, 400))
 sbuf, ebuf, lens = synthetic.end_windows(blob, off)
@@ -13,6 +14,8 @@ eng = AlignmentEngine(0)
 eng.set_adapters(adapters)
 ad_len = np.array([len(a) for a in adapters])
 for name, ids in (('all start ids', s_ids), ('24-mers only', [i for i in s_ids if ad_len[i] == 24]), ('<24', [i for i in s_ids if ad_len[i] < 24]), ('25..32', [i for i in s_ids if 24 < ad_len[i] <= 32]), ('33..40', [i for i in s_ids if 32 < ad_len[i] <= 40]), ('41..52', [i for i in s_ids if 40 < ad_len[i] <= 52])):
+    if only24 and name != '24-mers only':
+        continue
     eng.stage_windows(sbuf, lens, ids)
     eng.run_windows_resident(); eng.synchronize()
     eng.timer_start()

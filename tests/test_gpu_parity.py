@@ -294,10 +294,11 @@ def test_ultra_long_reads_and_barcode_sets(engine):
 
 
 def test_trace_queue_many_units_per_warp_and_long_paths():
-    """The trace kernels take pass 2 through a per-warp ring of entries (pcb_fast.cu: trace_round).  A context limited to
-    two CTAs gives every warp dozens of units, so the ring runs full rounds across unit boundaries, wraps, and re-uses its
-    checkpoint slots; cheap gaps make paths that cross up to ten flag blocks (entries that stay in the ring for many rounds
-    and force a slot to be drained); adapters of several classes alternate.  Every record against the oracle."""
+    """The fast trace is two kernels per batch of units: pass 1 leaves checkpoints and end cells in scratch, the rounds
+    kernel takes every task through pass 2 with a per-warp queue of continuation entries (pcb_fast.cu: trace_round).
+    A context limited to two CTAs gives every warp dozens of units, so the queue runs full rounds across unit boundaries and
+    wraps; a 1 MB scratch budget cuts the launch into many batches; cheap gaps make paths that cross up to ten flag blocks
+    (entries that stay queued for many rounds); adapters of several classes alternate.  Every record against the oracle."""
     import os
     from custom_porechop_abi_b200.engine import AlignmentEngine
     rng = random.Random(77)
@@ -320,10 +321,12 @@ def test_trace_queue_many_units_per_warp_and_long_paths():
             s = ''.join(rng.choice('ACGT') for _ in range(pos)) + a + ''.join(rng.choice('ACGTN') for _ in range(rng.randrange(0, 40)))
         wins.append(s[:150].encode())
     os.environ['PCB_GRID_LIMIT'] = '2'
+    os.environ['PCB_SCRATCH_MB'] = '1'
     try:
         eng = AlignmentEngine(0)
     finally:
         del os.environ['PCB_GRID_LIMIT']
+        del os.environ['PCB_SCRATCH_MB']
     try:
         eng.set_adapters(ads)
         buf, lens = eng.pack_windows(wins, stride=160)
