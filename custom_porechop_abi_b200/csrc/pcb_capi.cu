@@ -117,6 +117,7 @@ struct pcb_context {
                                          // would otherwise queue behind the whole blob on the copy engine)
     // outputs / scratch
     DevBuf<uint32_t> d_scratch;
+    DevBuf<int32_t> d_meta;               // fast trace, pass 2: bucket counts and chunk table (pcf_meta_words)
     DevBuf<int32_t> d_err;
     int grid_trace = 0, grid_scan = 0, grid_fp1[PCF_NCLS] = {}, grid_fp2[PCF_NCLS] = {}, grid_fscan[PCF_NCLS] = {};   // fast kernels: pass 1, rounds, scan
     uint64_t scratch_budget = 6144ull << 18;   // words of checkpoint scratch a batch of the fast trace may use (PCB_SCRATCH_MB)
@@ -202,7 +203,7 @@ extern "C" void pcb_destroy(pcb_context *c)
     for (auto &sl : c->slots) { sl.d_arena.release(); sl.d_ascii.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release(); if (sl.staged) cudaEventDestroy(sl.staged); }
     for (auto &pl : c->plans) { pl.release(); if (pl.ready) cudaEventDestroy(pl.ready); }
     c->d_seg_off.release(); c->d_plan_i64.release(); c->d_seg_len.release(); c->d_seg_ad.release(); c->d_plan_i32.release(); c->d_adinfo.release();
-    c->d_scratch.release(); c->d_err.release();
+    c->d_scratch.release(); c->d_meta.release(); c->d_err.release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->kev0); cudaEventDestroy(c->kev1);
     for (auto &ev : c->pipe_ev) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(c->cstream);
@@ -309,7 +310,7 @@ static int max_adapter_len(pcb_context *c, const int32_t *ids, int n)
 static void fill_launch_common(pcb_context *c, PcbLaunch &L, bool task_arena = false)
 {
     memset(&L, 0, sizeof L);
-    L.ad.codes = c->d_ad_codes.p; L.ad.off = c->d_ad_off.p;
+    L.ad.codes = c->d_ad_codes.p; L.ad.off = c->d_ad_off.p; L.ad.n = c->n_adapters;
     L.sc = c->sc;
     L.arena = task_arena ? c->d_arena_t.p : c->S().d_arena.p; L.arena_len = task_arena ? c->arena_t_len : c->S().arena_len;
     L.out = c->S().d_out.p; L.scan_out = nullptr;
@@ -327,12 +328,18 @@ static int launch_dp(pcb_context *c, PcbLaunch &L, bool trace, int64_t cells, in
     if (c->ktiming) PCB_CUDA(c, cudaEventRecord(c->kev0, c->stream));
     int launches = 1;
     if (cls < PCF_NCLS && trace) {
-        const uint64_t per_unit = pcf_unit_words_trace(L.mmax, cls);
-        const int64_t per_batch = (int64_t)std::max<uint64_t>(1, std::min<uint64_t>({(uint64_t)n_units, c->scratch_budget / per_unit, 1ull << 25}));
+        // scratch of a batch of units: checkpoints | end cells (4 words per thread) | sorted items | surviving items
+        const uint64_t per_unit = pcf_unit_words_trace(L.mmax, cls), ck_unit = per_unit - 128 - 1024;
+        const int64_t per_batch = (int64_t)std::max<uint64_t>(1, std::min<uint64_t>({(uint64_t)n_units, c->scratch_budget / per_unit, 1ull << 24}));
         cudaError_t e = c->d_scratch.reserve((size_t)(per_unit * (uint64_t)per_batch));
         if (e != cudaSuccess) { cudaGetLastError(); return c->fail(PCB_ERR_NOMEM, "trace scratch of %.1f MB: %s", per_unit * per_batch * 4 / 1e6, cudaGetErrorString(e)); }
+        L.n_major = L.src.units ? c->n_adapters : L.src.n_ids;
+        PCB_CUDA(c, c->d_meta.reserve((size_t)pcf_meta_words(L.n_major)));
+        L.meta = c->d_meta.p;
         L.scratch = c->d_scratch.p;
-        L.entries = reinterpret_cast<uint4 *>(c->d_scratch.p + (per_unit - 128) * (uint64_t)per_batch);
+        L.entries = reinterpret_cast<uint4 *>(c->d_scratch.p + ck_unit * (uint64_t)per_batch);
+        L.sorted = reinterpret_cast<PcfItem *>(c->d_scratch.p + (ck_unit + 128) * (uint64_t)per_batch);
+        L.surv = reinterpret_cast<PcfItem *>(c->d_scratch.p + (ck_unit + 128 + 512) * (uint64_t)per_batch);
         const int W = PCB_BLOCK / 32;
         launches = 0;
         for (int64_t u0 = 0; u0 < n_units; u0 += per_batch) {
@@ -340,7 +347,7 @@ static int launch_dp(pcb_context *c, PcbLaunch &L, bool trace, int64_t cells, in
             const int64_t ctas = (L.unit1 - L.unit0 + W - 1) / W;
             L.grid = (int)std::min<int64_t>(c->grid_fp1[cls], ctas);
             PCB_CUDA(c, pcf_launch_trace(L, cls, (int)std::min<int64_t>(c->grid_fp2[cls], ctas), c->stream));
-            launches += 2;
+            launches += pcf_trace_launches();
         }
     } else {
         L.unit0 = 0; L.unit1 = n_units;
@@ -381,7 +388,7 @@ extern "C" int pcb_stage_windows(pcb_context *c, const char *windows, int64_t n_
     c->S().sum_winlen = sumlen;
     const uint64_t bytes = (uint64_t)n_windows * stride;
     PCB_CUDA(c, c->S().d_ascii.reserve((size_t)bytes + 16));
-    PCB_CUDA(c, c->S().d_arena.reserve((size_t)bytes + 16));
+    PCB_CUDA(c, c->S().d_arena.reserve((size_t)bytes + 64));
     PCB_CUDA(c, c->S().d_winlen.reserve((size_t)n_windows + 1));
     if (bytes) {
         PCB_CUDA(c, cudaMemcpyAsync(c->S().d_ascii.p, windows, bytes, cudaMemcpyHostToDevice, c->in_stream()));
@@ -394,7 +401,7 @@ extern "C" int pcb_stage_windows(pcb_context *c, const char *windows, int64_t n_
         c->cnt.kernel_launches++;
     }
     // the kernels fetch bases a few bytes past a segment's end: keep valid codes there
-    PCB_CUDA(c, cudaMemsetAsync(c->S().d_arena.p + bytes, 0, 16, c->stream));
+    PCB_CUDA(c, cudaMemsetAsync(c->S().d_arena.p + bytes, 0, 64, c->stream));
     c->cnt.h2d_bytes += (int64_t)bytes + (int64_t)sizeof(int32_t) * n_windows;
     c->S().arena_len = bytes; c->S().n_windows = n_windows; c->S().stride = stride; c->S().win_mmax = mmax;
     return PCB_OK;
@@ -626,12 +633,12 @@ static int setup_blob(pcb_context *c, const char *seq_blob, int64_t blob_len, in
 {
     for (auto &pl : c->plans) pl.valid = false;
     PCB_CUDA(c, c->d_ascii_t.reserve((size_t)blob_len + 16));
-    PCB_CUDA(c, c->d_arena_t.reserve((size_t)blob_len + 16));
+    PCB_CUDA(c, c->d_arena_t.reserve((size_t)blob_len + 64));
     n_pieces = std::max(1, std::min<int>(n_pieces, pcb_context::MAX_PIECES));
     c->n_pieces = n_pieces;
     c->plan_pieces = one_plan ? 1 : n_pieces;
     c->pending_blob = nullptr;
-    PCB_CUDA(c, cudaMemsetAsync(c->d_arena_t.p + blob_len, 0, 16, c->stream));   // valid codes past the last segment
+    PCB_CUDA(c, cudaMemsetAsync(c->d_arena_t.p + blob_len, 0, 64, c->stream));   // valid codes past the last segment
     if (n_pieces == 1) {
         if (blob_len) {
             PCB_CUDA(c, cudaMemcpyAsync(c->d_ascii_t.p, seq_blob, (size_t)blob_len, cudaMemcpyHostToDevice, c->stream));

@@ -18,7 +18,8 @@
  *   2. two passes, two kernels, instead of a trace matrix.  k_fast<1> (pass 1) is score-only: it finds SeqAn's end cell
  *      (dp_scout.h:167-180) and leaves the DP column of every C-th column in HBM (one 2*NR-word record per thread and
  *      checkpoint, streaming stores).  k_rounds (pass 2) recomputes, with trace flags, only the C-column blocks a traceback
- *      actually walks through (1.8 of them on average), keeps the flags in shared memory and walks them.  Values are
+ *      actually walks through (1.8 of them on average) -- and of those only the columns and rows the walk can reach, 64
+ *      tracebacks of a kind per warp (they are sorted first) --, keeps the flags in shared memory and walks them.  Values are
  *      15-bit non-negative, so "a >= b" is bit 15 of (a + 0x8000 - b): one IADD3 per flag, extracted four at a time with
  *      PRMT in sign-replicate mode.  Two kernels because the passes want different things: pass 1 is a register-bound
  *      integer stream with no memory stalls, the rounds are short latency-bound phases (checkpoint fetch, flag walk) that
@@ -105,6 +106,15 @@ __device__ __forceinline__ uint32_t vmax_keep(uint32_t a, uint32_t b, bool &keep
 }
 // a + GUARD - b on the packed pair: bit 15 / 31 = (a >= b) per half, for 15-bit non-negative a, b
 __device__ __forceinline__ uint32_t cmpge(uint32_t a, uint32_t b) { return a + GUARD - b; }
+// 256-bit streaming accesses (sm_100a: STG / LDG.E.EF.ENL2.256): a warp moves 1 KB per instruction
+__device__ __forceinline__ void st256(uint32_t *p, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t a4, uint32_t a5, uint32_t a6, uint32_t a7)
+{
+    asm volatile("st.global.cs.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" :: "l"(p), "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(a4), "r"(a5), "r"(a6), "r"(a7) : "memory");
+}
+__device__ __forceinline__ void ld256(const uint32_t *p, uint32_t (&v)[8])
+{
+    asm volatile("ld.global.cs.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "l"(p));
+}
 
 struct HalfTask {            // one of the two tasks of a thread
     uint64_t off;
@@ -180,10 +190,11 @@ __device__ __forceinline__ void col_score(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR]
 //      bit 16+8h+2q: V extended                                  bit 16+8h+2q+1 : diagonal >= max(V, H)
 // (tie rules of dp_formula_affine.h:65-124 / dp_formula.h:147-163: the left operand of each _maxScore wins ties).
 // "x >= y" is bit 15 of x + GUARD - y (one IADD3) for 15-bit non-negative x, y.  fp: this thread's flag words of the
-// column, stride PCB_BLOCK.
+// column, stride PCB_BLOCK.  Only register rows < rlim (a multiple of 4, the same for the whole warp) are computed: a
+// traceback that stands in row i never looks at a row below i.
 template <int NR, bool EXACT>
 __device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *tp,
-                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, uint32_t *fp,
+                                          uint32_t rowTp, uint32_t rowT, uint32_t GEB, uint32_t *fp, const int rlim,
                                           uint32_t &Ml, uint32_t &Vl, uint32_t &Hlast)
 {
     // the substitution scores of the column come from shared memory PF rows ahead of their use
@@ -199,6 +210,7 @@ __device__ __forceinline__ void col_flags(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR]
     const uint32_t GEBG = GEB + GUARD;
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
+        if ((r & 3) == 0 && r > 0 && r >= rlim) break;
         const uint32_t D = Dn;
         if (r + PF < NR) tv[r % PF] = tp[(r + PF) * TP];
         const uint32_t Mup = (r == 0) ? rowT : Mo[(r > 0) ? r - 1 : 0];
@@ -232,29 +244,6 @@ __device__ __forceinline__ uint32_t join4(const Raw4 &r) { return __funnelshift_
 __device__ __forceinline__ uint32_t pair_index(uint32_t c8_0, uint32_t c8_1) { return (c8_0 * 5u + c8_1) >> 3; }
 
 __device__ __forceinline__ uint64_t ckw_of(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * NR; }   // = pcf_ck_words (pcb_kernels.h)
-
-// One op of the reverse walk for half h of this thread (dp_traceback_impl.h:379-451).  Flag word layout as col_flags writes
-// it; the block's read bases sit behind the C*FW flag words.  State 0 = M, 1 = V, 2 = H.  In state M a cell whose diagonal
-// flag is off hands over to V or H and that state's step is taken at once, from the same cell's flags, as SeqAn does.
-template <int FW, int C>
-__device__ __forceinline__ void walk_step(const uint32_t *s_fl, const uint32_t *s_code, const int h, const int base, const int r0,
-                                          int &i, int &j, int &s, WalkAcc &a)
-{
-    const int ar = r0 + i - 1, jc = j - base - 1;         // register row of adapter row i
-    const uint32_t f = s_fl[(jc * FW + (ar >> 2)) * PCB_BLOCK] >> (8 * h + 2 * (ar & 3));
-    const bool fh = f & 1u, fg = f & 2u, fv = f & 0x10000u, fd = f & 0x20000u;
-    if (s == 0 && fd) {
-        const uint32_t code8 = (s_fl[(C * FW + h * (C / 4) + (jc >> 2)) * PCB_BLOCK] >> (8 * (jc & 3))) & 0xFFu;
-        walk_acc_D(a, i, j, code8 == s_code[ar] * PCB_CODE_SCALE);
-        --i; --j;
-    } else if (s == 1 || (s == 0 && fg)) {
-        walk_acc_V(a, i, j);
-        --i; s = fv ? 1 : 0;
-    } else {
-        walk_acc_H(a, i, j);
-        --j; s = fh ? 2 : 0;
-    }
-}
 
 // ------------------------------------------------------------------------------------------------
 // k_fast<MODE, NR, EXACT, C>: the score-only pass
@@ -377,8 +366,8 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(MODE, NR)) k_fast(const Pc
         for (int r = 0; r < NR; ++r) { Mo[r] = pk2(B0 + b * (r + 1)); Hl[r] = 0; }   // column 0: M = 0, H = -inf
         uint32_t rowT = pk2(B0);                                 // biased M(0, j) = bias of row 0 at the current column
         const uint32_t candK = pk2(OFF - b * NR);                // candidate = M(n, j) + candK - rowT = score + OFF
-        // this thread's checkpoint records of the unit: [unit - unit0][lane][k][2 * NR]
-        uint32_t *const ckp = TRACE ? L.scratch + ((uint64_t)(unit - L.unit0) * 32u + (uint64_t)lane) * ckw : nullptr;
+        // this thread's part of the unit's checkpoints: [unit - unit0][k][NR / 4][lane][8 words = (M, H) of 4 rows]
+        uint32_t *const ckp = TRACE ? L.scratch + (uint64_t)(unit - L.unit0) * 32u * ckw + (uint64_t)lane * 8u : nullptr;
         uint32_t ckoff = 0;
         int ckc = 0;                                             // columns since the last checkpoint
         Raw4 nx0 = load4(seq0, 0, lim0), nx1 = load4(seq1, 0, lim1);
@@ -428,11 +417,14 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(MODE, NR)) k_fast(const Pc
             nx0 = load4(seq0, j0 + 3, lim0); nx1 = load4(seq1, j0 + 3, lim1);       // used one group later
             if (TRACE && ckc == 0) {                             // checkpoint = state after column j0-1 (a multiple of C)
                 // (address from base + running offset: a pointer bumped after the stores waits for all of them to read it;
-                //  streaming stores: a record is read back at most once, by another SM, much later)
-                uint4 *const cq = reinterpret_cast<uint4 *>(ckp + ckoff);
+                //  streaming stores: a record is read back at most once, by another SM, much later.  Every store of the warp
+                //  is one contiguous KB: records kept per thread -- 32 scattered 16-byte pieces per instruction -- held the
+                //  shared-memory loads of the column loop up behind them in the memory pipe)
+                uint32_t *const cq = ckp + ckoff;
 #pragma unroll
-                for (int g = 0; g < NR / 2; ++g) __stcs(cq + g, make_uint4(Mo[2 * g], Hl[2 * g], Mo[2 * g + 1], Hl[2 * g + 1]));
-                ckoff += 2 * NR;
+                for (int g = 0; g < NR / 4; ++g)
+                    st256(cq + g * 256, Mo[4 * g], Hl[4 * g], Mo[4 * g + 1], Hl[4 * g + 1], Mo[4 * g + 2], Hl[4 * g + 2], Mo[4 * g + 3], Hl[4 * g + 3]);
+                ckoff += (NR / 4) * 256;
             }
             if (TRACE) { ckc += 4; if (ckc == C) ckc = 0; }
             if (!TRACE && ((j0 - 1) & (REBASE - 1)) == 0 && j0 > 1) {   // keep the growing bias inside 15 bits
@@ -484,285 +476,418 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(MODE, NR)) k_fast(const Pc
 }
 
 // ------------------------------------------------------------------------------------------------
-// k_rounds<NR, EXACT, C>: pass 2 of the trace.  A task's traceback crosses 1.8 flag blocks on average but the longest of
-// 64 crosses 3+, so a warp that took its 64 tasks through pass 2 in lockstep would spend a third of its time on a few
-// lanes.  Instead a unit gets ONE round: every task's flag block holding its end cell is rebuilt from the checkpoint on
-// its left and walked; the paths that end inside it are finished (statistics, result record), the others become ENTRIES
-// of the warp's continuation queue in shared memory (5 words: which task, where the walk stands, the walk's
-// accumulators).  A continuation round pops 64 entries -- from whatever units, the adapter is the same -- and does the
-// same for each entry's next block; it runs whenever the queue holds 64, so every lane of a round works.  The queue is
-// drained when the warp's adapter changes and at the end.
-// dynamic smem: [W][NR*25] score tables, [W][NR] adapter codes, [W][5][PCF_QCAP] queues, then per thread (strided by
-//               PCB_BLOCK) C*NR/4 flag words + 2*C/4 words of block bases.
+// Pass 2 of the trace: sort, then rounds.
+//
+// A traceback crosses 1.8 flag blocks (C columns) on average; its first block is 1..C columns wide (7 on average: the
+// end cell sits anywhere in it) and needs all adapter rows, every later block is C columns wide but only needs the rows
+// above the row in which the path enters it (13 of 24 on average, 5 for a third block).  A warp recomputes a block for 64
+// tracebacks in lockstep, so what a round costs is the LARGEST width x the LARGEST row count among them.  Hence:
+//   generation 0 = the first block of every traceback, generation 1 = all later blocks.  Before a generation runs, its
+//   items are sorted (counting sort: k_count0 / in-kernel counts, k_bucket_scan, k_scatter) by adapter and then by
+//   width (first blocks of paths that end in the last adapter row) or by rows (everything else), and a round takes 64
+//   neighbours of that order: 300 instead of 690 flag cells per traceback.
+//   A generation-0 round walks each path to the left edge of its block; paths that end there are finished (statistics,
+//   result record), the others go to the list of generation 1 with the state of their walk.  A generation-1 round keeps
+//   its 64 items until all of them are finished (sorted by rows, the ones that go on are neighbours).
+// dynamic smem of k_rounds: [W][NR*25] score tables, [W][NR] adapter codes, then per thread (strided by PCB_BLOCK) C*NR/4
+//   flag words.
 // ------------------------------------------------------------------------------------------------
-constexpr int QW = 5;
-// queue words: 0 task = (unit - unit0) << 6 | slot        1 walk position = row | column << 6 | state << 18
-//              2 end cell = row | column << 6 | (raw score + OFF) << 18
-//              3 nD | matches << 6 | (kA + 1) << 12 | (kR + 1) << 24       4 jA | iR << 12      (WalkAcc, align_stats.h)
-struct RoundCtx {
-    int head, count;                               // queue state, warp-uniform
-    int tbl_off, code_off, fl_off, q_off;          // word offsets into the CTA's dynamic shared memory (pointers through this
-                                                   // struct would lose their address space: every LDS / STS a generic access)
-    const uint32_t *ck;                            // checkpoints of the batch: [unit - unit0][lane][k][2 * NR]
-    const uint4 *entries;
-    uint64_t ckw;                                  // checkpoint words per thread and unit
-    const PcbUnit *units;                          // explicit source: units of the batch (nullptr: cross product)
-    const PcbTask *tasks;
-    const int32_t *win_len;                        // cross product
-    int64_t gbase;                                 // cross product: window group of batch unit u = u + gbase
-    int32_t stride, n_ids_total, out_col;
-    const uint8_t *arena;
-    pcb_result *out;
-    int32_t *err_flag;
-    int n, r0, b, lane;
-    uint32_t GEB, Bp;
+constexpr int NB = PCF_NB;
+struct Meta {                      // views into L.meta (pcf_meta_words)
+    int32_t *hist0, *hist1, *base, *cursor, *chunk_base, *counters;
 };
-
-template <int NR, bool EXACT, int C>
-__device__ __noinline__ void trace_round(RoundCtx &q, const int64_t fresh_u /* >= 0: the entries of batch unit fresh_u; -1: pop */)
+__device__ __forceinline__ Meta meta_of(const PcbLaunch &L)
 {
-    constexpr int FW = NR / 4;
-    // the context lives in local memory: take what the loops use into registers once
-    const int lane = q.lane, n = q.n, r0 = q.r0, b = q.b;
-    const uint64_t ckw = q.ckw;
-    extern __shared__ uint32_t smem[];
-    const uint32_t *const tbl = smem + q.tbl_off, *const s_code = smem + q.code_off;
-    uint32_t *const s_fl = smem + q.fl_off, *const s_q = smem + q.q_off;
-    const uint32_t GEB = q.GEB, Bp = q.Bp;
-    const bool cross = q.units == nullptr;
+    Meta m; const int64_t A = L.n_major;
+    m.hist0 = L.meta; m.hist1 = m.hist0 + A * NB; m.base = m.hist1 + A * NB; m.cursor = m.base + A * NB + 1;
+    m.chunk_base = m.cursor + A * NB; m.counters = m.chunk_base + A + 1;
+    return m;
+}
+// counters: 0 = items in `surv`
+__device__ __forceinline__ int32_t major_of(const PcbLaunch &L, int64_t u /* unit - unit0 */, int64_t groups)
+{
+    return L.src.units ? L.src.units[L.unit0 + u].adapter : (int32_t)((L.unit0 + u) / groups);
+}
+// bucket of a first block: 0 = no block at all (empty path), 1..C = its width for paths that end in the last adapter row,
+// 17 + (rows - 1) / 4 for paths that end in the read's final column (fewer rows, all of one width)
+__device__ __forceinline__ int bucket0(uint32_t x, int C)
+{
+    const int ci = (int)(x & 63u), cj = (int)((x >> 6) & 0xFFFu), st = (int)((x >> 18) & 7u);
+    if (ci == 0 || cj == 0) return 0;
+    return st == 4 ? cj - ((cj - 1) / C) * C : 17 + ((ci - 1) >> 2);
+}
+__device__ __forceinline__ int bucket1(uint32_t pos) { return (int)(((pos & 63u) - 1u) >> 2); }
 
-    uint32_t tref[2], w2[2];
-    int ci[2], cj[2], st[2], qpos[2];
-    bool valid[2];
-    if (fresh_u >= 0) {
-        const uint4 e = q.entries[fresh_u * 32 + lane];
-        tref[0] = ((uint32_t)fresh_u << 6) | (uint32_t)(2 * lane); tref[1] = tref[0] | 1u;
-        valid[0] = (e.x >> 31) != 0u; valid[1] = (e.z >> 31) != 0u;
-        ci[0] = (int)(e.x & 63u); cj[0] = (int)((e.x >> 6) & 0xFFFu); st[0] = (int)((e.x >> 18) & 7u);
-        ci[1] = (int)(e.z & 63u); cj[1] = (int)((e.z >> 6) & 0xFFFu); st[1] = (int)((e.z >> 18) & 7u);
-        w2[0] = (e.x & 0x3FFFFu) | (e.y << 18); w2[1] = (e.z & 0x3FFFFu) | (e.w << 18);
-        qpos[0] = qpos[1] = -1;
-    } else {
-        const int take = min(q.count, 64);
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            valid[h] = 2 * lane + h < take;
-            qpos[h] = (q.head + 2 * lane + h) & (PCF_QCAP - 1);
-            tref[h] = 0u; w2[h] = 0u; ci[h] = cj[h] = st[h] = 0;
-            if (valid[h]) {
-                tref[h] = s_q[qpos[h]];
-                const uint32_t w1 = s_q[PCF_QCAP + qpos[h]];
-                ci[h] = (int)(w1 & 63u); cj[h] = (int)((w1 >> 6) & 0xFFFu); st[h] = (int)((w1 >> 18) & 7u);
-                w2[h] = s_q[2 * PCF_QCAP + qpos[h]];
-            }
-        }
-        q.head = (q.head + take) & (PCF_QCAP - 1); q.count -= take;
-    }
-    // where the task's bases are
-    uint64_t off[2]; int len[2]; int64_t widx[2];
+// one thread per (unit, lane): counts the first blocks per (major, bucket)
+__global__ void k_count0(const PcbLaunch L, int C)
+{
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nu = L.unit1 - L.unit0;
+    if ((idx >> 5) >= nu) return;                                     // whole warps leave together
+    const Meta M = meta_of(L);
+    const int64_t groups = L.src.units ? 0 : (L.src.n_windows + 63) / 64;
+    const int lane = threadIdx.x & 31;
+    const uint4 e = L.entries[idx];
+    const int32_t a = major_of(L, idx >> 5, groups);
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-        off[h] = 0; len[h] = 0; widx[h] = 0;
-        if (!valid[h]) continue;
-        if (cross) {
-            const int64_t w = ((int64_t)(tref[h] >> 6) + q.gbase) * 64 + (int64_t)(tref[h] & 63u);
-            widx[h] = w; off[h] = (uint64_t)w * (uint64_t)q.stride; len[h] = q.win_len[w];
-        } else {
-            const int64_t t = q.units[tref[h] >> 6].task0 + (int64_t)(tref[h] & 63u);
-            widx[h] = t; off[h] = q.tasks[t].off; len[h] = q.tasks[t].len;
-        }
+        const uint32_t x = h ? e.z : e.x;
+        const int key = (x >> 31) ? bucket0(x, C) : -1;
+        const uint32_t m = __match_any_sync(0xffffffffu, key);
+        if (key >= 0 && lane == __ffs(m) - 1) atomicAdd(M.hist0 + (int64_t)a * NB + key, __popc(m));
     }
-    WalkAcc acc[2];
-    auto load_acc = [&]() {                        // the walk's accumulators are fetched where the walk starts: the column loop wants the registers
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            walk_acc_init(acc[h]);
-            if (valid[h] && qpos[h] >= 0) {
-                const uint32_t a = s_q[3 * PCF_QCAP + qpos[h]], c = s_q[4 * PCF_QCAP + qpos[h]];
-                acc[h].nD = (int)(a & 63u); acc[h].matches = (int)((a >> 6) & 63u);
-                acc[h].kA = (int)((a >> 12) & 0xFFFu) - 1; acc[h].kR = (int)(a >> 24) - 1;
-                acc[h].jA = (int)(c & 0xFFFu); acc[h].iR = (int)(c >> 12);
-            }
-        }
-    };
+}
 
-    // block of each half: columns k*C+1 .. k*C+C, holding its current column
-    const bool go0 = valid[0] && ci[0] > 0 && cj[0] > 0, go1 = valid[1] && ci[1] > 0 && cj[1] > 0;
-    const int k0 = go0 ? (cj[0] - 1) / C : 0, k1 = go1 ? (cj[1] - 1) / C : 0;
-    const int jb0 = k0 * C, jb1 = k1 * C;
-    const int tmax = __reduce_max_sync(0xffffffffu, max(go0 ? cj[0] - jb0 : 0, go1 ? cj[1] - jb1 : 0));
-    if (tmax > 0) {
-        const uint8_t *const seq0 = q.arena + off[0], *const seq1 = q.arena + off[1];
-        const int lim0 = max(len[0] - 1, 0), lim1 = max(len[1] - 1, 0);
-        // the block's read bases (C per half), then the checkpointed column the block starts from
-        uint32_t q0[C / 4], q1[C / 4];
-#pragma unroll
-        for (int g = 0; g < C / 4; ++g) {
-            q0[g] = join4(load4(seq0, jb0 + 4 * g, lim0)); q1[g] = join4(load4(seq1, jb1 + 4 * g, lim1));
-            s_fl[(C * FW + g) * PCB_BLOCK] = q0[g]; s_fl[(C * FW + C / 4 + g) * PCB_BLOCK] = q1[g];   // for the walk
+// one CTA: bucket counts -> first slot of every (major, bucket) in the sorted order, and the chunk table of the rounds
+// (a chunk = 64 consecutive items of one major).  Clears the counts for their next use.
+__global__ void k_bucket_scan(const PcbLaunch L, int which)
+{
+    const Meta M = meta_of(L);
+    int32_t *const hist = which ? M.hist1 : M.hist0;
+    const int A = L.n_major, tid = threadIdx.x;
+    __shared__ int s_n[1024], s_c[1024];
+    __shared__ int carry_n, carry_c;
+    if (tid == 0) { carry_n = 0; carry_c = 0; }
+    __syncthreads();
+    for (int a0 = 0; a0 < A; a0 += 1024) {
+        const int a = a0 + tid;
+        int n = 0;
+        if (a < A) for (int b = 0; b < NB; ++b) n += hist[(int64_t)a * NB + b];
+        s_n[tid] = n; s_c[tid] = (n + 63) >> 6;
+        __syncthreads();
+        for (int d = 1; d < 1024; d <<= 1) {                          // inclusive scans
+            const int vn = tid >= d ? s_n[tid - d] : 0, vc = tid >= d ? s_c[tid - d] : 0;
+            __syncthreads();
+            s_n[tid] += vn; s_c[tid] += vc;
+            __syncthreads();
         }
-        uint32_t Mo[NR], Hl[NR];
-        {
-            // a task's checkpoints were written by the thread that ran its pass 1 (task >> 1 = batch unit * 32 + lane), two
-            // tasks per word; a record is 2*NR contiguous words, so any lane can fetch any task's with full sectors
-            const uint4 *p0 = reinterpret_cast<const uint4 *>(q.ck + ((uint64_t)(tref[0] >> 1) * ckw + (uint64_t)k0 * 2ull * NR));
-            const uint4 *p1 = reinterpret_cast<const uint4 *>(q.ck + ((uint64_t)(tref[1] >> 1) * ckw + (uint64_t)k1 * 2ull * NR));
-            const uint32_t sel = ((tref[0] & 1u) ? 0x0032u : 0x0010u) | ((tref[1] & 1u) ? 0x7600u : 0x5400u);
-#pragma unroll
-            for (int g = 0; g < NR / 2; ++g) {
-                const uint4 a = __ldcs(p0 + g), c = __ldcs(p1 + g);
-                Mo[2 * g] = prmt(a.x, c.x, sel); Hl[2 * g] = prmt(a.y, c.y, sel);
-                Mo[2 * g + 1] = prmt(a.z, c.z, sel); Hl[2 * g + 1] = prmt(a.w, c.w, sel);
+        if (a < A) {
+            int run = carry_n + s_n[tid] - n;
+            M.chunk_base[a] = carry_c + s_c[tid] - ((n + 63) >> 6);
+            for (int b = 0; b < NB; ++b) {
+                const int64_t k = (int64_t)a * NB + b;
+                M.base[k] = run; M.cursor[k] = 0; run += hist[k]; hist[k] = 0;
             }
         }
-        uint32_t rT = pk(B0 + b * jb0, B0 + b * jb1);
-        const bool pend0 = go0 && (st[0] & 4), pend1 = go1 && (st[1] & 4);
-        const bool anypend = __any_sync(0xffffffffu, pend0 || pend1);
-        int s0 = st[0] & 3, s1 = st[1] & 3;
-#pragma unroll UNR2
-        for (int t = 1; t <= tmax; ++t) {
-            const uint32_t *tp = tbl + pair_index(q0[0] & 0xFFu, q1[0] & 0xFFu);
-#pragma unroll
-            for (int g = 0; g < C / 4; ++g) {                  // shift the base queues by one byte
-                q0[g] = __funnelshift_r(q0[g], g + 1 < C / 4 ? q0[(g + 1) % (C / 4)] : 0u, 8);
-                q1[g] = __funnelshift_r(q1[g], g + 1 < C / 4 ? q1[(g + 1) % (C / 4)] : 0u, 8);
-            }
-            const uint32_t rowTp = rT;
-            rT += Bp;
-            uint32_t Ml, Vl, Hlast;
-            col_flags<NR, EXACT>(Mo, Hl, tp, rowTp, rT, GEB, s_fl + (t - 1) * FW * PCB_BLOCK, Ml, Vl, Hlast);
-            if (anypend) {
-                // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
-                // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
-                const uint32_t xv = Ml ^ Vl, xh = Ml ^ Hlast;
-                if (pend0 && jb0 + t == cj[0]) s0 = ((xv & 0xFFFFu) == 0) ? 1 : (((xh & 0xFFFFu) == 0) ? 2 : 0);
-                if (pend1 && jb1 + t == cj[1]) s1 = ((xv >> 16) == 0) ? 1 : (((xh >> 16) == 0) ? 2 : 0);
-            }
-        }
-        __syncwarp();
-        load_acc();
-        // walk (dp_traceback_impl.h:379-451, :498-545) inside the block: both halves together, one path op per half and trip
-        {
-            int i0 = ci[0], j0 = cj[0], i1 = ci[1], j1 = cj[1];
-            WalkAcc a0 = acc[0], a1 = acc[1];
-            bool act0 = go0 && j0 > jb0, act1 = go1 && j1 > jb1;
-            while (act0 || act1) {
-                if (act0) { walk_step<FW, C>(s_fl, s_code, 0, jb0, r0, i0, j0, s0, a0); act0 = i0 > 0 && j0 > jb0; }
-                if (act1) { walk_step<FW, C>(s_fl, s_code, 1, jb1, r0, i1, j1, s1, a1); act1 = i1 > 0 && j1 > jb1; }
-            }
-            ci[0] = i0; cj[0] = j0; acc[0] = a0; ci[1] = i1; cj[1] = j1; acc[1] = a1;
-        }
-        st[0] = s0; st[1] = s1;                                  // the pending bit is spent
-    } else {
-        load_acc();
+        __syncthreads();
+        if (tid == 1023) { carry_n += s_n[1023]; carry_c += s_c[1023]; }
+        __syncthreads();
     }
-    __syncwarp();                                                // every lane has read its entry before a queue slot is written again
+    if (tid == 0) { M.base[(int64_t)A * NB] = carry_n; M.chunk_base[A] = carry_c; if (which == 0) M.counters[0] = 0; }
+}
 
-    // paths that reached row 0 / column 0 are complete (this also covers the empty path); the others go (back) into the queue
-    bool keep[2];
+__device__ __forceinline__ void put_item(PcfItem *dst, uint32_t ref, uint32_t pos, uint32_t endc, uint32_t a0, uint32_t a1, uint32_t a2, uint64_t off)
+{
+    st256(reinterpret_cast<uint32_t *>(dst), ref, pos, endc, a0, a1, a2, (uint32_t)off, (uint32_t)(off >> 32));
+}
+// slot of an item of `key` in the sorted order (one atomic per distinct key of the warp)
+__device__ __forceinline__ int64_t sorted_slot(const Meta &M, int key, int lane)
+{
+    const uint32_t m = __match_any_sync(0xffffffffu, key);
+    const int leader = __ffs(m) - 1;
+    int first = 0;
+    if (key >= 0 && lane == leader) first = atomicAdd(M.cursor + key, __popc(m));
+    first = __shfl_sync(0xffffffffu, first, leader);
+    return key >= 0 ? (int64_t)M.base[key] + first + __popc(m & ((1u << lane) - 1u)) : -1;
+}
+// generation 0: one thread per (unit, lane); the end cells of pass 1 become items, in sorted order
+__global__ void k_scatter0(const PcbLaunch L, int C)
+{
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nu = L.unit1 - L.unit0;
+    if ((idx >> 5) >= nu) return;
+    const Meta M = meta_of(L);
+    const int64_t groups = L.src.units ? 0 : (L.src.n_windows + 63) / 64;
+    const int lane = threadIdx.x & 31;
+    const uint4 e = L.entries[idx];
+    const int32_t a = major_of(L, idx >> 5, groups);
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-        keep[h] = valid[h] && ci[h] > 0 && cj[h] > 0;
-        if (!valid[h] || keep[h]) continue;
-        int col0 = 0, mtrue = len[h];
-        int64_t oidx;
-        if (cross) oidx = widx[h] * q.n_ids_total + q.out_col;
-        else { const PcbTask &k = q.tasks[widx[h]]; col0 = k.col0; mtrue = k.m_true; oidx = k.out_idx; }
-        const int endi = (int)(w2[h] & 63u), endj = (int)((w2[h] >> 6) & 0xFFFu);
-        if (cj[h] == 0 && ci[h] > 0 && col0 > 0) atomicOr(q.err_flag, 1);      // window too narrow for this path
-        PathAcc pa; walk_acc_finish(acc[h], endi, endj, ci[h], cj[h], pa);
-        PathStats ps;
-        path_finalize(pa, (int64_t)col0 + cj[h], ci[h], (int64_t)mtrue - (col0 + endj), n - endi, mtrue, n, ps);
-        pcb_result res;
-        res.read_start = ps.read_start; res.read_end = ps.read_end;
-        res.adapter_start = ps.adapter_start; res.adapter_end = ps.adapter_end;
-        res.raw_score = (int)(w2[h] >> 18) - OFF; res.matches = ps.matches;
-        res.aligned_len = ps.aligned_len; res.full_len = ps.full_len;
-        q.out[oidx] = res;
+        const uint32_t x = h ? e.z : e.x, y = h ? e.w : e.y;
+        const int key = (x >> 31) ? a * NB + bucket0(x, C) : -1;
+        const int64_t slot = sorted_slot(M, key, lane);
+        if (slot >= 0) {
+            // where the task's bases are: pass 2 then starts from the item alone
+            const int64_t unit = L.unit0 + (idx >> 5);
+            const uint64_t off = L.src.units ? L.src.tasks[L.src.units[unit].task0 + 2 * lane + h].off
+                                             : (uint64_t)((unit - (int64_t)a * groups) * 64 + 2 * lane + h) * (uint64_t)L.src.stride;
+            put_item(L.sorted + slot, ((uint32_t)(idx >> 5) << 6) | (uint32_t)(2 * lane + h), x & 0x1FFFFFu, (x & 0x3FFFFu) | (y << 18), 0u, 0u, 0u, off);
+        }
     }
-    const uint32_t m0 = __ballot_sync(0xffffffffu, keep[0]), m1 = __ballot_sync(0xffffffffu, keep[1]);
-    const uint32_t lt = (1u << lane) - 1u;
-    const int tail = q.head + q.count;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        if (!keep[h]) continue;
-        const int pos = (tail + (h ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt))) & (PCF_QCAP - 1);
-        s_q[pos] = tref[h];
-        s_q[PCF_QCAP + pos] = (uint32_t)ci[h] | ((uint32_t)cj[h] << 6) | ((uint32_t)st[h] << 18);
-        s_q[2 * PCF_QCAP + pos] = w2[h];
-        s_q[3 * PCF_QCAP + pos] = (uint32_t)acc[h].nD | ((uint32_t)acc[h].matches << 6) | ((uint32_t)(acc[h].kA + 1) << 12) | ((uint32_t)(acc[h].kR + 1) << 24);
-        s_q[4 * PCF_QCAP + pos] = (uint32_t)acc[h].jA | ((uint32_t)acc[h].iR << 12);
+}
+// generation 1: one thread per surviving item
+__global__ void k_scatter1(const PcbLaunch L)
+{
+    const Meta M = meta_of(L);
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, n = M.counters[0];
+    if ((idx & ~(int64_t)31) >= n) return;
+    const int64_t groups = L.src.units ? 0 : (L.src.n_windows + 63) / 64;
+    const int lane = threadIdx.x & 31;
+    uint32_t v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int key = -1;
+    if (idx < n) {
+        ld256(reinterpret_cast<const uint32_t *>(L.surv + idx), v);
+        key = major_of(L, v[0] >> 6, groups) * NB + bucket1(v[1]);
     }
-    q.count += __popc(m0) + __popc(m1);
-    __syncwarp();
+    const int64_t slot = sorted_slot(M, key, lane);
+    if (slot >= 0) put_item(L.sorted + slot, v[0], v[1], v[2], v[3], v[4], v[5], (uint64_t)v[6] | ((uint64_t)v[7] << 32));
+}
+
+// The walk's state and accumulators for one traceback (dp_traceback_impl.h:379-451), packed so that a step is branch-free.
+//   i, j : cell the walk stands in;  s : state, 0 = M, 1 = V, 2 = H
+//   kAR  : low half = 1 + max over the ops that hold an adapter base (D, V) of 2 * column + isV (the FIRST such op has the
+//          largest; 0 = none yet), high half = the same for read bases (D, H) with rows
+//   tHV  : low = H ops since the last op with an adapter base, high = V ops since the last op with a read base
+//   nHV  : low = H ops, high = V ops;   op : gap openings (gap ops after which the walk is back in state M)
+struct Walk { int i, j, s; uint32_t kAR, tHV, nHV; int op; };
+__device__ __forceinline__ void walk_unpack(Walk &w, uint32_t pos, uint32_t a0, uint32_t a1, uint32_t a2)
+{
+    w.i = (int)(pos & 63u); w.j = (int)((pos >> 6) & 0xFFFu); w.s = (int)((pos >> 18) & 7u); w.op = (int)(pos >> 21);
+    w.kAR = a0; w.tHV = a1; w.nHV = a2;
+}
+__device__ __forceinline__ uint32_t walk_pos(const Walk &w)
+{
+    return (uint32_t)w.i | ((uint32_t)w.j << 6) | ((uint32_t)w.s << 18) | ((uint32_t)w.op << 21);
+}
+// One op of the reverse walk; flag word layout as col_flags writes it.  ar = register row of the walk's adapter row, jc = its
+// column inside the flag block, pos2 = (2 * column + 1) | (2 * row + 1) << 16.  In state M a cell whose diagonal flag is off
+// hands over to V or H and that state's step is taken at once, from the same cell's flags, as SeqAn does.  No branches:
+// the two tracebacks of a thread are stepped together and their shared-memory loads overlap.
+template <int FW>
+__device__ __forceinline__ uint32_t walk_flags(const uint32_t *s_fl, const int h, const int ar, const int jc)
+{
+    return s_fl[(jc * FW + (ar >> 2)) * PCB_BLOCK] >> (8 * h + 2 * (ar & 3));
+}
+template <int FW>
+__device__ __forceinline__ void walk_step(const uint32_t *s_fl, const int h, int &ar, int &jc, uint32_t &pos2, Walk &w)
+{
+    const uint32_t f = walk_flags<FW>(s_fl, h, ar, jc);
+    const uint32_t fh = f & 1u, fg = (f >> 1) & 1u, fv = (f >> 16) & 1u, fd = (f >> 17) & 1u;
+    const uint32_t sM = w.s == 0 ? 1u : 0u, sV = w.s == 1 ? 1u : 0u;
+    const uint32_t isD = sM & fd, isV = sV | (sM & (fd ^ 1u) & fg), isH = (isD | isV) ^ 1u;
+    const uint32_t inc = isH | (isV << 16), incs = isV | (isH << 16);
+    const uint32_t keep = inc * 0xFFFFu;                          // H: 0x0000FFFF, V: 0xFFFF0000, D: 0
+    w.kAR = __vmaxs2(w.kAR, (pos2 + incs) & ~keep);
+    w.tHV = (w.tHV & keep) + inc;
+    w.nHV += inc;
+    pos2 = pos2 - 0x00020002u + 2u * incs;
+    const uint32_t extV = isV & fv, extH = isH & fh;
+    w.op += (int)((isD | extV | extH) ^ 1u);
+    w.s = (int)(extV | (extH << 1));
+    ar -= (int)(isH ^ 1u); jc -= (int)(isV ^ 1u);
 }
 
 template <int NR, bool EXACT, int C>
 __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const PcbLaunch L)
 {
     extern __shared__ uint32_t smem[];
-    constexpr int FW = NR / 4;
-    constexpr int W = PCB_BLOCK / 32;
+    constexpr int FW = NR / 4, W = PCB_BLOCK / 32;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t *const tbl = smem + warp * (NR * TP);
     uint32_t *const s_code = smem + W * (NR * TP) + warp * NR;
+    uint32_t *const s_fl = smem + W * (NR * TP + NR) + threadIdx.x;
 
+    const Meta M = meta_of(L);
+    const int A = L.n_major;
+    const bool gen0 = L.gen == 0;
     const int b = -L.sc.gap_open;
     const int s_match = L.sc.match + 2 * b, s_mis = L.sc.mismatch + 2 * b;
-    const int64_t nwarps = (int64_t)gridDim.x * W, gw = (int64_t)blockIdx.x * W + warp;
+    const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b);
     const bool cross = L.src.units == nullptr;
     const int64_t groups = cross ? (L.src.n_windows + 63) / 64 : 0;
-    const int64_t nu = L.unit1 - L.unit0;
-    int64_t u_begin, u_end, u_step;
-    if (cross) { u_begin = L.unit0 + gw * nu / nwarps; u_end = L.unit0 + (gw + 1) * nu / nwarps; u_step = 1; }
-    else       { u_begin = L.unit0 + gw; u_end = L.unit1; u_step = nwarps; }
+    const uint64_t ckw = ckw_of(L.mmax, C, NR);                  // checkpoint words per thread and unit
 
-    RoundCtx q;
-    q.head = 0; q.count = 0;
-    q.tbl_off = (int)(tbl - smem); q.code_off = (int)(s_code - smem);
-    q.q_off = W * (NR * TP + NR) + warp * (QW * PCF_QCAP);
-    q.fl_off = W * (NR * TP + NR + QW * PCF_QCAP) + (int)threadIdx.x;
-    q.ck = L.scratch; q.entries = L.entries; q.ckw = ckw_of(L.mmax, C, NR);
-    q.units = cross ? nullptr : L.src.units + L.unit0; q.tasks = L.src.tasks;
-    q.win_len = L.src.win_len; q.gbase = 0; q.stride = L.src.stride; q.n_ids_total = L.src.n_ids_total; q.out_col = 0;
-    q.arena = L.arena; q.out = L.out; q.err_flag = L.err_flag;
-    q.n = 0; q.r0 = 0; q.b = b; q.lane = lane;
-    q.GEB = pk2(L.sc.gap_extend + b); q.Bp = pk2(b);
-    (void)FW;
+    const int64_t nwarps = (int64_t)gridDim.x * W, gw = (int64_t)blockIdx.x * W + warp;
+    const int64_t total = M.chunk_base[A];
+    const int64_t c_begin = gw * total / nwarps, c_end = (gw + 1) * total / nwarps;
+    int a = -1, n = 0, r0 = 0;
+    int32_t tbl_adapter = -1, out_col = 0;
+    int64_t a_item0 = 0, a_item1 = 0, a_chunk0 = 0, a_chunk1 = 0;
 
-    int32_t tbl_adapter = -1;
-    int64_t cur_k = -1;
-    for (int64_t unit = u_begin; unit < u_end; unit += u_step) {
-        int32_t adapter;
-        int64_t k = 0;
-        if (cross) { k = unit / groups; adapter = L.src.ids[k]; }
-        else adapter = L.src.units[unit].adapter;
-        const int64_t aoff = L.ad.off[adapter];
-        const int n = (int)(L.ad.off[adapter + 1] - aoff);
-        if (n <= 0 || n > NR || (EXACT && n != NR)) continue;          // pass 1 wrote the failed records and raised the flag
-        const int r0 = EXACT ? 0 : NR - n;
-        if (adapter != tbl_adapter || k != cur_k) {
-            while (q.count > 0) trace_round<NR, EXACT, C>(q, -1);     // the queue's entries belong to the old adapter / result column
-            if (cross) { q.gbase = L.unit0 - k * groups; q.out_col = L.src.id_pos ? L.src.id_pos[k] : (int32_t)k; }
-            cur_k = k;
-        }
-        if (adapter != tbl_adapter) {
-            q.n = n; q.r0 = r0;
-            __syncwarp();
-            for (int i = lane; i < NR; i += 32) s_code[i] = i >= r0 ? (uint32_t)(L.ad.codes[aoff + i - r0] / PCB_CODE_SCALE) : 0u;
-            __syncwarp();
-            for (int e = lane; e < NR * TP; e += 32) {
-                const int r = e / TP, p = e - r * TP;
-                const uint32_t a = s_code[r], c0 = (uint32_t)(p / 5), c1 = (uint32_t)(p % 5);
-                tbl[e] = r >= r0 ? pk(c0 == a ? s_match : s_mis, c1 == a ? s_match : s_mis) : pk(2 * b, 2 * b);
+    for (int64_t c = c_begin; c < c_end; ++c) {
+        if (c >= a_chunk1) {                                     // the chunks of the next major(s) begin
+            do { ++a; a_chunk1 = M.chunk_base[a + 1]; } while (c >= a_chunk1);
+            a_item0 = M.base[(int64_t)a * NB]; a_item1 = M.base[(int64_t)(a + 1) * NB]; a_chunk0 = M.chunk_base[a];
+            const int32_t adapter = cross ? L.src.ids[a] : a;
+            if (cross) out_col = L.src.id_pos ? L.src.id_pos[a] : a;
+            const int64_t aoff = L.ad.off[adapter];
+            n = (int)(L.ad.off[adapter + 1] - aoff);
+            r0 = EXACT ? 0 : NR - n;
+            if (adapter != tbl_adapter) {
+                __syncwarp();
+                for (int i = lane; i < NR; i += 32) s_code[i] = i >= r0 ? (uint32_t)(L.ad.codes[aoff + i - r0] / PCB_CODE_SCALE) : 0u;
+                __syncwarp();
+                for (int e = lane; e < NR * TP; e += 32) {
+                    const int r = e / TP, p = e - r * TP;
+                    const uint32_t ac = s_code[r], c0 = (uint32_t)(p / 5), c1 = (uint32_t)(p % 5);
+                    tbl[e] = r >= r0 ? pk(c0 == ac ? s_match : s_mis, c1 == ac ? s_match : s_mis) : pk(2 * b, 2 * b);
+                }
+                __syncwarp();
+                tbl_adapter = adapter;
             }
-            __syncwarp();
-            tbl_adapter = adapter;
         }
-        trace_round<NR, EXACT, C>(q, unit - L.unit0);
-        while (q.count >= 64) trace_round<NR, EXACT, C>(q, -1);
+        // this lane's two items
+        const int64_t i0 = a_item0 + (c - a_chunk0) * 64 + 2 * lane;
+        bool valid[2];
+        uint32_t ref[2], endc[2];
+        Walk wk[2];
+        uint64_t off[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            valid[h] = i0 + h < a_item1;
+            uint32_t v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            if (valid[h]) ld256(reinterpret_cast<const uint32_t *>(L.sorted + i0 + h), v);
+            ref[h] = v[0]; endc[h] = v[2];
+            walk_unpack(wk[h], v[1], v[3], v[4], v[5]);
+            off[h] = (uint64_t)v[6] | ((uint64_t)v[7] << 32);
+        }
+        // (bases are fetched a few bytes past a segment's end: the arenas are padded, and columns past the end never count)
+        const uint8_t *const seq0 = L.arena + off[0], *const seq1 = L.arena + off[1];
+        constexpr int lim0 = 0x7fffffff, lim1 = 0x7fffffff;
+
+        for (;;) {
+            // block of each half: columns k*C+1 .. k*C+C, holding its current column
+            const bool go0 = valid[0] && wk[0].i > 0 && wk[0].j > 0, go1 = valid[1] && wk[1].i > 0 && wk[1].j > 0;
+            const int k0 = go0 ? (wk[0].j - 1) / C : 0, k1 = go1 ? (wk[1].j - 1) / C : 0;
+            const int jb0 = k0 * C, jb1 = k1 * C;
+            const int tmax = __reduce_max_sync(0xffffffffu, max(go0 ? wk[0].j - jb0 : 0, go1 ? wk[1].j - jb1 : 0));
+            // register rows the flags are needed for: everything above the rows the walks stand in
+            const int rlim = __reduce_max_sync(0xffffffffu, max(go0 ? (r0 + wk[0].i + 3) & ~3 : 0, go1 ? (r0 + wk[1].i + 3) & ~3 : 0));
+            if (tmax > 0) {
+                uint32_t q0[C / 4], q1[C / 4];                   // the block's read bases
+#pragma unroll
+                for (int g = 0; g < C / 4; ++g) { q0[g] = join4(load4(seq0, jb0 + 4 * g, lim0)); q1[g] = join4(load4(seq1, jb1 + 4 * g, lim1)); }
+                uint32_t Mo[NR], Hl[NR];
+                {
+                    // the checkpointed column the block starts from: written by the thread that ran the task's pass 1
+                    // (slot >> 1), two tasks per word
+                    const uint32_t *p0 = L.scratch + ((uint64_t)(ref[0] >> 6) * 32u * ckw + (uint64_t)k0 * (NR / 4) * 256u + (uint64_t)((ref[0] & 63u) >> 1) * 8u);
+                    const uint32_t *p1 = L.scratch + ((uint64_t)(ref[1] >> 6) * 32u * ckw + (uint64_t)k1 * (NR / 4) * 256u + (uint64_t)((ref[1] & 63u) >> 1) * 8u);
+                    const uint32_t sel = ((ref[0] & 1u) ? 0x0032u : 0x0010u) | ((ref[1] & 1u) ? 0x7600u : 0x5400u);
+#pragma unroll
+                    for (int g = 0; g < NR / 4; ++g) {
+                        if (4 * g < rlim) {
+                            uint32_t x[8], y[8];
+                            ld256(p0 + g * 256, x); ld256(p1 + g * 256, y);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) { Mo[4 * g + e] = prmt(x[2 * e], y[2 * e], sel); Hl[4 * g + e] = prmt(x[2 * e + 1], y[2 * e + 1], sel); }
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) { Mo[4 * g + e] = 0u; Hl[4 * g + e] = 0u; }
+                        }
+                    }
+                }
+                uint32_t rT = pk(B0 + b * jb0, B0 + b * jb1);
+                const bool pend0 = go0 && (wk[0].s & 4), pend1 = go1 && (wk[1].s & 4);
+                const bool anypend = __any_sync(0xffffffffu, pend0 || pend1);
+                int s0 = wk[0].s & 3, s1 = wk[1].s & 3;
+#pragma unroll UNR2
+                for (int t = 1; t <= tmax; ++t) {
+                    const uint32_t *tp = tbl + pair_index(q0[0] & 0xFFu, q1[0] & 0xFFu);
+#pragma unroll
+                    for (int g = 0; g < C / 4; ++g) {                  // shift the base queues by one byte
+                        q0[g] = __funnelshift_r(q0[g], g + 1 < C / 4 ? q0[(g + 1) % (C / 4)] : 0u, 8);
+                        q1[g] = __funnelshift_r(q1[g], g + 1 < C / 4 ? q1[(g + 1) % (C / 4)] : 0u, 8);
+                    }
+                    const uint32_t rowTp = rT;
+                    rT += Bp;
+                    uint32_t Ml, Vl, Hlast;
+                    col_flags<NR, EXACT>(Mo, Hl, tp, rowTp, rT, GEB, s_fl + (t - 1) * FW * PCB_BLOCK, rlim, Ml, Vl, Hlast);
+                    if (anypend) {
+                        // end cell in the last adapter row: V == M / H == M of that cell decide how the trace starts
+                        // (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
+                        const uint32_t xv = Ml ^ Vl, xh = Ml ^ Hlast;
+                        if (pend0 && jb0 + t == wk[0].j) s0 = ((xv & 0xFFFFu) == 0) ? 1 : (((xh & 0xFFFFu) == 0) ? 2 : 0);
+                        if (pend1 && jb1 + t == wk[1].j) s1 = ((xv >> 16) == 0) ? 1 : (((xh >> 16) == 0) ? 2 : 0);
+                    }
+                }
+                __syncwarp();
+                wk[0].s = s0; wk[1].s = s1;                              // the pending bit is spent
+                // walk (dp_traceback_impl.h:379-451, :498-545) inside the block: both halves together while both are on their way
+                {
+                    Walk w0 = wk[0], w1 = wk[1];
+                    int ar0 = r0 + w0.i - 1, jc0 = w0.j - jb0 - 1, ar1 = r0 + w1.i - 1, jc1 = w1.j - jb1 - 1;
+                    uint32_t pz0 = (uint32_t)(2 * w0.j + 1) | ((uint32_t)(2 * w0.i + 1) << 16), pz1 = (uint32_t)(2 * w1.j + 1) | ((uint32_t)(2 * w1.i + 1) << 16);
+                    bool act0 = go0, act1 = go1;
+                    while (act0 && act1) {
+                        walk_step<FW>(s_fl, 0, ar0, jc0, pz0, w0); walk_step<FW>(s_fl, 1, ar1, jc1, pz1, w1);
+                        act0 = ar0 >= r0 && jc0 >= 0; act1 = ar1 >= r0 && jc1 >= 0;
+                    }
+                    while (act0) { walk_step<FW>(s_fl, 0, ar0, jc0, pz0, w0); act0 = ar0 >= r0 && jc0 >= 0; }
+                    while (act1) { walk_step<FW>(s_fl, 1, ar1, jc1, pz1, w1); act1 = ar1 >= r0 && jc1 >= 0; }
+                    if (go0) { w0.i = ar0 - r0 + 1; w0.j = jc0 + jb0 + 1; }
+                    if (go1) { w1.i = ar1 - r0 + 1; w1.j = jc1 + jb1 + 1; }
+                    wk[0] = w0; wk[1] = w1;
+                }
+                __syncwarp();                                            // the flag words are rewritten by the next round
+            }
+
+            // paths that reached row 0 / column 0 are complete (this also covers the empty path)
+            bool keep[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const Walk &w = wk[h];
+                keep[h] = valid[h] && w.i > 0 && w.j > 0;
+                if (!valid[h] || keep[h]) continue;
+                valid[h] = false;
+                int col0 = 0, mtrue;
+                int64_t oidx;
+                if (cross) {
+                    const int64_t wi = (L.unit0 + (int64_t)(ref[h] >> 6) - (int64_t)a * groups) * 64 + (int64_t)(ref[h] & 63u);
+                    mtrue = L.src.win_len[wi]; oidx = wi * L.src.n_ids_total + out_col;
+                } else {
+                    const PcbTask &k = L.src.tasks[L.src.units[L.unit0 + (int64_t)(ref[h] >> 6)].task0 + (int64_t)(ref[h] & 63u)];
+                    col0 = k.col0; mtrue = k.m_true; oidx = k.out_idx;
+                }
+                const int endi = (int)(endc[h] & 63u), endj = (int)((endc[h] >> 6) & 0xFFFu), score = (int)(endc[h] >> 18) - OFF;
+                if (w.j == 0 && w.i > 0 && col0 > 0) atomicOr(L.err_flag, 1);      // window too narrow for this path
+                // the path as align_stats.h wants it.  Matches are not counted on the way: the path's ops and the end
+                // cell's score determine them (every D op scores match or mismatch, every gap of g ops go + (g-1) ge)
+                const int nH = (int)(w.nHV & 0xFFFFu), nV = (int)(w.nHV >> 16), kA = (int)(w.kAR & 0xFFFFu) - 1, kR = (int)(w.kAR >> 16) - 1;
+                const int rows = endi - w.i, cols = endj - w.j, nD = rows - nV;
+                const int num = score - L.sc.mismatch * nD - L.sc.gap_open * w.op - L.sc.gap_extend * (nV + nH - w.op);
+                const int den = L.sc.match - L.sc.mismatch;
+                if (nD != cols - nH || num < 0 || num % den != 0) atomicOr(L.err_flag, 16);
+                PathAcc pa;
+                pa.K = nD + nV + nH; pa.matches = num / den;
+                pa.kA_last_rev = -1; pa.kA_first_rev = -1; pa.kR_last_rev = -1; pa.kR_first_rev = -1; pa.A_last_isD = 0; pa.R_last_isD = 0;
+                if (kA >= 0) { pa.kA_last_rev = endj - (kA >> 1); pa.A_last_isD = !(kA & 1); pa.kA_first_rev = pa.K - 1 - (int)(w.tHV & 0xFFFFu); }
+                if (kR >= 0) { pa.kR_last_rev = endi - (kR >> 1); pa.R_last_isD = !(kR & 1); pa.kR_first_rev = pa.K - 1 - (int)(w.tHV >> 16); }
+                PathStats ps;
+                path_finalize(pa, (int64_t)col0 + w.j, w.i, (int64_t)mtrue - (col0 + endj), n - endi, mtrue, n, ps);
+                pcb_result res;
+                res.read_start = ps.read_start; res.read_end = ps.read_end;
+                res.adapter_start = ps.adapter_start; res.adapter_end = ps.adapter_end;
+                res.raw_score = score; res.matches = ps.matches;
+                res.aligned_len = ps.aligned_len; res.full_len = ps.full_len;
+                L.out[oidx] = res;
+            }
+            if (!gen0) {
+                if (!__any_sync(0xffffffffu, keep[0] || keep[1])) break;
+                continue;                                                // these 64 stay together until the last is done
+            }
+            // generation 0: the others go to generation 1, counted per (major, rows)
+            const uint32_t m0 = __ballot_sync(0xffffffffu, keep[0]), m1 = __ballot_sync(0xffffffffu, keep[1]);
+            const int nk = __popc(m0) + __popc(m1);
+            if (nk) {
+                int first = 0;
+                if (lane == 0) first = atomicAdd(M.counters, nk);
+                first = __shfl_sync(0xffffffffu, first, 0);
+                const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const Walk &w = wk[h];
+                    const uint32_t pos = walk_pos(w);
+                    const int key = keep[h] ? a * NB + bucket1(pos) : -1;
+                    const uint32_t mk = __match_any_sync(0xffffffffu, key);
+                    if (keep[h]) {
+                        if (lane == __ffs(mk) - 1) atomicAdd(M.hist1 + key, __popc(mk));
+                        const int slot = first + (h ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt));
+                        put_item(L.surv + slot, ref[h], pos, endc[h], w.kAR, w.tHV, w.nHV, off[h]);
+                    }
+                }
+            }
+            break;
+        }
     }
-    while (q.count > 0) trace_round<NR, EXACT, C>(q, -1);
 }
 
 }  // namespace
@@ -773,8 +898,8 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
 static size_t fast_smem(int kind, int nr, int c)
 {
     const size_t W = PCB_BLOCK / 32;
-    if (kind == 2)       // rounds: tables, codes, queues, then flags + block bases per thread
-        return (W * (size_t)(nr * TP + nr + QW * PCF_QCAP) + (size_t)PCB_BLOCK * ((size_t)c * (nr / 4) + 2 * (c / 4))) * sizeof(uint32_t);
+    if (kind == 2)       // rounds: tables, codes, then the flag words per thread
+        return (W * (size_t)(nr * TP + nr) + (size_t)PCB_BLOCK * ((size_t)c * (nr / 4))) * sizeof(uint32_t);
     return (W * (size_t)(nr * TP + nr) + (size_t)PCB_BLOCK * 2 * nr) * sizeof(uint32_t);      // column dump
 }
 
@@ -839,14 +964,37 @@ cudaError_t pcf_launch_scan(const PcbLaunch &L, int cls, cudaStream_t st)
     return cudaSuccess;
 }
 
-cudaError_t pcf_launch_trace(const PcbLaunch &L, int cls, int grid_rounds, cudaStream_t st)
+// Trace of the units [L.unit0, L.unit1): pass 1, then per generation count / scan / scatter / rounds.  Everything on one
+// stream, nothing comes back to the host.
+cudaError_t pcf_launch_trace(const PcbLaunch &L0, int cls, int grid_rounds, cudaStream_t st)
 {
-    if (L.unit1 <= L.unit0) return cudaSuccess;
+    if (L0.unit1 <= L0.unit0) return cudaSuccess;
     if (cls < 0 || cls >= PCF_NCLS) return cudaErrorInvalidValue;
-    cudaError_t e = cudaSuccess;
-    PCF_BY_CLASS(e = launch_fast<1, NR, EX, C>(L, L.grid, st); if (e == cudaSuccess) e = launch_rounds<NR, EX, C>(L, grid_rounds, st))
-    return e;
+    PcbLaunch L = L0;
+    const int C = pcf_class_c(cls);
+    const int64_t nu = L.unit1 - L.unit0;
+    cudaError_t e = cudaMemsetAsync(L.meta, 0, pcf_meta_words(L.n_major) * sizeof(int32_t), st);
+    if (e != cudaSuccess) return e;
+    PCF_BY_CLASS(e = launch_fast<1, NR, EX, C>(L, L.grid, st))
+    if (e != cudaSuccess) return e;
+    const unsigned g0 = (unsigned)((nu * 32 + 255) / 256);
+    k_count0<<<g0, 256, 0, st>>>(L, C);
+    k_bucket_scan<<<1, 1024, 0, st>>>(L, 0);
+    k_scatter0<<<g0, 256, 0, st>>>(L, C);
+    L.gen = 0;
+    PCF_BY_CLASS(e = launch_rounds<NR, EX, C>(L, grid_rounds, st))
+    if (e != cudaSuccess) return e;
+    k_bucket_scan<<<1, 1024, 0, st>>>(L, 1);
+    // the survivors are counted on the device: the scatter is sized for the worst case and leaves early
+    const unsigned g1 = (unsigned)((nu * 64 + 255) / 256);
+    k_scatter1<<<g1, 256, 0, st>>>(L);
+    L.gen = 1;
+    PCF_BY_CLASS(e = launch_rounds<NR, EX, C>(L, grid_rounds, st))
+    if (e != cudaSuccess) return e;
+    return cudaGetLastError();
 }
+
+int pcf_trace_launches() { return 8; }
 
 int pcf_occupancy_grid(int kind, int cls)
 {

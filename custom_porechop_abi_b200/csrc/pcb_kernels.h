@@ -84,6 +84,17 @@ struct PcbAdapters {
     const uint8_t *codes;        /* all adapters, Dna5 codes                                     */
     const int64_t *off;          /* n_adapters + 1                                               */
     int32_t  max_len;
+    int32_t  n;                  /* adapters in the set                                          */
+};
+
+/* Work item of pass 2 of the fast trace (pcb_fast.cu): one traceback in progress.  32 bytes = one sector. */
+struct PcfItem {
+    uint32_t ref;        /* (unit - unit0) << 6 | task slot in the unit                                   */
+    uint32_t pos;        /* where the walk stands: row | column << 6 | state << 18 (state 4: still to be   */
+                         /* decided from V == M / H == M of the end cell)                                  */
+    uint32_t endc;       /* end cell: row | column << 6 | (raw score + 2048) << 18                         */
+    uint32_t a0, a1, a2; /* the walk's accumulators, see trace_finish                                      */
+    uint32_t pad0, pad1;
 };
 
 /* scan (score-only) output per task slot */
@@ -108,6 +119,10 @@ struct PcbLaunch {
      * every task's checkpoints in scratch ([unit - unit0][lane][pcf_ck_words]) and its end cell in entries */
     int64_t     unit0, unit1;
     uint4      *entries;         /* [unit - unit0][lane]: {end cell, score} of the lane's two tasks */
+    PcfItem    *sorted, *surv;   /* pass 2: items in processing order; items that go on to the next generation */
+    int32_t    *meta;            /* pass 2: bucket counts, bases, chunk table (pcf_meta_words)      */
+    int32_t     n_major;         /* pass 2: majors = adapters of the launch (cross product: its id list; task lists: the adapter set) */
+    int32_t     gen;             /* pass 2: 0 = first block of every traceback, 1 = all later blocks */
 };
 
 /* words of scratch per thread slot */
@@ -176,15 +191,19 @@ int pcb_occupancy_grid(int which /*0 trace, 1 scan*/);
 cudaError_t pcf_launch_scan(const PcbLaunch &L, int cls, cudaStream_t st);
 cudaError_t pcf_launch_trace(const PcbLaunch &L, int cls, int grid_rounds, cudaStream_t st);
 int pcf_occupancy_grid(int kind /* 0 scan, 1 pass 1, 2 rounds */, int cls);
-/* Trace of the fast classes = two kernels over a batch of units (pcf_launch_trace): pass 1 (score only) leaves the DP column
- * of every task at every C-th column in scratch, one record of 2*NR words per (thread, checkpoint), and each task's end
- * cell in `entries`; the rounds kernel recomputes, with trace flags, only the C-column blocks a path crosses.
- * Words of scratch per unit (64 tasks = 32 threads): checkpoints, then 4 words of entries per thread. */
-#define PCF_QCAP 128              /* entries in a warp's continuation queue (shared memory) */
+int pcf_trace_launches(void);       /* kernel launches of one pcf_launch_trace call */
+/* Trace of the fast classes over a batch of units (pcf_launch_trace): pass 1 (score only) leaves the DP column of every
+ * task at every C-th column in scratch (per unit and checkpoint NR/4 warp-wide 1 KB lines: 4 rows x (M, H) per thread)
+ * and each task's end cell in `entries`; pass 2 recomputes, with trace flags, only the C-column blocks a path crosses:
+ * the tracebacks are sorted by what their next block costs (columns x rows), 64 of a kind make a round. */
+#define PCF_NB 32                 /* sort buckets per major (first blocks: by width / rows; later blocks: by rows) */
 static inline uint64_t pcf_ck_words(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * NR; }
+/* words per unit: checkpoints, entries (4 per thread), sorted items and surviving items (8 words per task each) */
 static inline uint64_t pcf_unit_words_trace(int mmax, int cls)
 {
-    return 32ull * (pcf_ck_words(mmax, pcf_class_c(cls), pcf_class_nr(cls)) + 4);
+    return 32ull * (pcf_ck_words(mmax, pcf_class_c(cls), pcf_class_nr(cls)) + 4) + 2ull * 64 * 8;
 }
+/* meta (int32): hist[2][A * NB] | base[A * NB + 1] | cursor[A * NB] | chunk_base[A + 1] | counters[8] */
+static inline uint64_t pcf_meta_words(int n_major) { return 4ull * n_major * PCF_NB + n_major + 16; }
 
 #endif
