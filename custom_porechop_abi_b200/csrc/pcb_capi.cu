@@ -288,8 +288,11 @@ static int check_range(pcb_context *c, int nmax, int mmax)
 static bool fast_scheme(const PcbScores &s)
 {
     const int b = -s.gap_open;
-    return s.gap_open < 0 && s.gap_extend < 0 && s.gap_extend > s.gap_open && b <= 20 && s.match > 0 &&
-           s.match > s.mismatch && s.mismatch + 2 * b >= 0 && s.match + 2 * b <= 127;
+    // b <= 7: the trace checkpoints hold a DP value in 13 bits (64 + b * (52 + 1000) + 52 * match < 8192) and M - H, clamped
+    // to gapExtend - gapOpen + 1, in 3
+    return s.gap_open < 0 && s.gap_extend < 0 && s.gap_extend > s.gap_open && b <= 7 && s.match > 0 &&
+           s.match > s.mismatch && s.mismatch + 2 * b >= 0 && s.match + 2 * b <= 127 &&
+           64 + b * (PCF_MAX_N + PCF_MAX_TRACE_M) + PCF_MAX_N * s.match < 8192;
 }
 
 static int ensure_scratch(pcb_context *c, uint64_t words_per_slot, int grid)

@@ -243,7 +243,7 @@ __device__ __forceinline__ uint32_t join4(const Raw4 &r) { return __funnelshift_
 // offset (in words) into a row of the score table for the two code bytes (Dna5 code * 8) of a column
 __device__ __forceinline__ uint32_t pair_index(uint32_t c8_0, uint32_t c8_1) { return (c8_0 * 5u + c8_1) >> 3; }
 
-__device__ __forceinline__ uint64_t ckw_of(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * NR; }   // = pcf_ck_words (pcb_kernels.h)
+__device__ __forceinline__ uint64_t ckw_of(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C) * (uint64_t)((NR + 7) / 8) * 8ull; }   // = pcf_ck_words (pcb_kernels.h)
 
 // ------------------------------------------------------------------------------------------------
 // k_fast<MODE, NR, EXACT, C>: the score-only pass
@@ -366,7 +366,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(MODE, NR)) k_fast(const Pc
         for (int r = 0; r < NR; ++r) { Mo[r] = pk2(B0 + b * (r + 1)); Hl[r] = 0; }   // column 0: M = 0, H = -inf
         uint32_t rowT = pk2(B0);                                 // biased M(0, j) = bias of row 0 at the current column
         const uint32_t candK = pk2(OFF - b * NR);                // candidate = M(n, j) + candK - rowT = score + OFF
-        // this thread's part of the unit's checkpoints: [unit - unit0][k][NR / 4][lane][8 words = (M, H) of 4 rows]
+        // this thread's part of the unit's checkpoints: [unit - unit0][k - 1][(NR + 7) / 8][lane][8 words = 8 rows, 16 bits per task]
         uint32_t *const ckp = TRACE ? L.scratch + (uint64_t)(unit - L.unit0) * 32u * ckw + (uint64_t)lane * 8u : nullptr;
         uint32_t ckoff = 0;
         int ckc = 0;                                             // columns since the last checkpoint
@@ -415,16 +415,24 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(MODE, NR)) k_fast(const Pc
         for (int j0 = 1; j0 <= mw; j0 += 4) {
             uint32_t cur0 = join4(nx0), cur1 = join4(nx1);
             nx0 = load4(seq0, j0 + 3, lim0); nx1 = load4(seq1, j0 + 3, lim1);       // used one group later
-            if (TRACE && ckc == 0) {                             // checkpoint = state after column j0-1 (a multiple of C)
+            if (TRACE && ckc == 0 && j0 > 1) {                   // checkpoint k = state after column j0 - 1 = k * C  (column 0 is known)
+                // One 16-bit word per cell and task: M in 13 bits, M - H in 3.  H only matters to the next column while
+                // H + ge >= M + go, i.e. M - H <= ge - go =: t; any H further down gives the same value and the same flag, so
+                // M - H is stored clamped to t + 1 <= 7 (pcf: fast schemes have go >= -7, which also keeps M below 2^13).
                 // (address from base + running offset: a pointer bumped after the stores waits for all of them to read it;
                 //  streaming stores: a record is read back at most once, by another SM, much later.  Every store of the warp
                 //  is one contiguous KB: records kept per thread -- 32 scattered 16-byte pieces per instruction -- held the
                 //  shared-memory loads of the column loop up behind them in the memory pipe)
                 uint32_t *const cq = ckp + ckoff;
+                const uint32_t T1 = GEB + 0x00010001u;
 #pragma unroll
-                for (int g = 0; g < NR / 4; ++g)
-                    st256(cq + g * 256, Mo[4 * g], Hl[4 * g], Mo[4 * g + 1], Hl[4 * g + 1], Mo[4 * g + 2], Hl[4 * g + 2], Mo[4 * g + 3], Hl[4 * g + 3]);
-                ckoff += (NR / 4) * 256;
+                for (int g = 0; g < (NR + 7) / 8; ++g) {
+                    uint32_t v[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) { const int r = 8 * g + e; v[e] = r < NR ? Mo[r < NR ? r : 0] + __vminu2(Mo[r < NR ? r : 0] - Hl[r < NR ? r : 0], T1) * 8192u : 0u; }
+                    st256(cq + g * 256, v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
+                }
+                ckoff += ((NR + 7) / 8) * 256;
             }
             if (TRACE) { ckc += 4; if (ckc == C) ckc = 0; }
             if (!TRACE && ((j0 - 1) & (REBASE - 1)) == 0 && j0 > 1) {   // keep the growing bias inside 15 bits
@@ -758,20 +766,31 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
                 uint32_t Mo[NR], Hl[NR];
                 {
                     // the checkpointed column the block starts from: written by the thread that ran the task's pass 1
-                    // (slot >> 1), two tasks per word
-                    const uint32_t *p0 = L.scratch + ((uint64_t)(ref[0] >> 6) * 32u * ckw + (uint64_t)k0 * (NR / 4) * 256u + (uint64_t)((ref[0] & 63u) >> 1) * 8u);
-                    const uint32_t *p1 = L.scratch + ((uint64_t)(ref[1] >> 6) * 32u * ckw + (uint64_t)k1 * (NR / 4) * 256u + (uint64_t)((ref[1] & 63u) >> 1) * 8u);
+                    // (slot >> 1), two tasks per word, M | (M - H) << 13 per task; column 0 is not stored (M = 0, H = -inf)
+                    constexpr int G8 = (NR + 7) / 8;
+                    const uint32_t *p0 = L.scratch + ((uint64_t)(ref[0] >> 6) * 32u * ckw + (uint64_t)max(k0 - 1, 0) * G8 * 256u + (uint64_t)((ref[0] & 63u) >> 1) * 8u);
+                    const uint32_t *p1 = L.scratch + ((uint64_t)(ref[1] >> 6) * 32u * ckw + (uint64_t)max(k1 - 1, 0) * G8 * 256u + (uint64_t)((ref[1] & 63u) >> 1) * 8u);
                     const uint32_t sel = ((ref[0] & 1u) ? 0x0032u : 0x0010u) | ((ref[1] & 1u) ? 0x7600u : 0x5400u);
+                    const uint32_t T1s = (GEB + 0x00010001u) * 8192u;
+                    const bool ld0 = go0 && k0 > 0, ld1 = go1 && k1 > 0;
 #pragma unroll
-                    for (int g = 0; g < NR / 4; ++g) {
-                        if (4 * g < rlim) {
+                    for (int g = 0; g < G8; ++g) {
+                        if (8 * g < rlim) {
                             uint32_t x[8], y[8];
-                            ld256(p0 + g * 256, x); ld256(p1 + g * 256, y);
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) { Mo[4 * g + e] = prmt(x[2 * e], y[2 * e], sel); Hl[4 * g + e] = prmt(x[2 * e + 1], y[2 * e + 1], sel); }
+                            for (int e = 0; e < 8; ++e) x[e] = y[e] = pk2(B0 + b * (8 * g + e + 1)) + T1s;
+                            if (ld0) ld256(p0 + g * 256, x);
+                            if (ld1) ld256(p1 + g * 256, y);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                if (8 * g + e < NR) {
+                                    const uint32_t v = prmt(x[e], y[e], sel), m = v & 0x1FFF1FFFu;
+                                    Mo[8 * g + e] = m; Hl[8 * g + e] = m - ((v >> 13) & 0x00070007u);
+                                }
+                            }
                         } else {
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) { Mo[4 * g + e] = 0u; Hl[4 * g + e] = 0u; }
+                            for (int e = 0; e < 8; ++e) if (8 * g + e < NR) { Mo[8 * g + e] = 0u; Hl[8 * g + e] = 0u; }
                         }
                     }
                 }

@@ -193,11 +193,12 @@ cudaError_t pcf_launch_trace(const PcbLaunch &L, int cls, int grid_rounds, cudaS
 int pcf_occupancy_grid(int kind /* 0 scan, 1 pass 1, 2 rounds */, int cls);
 int pcf_trace_launches(void);       /* kernel launches of one pcf_launch_trace call */
 /* Trace of the fast classes over a batch of units (pcf_launch_trace): pass 1 (score only) leaves the DP column of every
- * task at every C-th column in scratch (per unit and checkpoint NR/4 warp-wide 1 KB lines: 4 rows x (M, H) per thread)
+ * task at every C-th column in scratch (per unit and checkpoint NR/8 warp-wide 1 KB lines: 8 rows per thread, 16 bits per
+ * cell and task = M in 13 bits, M - H clamped in 3)
  * and each task's end cell in `entries`; pass 2 recomputes, with trace flags, only the C-column blocks a path crosses:
  * the tracebacks are sorted by what their next block costs (columns x rows), 64 of a kind make a round. */
 #define PCF_NB 32                 /* sort buckets per major (first blocks: by width / rows; later blocks: by rows) */
-static inline uint64_t pcf_ck_words(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C + 1) * 2ull * NR; }
+static inline uint64_t pcf_ck_words(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C) * (uint64_t)((NR + 7) / 8) * 8ull; }
 /* words per unit: checkpoints, entries (4 per thread), sorted items and surviving items (8 words per task each) */
 static inline uint64_t pcf_unit_words_trace(int mmax, int cls)
 {
