@@ -47,6 +47,20 @@ class PcbResult(Structure):
                 ('aligned_len', c_int32), ('full_len', c_int32)]
 
 
+class PcbBest(Structure):
+    _fields_ = [('matches', c_int32), ('full_len', c_int32)]
+
+
+class PcbHitFilter(Structure):
+    _fields_ = [('threshold_e6', c_int64), ('at_end', c_int32), ('end_size', c_int32), ('min_trim_size', c_int32),
+                ('reserved', c_int32)]
+
+
+class PcbHit(Structure):
+    _fields_ = [('window', c_int32), ('id_pos', c_int32), ('read_start', c_int32), ('read_end', c_int32),
+                ('raw_score', c_int32), ('matches', c_int32), ('aligned_len', c_int32), ('full_len', c_int32)]
+
+
 class PcbCounters(Structure):
     _fields_ = [('kernel_launches', c_int64), ('dp_cells', c_int64), ('h2d_bytes', c_int64),
                 ('d2h_bytes', c_int64), ('dp_kernel_launches', c_int64), ('dp_kernel_ms', c_float)]
@@ -63,6 +77,9 @@ C_LIB.pcb_select_slot.argtypes = [_P, c_int]
 C_LIB.pcb_set_scoring.argtypes = [_P, c_int, c_int, c_int, c_int]
 C_LIB.pcb_set_adapters.argtypes = [_P, c_char_p, POINTER(c_int64), c_int32]
 C_LIB.pcb_align_windows.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, c_void_p]
+C_LIB.pcb_align_windows_best.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, c_void_p]
+C_LIB.pcb_align_windows_hits.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, POINTER(PcbHitFilter),
+                                         c_void_p, c_void_p, c_int64, POINTER(c_int64), c_void_p]
 C_LIB.pcb_align_tasks.argtypes = [_P, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
 C_LIB.pcb_upload_reads.argtypes = [_P, c_void_p, c_int64]
 C_LIB.pcb_set_deferred.argtypes = [_P, c_int]

@@ -82,6 +82,14 @@ struct pcb_context {
         int64_t n_windows = 0; int32_t stride = 0, n_ids = 0, win_mmax = 0;
         DevBuf<pcb_result> d_out;
         int64_t n_results = 0;
+        // reduced outputs (pcb_align_windows_best / _hits)
+        DevBuf<unsigned long long> d_keys;
+        DevBuf<pcb_best> d_best;
+        DevBuf<int32_t> d_cnt, d_identcol;
+        DevBuf<pcb_hit> d_hits;
+        DevBuf<uint16_t> d_ident;
+        DevBuf<long long> d_total;
+        std::vector<int32_t> h_identcol;
     };
     Slot slots[4];
     int cur = 0;
@@ -123,6 +131,10 @@ struct pcb_context {
     uint64_t scratch_budget = 6144ull << 18;   // words of checkpoint scratch a batch of the fast trace may use (PCB_SCRATCH_MB)
     pcb_counters cnt{};
     bool ktiming = false;
+    // deferred pcb_align_windows_hits calls: their hit lists are copied once the counts are known (pcb_wait)
+    struct PendingHits { const pcb_hit *d_hits; pcb_hit *hits; int64_t cap; int64_t *n_hits; int idx; };
+    std::vector<PendingHits> pending_hits;
+    long long *h_totals = nullptr;        // pinned, one per slot
 
     int fail(int code, const char *fmt, ...)
     {
@@ -189,7 +201,9 @@ extern "C" int pcb_create(int device, pcb_context **out)
         }
     }
     if (const char *mb = getenv("PCB_SCRATCH_MB")) c->scratch_budget = (uint64_t)std::max(1, atoi(mb)) << 18;   // tests: many batches from a small input
-    if (c->d_err.reserve(1) != cudaSuccess) { g_global_err = "cudaMalloc failed"; delete c; return PCB_ERR_NOMEM; }
+    if (c->d_err.reserve(1) != cudaSuccess || cudaHostAlloc((void **)&c->h_totals, sizeof(long long) * 4, cudaHostAllocDefault) != cudaSuccess) {
+        g_global_err = "cudaMalloc failed"; delete c; return PCB_ERR_NOMEM;
+    }
     *out = c;
     return PCB_OK;
 }
@@ -200,7 +214,12 @@ extern "C" void pcb_destroy(pcb_context *c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->cstream); cudaStreamSynchronize(c->ustream); cudaStreamSynchronize(c->pstream);
     c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_ascii_t.release(); c->d_arena_t.release();
-    for (auto &sl : c->slots) { sl.d_arena.release(); sl.d_ascii.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release(); if (sl.staged) cudaEventDestroy(sl.staged); }
+    for (auto &sl : c->slots) {
+        sl.d_arena.release(); sl.d_ascii.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release();
+        sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release();
+        if (sl.staged) cudaEventDestroy(sl.staged);
+    }
+    if (c->h_totals) cudaFreeHost(c->h_totals);
     for (auto &pl : c->plans) { pl.release(); if (pl.ready) cudaEventDestroy(pl.ready); }
     c->d_seg_off.release(); c->d_plan_i64.release(); c->d_seg_len.release(); c->d_seg_ad.release(); c->d_plan_i32.release(); c->d_adinfo.release();
     c->d_scratch.release(); c->d_meta.release(); c->d_err.release();
@@ -331,25 +350,29 @@ static int launch_dp(pcb_context *c, PcbLaunch &L, bool trace, int64_t cells, in
     if (c->ktiming) PCB_CUDA(c, cudaEventRecord(c->kev0, c->stream));
     int launches = 1;
     if (cls < PCF_NCLS && trace) {
-        // scratch of a batch of units: checkpoints | end cells (4 words per thread) | sorted items | surviving items
+        // scratch of a batch of units: checkpoints | end cells (4 words per thread) | sorted items | surviving items.
+        // (Measured and dropped: batches as a two-stream pipeline, pass 2 of batch i beside pass 1 of batch i + 1 with half
+        //  the CTA slots each: 18.5 ms instead of 15.7 ms for 131072 windows x 108 adapters.)
         const uint64_t per_unit = pcf_unit_words_trace(L.mmax, cls), ck_unit = per_unit - 128 - 1024;
+        const int W = PCB_BLOCK / 32;
         const int64_t per_batch = (int64_t)std::max<uint64_t>(1, std::min<uint64_t>({(uint64_t)n_units, c->scratch_budget / per_unit, 1ull << 24}));
         cudaError_t e = c->d_scratch.reserve((size_t)(per_unit * (uint64_t)per_batch));
         if (e != cudaSuccess) { cudaGetLastError(); return c->fail(PCB_ERR_NOMEM, "trace scratch of %.1f MB: %s", per_unit * per_batch * 4 / 1e6, cudaGetErrorString(e)); }
         L.n_major = L.src.units ? c->n_adapters : L.src.n_ids;
         PCB_CUDA(c, c->d_meta.reserve((size_t)pcf_meta_words(L.n_major)));
+        uint32_t *const sp = c->d_scratch.p;
         L.meta = c->d_meta.p;
-        L.scratch = c->d_scratch.p;
-        L.entries = reinterpret_cast<uint4 *>(c->d_scratch.p + ck_unit * (uint64_t)per_batch);
-        L.sorted = reinterpret_cast<PcfItem *>(c->d_scratch.p + (ck_unit + 128) * (uint64_t)per_batch);
-        L.surv = reinterpret_cast<PcfItem *>(c->d_scratch.p + (ck_unit + 128 + 512) * (uint64_t)per_batch);
-        const int W = PCB_BLOCK / 32;
+        L.scratch = sp;
+        L.entries = reinterpret_cast<uint4 *>(sp + ck_unit * (uint64_t)per_batch);
+        L.sorted = reinterpret_cast<PcfItem *>(sp + (ck_unit + 128) * (uint64_t)per_batch);
+        L.surv = reinterpret_cast<PcfItem *>(sp + (ck_unit + 128 + 512) * (uint64_t)per_batch);
         launches = 0;
         for (int64_t u0 = 0; u0 < n_units; u0 += per_batch) {
             L.unit0 = u0; L.unit1 = std::min(n_units, u0 + per_batch);
             const int64_t ctas = (L.unit1 - L.unit0 + W - 1) / W;
             L.grid = (int)std::min<int64_t>(c->grid_fp1[cls], ctas);
-            PCB_CUDA(c, pcf_launch_trace(L, cls, (int)std::min<int64_t>(c->grid_fp2[cls], ctas), c->stream));
+            PCB_CUDA(c, pcf_launch_pass1(L, cls, c->stream));
+            PCB_CUDA(c, pcf_launch_pass2(L, cls, (int)std::min<int64_t>(c->grid_fp2[cls], ctas), c->stream));
             launches += pcf_trace_launches();
         }
     } else {
@@ -534,6 +557,24 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
     return PCB_OK;
 }
 
+// Copies the hit lists of the queued pcb_align_windows_hits calls, now that their sizes are on the host.
+static int collect_hits(pcb_context *c)
+{
+    if (c->pending_hits.empty()) return PCB_OK;
+    PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
+    int rc = PCB_OK;
+    for (const auto &p : c->pending_hits) {
+        const int64_t total = (int64_t)c->h_totals[p.idx], n = std::min<int64_t>(total, p.cap);
+        *p.n_hits = total;
+        if (n > 0) PCB_CUDA(c, cudaMemcpyAsync(p.hits, p.d_hits, sizeof(pcb_hit) * (size_t)n, cudaMemcpyDeviceToHost, c->cstream));
+        c->cnt.d2h_bytes += (int64_t)sizeof(pcb_hit) * n;
+        if (total > p.cap) rc = c->fail(PCB_ERR_RANGE, "%lld hits, room for %lld", (long long)total, (long long)p.cap);
+    }
+    c->pending_hits.clear();
+    PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
+    return rc;
+}
+
 extern "C" int pcb_run_windows_resident(pcb_context *c)
 {
     if (!c) return PCB_ERR_ARG;
@@ -560,6 +601,68 @@ extern "C" int pcb_align_windows(pcb_context *c, const char *windows, int64_t n_
     if (n_windows * (int64_t)n_ids > 0 && !out) return PCB_ERR_ARG;
     if ((rc = run_windows(c, out))) return rc;
     return c->deferred ? PCB_OK : check_err_flag(c);        // deferred: pcb_wait reports
+}
+
+// ------------------------------------------------------------------------------------------------
+// the cross product, reduced on the device (pcb_reduce.cu)
+// ------------------------------------------------------------------------------------------------
+extern "C" int pcb_align_windows_best(pcb_context *c, const char *windows, int64_t n_windows, int32_t stride,
+                                      const int32_t *win_len, const int32_t *adapter_ids, int32_t n_ids, pcb_best *best)
+{
+    int rc;
+    if ((rc = pcb_stage_windows(c, windows, n_windows, stride, win_len))) return rc;
+    if ((rc = pcb_stage_ids(c, adapter_ids, n_ids))) return rc;
+    if (n_ids > 0 && !best) return PCB_ERR_ARG;
+    if ((rc = run_windows(c, nullptr))) return rc;
+    if (n_ids == 0) return PCB_OK;
+    pcb_context::Slot &S = c->S();
+    PCB_CUDA(c, S.d_keys.reserve((size_t)n_ids));
+    PCB_CUDA(c, S.d_best.reserve((size_t)n_ids));
+    PCB_CUDA(c, pcb_launch_best(S.d_out.p, n_windows, n_ids, S.d_keys.p, S.d_best.p, c->stream));
+    c->cnt.kernel_launches += 2;
+    PCB_CUDA(c, cudaMemcpyAsync(best, S.d_best.p, sizeof(pcb_best) * n_ids, cudaMemcpyDeviceToHost, c->stream));
+    c->cnt.d2h_bytes += (int64_t)sizeof(pcb_best) * n_ids;
+    return c->deferred ? PCB_OK : check_err_flag(c);
+}
+
+extern "C" int pcb_align_windows_hits(pcb_context *c, const char *windows, int64_t n_windows, int32_t stride,
+                                      const int32_t *win_len, const int32_t *adapter_ids, int32_t n_ids,
+                                      const pcb_hit_filter *filter, const uint8_t *want_ident,
+                                      pcb_hit *hits, int64_t hits_cap, int64_t *n_hits, uint16_t *ident)
+{
+    int rc;
+    if (!c || !filter || !n_hits || hits_cap < 0 || (hits_cap > 0 && !hits)) return PCB_ERR_ARG;
+    if ((rc = pcb_stage_windows(c, windows, n_windows, stride, win_len))) return rc;
+    if ((rc = pcb_stage_ids(c, adapter_ids, n_ids))) return rc;
+    if ((rc = run_windows(c, nullptr))) return rc;
+    pcb_context::Slot &S = c->S();
+    *n_hits = 0;
+    int32_t n_want = 0;
+    S.h_identcol.assign((size_t)std::max(1, n_ids), -1);
+    if (want_ident) for (int k = 0; k < n_ids; ++k) if (want_ident[k]) S.h_identcol[(size_t)k] = n_want++;
+    if (n_want > 0 && !ident) return PCB_ERR_ARG;
+    if (n_windows == 0 || n_ids == 0) return PCB_OK;
+    const int64_t nb = (n_windows + 1023) / 1024;
+    PCB_CUDA(c, S.d_cnt.reserve((size_t)(n_windows + nb + 2)));
+    PCB_CUDA(c, S.d_identcol.reserve((size_t)n_ids));
+    PCB_CUDA(c, S.d_hits.reserve((size_t)std::max<int64_t>(1, hits_cap)));
+    PCB_CUDA(c, S.d_ident.reserve((size_t)std::max<int64_t>(1, n_windows * n_want)));
+    PCB_CUDA(c, S.d_total.reserve(1));
+    PCB_CUDA(c, cudaMemcpyAsync(S.d_identcol.p, S.h_identcol.data(), sizeof(int32_t) * n_ids, cudaMemcpyHostToDevice, c->stream));
+    PCB_CUDA(c, pcb_launch_hits(S.d_out.p, n_windows, n_ids, *filter, S.d_cnt.p, S.d_cnt.p + n_windows + 1, S.d_total.p, S.d_hits.p, hits_cap,
+                                S.d_identcol.p, n_want, n_want ? S.d_ident.p : nullptr, c->d_err.p, c->stream));
+    c->cnt.kernel_launches += 5;
+    // results travel on the copy stream, beside the kernels of the next call
+    cudaEvent_t ev = c->pipe_ev[4 + c->cur];
+    PCB_CUDA(c, cudaEventRecord(ev, c->stream));
+    PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, ev, 0));
+    if (n_want) PCB_CUDA(c, cudaMemcpyAsync(ident, S.d_ident.p, sizeof(uint16_t) * (size_t)(n_windows * n_want), cudaMemcpyDeviceToHost, c->cstream));
+    PCB_CUDA(c, cudaMemcpyAsync(c->h_totals + c->cur, S.d_total.p, sizeof(long long), cudaMemcpyDeviceToHost, c->cstream));
+    c->cnt.d2h_bytes += (int64_t)sizeof(uint16_t) * n_windows * n_want + 8;
+    c->pending_hits.push_back({S.d_hits.p, hits, hits_cap, n_hits, c->cur});
+    if (c->deferred) return PCB_OK;
+    if ((rc = collect_hits(c))) return rc;
+    return check_err_flag(c);
 }
 
 extern "C" int pcb_timer_start(pcb_context *c) { if (!c) return PCB_ERR_ARG; cudaSetDevice(c->device); PCB_CUDA(c, cudaEventRecord(c->ev0, c->stream)); return PCB_OK; }
@@ -961,12 +1064,13 @@ extern "C" int pcb_wait(pcb_context *c)
     if (!c) return PCB_ERR_ARG;
     cudaSetDevice(c->device);
     for (cudaStream_t st : {c->pstream, c->ustream, c->stream, c->cstream}) PCB_CUDA(c, cudaStreamSynchronize(st));
+    const int rc_hits = collect_hits(c);
     int32_t f = 0;
     PCB_CUDA(c, cudaMemcpyAsync(&f, c->d_err.p, sizeof f, cudaMemcpyDeviceToHost, c->stream));
     PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
     PCB_CUDA(c, cudaStreamSynchronize(c->stream));
     if (f) return c->fail(PCB_ERR_RANGE, "device reported alignment-window violation (flag %d)", f);
-    return PCB_OK;
+    return rc_hits;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -48,10 +48,10 @@ namespace {
 #define PCF_MINB_SCAN 2
 #endif
 #ifndef PCF_MINB_P1
-#define PCF_MINB_P1(NR) ((NR) <= 32 ? 3 : 2)
+#define PCF_MINB_P1(NR) ((NR) <= 24 ? 4 : ((NR) <= 32 ? 3 : 2))
 #endif
 #ifndef PCF_MINB_P2
-#define PCF_MINB_P2(NR) ((NR) <= 24 ? 3 : 2)      /* shared memory (flags + queue) allows no more */
+#define PCF_MINB_P2(NR) ((NR) <= 24 ? 4 : 2)
 #endif
 #define PCF_MINB(MODE, NR) ((MODE) ? PCF_MINB_P1(NR) : PCF_MINB_SCAN)
 #ifndef PCF_UNROLL
@@ -983,9 +983,18 @@ cudaError_t pcf_launch_scan(const PcbLaunch &L, int cls, cudaStream_t st)
     return cudaSuccess;
 }
 
-// Trace of the units [L.unit0, L.unit1): pass 1, then per generation count / scan / scatter / rounds.  Everything on one
-// stream, nothing comes back to the host.
-cudaError_t pcf_launch_trace(const PcbLaunch &L0, int cls, int grid_rounds, cudaStream_t st)
+// Trace of the units [L.unit0, L.unit1), in two parts: pass 1 ...
+cudaError_t pcf_launch_pass1(const PcbLaunch &L, int cls, cudaStream_t st)
+{
+    if (L.unit1 <= L.unit0) return cudaSuccess;
+    if (cls < 0 || cls >= PCF_NCLS) return cudaErrorInvalidValue;
+    cudaError_t e = cudaSuccess;
+    PCF_BY_CLASS(e = launch_fast<1, NR, EX, C>(L, L.grid, st))
+    return e;
+}
+
+// pass 2: per generation count / scan / scatter / rounds.  Nothing comes back to the host.
+cudaError_t pcf_launch_pass2(const PcbLaunch &L0, int cls, int grid_rounds, cudaStream_t st)
 {
     if (L0.unit1 <= L0.unit0) return cudaSuccess;
     if (cls < 0 || cls >= PCF_NCLS) return cudaErrorInvalidValue;
@@ -993,8 +1002,6 @@ cudaError_t pcf_launch_trace(const PcbLaunch &L0, int cls, int grid_rounds, cuda
     const int C = pcf_class_c(cls);
     const int64_t nu = L.unit1 - L.unit0;
     cudaError_t e = cudaMemsetAsync(L.meta, 0, pcf_meta_words(L.n_major) * sizeof(int32_t), st);
-    if (e != cudaSuccess) return e;
-    PCF_BY_CLASS(e = launch_fast<1, NR, EX, C>(L, L.grid, st))
     if (e != cudaSuccess) return e;
     const unsigned g0 = (unsigned)((nu * 32 + 255) / 256);
     k_count0<<<g0, 256, 0, st>>>(L, C);

@@ -28,7 +28,7 @@
 #define PCF_MAX_TRACE_M   1000    /* widest segment of the two-pass trace kernel (no bias re-basing) */
 #define PCF_MAX_SCAN_M    12000   /* widest scan chunk (order key is 14 bit)                      */
 #ifndef PCF_C_SMALL
-#define PCF_C_SMALL       16      /* C for NR <= 32 */
+#define PCF_C_SMALL       8       /* C for NR <= 32 */
 #endif
 #ifndef PCF_C_LARGE
 #define PCF_C_LARGE       8       /* C for NR > 32  */
@@ -181,15 +181,22 @@ struct PcbPlanArgs {
 };
 cudaError_t pcb_launch_plan(const PcbPlanArgs &a, bool fill, cudaStream_t st);
 
+/* reductions of the cross-product records (pcb_reduce.cu) */
+cudaError_t pcb_launch_best(const pcb_result *rec, int64_t n_windows, int32_t n_ids, unsigned long long *keys, pcb_best *out, cudaStream_t st);
+cudaError_t pcb_launch_hits(const pcb_result *rec, int64_t n_windows, int32_t n_ids, const pcb_hit_filter &f, int32_t *cnt, int32_t *bsum,
+                            long long *total, pcb_hit *hits, int64_t cap, const int32_t *ident_col, int32_t n_want, uint16_t *ident,
+                            int32_t *err_flag, cudaStream_t st);
+
 cudaError_t pcb_launch_encode(const char *ascii, uint8_t *codes, uint64_t n, cudaStream_t st);
 cudaError_t pcb_launch_trace(const PcbLaunch &L, cudaStream_t st);
 cudaError_t pcb_launch_scan(const PcbLaunch &L, cudaStream_t st);
 int pcb_occupancy_grid(int which /*0 trace, 1 scan*/);
 
-/* fast kernels, by class (see above).  pcf_launch_scan: score-only keys.  pcf_launch_trace: pass 1 + rounds over the units
- * [L.unit0, L.unit1), whose checkpoints must fit L.scratch (pcf_unit_words_trace per unit) */
+/* fast kernels, by class (see above).  pcf_launch_scan: score-only keys.  pcf_launch_pass1 / pass2: the two parts of the
+ * trace of the units [L.unit0, L.unit1), whose checkpoints must fit L.scratch (pcf_unit_words_trace per unit) */
 cudaError_t pcf_launch_scan(const PcbLaunch &L, int cls, cudaStream_t st);
-cudaError_t pcf_launch_trace(const PcbLaunch &L, int cls, int grid_rounds, cudaStream_t st);
+cudaError_t pcf_launch_pass1(const PcbLaunch &L, int cls, cudaStream_t st);
+cudaError_t pcf_launch_pass2(const PcbLaunch &L, int cls, int grid_rounds, cudaStream_t st);
 int pcf_occupancy_grid(int kind /* 0 scan, 1 pass 1, 2 rounds */, int cls);
 int pcf_trace_launches(void);       /* kernel launches of one pcf_launch_trace call */
 /* Trace of the fast classes over a batch of units (pcf_launch_trace): pass 1 (score only) leaves the DP column of every

@@ -21,6 +21,40 @@ RESULT_DTYPE = np.dtype([('read_start', '<i4'), ('read_end', '<i4'), ('adapter_s
                          ('adapter_end', '<i4'), ('raw_score', '<i4'), ('matches', '<i4'),
                          ('aligned_len', '<i4'), ('full_len', '<i4')])
 assert RESULT_DTYPE.itemsize == ctypes.sizeof(w.PcbResult)
+BEST_DTYPE = np.dtype([('matches', '<i4'), ('full_len', '<i4')])
+HIT_DTYPE = np.dtype([('window', '<i4'), ('id_pos', '<i4'), ('read_start', '<i4'), ('read_end', '<i4'),
+                      ('raw_score', '<i4'), ('matches', '<i4'), ('aligned_len', '<i4'), ('full_len', '<i4')])
+assert BEST_DTYPE.itemsize == ctypes.sizeof(w.PcbBest) and HIT_DTYPE.itemsize == ctypes.sizeof(w.PcbHit)
+
+
+def threshold_e6(threshold):
+    """floor(threshold * 10^6), computed in decimal (75.3 * 1e6 is not an integer in binary floating point)."""
+    import decimal
+    return int((decimal.Decimal(repr(float(threshold))) * 1000000).to_integral_value(rounding=decimal.ROUND_FLOOR))
+
+
+class WindowHits(object):
+    """What pcb_align_windows_hits returns: `hits` (HIT_DTYPE, ordered by window, then by adapter position) and `ident`
+    ([n_windows, n_wanted] uint16 = matches << 9 | full_len, 0 = failed alignment).  Valid once the call is collected
+    (at once, or after AlignmentEngine.wait() in deferred mode)."""
+
+    def __init__(self, hits_buf, n_hits, ident):
+        self._buf, self._n, self.ident = hits_buf, n_hits, ident
+
+    @property
+    def n_hits(self):
+        return int(self._n.value)
+
+    @property
+    def hits(self):
+        return self._buf[:min(self.n_hits, len(self._buf))]
+
+    def identities(self):
+        """full-adapter percent identity of every (window, wanted adapter) pair as the reference parses it from "%f"."""
+        m = (self.ident >> 9).astype(np.int64)
+        length = (self.ident & 0x1FF).astype(np.int64)
+        return m, length
+
 
 
 def _ptr(a):
@@ -102,6 +136,51 @@ class AlignmentEngine(object):
         if getattr(self, '_deferred', False):
             self._held.append((win_buf, win_len, out))
         return out
+
+    def align_windows_best(self, win_buf, win_len, adapter_ids):
+        """Phase A in one call: per listed adapter the (matches, full_len) of its best full-adapter identity over all windows
+        (pcb_align_windows_best).  Returns a BEST_DTYPE array of len(adapter_ids)."""
+        win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)
+        win_len = np.ascontiguousarray(win_len, dtype=np.int32)
+        ids = np.ascontiguousarray(adapter_ids, dtype=np.int32)
+        n, stride = win_buf.shape
+        out = np.zeros(len(ids), dtype=BEST_DTYPE)
+        self._check(w.C_LIB.pcb_align_windows_best(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids),
+                                                   _ptr(out)), 'pcb_align_windows_best')
+        if getattr(self, '_deferred', False):
+            self._held.append((win_buf, win_len, ids, out))
+        return out
+
+    def align_windows_hits(self, win_buf, win_len, adapter_ids, end_threshold, at_end, end_size, min_trim_size,
+                           want_ident=None, hits_cap=None, hits_buf=None, ident_buf=None):
+        """Phase B in one call (pcb_align_windows_hits): only the pairs find_start_trim / find_end_trim would keep, plus the
+        full-adapter identity of every window for the adapters flagged in want_ident.  Returns a WindowHits."""
+        win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)
+        win_len = np.ascontiguousarray(win_len, dtype=np.int32)
+        ids = np.ascontiguousarray(adapter_ids, dtype=np.int32)
+        n, stride = win_buf.shape
+        flt = w.PcbHitFilter(threshold_e6(end_threshold), 1 if at_end else 0, int(end_size), int(min_trim_size), 0)
+        want = None if want_ident is None else np.ascontiguousarray(want_ident, dtype=np.uint8)
+        n_want = 0 if want is None else int(np.count_nonzero(want))
+        if hits_buf is None:
+            cap = int(hits_cap) if hits_cap is not None else int(min(n * len(ids), max(16 * n, 4096)))
+            hits_buf = np.empty(max(cap, 1), dtype=HIT_DTYPE)
+        ident = ident_buf if ident_buf is not None else np.zeros((n, n_want), dtype=np.uint16)
+        n_hits = ctypes.c_int64(0)
+        deferred = getattr(self, '_deferred', False)
+        rc = w.C_LIB.pcb_align_windows_hits(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids), byref(flt),
+                                            None if want is None else _ptr(want), _ptr(hits_buf), len(hits_buf), byref(n_hits),
+                                            _ptr(ident) if n_want else None)
+        if rc == 3 and not deferred and n_hits.value > len(hits_buf):      # more hits than room: once more with room for all
+            hits_buf = np.empty(int(n_hits.value), dtype=HIT_DTYPE)
+            rc = w.C_LIB.pcb_align_windows_hits(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids), byref(flt),
+                                                None if want is None else _ptr(want), _ptr(hits_buf), len(hits_buf), byref(n_hits),
+                                                _ptr(ident) if n_want else None)
+        self._check(rc, 'pcb_align_windows_hits')
+        res = WindowHits(hits_buf, n_hits, ident)
+        if deferred:
+            self._held.append((win_buf, win_len, ids, want, flt, res))
+        return res
 
     def stage_windows(self, win_buf, win_len, adapter_ids):
         win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)

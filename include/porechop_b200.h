@@ -82,6 +82,46 @@ int pcb_align_windows(pcb_context *ctx, const char *windows, int64_t n_windows, 
                       const int32_t *win_len, const int32_t *adapter_ids, int32_t n_ids,
                       pcb_result *out);
 
+/* ---- 2b. the cross product, reduced on the device to what the reference's callers consume ---------------------
+ * pcb_align_windows returns 32 bytes per (window, adapter) pair; the two calls below run the same kernels and hand back
+ * a few percent of that. */
+
+/* Phase A (porechop_abi.py:200-245): NanoporeRead.align_adapter_set keeps, per adapter sequence, the MAXIMUM
+ * fullAdapterPercentIdentity over all check reads (nanopore_read.py:158-173).  best[k] = (matches, full_len) of a pair
+ * with the largest 100 * matches / full_len for adapter_ids[k]; (0, 0) when no window aligned (identity 0.0).  Ratios
+ * are compared exactly (as integers); the printed "%f" of two different ratios of lengths < 4096 always differs. */
+typedef struct pcb_best { int32_t matches, full_len; } pcb_best;
+int pcb_align_windows_best(pcb_context *ctx, const char *windows, int64_t n_windows, int32_t stride,
+                           const int32_t *win_len, const int32_t *adapter_ids, int32_t n_ids, pcb_best *best);
+
+/* Phase B (porechop_abi.py:359-438): find_start_trim / find_end_trim keep a pair only if (nanopore_read.py:187-188,
+ * :209-210)  partial_score > end_threshold  and  read_end != end_size (start windows) / read_start != 0 (end windows)
+ * and  read_end - read_start >= min_trim_size,  where partial_score is the aligned-region identity as parsed from the
+ * printed "%f" and read_end is exclusive.  threshold_e6 = floor(end_threshold * 10^6): the printed identity exceeds the
+ * threshold exactly when 100 * matches / aligned_len >= (threshold_e6 + 1/2) * 10^-6. */
+typedef struct pcb_hit_filter {
+    int64_t threshold_e6;
+    int32_t at_end;          /* 0: start windows, 1: end windows */
+    int32_t end_size;
+    int32_t min_trim_size;
+    int32_t reserved;
+} pcb_hit_filter;
+/* A kept pair: window index, position of the adapter in adapter_ids, and the record's fields the callers read
+ * (read_end inclusive, as in pcb_result). */
+typedef struct pcb_hit {
+    int32_t window, id_pos, read_start, read_end, raw_score, matches, aligned_len, full_len;
+} pcb_hit;
+/* hits: the kept pairs, ordered by window and then by id_pos (the order in which the reference appends them to
+ * start_adapter_alignments / end_adapter_alignments); *n_hits = their number (more than hits_cap: the call fails with
+ * PCB_ERR_RANGE after filling hits_cap of them).  want_ident (may be NULL): per adapter of the list 1 = also return its
+ * full-adapter identity for EVERY window (barcode scores, nanopore_read.py:190-195, :212-217): ident[w * n_want + j]
+ * for the j-th wanted adapter = matches << 9 | full_len (0: the alignment failed, identity 0.0).  In deferred mode
+ * hits / *n_hits are valid after pcb_wait. */
+int pcb_align_windows_hits(pcb_context *ctx, const char *windows, int64_t n_windows, int32_t stride,
+                           const int32_t *win_len, const int32_t *adapter_ids, int32_t n_ids,
+                           const pcb_hit_filter *filter, const uint8_t *want_ident,
+                           pcb_hit *hits, int64_t hits_cap, int64_t *n_hits, uint16_t *ident);
+
 /* Explicit task list (phase C, porechop_abi.py:457-522, and anything irregular): task t aligns
  * seq_blob[seg_off[t] .. seg_off[t]+seg_len[t]) against adapter task_adapter[t].  Any length.
  * HOST buffers. */

@@ -346,3 +346,58 @@ def test_trace_queue_many_units_per_warp_and_long_paths():
             assert t.tobytes() == out[:512].reshape(-1).tobytes()
     finally:
         eng.close()
+
+
+def _ref_hits(rec, thr, at_end, end_size, min_trim):
+    """The pairs nanopore_read.find_start_trim / find_end_trim keep (nanopore_read.py:187-188, :209-210), from full records."""
+    from custom_porechop_abi_b200.porechop_batch import _parsed_identities, _read_ends
+    partial, _ = _parsed_identities(rec)
+    rs, re = rec['read_start'], _read_ends(rec)
+    with np.errstate(invalid='ignore'):
+        edge = (rs != 0) if at_end else (re != end_size)
+        hit = (partial > thr) & edge & (re - rs >= min_trim)
+    return hit
+
+
+@pytest.mark.parametrize('thr,at_end,min_trim', [(75.0, False, 4), (75.0, True, 4), (60.5, False, 1), (99.999999, True, 6), (-1.0, False, 0)])
+def test_reduced_outputs_match_full_records(engine, thr, at_end, min_trim):
+    """pcb_align_windows_best / pcb_align_windows_hits against the same reductions done on the host from the full records
+    (which the other tests check against the oracle)."""
+    from custom_porechop_abi_b200 import synthetic
+    from custom_porechop_abi_b200.porechop_batch import _percent_table
+    engine.set_scoring(DEFAULT)
+    adapters, s_ids, e_ids = synthetic.adapter_set()
+    blob, off = synthetic.make_reads(700, adapters, s_ids, e_ids, seed=11, lengths=np.r_[np.full(650, 900), np.arange(0, 50) * 7])
+    sbuf, ebuf, lens = synthetic.end_windows(blob, off, 150, 160)
+    buf = ebuf if at_end else sbuf
+    ids = np.array((e_ids if at_end else s_ids)[:57], dtype=np.int32)
+    engine.set_adapters(adapters)
+    rec = engine.align_windows(buf, lens, ids)
+    # phase A
+    best = engine.align_windows_best(buf, lens, ids)
+    full = _percent_table(rec['matches'], rec['full_len']); full[rec['read_start'] == -1] = 0.0
+    got = _percent_table(best['matches'], np.maximum(best['full_len'], 1)); got[best['full_len'] == 0] = 0.0
+    assert np.array_equal(got, full.max(axis=0))
+    # phase B
+    want = np.zeros(len(ids), dtype=np.uint8); want[::3] = 1
+    res = engine.align_windows_hits(buf, lens, ids, thr, at_end, 150, min_trim, want_ident=want)
+    hit = _ref_hits(rec, thr, at_end, 150, min_trim)
+    ii, kk = np.nonzero(hit)
+    h = res.hits
+    assert res.n_hits == len(ii)
+    assert np.array_equal(h['window'], ii) and np.array_equal(h['id_pos'], kk)
+    for f in ('read_start', 'read_end', 'raw_score', 'matches', 'aligned_len', 'full_len'):
+        assert np.array_equal(h[f], rec[f][ii, kk]), f
+    m, length = res.identities()
+    cols = np.nonzero(want)[0]
+    failed = rec['read_start'][:, cols] == -1
+    assert np.array_equal(m, np.where(failed, 0, rec['matches'][:, cols])) and np.array_equal(length, np.where(failed, 0, rec['full_len'][:, cols]))
+    # the same through submit / collect
+    with engine.deferred():                      # every queued call in its own slot
+        engine.select_slot(1)
+        res2 = engine.align_windows_hits(buf, lens, ids, thr, at_end, 150, min_trim, want_ident=want, hits_cap=rec.size)
+        engine.select_slot(2)
+        best2 = engine.align_windows_best(buf, lens, ids)
+    engine.select_slot(0)
+    assert res2.n_hits == res.n_hits and np.array_equal(res2.hits, res.hits) and np.array_equal(res2.ident, res.ident)
+    assert np.array_equal(best2, best)
