@@ -80,6 +80,7 @@ C_LIB.pcb_align_windows.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_
 C_LIB.pcb_align_windows_best.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, c_void_p]
 C_LIB.pcb_align_windows_hits.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, POINTER(PcbHitFilter),
                                          c_void_p, c_void_p, c_int64, POINTER(c_int64), c_void_p]
+C_LIB.pcb_fetch_top2.argtypes = [_P, c_void_p, c_int64]
 C_LIB.pcb_align_tasks.argtypes = [_P, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
 C_LIB.pcb_upload_reads.argtypes = [_P, c_void_p, c_int64]
 C_LIB.pcb_set_deferred.argtypes = [_P, c_int]

@@ -89,6 +89,8 @@ struct pcb_context {
         DevBuf<pcb_hit> d_hits;
         DevBuf<uint16_t> d_ident;
         DevBuf<long long> d_total;
+        DevBuf<pcb_top2> d_top2;
+        int32_t n_want = 0;
         std::vector<int32_t> h_identcol;
     };
     Slot slots[4];
@@ -216,7 +218,7 @@ extern "C" void pcb_destroy(pcb_context *c)
     c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_ascii_t.release(); c->d_arena_t.release();
     for (auto &sl : c->slots) {
         sl.d_arena.release(); sl.d_ascii.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release();
-        sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release();
+        sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release(); sl.d_top2.release();
         if (sl.staged) cudaEventDestroy(sl.staged);
     }
     if (c->h_totals) cudaFreeHost(c->h_totals);
@@ -640,7 +642,7 @@ extern "C" int pcb_align_windows_hits(pcb_context *c, const char *windows, int64
     int32_t n_want = 0;
     S.h_identcol.assign((size_t)std::max(1, n_ids), -1);
     if (want_ident) for (int k = 0; k < n_ids; ++k) if (want_ident[k]) S.h_identcol[(size_t)k] = n_want++;
-    if (n_want > 0 && !ident) return PCB_ERR_ARG;
+    S.n_want = n_want;                                      // ident == NULL: the identities stay on the device (pcb_fetch_top2)
     if (n_windows == 0 || n_ids == 0) return PCB_OK;
     const int64_t nb = (n_windows + 1023) / 1024;
     PCB_CUDA(c, S.d_cnt.reserve((size_t)(n_windows + nb + 2)));
@@ -656,13 +658,29 @@ extern "C" int pcb_align_windows_hits(pcb_context *c, const char *windows, int64
     cudaEvent_t ev = c->pipe_ev[4 + c->cur];
     PCB_CUDA(c, cudaEventRecord(ev, c->stream));
     PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, ev, 0));
-    if (n_want) PCB_CUDA(c, cudaMemcpyAsync(ident, S.d_ident.p, sizeof(uint16_t) * (size_t)(n_windows * n_want), cudaMemcpyDeviceToHost, c->cstream));
+    if (n_want && ident) PCB_CUDA(c, cudaMemcpyAsync(ident, S.d_ident.p, sizeof(uint16_t) * (size_t)(n_windows * n_want), cudaMemcpyDeviceToHost, c->cstream));
     PCB_CUDA(c, cudaMemcpyAsync(c->h_totals + c->cur, S.d_total.p, sizeof(long long), cudaMemcpyDeviceToHost, c->cstream));
-    c->cnt.d2h_bytes += (int64_t)sizeof(uint16_t) * n_windows * n_want + 8;
+    c->cnt.d2h_bytes += (ident ? (int64_t)sizeof(uint16_t) * n_windows * n_want : 0) + 8;
     c->pending_hits.push_back({S.d_hits.p, hits, hits_cap, n_hits, c->cur});
     if (c->deferred) return PCB_OK;
     if ((rc = collect_hits(c))) return rc;
     return check_err_flag(c);
+}
+
+extern "C" int pcb_fetch_top2(pcb_context *c, pcb_top2 *top2, int64_t n_windows)
+{
+    if (!c || n_windows < 0 || (n_windows > 0 && !top2)) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    pcb_context::Slot &S = c->S();
+    if (n_windows != S.n_windows) return c->fail(PCB_ERR_ARG, "asked for %lld windows, the slot's last call had %lld", (long long)n_windows, (long long)S.n_windows);
+    if (n_windows == 0) return PCB_OK;
+    PCB_CUDA(c, S.d_top2.reserve((size_t)n_windows));
+    PCB_CUDA(c, pcb_launch_top2(S.d_ident.p, n_windows, S.n_want, S.d_top2.p, c->stream));
+    c->cnt.kernel_launches++;
+    PCB_CUDA(c, cudaMemcpyAsync(top2, S.d_top2.p, sizeof(pcb_top2) * (size_t)n_windows, cudaMemcpyDeviceToHost, c->stream));
+    c->cnt.d2h_bytes += (int64_t)sizeof(pcb_top2) * n_windows;
+    if (!c->deferred) PCB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PCB_OK;
 }
 
 extern "C" int pcb_timer_start(pcb_context *c) { if (!c) return PCB_ERR_ARG; cudaSetDevice(c->device); PCB_CUDA(c, cudaEventRecord(c->ev0, c->stream)); return PCB_OK; }

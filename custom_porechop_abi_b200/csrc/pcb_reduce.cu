@@ -180,7 +180,36 @@ __global__ void k_hits_fill(const pcb_result *__restrict__ rec, int64_t n_window
     }
 }
 
+// ---- barcode binning: the two best barcode identities of every window ---------------------------------------------------
+// determine_barcode (nanopore_read.py:408-482) sorts a read's barcode scores in descending order (stable: the first in
+// adapter order among equals) and looks at the first two.  One thread per window over its identity words.
+__device__ __forceinline__ bool ident_gt(uint32_t a, uint32_t b)      // identity a > identity b, exactly (0 = failed = 0.0)
+{
+    const uint32_t ma = a >> 9, la = a & 0x1FFu, mb = b >> 9, lb = b & 0x1FFu;
+    return ma * (lb ? lb : 1u) * (la ? 1u : 0u) > mb * (la ? la : 1u) * (lb ? 1u : 0u);
+}
+__global__ void k_top2(const uint16_t *__restrict__ ident, int64_t n_windows, int32_t n_want, pcb_top2 *__restrict__ out)
+{
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= n_windows) return;
+    int b1 = -1, b2 = -1; uint32_t v1 = 0, v2 = 0;
+    for (int j = 0; j < n_want; ++j) {
+        const uint32_t v = ident[w * n_want + j];
+        if (b1 < 0 || ident_gt(v, v1)) { b2 = b1; v2 = v1; b1 = j; v1 = v; }
+        else if (b2 < 0 || ident_gt(v, v2)) { b2 = j; v2 = v; }
+    }
+    pcb_top2 t; t.best = (int16_t)b1; t.second = (int16_t)b2; t.best_ident = (uint16_t)v1; t.second_ident = (uint16_t)v2;
+    out[w] = t;
+}
+
 }  // namespace
+
+cudaError_t pcb_launch_top2(const uint16_t *ident, int64_t n_windows, int32_t n_want, pcb_top2 *out, cudaStream_t st)
+{
+    if (n_windows <= 0) return cudaSuccess;
+    k_top2<<<(unsigned)((n_windows + 127) / 128), 128, 0, st>>>(ident, n_windows, n_want, out);
+    return cudaGetLastError();
+}
 
 cudaError_t pcb_launch_best(const pcb_result *rec, int64_t n_windows, int32_t n_ids, unsigned long long *keys, pcb_best *out, cudaStream_t st)
 {

@@ -24,6 +24,7 @@ assert RESULT_DTYPE.itemsize == ctypes.sizeof(w.PcbResult)
 BEST_DTYPE = np.dtype([('matches', '<i4'), ('full_len', '<i4')])
 HIT_DTYPE = np.dtype([('window', '<i4'), ('id_pos', '<i4'), ('read_start', '<i4'), ('read_end', '<i4'),
                       ('raw_score', '<i4'), ('matches', '<i4'), ('aligned_len', '<i4'), ('full_len', '<i4')])
+TOP2_DTYPE = np.dtype([('best', '<i2'), ('second', '<i2'), ('best_ident', '<u2'), ('second_ident', '<u2')])
 assert BEST_DTYPE.itemsize == ctypes.sizeof(w.PcbBest) and HIT_DTYPE.itemsize == ctypes.sizeof(w.PcbHit)
 
 
@@ -165,22 +166,32 @@ class AlignmentEngine(object):
         if hits_buf is None:
             cap = int(hits_cap) if hits_cap is not None else int(min(n * len(ids), max(16 * n, 4096)))
             hits_buf = np.empty(max(cap, 1), dtype=HIT_DTYPE)
-        ident = ident_buf if ident_buf is not None else np.zeros((n, n_want), dtype=np.uint16)
+        keep_ident = ident_buf is not False                      # ident_buf=False: the identities stay on the device (fetch_top2)
+        ident = ident_buf if (ident_buf is not None and keep_ident) else np.zeros((n, n_want if keep_ident else 0), dtype=np.uint16)
         n_hits = ctypes.c_int64(0)
         deferred = getattr(self, '_deferred', False)
         rc = w.C_LIB.pcb_align_windows_hits(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids), byref(flt),
                                             None if want is None else _ptr(want), _ptr(hits_buf), len(hits_buf), byref(n_hits),
-                                            _ptr(ident) if n_want else None)
+                                            _ptr(ident) if (n_want and keep_ident) else None)
         if rc == 3 and not deferred and n_hits.value > len(hits_buf):      # more hits than room: once more with room for all
             hits_buf = np.empty(int(n_hits.value), dtype=HIT_DTYPE)
             rc = w.C_LIB.pcb_align_windows_hits(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids), byref(flt),
                                                 None if want is None else _ptr(want), _ptr(hits_buf), len(hits_buf), byref(n_hits),
-                                                _ptr(ident) if n_want else None)
+                                                _ptr(ident) if (n_want and keep_ident) else None)
         self._check(rc, 'pcb_align_windows_hits')
         res = WindowHits(hits_buf, n_hits, ident)
         if deferred:
             self._held.append((win_buf, win_len, ids, want, flt, res))
         return res
+
+    def fetch_top2(self, n_windows, out=None):
+        """The best and second-best barcode identity of every window of this slot's last align_windows_hits call
+        (pcb_fetch_top2): TOP2_DTYPE records, positions counted among the wanted adapters."""
+        out = np.empty(n_windows, dtype=TOP2_DTYPE) if out is None else out
+        self._check(w.C_LIB.pcb_fetch_top2(self._h, _ptr(out), n_windows), 'pcb_fetch_top2')
+        if getattr(self, '_deferred', False):
+            self._held.append((out,))
+        return out
 
     def stage_windows(self, win_buf, win_len, adapter_ids):
         win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)
@@ -209,32 +220,27 @@ class AlignmentEngine(object):
         self._check(w.C_LIB.pcb_upload_reads(self._h, _ptr(blob), blob.size), 'pcb_upload_reads')
         self._uploaded = blob
 
-    def align_tasks(self, blob, seg_off, seg_len, task_adapter):
+    def align_tasks(self, blob, seg_off, seg_len, task_adapter, out=None):
         """task t = blob[seg_off[t] : seg_off[t] + seg_len[t]] vs adapter task_adapter[t]; any length.
-        blob None: the blob announced with upload_reads."""
+        blob None: the blob announced with upload_reads.  out: result buffer to fill (e.g. pinned), else a new array."""
+        seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+        seg_len = np.ascontiguousarray(seg_len, dtype=np.int32)
+        ad = np.ascontiguousarray(task_adapter, dtype=np.int32)
+        if out is None:
+            out = np.empty(len(ad), dtype=RESULT_DTYPE)
         if blob is None:
             if getattr(self, '_uploaded', None) is None:
                 raise w.AlignmentError('align_tasks(None, ...) without upload_reads')
             held, self._uploaded = self._uploaded, None
-            seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
-            seg_len = np.ascontiguousarray(seg_len, dtype=np.int32)
-            ad = np.ascontiguousarray(task_adapter, dtype=np.int32)
-            out = np.empty(len(ad), dtype=RESULT_DTYPE)
-            self._check(w.C_LIB.pcb_align_tasks(self._h, None, held.size, _ptr(seg_off), _ptr(seg_len), _ptr(ad),
-                                                len(ad), _ptr(out)), 'pcb_align_tasks')
-            if getattr(self, '_deferred', False):
-                self._held.append((held, seg_off, seg_len, ad, out))
-            return out
-        self._uploaded = None
-        blob = np.frombuffer(blob, dtype=np.uint8) if isinstance(blob, (bytes, bytearray)) else np.ascontiguousarray(blob, dtype=np.uint8)
-        seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
-        seg_len = np.ascontiguousarray(seg_len, dtype=np.int32)
-        ad = np.ascontiguousarray(task_adapter, dtype=np.int32)
-        out = np.empty(len(ad), dtype=RESULT_DTYPE)
-        self._check(w.C_LIB.pcb_align_tasks(self._h, _ptr(blob), blob.size, _ptr(seg_off), _ptr(seg_len), _ptr(ad),
-                                            len(ad), _ptr(out)), 'pcb_align_tasks')
+            ptr, size = None, held.size
+        else:
+            self._uploaded = None
+            held = np.frombuffer(blob, dtype=np.uint8) if isinstance(blob, (bytes, bytearray)) else np.ascontiguousarray(blob, dtype=np.uint8)
+            ptr, size = _ptr(held), held.size
+        self._check(w.C_LIB.pcb_align_tasks(self._h, ptr, size, _ptr(seg_off), _ptr(seg_len), _ptr(ad), len(ad), _ptr(out)),
+                    'pcb_align_tasks')
         if getattr(self, '_deferred', False):
-            self._held.append((blob, seg_off, seg_len, ad, out))
+            self._held.append((held, seg_off, seg_len, ad, out))
         return out
 
     def stage_tasks(self, blob, seg_off, seg_len, task_adapter):

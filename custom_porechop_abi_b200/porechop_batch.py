@@ -108,12 +108,20 @@ def _engine(engine, scoring_scheme_vals):
     return eng
 
 
+def _ratio_percent(matches, length):
+    """float('%f' % (100.0 * m / l)) per element (see _percent_table); 0.0 where l == 0 (no alignment)."""
+    out = _percent_table(matches, np.maximum(length, 1))
+    out[np.asarray(length) == 0] = 0.0
+    return out
+
+
 def find_matching_adapter_sets(check_reads, verbosity, end_size, scoring_scheme_vals, print_dest, adapter_threshold,
-                               threads, search_adapters, engine=None):
+                               threads, search_adapters, engine=None, read_blob=None):
     """
     Phase A (porechop_abi.py:200-245): every check read's start / end window against every adapter set's start / end
     sequence; each set keeps the best full-adapter identity seen (nanopore_read.py:158-173).  Returns the sets whose
     best_start_or_end_score() reaches adapter_threshold, in search order, as the reference does.
+    The maximum is taken on the device (pcb_align_windows_best): 8 bytes per sequence come back, not 32 per pair.
     """
     eng = _engine(engine, scoring_scheme_vals)
     with_start = [a for a in search_adapters if a.start_sequence]
@@ -121,6 +129,7 @@ def find_matching_adapter_sets(check_reads, verbosity, end_size, scoring_scheme_
     seqs = [a.start_sequence[1] for a in with_start] + [a.end_sequence[1] for a in with_end]
     if check_reads and seqs:
         eng.set_adapters(seqs)
+        reduced = hasattr(eng, 'align_windows_best')
         submitted = {}
         with _collect_after(eng):                          # both submits queued, then collected together
             for slot, (at_end, sets, id0) in enumerate(((False, with_start, 0), (True, with_end, len(with_start)))):
@@ -128,16 +137,20 @@ def find_matching_adapter_sets(check_reads, verbosity, end_size, scoring_scheme_
                     continue
                 if hasattr(eng, 'select_slot'):
                     eng.select_slot(slot)
-                buf, lens = _windows(check_reads, end_size, at_end)
-                submitted[at_end] = eng.align_windows(buf, lens, np.arange(id0, id0 + len(sets), dtype=np.int32))
+                buf, lens = read_blob.windows(end_size, at_end) if read_blob is not None else _windows(check_reads, end_size, at_end)
+                ids = np.arange(id0, id0 + len(sets), dtype=np.int32)
+                submitted[at_end] = eng.align_windows_best(buf, lens, ids) if reduced else eng.align_windows(buf, lens, ids)
         if hasattr(eng, 'select_slot'):
             eng.select_slot(0)
         for at_end, sets in ((False, with_start), (True, with_end)):
             if at_end not in submitted:
                 continue
             rec = submitted[at_end]
-            _, full = _parsed_identities(rec, aligned=False)
-            best = full.max(axis=0)                       # no NaN here: full_len >= 1 whenever the alignment exists
+            if reduced:
+                best = _ratio_percent(rec['matches'], rec['full_len'])
+            else:
+                _, full = _parsed_identities(rec, aligned=False)
+                best = full.max(axis=0)                   # no NaN here: full_len >= 1 whenever the alignment exists
             for a, score in zip(sets, best):
                 if at_end:
                     a.best_end_score = max(a.best_end_score, float(score))
@@ -146,13 +159,44 @@ def find_matching_adapter_sets(check_reads, verbosity, end_size, scoring_scheme_
     return [x for x in search_adapters if x.best_start_or_end_score() >= adapter_threshold]
 
 
+def determine_barcode(read, barcode_threshold, barcode_diff, require_two_barcodes):
+    """NanoporeRead.determine_barcode (nanopore_read.py:408-482) for read classes that do not bring their own: best and
+    second-best barcode per end (Python's stable descending sort: the first in insertion order among equals), then the
+    reference's rules for --require_two_barcodes or for the combined list, then the agreement with Albacore's call."""
+    start = sorted(read.start_barcode_scores.items(), reverse=True, key=lambda x: x[1])
+    end = sorted(read.end_barcode_scores.items(), reverse=True, key=lambda x: x[1])
+    none = ('none', 0.0)
+    read.best_start_barcode = start[0] if len(start) >= 1 else getattr(read, 'best_start_barcode', none)
+    read.second_best_start_barcode = start[1] if len(start) >= 2 else getattr(read, 'second_best_start_barcode', none)
+    read.best_end_barcode = end[0] if len(end) >= 1 else getattr(read, 'best_end_barcode', none)
+    read.second_best_end_barcode = end[1] if len(end) >= 2 else getattr(read, 'second_best_end_barcode', none)
+    if require_two_barcodes:
+        ok = (read.best_start_barcode[1] >= barcode_threshold and read.best_end_barcode[1] >= barcode_threshold and
+              read.best_start_barcode[1] >= read.second_best_start_barcode[1] + barcode_diff and
+              read.best_end_barcode[1] >= read.second_best_end_barcode[1] + barcode_diff and
+              read.best_start_barcode[0] == read.best_end_barcode[0])
+        read.barcode_call = read.best_start_barcode[0] if ok else 'none'
+    else:
+        combined, seen = [], set()
+        for name, score in sorted(start + end, reverse=True, key=lambda x: x[1]):
+            if name not in seen:
+                combined.append((name, score)); seen.add(name)
+        best = combined[0] if len(combined) >= 1 else none
+        second = combined[1] if len(combined) >= 2 else none
+        read.barcode_call = best[0] if (best[1] >= barcode_threshold and best[1] >= second[1] + barcode_diff) else 'none'
+    if getattr(read, 'albacore_barcode_call', None) is not None and read.barcode_call != read.albacore_barcode_call:
+        read.barcode_call = 'none'
+
+
 def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_trim_size, end_threshold,
                                scoring_scheme_vals, print_dest, min_trim_size, threads, check_barcodes,
                                barcode_threshold, barcode_diff, require_two_barcodes, forward_or_reverse_barcodes,
                                engine=None, read_blob=None):
     """
     Phase B (porechop_abi.py:359-438): find_start_trim + find_end_trim (nanopore_read.py:175-217) for every read, then
-    determine_barcode.  Start windows x start sequences and end windows x end sequences are two GPU submits.
+    determine_barcode.  Start windows x start sequences and end windows x end sequences are two GPU submits; what comes
+    back is already reduced on the device (pcb_align_windows_hits): the pairs the two methods keep, in the reference's
+    order, and -- when barcodes are checked -- one 16-bit identity per (read, barcode sequence).
     read_blob: the same reads as a read_blob.ReadBlob (same order); the windows then come out of its buffer with one
     numpy gather instead of a Python slice per read.
     """
@@ -162,6 +206,11 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
     seqs = [a.start_sequence[1] for a in starts] + [a.end_sequence[1] for a in ends]
     if reads and seqs:
         eng.set_adapters(seqs)
+    reduced = hasattr(eng, 'align_windows_hits')
+
+    def wanted(sets):                                      # the sets whose full identity every read records (nanopore_read.py:190-195)
+        return np.array([1 if (check_barcodes and a.is_barcode() and a.barcode_direction() == forward_or_reverse_barcodes) else 0
+                         for a in sets], dtype=np.uint8)
     # both submits are queued before either is collected (submit / collect: the copies of the second run under the
     # kernels of the first), as the reference queues all reads on its pool before it collects (porechop_abi.py:395-407)
     submitted = {}
@@ -172,21 +221,46 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
             if hasattr(eng, 'select_slot'):
                 eng.select_slot(slot)
             buf, lens = read_blob.windows(end_size, at_end) if read_blob is not None else _windows(reads, end_size, at_end)
-            submitted[at_end] = eng.align_windows(buf, lens, np.arange(id0, id0 + len(sets), dtype=np.int32))
+            ids = np.arange(id0, id0 + len(sets), dtype=np.int32)
+            if reduced:                                    # room for every pair when the list is short, else 16 per read (and once more if not)
+                submitted[at_end] = eng.align_windows_hits(buf, lens, ids, end_threshold, at_end, end_size, min_trim_size,
+                                                           want_ident=wanted(sets), hits_cap=len(reads) * min(len(sets), 16))
+            else:
+                submitted[at_end] = eng.align_windows(buf, lens, ids)
     if hasattr(eng, 'select_slot'):
         eng.select_slot(0)
     for at_end, sets, id0 in ((False, starts, 0), (True, ends, len(starts))):
         if at_end not in submitted:
             continue
-        rec = submitted[at_end]
-        partial, full = _parsed_identities(rec)
-        r_start, r_end = rec['read_start'], _read_ends(rec)
-        with np.errstate(invalid='ignore'):
-            edge_ok = (r_start != 0) if at_end else (r_end != end_size)
-            hit = (partial > end_threshold) & edge_ok & (r_end - r_start >= min_trim_size)
-        ii, kk = np.nonzero(hit)                           # row-major: per read, in adapter order, as the reference appends
-        fulls, parts = full[ii, kk].tolist(), partial[ii, kk].tolist()
-        starts_, ends_ = r_start[ii, kk].tolist(), r_end[ii, kk].tolist()
+        want = wanted(sets)
+        if reduced:
+            res = submitted[at_end]
+            if res.n_hits > len(res.hits):                 # more hits than the deferred call had room for: once more, alone
+                buf, lens = read_blob.windows(end_size, at_end) if read_blob is not None else _windows(reads, end_size, at_end)
+                res = eng.align_windows_hits(buf, lens, np.arange(id0, id0 + len(sets), dtype=np.int32), end_threshold, at_end,
+                                             end_size, min_trim_size, want_ident=want, hits_cap=res.n_hits)
+            h = res.hits
+            partial = _ratio_percent(h['matches'], h['aligned_len'])
+            full = _ratio_percent(h['matches'], h['full_len'])
+            ok = partial > end_threshold                   # the device keeps a tie at six decimals; the parsed value decides
+            ii, kk = h['window'][ok], h['id_pos'][ok]
+            fulls, parts = full[ok].tolist(), partial[ok].tolist()
+            starts_, ends_ = h['read_start'][ok].tolist(), (h['read_end'][ok] + 1).tolist()
+            if check_barcodes and want.any():
+                m, length = res.identities()
+                scores = _ratio_percent(m, length)         # [reads, wanted sets]
+        else:
+            rec = submitted[at_end]
+            partial, full = _parsed_identities(rec)
+            r_start, r_end = rec['read_start'], _read_ends(rec)
+            with np.errstate(invalid='ignore'):
+                edge_ok = (r_start != 0) if at_end else (r_end != end_size)
+                hit = (partial > end_threshold) & edge_ok & (r_end - r_start >= min_trim_size)
+            ii, kk = np.nonzero(hit)                       # row-major: per read, in adapter order, as the reference appends
+            fulls, parts = full[ii, kk].tolist(), partial[ii, kk].tolist()
+            starts_, ends_ = r_start[ii, kk].tolist(), r_end[ii, kk].tolist()
+            if check_barcodes and want.any():
+                scores = full[:, np.flatnonzero(want)]
         for i, k, f, pa, rs_, re_ in zip(ii.tolist(), kk.tolist(), fulls, parts, starts_, ends_):
             read = reads[i]
             entry = (sets[k], f, pa, rs_, re_)
@@ -196,15 +270,20 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
             else:
                 read.start_trim_amount = max(read.start_trim_amount, re_ + extra_trim_size)
                 read.start_adapter_alignments.append(entry)
-        if check_barcodes:
-            for k, adapter in enumerate(sets):
-                if adapter.is_barcode() and adapter.barcode_direction() == forward_or_reverse_barcodes:
-                    name = adapter.get_barcode_name()
-                    for i, read in enumerate(reads):
-                        (read.end_barcode_scores if at_end else read.start_barcode_scores)[name] = float(full[i, k])
+        if check_barcodes and want.any():
+            # one dict per read, keys in adapter order (a later set with the same barcode name overwrites the value, not
+            # the position, as the reference's assignment does)
+            names = [a.get_barcode_name() for a, wt in zip(sets, want) if wt]
+            rows = scores.tolist()
+            attr = 'end_barcode_scores' if at_end else 'start_barcode_scores'
+            for read, row in zip(reads, rows):
+                getattr(read, attr).update(zip(names, row))
     if check_barcodes:
         for read in reads:
-            read.determine_barcode(barcode_threshold, barcode_diff, require_two_barcodes)
+            if hasattr(read, 'determine_barcode'):
+                read.determine_barcode(barcode_threshold, barcode_diff, require_two_barcodes)
+            else:
+                determine_barcode(read, barcode_threshold, barcode_diff, require_two_barcodes)
 
 
 def find_adapters_in_read_middles(reads, matching_sets, verbosity, middle_threshold, extra_trim_good_side,

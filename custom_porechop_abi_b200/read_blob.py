@@ -58,6 +58,23 @@ class ReadBlob(object):
     def __len__(self):
         return len(self.seq_off)
 
+    @classmethod
+    def from_buffer(cls, buf, offsets):
+        """Reads that already sit back to back in one buffer: read i = buf[offsets[i] : offsets[i + 1]]; names r0, r1, ..."""
+        offsets = np.asarray(offsets, dtype=np.int64)
+        n = len(offsets) - 1
+        z = np.zeros(n, dtype=np.int64)
+        return cls(np.asarray(buf, dtype=np.uint8), offsets[:-1], offsets[1:] - offsets[:-1], z, z, None, None, 'FASTA')
+
+    def head(self, k):
+        """The first k reads (views, nothing is copied)."""
+        q = (None, None) if self.qual_off is None else (self.qual_off[:k], self.qual_len[:k])
+        return ReadBlob(self.buf, self.seq_off[:k], self.seq_len[:k], self.name_off[:k], self.name_len[:k], q[0], q[1], self.file_type)
+
+    def make_reads(self):
+        """One BlobRead per record: what the phase functions need of the reference's NanoporeRead, the sequence on demand."""
+        return [BlobRead(self, i) for i in range(len(self))]
+
     def seq(self, i):
         """The sequence as NanoporeRead stores it (nanopore_read.py:36-39): upper case, U -> T when U outnumbers T."""
         s = self.buf[self.seq_off[i]:self.seq_off[i] + self.seq_len[i]].tobytes().decode().upper()
@@ -103,6 +120,52 @@ class ReadBlob(object):
         stop = np.where(stop < 0, np.maximum(stop + n, 0), np.minimum(stop, n))
         hi = np.maximum(lo, stop)
         return self.seq_off + lo, hi - lo
+
+
+class BlobRead(object):
+    """A read of a ReadBlob with the attributes of the reference's NanoporeRead that the three phases touch
+    (nanopore_read.py:32-75).  The sequence string is only built when someone asks for it (a read with a middle hit)."""
+    __slots__ = ('_blob', '_i', '_seq', 'start_trim_amount', 'end_trim_amount', 'start_adapter_alignments', 'end_adapter_alignments',
+                 'middle_adapter_positions', 'middle_trim_positions', 'middle_hit_str', 'start_barcode_scores', 'end_barcode_scores',
+                 'barcode_call', 'albacore_barcode_call', 'best_start_barcode', 'second_best_start_barcode', 'best_end_barcode',
+                 'second_best_end_barcode')
+
+    def __init__(self, blob, i):
+        self._blob, self._i, self._seq = blob, i, None
+        self.start_trim_amount = 0
+        self.end_trim_amount = 0
+        self.start_adapter_alignments = []
+        self.end_adapter_alignments = []
+        self.middle_adapter_positions = set()
+        self.middle_trim_positions = set()
+        self.middle_hit_str = ''
+        self.start_barcode_scores = {}
+        self.end_barcode_scores = {}
+        self.barcode_call = 'none'
+        self.albacore_barcode_call = None
+        self.best_start_barcode = ('none', 0.0)
+        self.second_best_start_barcode = ('none', 0.0)
+        self.best_end_barcode = ('none', 0.0)
+        self.second_best_end_barcode = ('none', 0.0)
+
+    @property
+    def name(self):
+        return self._blob.name(self._i) if self._blob.name_len[self._i] else 'r%d' % self._i
+
+    @property
+    def seq(self):
+        if self._seq is None:
+            self._seq = self._blob.seq(self._i)
+        return self._seq
+
+    def get_seq_with_start_end_adapters_trimmed(self):
+        if not self.start_trim_amount and not self.end_trim_amount:
+            return self.seq
+        return self.seq[self.start_trim_amount:len(self.seq) - self.end_trim_amount]
+
+    def adapters_found(self):
+        """The fork's filter (nanopore_read.py:23-30, porechop_abi.py:36-39): an adapter at BOTH ends."""
+        return bool(self.start_adapter_alignments) and bool(self.end_adapter_alignments)
 
 
 def load_read_blob(filename):

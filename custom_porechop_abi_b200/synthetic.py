@@ -89,3 +89,37 @@ def end_windows(blob, off, end_size=150, stride=160):
     start = np.where(valid, blob[s_idx], 0).astype(np.uint8)
     end = np.where(valid, blob[e_idx], 0).astype(np.uint8)
     return start, end, lens
+
+
+class AdapterSet(object):
+    """The attributes of the reference's Adapter (adapters.py:18-53) that the batched phases touch: a named set with an
+    optional start and end sequence, and the best scores phase A leaves on it."""
+
+    def __init__(self, name, start_sequence=None, end_sequence=None):
+        self.name = name
+        self.start_sequence = start_sequence        # (name, sequence) or None
+        self.end_sequence = end_sequence
+        self.best_start_score, self.best_end_score = 0.0, 0.0
+
+    def best_start_or_end_score(self):
+        return max(self.best_start_score, self.best_end_score)
+
+    def is_barcode(self):
+        return self.name.startswith('Barcode ')
+
+    def barcode_direction(self):
+        return 'reverse' if '_rev' in self.start_sequence[0] else 'forward'
+
+    def get_barcode_name(self):
+        names = [self.name] + ([self.start_sequence[0]] if self.start_sequence else []) + ([self.end_sequence[0]] if self.end_sequence else [])
+        return sorted(names, key=lambda x: len(x))[0].replace(' ', '_')
+
+
+def adapter_sets(adapters, start_ids, end_ids):
+    """The synthetic sequences as adapter sets (set k = k-th start + k-th end sequence), for the phase functions."""
+    sets = []
+    for k in range(max(len(start_ids), len(end_ids))):
+        s = ('set%d_start' % k, adapters[start_ids[k]].decode()) if k < len(start_ids) else None
+        e = ('set%d_end' % k, adapters[end_ids[k]].decode()) if k < len(end_ids) else None
+        sets.append(AdapterSet('set %d' % k, s, e))
+    return sets

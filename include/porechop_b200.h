@@ -115,12 +115,20 @@ typedef struct pcb_hit {
  * start_adapter_alignments / end_adapter_alignments); *n_hits = their number (more than hits_cap: the call fails with
  * PCB_ERR_RANGE after filling hits_cap of them).  want_ident (may be NULL): per adapter of the list 1 = also return its
  * full-adapter identity for EVERY window (barcode scores, nanopore_read.py:190-195, :212-217): ident[w * n_want + j]
- * for the j-th wanted adapter = matches << 9 | full_len (0: the alignment failed, identity 0.0).  In deferred mode
- * hits / *n_hits are valid after pcb_wait. */
+ * for the j-th wanted adapter = matches << 9 | full_len (0: the alignment failed, identity 0.0); ident == NULL keeps
+ * them on the device (for pcb_fetch_top2).  In deferred mode hits / *n_hits are valid after pcb_wait. */
 int pcb_align_windows_hits(pcb_context *ctx, const char *windows, int64_t n_windows, int32_t stride,
                            const int32_t *win_len, const int32_t *adapter_ids, int32_t n_ids,
                            const pcb_hit_filter *filter, const uint8_t *want_ident,
                            pcb_hit *hits, int64_t hits_cap, int64_t *n_hits, uint16_t *ident);
+
+/* Barcode binning (nanopore_read.py:408-482): determine_barcode sorts a read's barcode scores in descending order
+ * (stable: the first in adapter order among equals) and decides on the first two.  After a pcb_align_windows_hits call
+ * with want_ident, top2[w] = positions (among the wanted adapters) and identity words of the best and second-best
+ * barcode of window w (-1 / 0 when there are fewer); identities are compared exactly.  Same slot as the hits call;
+ * in deferred mode valid after pcb_wait. */
+typedef struct pcb_top2 { int16_t best, second; uint16_t best_ident, second_ident; } pcb_top2;
+int pcb_fetch_top2(pcb_context *ctx, pcb_top2 *top2, int64_t n_windows);
 
 /* Explicit task list (phase C, porechop_abi.py:457-522, and anything irregular): task t aligns
  * seq_blob[seg_off[t] .. seg_off[t]+seg_len[t]) against adapter task_adapter[t].  Any length.

@@ -24,12 +24,11 @@ DEFAULTS = dict(end_size=150, scoring=[3, -6, -5, -2], adapter_threshold=90.0, e
                 barcode_diff=5.0)
 
 
-def load_fastq(path):
-    out = []
-    lines = open(path).read().split('\n')
-    for i in range(0, len(lines) - 3, 4):
-        out.append((lines[i][1:], lines[i + 1].strip(), lines[i + 3].strip()))
-    return out
+def load_records(path, pc):
+    """(name, sequence, quals, albacore call) of every read of a file or Albacore directory, through the reference's own
+    loader (porechop_abi.py:133-187)."""
+    reads, _, _ = pc.load_reads(path, 0, open(os.devnull, 'w'), 10000)
+    return [(r.name, r.seq, r.quals, r.albacore_barcode_call) for r in reads]
 
 
 def adapter_dict(a):
@@ -55,12 +54,19 @@ def main():
     for fastq, check_barcodes, variants in (
             ('test_one_adapter_set.fastq', False, [dict(), dict(min_trim_size=7, end_size=100), dict(middle_threshold=80.0, extra_end_trim=0)]),
             ('test_two_adapter_sets.fastq', False, [dict()]),
-            ('test_barcodes.fastq', True, [dict(), dict(require_two=True)])):
+            ('test_barcodes.fastq', True, [dict(), dict(require_two=True)]),
+            ('test_choose_barcodes_1.fasta', True, [dict()]),
+            ('test_choose_barcodes_2.fasta', True, [dict(), dict(require_two=True, barcode_diff=1.0)]),
+            ('test_albacore_directory', True, [dict(), dict(barcode_threshold=60.0)]),
+            ('test_format.fastq', False, [dict()]),
+            ('test_format_barcodes.fasta', True, [dict(end_threshold=70.5)])):
         for var in variants:
             p = dict(P); p.update({k: v for k, v in var.items() if k != 'require_two'})
             require_two = var.get('require_two', False)
-            records = load_fastq(os.path.join(REF, 'test', fastq))
-            reads = [NanoporeRead(n, s, q) for n, s, q in records]
+            records = load_records(os.path.join(REF, 'test', fastq), pc)
+            reads = [NanoporeRead(n, s, q) for n, s, q, _ in records]
+            for r, rec in zip(reads, records):
+                r.albacore_barcode_call = rec[3]
             for a in ad.ADAPTERS:                          # the reference keeps scores on module-level objects
                 a.best_start_score, a.best_end_score = 0.0, 0.0
             search = [a for a in ad.ADAPTERS if '(full sequence)' not in a.name]
@@ -79,14 +85,15 @@ def main():
                         'end_alignments': [[a.name, f, pa, s, e] for a, f, pa, s, e in r.end_adapter_alignments],
                         'start_barcode_scores': r.start_barcode_scores, 'end_barcode_scores': r.end_barcode_scores,
                         'barcode_call': r.barcode_call} for r in reads]
+            # the fork's read filter (porechop_abi.py:36-39 -> nanopore_read.py:23-30) looks at the state phase B leaves
             pc.find_adapters_in_read_middles(reads, matching, 0, p['middle_threshold'], p['good_side'], p['bad_side'],
                                              p['scoring'], devnull, 1, False)
             phase_c = [{'middle_adapter_positions': sorted(r.middle_adapter_positions),
                         'middle_trim_positions': sorted(r.middle_trim_positions),
-                        'middle_hit_str': r.middle_hit_str} for r in reads]
+                        'middle_hit_str': r.middle_hit_str, 'adapters_found': bool(r.adapters_found())} for r in reads]
             cases.append({'fastq': fastq, 'params': p, 'check_barcodes': check_barcodes, 'require_two_barcodes': require_two,
                           'forward_or_reverse': forward_or_reverse,
-                          'reads': [[n, s] for n, s, _ in records],
+                          'reads': [[n, s] for n, s, _, _ in records], 'albacore': [a for _, _, _, a in records],
                           'search_adapters': [adapter_dict(a) for a in search],
                           'matching_used': [adapter_dict(a) for a in matching],
                           'phase_a': phase_a, 'phase_b': phase_b, 'phase_c': phase_c})

@@ -392,6 +392,13 @@ def test_reduced_outputs_match_full_records(engine, thr, at_end, min_trim):
     cols = np.nonzero(want)[0]
     failed = rec['read_start'][:, cols] == -1
     assert np.array_equal(m, np.where(failed, 0, rec['matches'][:, cols])) and np.array_equal(length, np.where(failed, 0, rec['full_len'][:, cols]))
+    # barcode binning input: the two best identities per window, descending, the first in adapter order among equals
+    top = engine.fetch_top2(len(lens))
+    sc = np.where(length > 0, m / np.maximum(length, 1), 0.0)              # exact enough to order ratios of lengths < 512
+    order = np.argsort(-sc, axis=1, kind='stable')
+    assert np.array_equal(top['best'], order[:, 0]) and np.array_equal(top['second'], order[:, 1])
+    rows = np.arange(len(lens))
+    assert np.array_equal(top['best_ident'], res.ident[rows, order[:, 0]]) and np.array_equal(top['second_ident'], res.ident[rows, order[:, 1]])
     # the same through submit / collect
     with engine.deferred():                      # every queued call in its own slot
         engine.select_slot(1)

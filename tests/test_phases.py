@@ -35,8 +35,12 @@ class Read(object):
             return self.seq
         return self.seq[self.start_trim_amount:len(self.seq) - self.end_trim_amount]
 
-    def determine_barcode(self, *args):
-        pass                                    # pure host logic of the reference, not on the alignment path
+    barcode_call = 'none'
+    albacore_barcode_call = None
+
+    def determine_barcode(self, barcode_threshold, barcode_diff, require_two_barcodes):
+        from custom_porechop_abi_b200.porechop_batch import determine_barcode
+        determine_barcode(self, barcode_threshold, barcode_diff, require_two_barcodes)
 
 
 class AdapterSet(object):
@@ -97,6 +101,49 @@ class OracleEngine(object):
         return out
 
 
+class ReducedOracleEngine(OracleEngine):
+    """The reduced-output calls (pcb_align_windows_best / _hits) answered from the oracle's full records: checks the host
+    logic of the phase functions on those outputs without a GPU."""
+
+    def align_windows_best(self, buf, lens, ids):
+        from custom_porechop_abi_b200.engine import BEST_DTYPE
+        rec = self.align_windows(buf, lens, ids)
+        out = np.zeros(len(ids), dtype=BEST_DTYPE)
+        for k in range(len(ids)):
+            best = None
+            for i in range(len(lens)):
+                r = rec[i, k]
+                if r['read_start'] != -1 and (best is None or int(r['matches']) * int(best['full_len']) > int(best['matches']) * int(r['full_len'])):
+                    best = r
+            if best is not None:
+                out[k] = (best['matches'], best['full_len'])
+        return out
+
+    def align_windows_hits(self, buf, lens, ids, end_threshold, at_end, end_size, min_trim_size, want_ident=None, hits_cap=None,
+                           hits_buf=None, ident_buf=None):
+        import ctypes
+        from custom_porechop_abi_b200.engine import HIT_DTYPE, WindowHits, threshold_e6
+        rec = self.align_windows(buf, lens, ids)
+        t6 = threshold_e6(end_threshold)
+        hits = []
+        for i in range(len(lens)):
+            for k in range(len(ids)):
+                r = rec[i, k]
+                failed = r['read_start'] == -1
+                if not failed and r['aligned_len'] <= 0:
+                    continue
+                num, den = (0, 1) if failed else (200000000 * int(r['matches']), int(r['aligned_len']))
+                rs, re = int(r['read_start']), (0 if failed else int(r['read_end']) + 1)
+                if num >= (2 * t6 + 1) * den and (rs != 0 if at_end else re != end_size) and re - rs >= min_trim_size:
+                    hits.append((i, k, r['read_start'], r['read_end'], r['raw_score'], r['matches'], r['aligned_len'], r['full_len']))
+        cols = np.flatnonzero(want_ident) if want_ident is not None else np.zeros(0, dtype=np.int64)
+        ident = np.zeros((len(lens), len(cols)), dtype=np.uint16)
+        for j, k in enumerate(cols):
+            ok = rec['read_start'][:, k] != -1
+            ident[:, j] = np.where(ok, (rec['matches'][:, k] << 9) | rec['full_len'][:, k], 0)
+        return WindowHits(np.array(hits, dtype=HIT_DTYPE), ctypes.c_int64(len(hits)), ident)
+
+
 def cases():
     with open(GOLDEN) as f:
         return json.load(f)['cases']
@@ -106,6 +153,8 @@ def run_case(c, eng, read_blob=None):
     from custom_porechop_abi_b200 import porechop_batch as pb
     p = c['params']
     reads = [Read(n, s) for n, s in c['reads']]
+    for r, alb in zip(reads, c.get('albacore', [None] * len(reads))):
+        r.albacore_barcode_call = alb                       # Albacore's bin, from the directory the read came from
     search = [AdapterSet(d) for d in c['search_adapters']]
     # phase A
     matching = pb.find_matching_adapter_sets(reads, 0, p['end_size'], p['scoring'], None, p['adapter_threshold'], 1, search, engine=eng)
@@ -121,25 +170,38 @@ def run_case(c, eng, read_blob=None):
         assert [[a.name, f, pa, s, e] for a, f, pa, s, e in r.start_adapter_alignments] == g['start_alignments'], r.name
         assert [[a.name, f, pa, s, e] for a, f, pa, s, e in r.end_adapter_alignments] == g['end_alignments'], r.name
         assert r.start_barcode_scores == g['start_barcode_scores'] and r.end_barcode_scores == g['end_barcode_scores'], r.name
+        assert list(r.start_barcode_scores) == list(g['start_barcode_scores']) and list(r.end_barcode_scores) == list(g['end_barcode_scores']), r.name
+        if c['check_barcodes']:
+            assert r.barcode_call == g['barcode_call'], (r.name, r.barcode_call, g['barcode_call'])
     pb.find_adapters_in_read_middles(reads, used, 0, p['middle_threshold'], p['good_side'], p['bad_side'], p['scoring'], None, 1,
                                      False, engine=eng, read_blob=read_blob)
     for r, g in zip(reads, c['phase_c']):
         assert sorted(r.middle_adapter_positions) == g['middle_adapter_positions'], r.name
         assert sorted(r.middle_trim_positions) == g['middle_trim_positions'], r.name
         assert r.middle_hit_str == g['middle_hit_str'], r.name
+        # the fork's read filter (porechop_abi.py:36-39, nanopore_read.py:23-30): an adapter alignment at both ends
+        assert (bool(r.start_adapter_alignments) and bool(r.end_adapter_alignments)) == g['adapters_found'], r.name
 
 
 def test_golden_has_hits():
     cs = cases()
-    assert len(cs) >= 6
+    assert len(cs) >= 13
+    assert sum(r['barcode_call'] != 'none' for c in cs if c['check_barcodes'] for r in c['phase_b']) >= 20
+    assert any(a for c in cs for a in c.get('albacore', []))
+    assert {True, False} <= {r['adapters_found'] for c in cs for r in c['phase_c']}
     assert sum(len(r['middle_adapter_positions']) > 0 for c in cs for r in c['phase_c']) >= 10
     assert sum(r['start_trim_amount'] > 0 for c in cs for r in c['phase_b']) >= 10
     assert any(r['start_barcode_scores'] for c in cs for r in c['phase_b'])
 
 
-@pytest.mark.parametrize('idx', [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize('idx', range(13))
 def test_phase_logic_with_oracle_engine(idx):
     run_case(cases()[idx], OracleEngine())
+
+
+@pytest.mark.parametrize('idx', range(13))
+def test_phase_logic_on_reduced_outputs(idx):
+    run_case(cases()[idx], ReducedOracleEngine())
 
 
 def test_trimmed_bounds_follow_python_slicing():
