@@ -66,15 +66,37 @@ def _dist():
 
 
 def merge_best_identities(best, device=None):
-    """all-reduce(MAX) of the per-(set, end) best full-adapter identities (NaN never wins, as Python's max)."""
+    """all-reduce(MAX) of the per-(set, end) best full-adapter identities.  A NaN never wins, as in the reference's
+    max(best, score) (nanopore_read.py:168,173), where best starts at 0.0."""
     import torch
     dist = _dist()
-    best = np.asarray(best, dtype=np.float64)
+    best = np.nan_to_num(np.asarray(best, dtype=np.float64), nan=0.0)
     if dist is None:
         return best
-    t = torch.from_numpy(np.nan_to_num(best, nan=-1.0)).to(device or 'cpu')
+    t = torch.from_numpy(best.copy()).to(device or 'cpu')
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return t.cpu().numpy()
+
+
+def merge_best(best, device=None):
+    """Phase A across ranks, exactly: `best` is what pcb_align_windows_best returns on this rank (matches, full_len per
+    adapter sequence; (0, 0) = nothing aligned).  Every rank gets, per sequence, the pair with the largest
+    matches / full_len over all ranks (compared by cross-multiplication, so no float is involved before the caller
+    prints it the way the reference's library does)."""
+    import torch
+    dist = _dist()
+    pairs = np.stack([np.asarray(best['matches'], dtype=np.int64), np.asarray(best['full_len'], dtype=np.int64)], axis=1)
+    if dist is None:
+        return pairs
+    t = torch.from_numpy(pairs.copy()).to(device or 'cpu')
+    parts = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(parts, t)
+    out = parts[0].cpu().numpy().copy()
+    for q in parts[1:]:
+        q = q.cpu().numpy()
+        better = q[:, 0] * np.maximum(out[:, 1], 1) * (q[:, 1] > 0) > out[:, 0] * np.maximum(q[:, 1], 1) * (out[:, 1] > 0)
+        out[better] = q[better]
+    return out
 
 
 def merge_counters(counts, device=None):
@@ -92,19 +114,40 @@ def merge_counters(counts, device=None):
 def gather_results(local_indices, local_records, n_total, device=None):
     """
     Rank 0 receives every rank's records in global read order (the only "collective" the data path has:
-    gathering per-read results).  local_records: numpy array whose first axis matches local_indices.
-    Returns the merged array on rank 0 and None elsewhere; identity without a process group.
+    gathering per-read results).  local_records: numpy array (structured dtypes welcome) whose first axis matches
+    local_indices.  Returns the merged array on rank 0 and None elsewhere; identity without a process group.
+    The records travel as raw bytes in tensors (a gather to rank 0, padded to the largest shard), not as pickles.
     """
+    import torch
     dist = _dist()
+    local_indices = np.asarray(local_indices, dtype=np.int64)
+    local_records = np.ascontiguousarray(local_records)
     if dist is None:
         out = np.empty((n_total,) + local_records.shape[1:], dtype=local_records.dtype)
         out[local_indices] = local_records
         return out
-    gathered = [None] * dist.get_world_size()
-    dist.all_gather_object(gathered, (np.asarray(local_indices), local_records))
-    if dist.get_rank() != 0:
+    world, rank = dist.get_world_size(), dist.get_rank()
+    dev = device or 'cpu'
+    row_bytes = local_records.dtype.itemsize * int(np.prod(local_records.shape[1:], dtype=np.int64))
+    counts = torch.zeros(world, dtype=torch.int64, device=dev)
+    counts[rank] = len(local_indices)
+    dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+    counts = counts.cpu().numpy()
+    cap = int(counts.max())
+    idx = torch.zeros(cap, dtype=torch.int64, device=dev)
+    idx[:len(local_indices)] = torch.from_numpy(local_indices).to(dev)
+    payload = torch.zeros(cap * row_bytes, dtype=torch.uint8, device=dev)
+    raw = np.frombuffer(local_records.tobytes(), dtype=np.uint8)
+    payload[:len(raw)] = torch.from_numpy(raw.copy()).to(dev)
+    idx_parts = [torch.empty_like(idx) for _ in range(world)] if rank == 0 else None
+    pay_parts = [torch.empty_like(payload) for _ in range(world)] if rank == 0 else None
+    dist.gather(idx, idx_parts, dst=0)
+    dist.gather(payload, pay_parts, dst=0)
+    if rank != 0:
         return None
     out = np.empty((n_total,) + local_records.shape[1:], dtype=local_records.dtype)
-    for idx, rec in gathered:
-        out[idx] = rec
+    for r in range(world):
+        k = int(counts[r])
+        rec = np.frombuffer(pay_parts[r][:k * row_bytes].cpu().numpy().tobytes(), dtype=local_records.dtype)
+        out[idx_parts[r][:k].cpu().numpy()] = rec.reshape((k,) + local_records.shape[1:])
     return out

@@ -22,6 +22,14 @@ WORKER = textwrap.dedent('''
     merged = sharding.gather_results(mine, rec, len(lengths))
     best_local = np.full(6, -1.0); best_local[rank::world] = 50.0 + rank
     best = sharding.merge_best_identities(best_local)
+    # structured records (the library's 32-byte results) through the tensor gather
+    srec = np.zeros(len(mine), dtype=[('a', '<i4'), ('b', '<i4')]); srec['a'] = mine; srec['b'] = lengths[mine] %% 1000
+    smerged = sharding.gather_results(mine, srec, len(lengths))
+    # phase A, exact: (matches, full_len) pairs, the larger ratio wins, (0, 0) never does
+    pairs = np.zeros(4, dtype=[('matches', '<i4'), ('full_len', '<i4')])
+    pairs['matches'] = [20, 0, 23, 11] if rank == 0 else [21, 5, 22, 0]
+    pairs['full_len'] = [24, 0, 24, 12] if rank == 0 else [25, 30, 24, 0]
+    mb = sharding.merge_best(pairs)
     counts = sharding.merge_counters([len(mine), int(lengths[mine].sum())])
     if rank == 0:
         assert merged is not None and np.array_equal(merged[:, 0], np.arange(len(lengths)) * 3 + 1)
@@ -31,6 +39,8 @@ WORKER = textwrap.dedent('''
         for r in range(world):
             expect[r::world] = 50.0 + r
         assert np.array_equal(best, expect), (best, expect)
+        assert np.array_equal(smerged['a'], np.arange(len(lengths))) and np.array_equal(smerged['b'], lengths %% 1000)
+        assert mb.tolist() == [[21, 25], [5, 30], [23, 24], [11, 12]], mb.tolist()
         print('GLOO_OK')
     else:
         assert merged is None
