@@ -419,36 +419,56 @@ def run_gpu_arm(args):
     state = {}
     binning = wl['kind'] == 'barcodes'
 
+    # the batch goes through in PARTS parts (the reference's pool works through the reads in order, too): phase C of a part
+    # is queued as soon as that part's phase B is on the host, beside phase B of the next part
+    PARTS = 2 if (has_windows and has_tasks) else 1
+    cut = [n * p // PARTS for p in range(PARTS + 1)]
+    A = N_MIDDLE_ADAPTERS
+
     def e2e_step():
         if has_tasks:
             # the reads are all in host memory before the first alignment (porechop_abi.py:61-71): announce the blob, so
             # that it crosses PCIe under the window kernels; every byte still travels inside the timed region, every step
             eng.upload_reads(blob)
+        res = []
         if has_windows:
-            eng.select_slot(0)
-            hs = eng.align_windows_hits(sbuf, wlen, wl['start_ids'], END_THRESHOLD, False, END_SIZE, MIN_TRIM_SIZE, want_ident=want_s,
-                                        hits_buf=hits_s, ident_buf=False if binning else ident_s)
-            if binning:
-                eng.fetch_top2(n, out=top_s)
-            eng.select_slot(1)
-            he = eng.align_windows_hits(ebuf, wlen, wl['end_ids'], END_THRESHOLD, True, END_SIZE, MIN_TRIM_SIZE, want_ident=want_e,
-                                        hits_buf=hits_e, ident_buf=False if binning else ident_e)
-            if binning:
-                eng.fetch_top2(n, out=top_e)
-            eng.wait()                   # phase B collected: hits and barcode identities are in the pinned buffers
-            state['hits'] = (hs.n_hits, he.n_hits)
-            if binning:
-                state['calls'] = two_barcode_calls(top_s, top_e)
-        if has_tasks:
-            if has_windows:              # the trimmed reads are what phase C aligns
-                st, et = trims_from_hits(n, hs, he)
-                lo = np.minimum(st, lens64)
-                hi = np.maximum(lens64 - et, lo)
-                seg_off[:] = np.repeat(off64 + lo, N_MIDDLE_ADAPTERS)
-                seg_len[:] = np.repeat(hi - lo, N_MIDDLE_ADAPTERS)
-            eng.select_slot(2)
-            eng.align_tasks(None, seg_off, seg_len, task_ad, out=out_m)
-            eng.wait()
+            for p in range(PARTS):
+                a, b = cut[p], cut[p + 1]
+                eng.select_slot(2 * p)
+                hs = eng.align_windows_hits(sbuf[a:b], wlen[a:b], wl['start_ids'], END_THRESHOLD, False, END_SIZE, MIN_TRIM_SIZE, want_ident=want_s,
+                                            hits_buf=hits_s[16 * a:16 * b], ident_buf=False if binning else ident_s[a:b])
+                if binning:
+                    eng.fetch_top2(b - a, out=top_s[a:b])
+                eng.select_slot(2 * p + 1)
+                he = eng.align_windows_hits(ebuf[a:b], wlen[a:b], wl['end_ids'], END_THRESHOLD, True, END_SIZE, MIN_TRIM_SIZE, want_ident=want_e,
+                                            hits_buf=hits_e[16 * a:16 * b], ident_buf=False if binning else ident_e[a:b])
+                if binning:
+                    eng.fetch_top2(b - a, out=top_e[a:b])
+                res.append((hs, he))
+        n_hits = [0, 0]
+        for p in range(PARTS):
+            a, b = cut[p], cut[p + 1]
+            if has_windows:
+                hs, he = res[p]
+                if PARTS > 1:
+                    eng.wait_slot(2 * p); eng.wait_slot(2 * p + 1)      # this part's phase B is on the host; the rest keeps running
+                else:
+                    eng.wait()
+                n_hits[0] += hs.n_hits; n_hits[1] += he.n_hits
+            if has_tasks:
+                if has_windows:          # the trimmed reads are what phase C aligns (nanopore_read.py:66-72, :225)
+                    st, et = trims_from_hits(b - a, hs, he)
+                    lo = np.minimum(st, lens64[a:b])
+                    hi = np.maximum(lens64[a:b] - et, lo)
+                    seg_off[A * a:A * b] = np.repeat(off64[a:b] + lo, A)
+                    seg_len[A * a:A * b] = np.repeat(hi - lo, A)
+                eng.select_slot(4 + p)
+                eng.align_tasks(None, seg_off[A * a:A * b], seg_len[A * a:A * b], task_ad[A * a:A * b], out=out_m[A * a:A * b])
+        eng.wait()
+        state['hits'] = tuple(n_hits)
+        state['parts'] = res
+        if binning:
+            state['calls'] = two_barcode_calls(top_s, top_e)
 
     eng.set_deferred(True)
     for _ in range(max(1, min(args.warmup, 2))):
@@ -470,7 +490,7 @@ def run_gpu_arm(args):
     if has_tasks:
         checksum += int(out_m['raw_score'].astype(np.int64).sum())
     if has_windows:
-        checksum += int(hits_s['raw_score'][:state['hits'][0]].astype(np.int64).sum() + hits_e['raw_score'][:state['hits'][1]].astype(np.int64).sum())
+        checksum += sum(int(h.hits['raw_score'].astype(np.int64).sum()) for pair in state['parts'] for h in pair)
         checksum += int(ident_s.astype(np.int64).sum() + ident_e.astype(np.int64).sum()) + int(top_s['best_ident'].astype(np.int64).sum())
     # the summary counters of the whole job, merged over NCCL as the reference sums them in-process (porechop_abi.py:441-454)
     local_counts = [n, state.get('hits', (0, 0))[0], state.get('hits', (0, 0))[1]]
@@ -542,7 +562,7 @@ def run_gpu_arm(args):
                     'h2d_bytes_per_step': int((c1['h2d_bytes'] - c0['h2d_bytes']) / args.steps),
                     'd2h_bytes_per_step': int((c1['d2h_bytes'] - c0['d2h_bytes']) / args.steps),
                     'gcups': cells_job * args.steps / e2e_s / 1e9, 'checksum': checksum,
-                    'phases': 'B (reduced: hits + 16-bit barcode identities) -> wait -> trims on the host -> C (32-byte records)'
+                    'phases': 'in %d parts: B (reduced: hits + 16-bit barcode identities) -> that part collected -> trims on the host -> C (32-byte records) beside the next part\'s B' % PARTS
                               if has_windows and has_tasks else ('B (reduced: hits + the two best barcode identities per read and end) -> wait -> binning decision on the host' if has_windows else 'C'),
                     'job_counters': {'reads': merged_counts[0], 'start_hits': merged_counts[1], 'end_hits': merged_counts[2],
                                      **({'reads_binned': merged_counts[3]} if len(merged_counts) > 3 else {})}},

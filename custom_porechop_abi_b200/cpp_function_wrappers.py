@@ -1,4 +1,9 @@
 """
+Derived from Porechop / Porechop_ABI's porechop_abi/cpp_function_wrappers.py (Copyright 2017 Ryan Wick; Porechop_ABI by
+Quentin Bonenfant et al.), which is distributed under the GNU General Public License v3 or later; the argtypes block of
+adapterAlignment and the two functions adapter_alignment / c_string_to_python_string below follow that file, because they
+ARE the drop-in boundary.  This file is distributed under the same terms.  See <http://www.gnu.org/licenses/>.
+
 ctypes binding of the B200 adapter-alignment library -- the drop-in for the reference's
 ``porechop_abi/cpp_function_wrappers.py`` (reference lines 21-63).
 
@@ -35,6 +40,8 @@ C_LIB.adapterAlignment.argtypes = [c_char_p,  # Read sequence
 C_LIB.adapterAlignment.restype = c_void_p     # String describing alignment
 C_LIB.freeCString.argtypes = [c_void_p]
 C_LIB.freeCString.restype = None
+C_LIB.pcb_set_dropin_fatal.argtypes = [c_int]
+C_LIB.pcb_set_dropin_fatal(0)                 # this wrapper checks pcb_last_error itself and raises (adapter_alignment below)
 
 
 class AlignmentError(RuntimeError):
@@ -85,6 +92,7 @@ C_LIB.pcb_align_tasks.argtypes = [_P, c_void_p, c_int64, c_void_p, c_void_p, c_v
 C_LIB.pcb_upload_reads.argtypes = [_P, c_void_p, c_int64]
 C_LIB.pcb_set_deferred.argtypes = [_P, c_int]
 C_LIB.pcb_wait.argtypes = [_P]
+C_LIB.pcb_wait_slot.argtypes = [_P, c_int]
 C_LIB.pcb_stage_windows.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p]
 C_LIB.pcb_stage_ids.argtypes = [_P, c_void_p, c_int32]
 C_LIB.pcb_run_windows_resident.argtypes = [_P]

@@ -47,6 +47,7 @@ struct pcb_context {
     cudaStream_t cstream = nullptr;       // result copies (D2H) that run beside the kernels of `stream`
     cudaStream_t ustream = nullptr;       // read-blob uploads (H2D + encode) that run beside them
     int64_t uploaded_len = -1;            // pcb_upload_reads announced a blob of this length
+    cudaStream_t hstream = nullptr;       // hit lists of single slots (pcb_wait_slot), beside everything else
     cudaStream_t pstream = nullptr;       // deferred mode: task staging + planning, beside the kernels of earlier calls
     cudaEvent_t tasks_done = nullptr;     // the task kernels of the last run no longer read the plan / segment arrays
     bool deferred = false;                // pcb_set_deferred: host-buffer calls only enqueue; pcb_wait collects
@@ -74,6 +75,7 @@ struct pcb_context {
         DevBuf<uint8_t> d_arena;          // window arena
         DevBuf<char> d_ascii;             // its ASCII staging (per slot: in deferred mode the next call's copy runs beside this one's kernels)
         cudaEvent_t staged = nullptr;     // deferred mode: the slot's staging copies have arrived
+        cudaEvent_t done = nullptr;       // deferred mode: the slot's last reduced call has delivered its fixed-size results (pcb_wait_slot)
         uint64_t arena_len = 0;
         int64_t sum_winlen = 0;
         DevBuf<int32_t> d_winlen, d_ids;      // d_ids: [fast ids | other ids | fast positions | other positions]
@@ -93,7 +95,8 @@ struct pcb_context {
         int32_t n_want = 0;
         std::vector<int32_t> h_identcol;
     };
-    Slot slots[4];
+    enum { N_SLOTS = 8 };
+    Slot slots[N_SLOTS];
     int cur = 0;
     Slot &S() { return slots[cur]; }
     // explicit tasks
@@ -154,7 +157,15 @@ struct pcb_context {
 #define PCB_CUDA(ctx, call)                                                                  \
     do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return (ctx)->cuda_fail(e__, #call); } while (0)
 
-static std::string g_global_err;
+// Error text of the process-wide entry points (pcb_create failures, adapterAlignment): one per thread, so that a pool of
+// threads calling adapterAlignment (the reference's ThreadPool, porechop_abi.py:25) cannot clear or tear each other's.
+static thread_local std::string g_global_err;
+// adapterAlignment has no error channel in the reference (its library cannot fail on non-empty input).  An unmodified
+// caller would read a failure record as "no adapter here" and write wrong output, so by default a library failure
+// inside the drop-in symbol ends the process with the reason on stderr, as the reference's wrapper does for a missing
+// library (cpp_function_wrappers.py:23-25).  A caller that checks pcb_last_error(NULL) itself switches that off.
+static bool g_dropin_fatal = true;
+extern "C" int pcb_set_dropin_fatal(int on) { g_dropin_fatal = on != 0; return PCB_OK; }
 
 extern "C" int pcb_device_count(void)
 {
@@ -181,6 +192,7 @@ extern "C" int pcb_create(int device, pcb_context **out)
         (e = cudaStreamCreateWithFlags(&c->cstream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&c->ustream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaStreamCreateWithPriority(&c->pstream, cudaStreamNonBlocking, -1)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&c->hstream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&c->tasks_done, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
         (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
@@ -189,7 +201,7 @@ extern "C" int pcb_create(int device, pcb_context **out)
         return PCB_ERR_CUDA;
     }
     for (auto &ev : c->pipe_ev) if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { g_global_err = "event creation failed"; delete c; return PCB_ERR_CUDA; }
-    for (auto &sl : c->slots) if (cudaEventCreateWithFlags(&sl.staged, cudaEventDisableTiming) != cudaSuccess) { g_global_err = "event creation failed"; delete c; return PCB_ERR_CUDA; }
+    for (auto &sl : c->slots) if (cudaEventCreateWithFlags(&sl.staged, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming) != cudaSuccess) { g_global_err = "event creation failed"; delete c; return PCB_ERR_CUDA; }
     c->grid_trace = pcb_occupancy_grid(0);
     c->grid_scan = pcb_occupancy_grid(1);
     for (int cls = 0; cls < PCF_NCLS; ++cls) {
@@ -203,7 +215,7 @@ extern "C" int pcb_create(int device, pcb_context **out)
         }
     }
     if (const char *mb = getenv("PCB_SCRATCH_MB")) c->scratch_budget = (uint64_t)std::max(1, atoi(mb)) << 18;   // tests: many batches from a small input
-    if (c->d_err.reserve(1) != cudaSuccess || cudaHostAlloc((void **)&c->h_totals, sizeof(long long) * 4, cudaHostAllocDefault) != cudaSuccess) {
+    if (c->d_err.reserve(1) != cudaSuccess || cudaHostAlloc((void **)&c->h_totals, sizeof(long long) * pcb_context::N_SLOTS, cudaHostAllocDefault) != cudaSuccess) {
         g_global_err = "cudaMalloc failed"; delete c; return PCB_ERR_NOMEM;
     }
     *out = c;
@@ -220,6 +232,7 @@ extern "C" void pcb_destroy(pcb_context *c)
         sl.d_arena.release(); sl.d_ascii.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release();
         sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release(); sl.d_top2.release();
         if (sl.staged) cudaEventDestroy(sl.staged);
+        if (sl.done) cudaEventDestroy(sl.done);
     }
     if (c->h_totals) cudaFreeHost(c->h_totals);
     for (auto &pl : c->plans) { pl.release(); if (pl.ready) cudaEventDestroy(pl.ready); }
@@ -230,6 +243,7 @@ extern "C" void pcb_destroy(pcb_context *c)
     cudaStreamDestroy(c->cstream);
     cudaStreamDestroy(c->ustream);
     cudaStreamDestroy(c->pstream);
+    if (c->hstream) cudaStreamDestroy(c->hstream);
     if (c->tasks_done) cudaEventDestroy(c->tasks_done);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -239,7 +253,7 @@ extern "C" const char *pcb_last_error(pcb_context *c) { return c ? c->err.c_str(
 
 extern "C" int pcb_select_slot(pcb_context *c, int slot)
 {
-    if (!c || slot < 0 || slot >= 4) return PCB_ERR_ARG;
+    if (!c || slot < 0 || slot >= pcb_context::N_SLOTS) return PCB_ERR_ARG;
     c->cur = slot;
     return PCB_OK;
 }
@@ -337,7 +351,7 @@ static void fill_launch_common(pcb_context *c, PcbLaunch &L, bool task_arena = f
     L.ad.codes = c->d_ad_codes.p; L.ad.off = c->d_ad_off.p; L.ad.n = c->n_adapters;
     L.sc = c->sc;
     L.arena = task_arena ? c->d_arena_t.p : c->S().d_arena.p; L.arena_len = task_arena ? c->arena_t_len : c->S().arena_len;
-    L.out = c->S().d_out.p; L.scan_out = nullptr;
+    L.out = c->S().d_out.p; L.scan_out = nullptr; L.n_out = c->S().n_results;
     L.scratch = c->d_scratch.p; L.err_flag = c->d_err.p;
 }
 
@@ -535,7 +549,7 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
             if (cls == PCF_NCLS && (rc = ensure_scratch(c, pcb_scratch_words_trace(mmax, smax), grid))) return rc;
             PcbLaunch L; fill_launch_common(c, L);
             L.arena = S.d_arena.p + (uint64_t)w0 * S.stride;
-            L.out = S.d_out.p + w0 * n;
+            L.out = S.d_out.p + w0 * n; L.n_out = S.n_results - w0 * n;
             L.src.units = nullptr; L.src.tasks = nullptr;
             L.src.n_windows = w1 - w0; L.src.stride = S.stride; L.src.win_len = S.d_winlen.p + w0;
             L.src.ids = S.d_ids.p + start; L.src.n_ids = cnt;
@@ -559,22 +573,37 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
     return PCB_OK;
 }
 
-// Copies the hit lists of the queued pcb_align_windows_hits calls, now that their sizes are on the host.
-static int collect_hits(pcb_context *c)
+// Copies the hit lists of the queued pcb_align_windows_hits calls (all of them, or one slot's), now that their sizes are on
+// the host.
+static int collect_hits(pcb_context *c, int only_slot = -1)
 {
     if (c->pending_hits.empty()) return PCB_OK;
-    PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
+    cudaStream_t st = only_slot < 0 ? c->cstream : c->hstream;
+    if (only_slot < 0) PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
     int rc = PCB_OK;
+    std::vector<pcb_context::PendingHits> rest;
     for (const auto &p : c->pending_hits) {
+        if (only_slot >= 0 && p.idx != only_slot) { rest.push_back(p); continue; }
         const int64_t total = (int64_t)c->h_totals[p.idx], n = std::min<int64_t>(total, p.cap);
         *p.n_hits = total;
-        if (n > 0) PCB_CUDA(c, cudaMemcpyAsync(p.hits, p.d_hits, sizeof(pcb_hit) * (size_t)n, cudaMemcpyDeviceToHost, c->cstream));
+        if (n > 0) PCB_CUDA(c, cudaMemcpyAsync(p.hits, p.d_hits, sizeof(pcb_hit) * (size_t)n, cudaMemcpyDeviceToHost, st));
         c->cnt.d2h_bytes += (int64_t)sizeof(pcb_hit) * n;
         if (total > p.cap) rc = c->fail(PCB_ERR_RANGE, "%lld hits, room for %lld", (long long)total, (long long)p.cap);
     }
-    c->pending_hits.clear();
-    PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
+    c->pending_hits.swap(rest);
+    PCB_CUDA(c, cudaStreamSynchronize(st));
     return rc;
+}
+
+// Deferred mode: waits for ONE slot's queued pcb_align_windows_hits call and delivers its results, while the calls of the
+// other slots keep running (the caller can derive that slot's trims and queue its phase C beside them).  Device-side
+// errors are still reported by pcb_wait.
+extern "C" int pcb_wait_slot(pcb_context *c, int slot)
+{
+    if (!c || slot < 0 || slot >= pcb_context::N_SLOTS) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    PCB_CUDA(c, cudaEventSynchronize(c->slots[slot].done));
+    return collect_hits(c, slot);
 }
 
 extern "C" int pcb_run_windows_resident(pcb_context *c)
@@ -655,13 +684,13 @@ extern "C" int pcb_align_windows_hits(pcb_context *c, const char *windows, int64
                                 S.d_identcol.p, n_want, n_want ? S.d_ident.p : nullptr, c->d_err.p, c->stream));
     c->cnt.kernel_launches += 5;
     // results travel on the copy stream, beside the kernels of the next call
-    cudaEvent_t ev = c->pipe_ev[4 + c->cur];
-    PCB_CUDA(c, cudaEventRecord(ev, c->stream));
-    PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, ev, 0));
+    PCB_CUDA(c, cudaEventRecord(S.done, c->stream));
+    PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, S.done, 0));
     if (n_want && ident) PCB_CUDA(c, cudaMemcpyAsync(ident, S.d_ident.p, sizeof(uint16_t) * (size_t)(n_windows * n_want), cudaMemcpyDeviceToHost, c->cstream));
     PCB_CUDA(c, cudaMemcpyAsync(c->h_totals + c->cur, S.d_total.p, sizeof(long long), cudaMemcpyDeviceToHost, c->cstream));
     c->cnt.d2h_bytes += (ident ? (int64_t)sizeof(uint16_t) * n_windows * n_want : 0) + 8;
     c->pending_hits.push_back({S.d_hits.p, hits, hits_cap, n_hits, c->cur});
+    PCB_CUDA(c, cudaEventRecord(S.done, c->cstream));
     if (c->deferred) return PCB_OK;
     if ((rc = collect_hits(c))) return rc;
     return check_err_flag(c);
@@ -1159,6 +1188,7 @@ extern "C" char *adapterAlignment(char *readSeq, char *adapterSeq, int matchScor
         if (const char *e = getenv("PCB_DEVICE")) dev = atoi(e);
         if (pcb_create(dev, &g_ctx) != PCB_OK) {
             fprintf(stderr, "cpp_functions.so (B200): %s\n", g_global_err.c_str());
+            if (g_dropin_fatal) exit(1);
             return dup_cstring(kFailed);
         }
     }
@@ -1173,6 +1203,7 @@ extern "C" char *adapterAlignment(char *readSeq, char *adapterSeq, int matchScor
     if (rc) {
         g_global_err = c->err;
         fprintf(stderr, "cpp_functions.so (B200): adapterAlignment failed: %s\n", c->err.c_str());
+        if (g_dropin_fatal) exit(1);
         return dup_cstring(kFailed);
     }
     char buf[192];

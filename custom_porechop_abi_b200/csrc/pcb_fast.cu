@@ -57,6 +57,13 @@ namespace {
 #ifndef PCF_UNROLL
 #define PCF_UNROLL 2
 #endif
+// -DPCF_CHECKED: every index the trace kernels compute into scratch, shared memory and the result array is range-checked
+// (device error flag bit 6); the GPU tests are run once against such a build (scripts/gpu_checked.sh -> profiles/)
+#ifdef PCF_CHECKED
+#define PCF_CHECK(L, cond) do { if (!(cond)) atomicOr((L).err_flag, 64); } while (0)
+#else
+#define PCF_CHECK(L, cond) do { } while (0)
+#endif
 constexpr int UNR = PCF_UNROLL;
 #ifndef PCF_UNROLL2
 #define PCF_UNROLL2 1
@@ -424,6 +431,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(MODE, NR)) k_fast(const Pc
                 //  is one contiguous KB: records kept per thread -- 32 scattered 16-byte pieces per instruction -- held the
                 //  shared-memory loads of the column loop up behind them in the memory pipe)
                 uint32_t *const cq = ckp + ckoff;
+                PCF_CHECK(L, (uint64_t)ckoff + ((NR + 7) / 8) * 256u <= 32u * ckw && unit - L.unit0 < L.unit1 - L.unit0);
                 const uint32_t T1 = GEB + 0x00010001u;
 #pragma unroll
                 for (int g = 0; g < (NR + 7) / 8; ++g) {
@@ -612,6 +620,7 @@ __global__ void k_scatter0(const PcbLaunch L, int C)
         const uint32_t x = h ? e.z : e.x, y = h ? e.w : e.y;
         const int key = (x >> 31) ? a * NB + bucket0(x, C) : -1;
         const int64_t slot = sorted_slot(M, key, lane);
+        PCF_CHECK(L, slot < 64 * nu);
         if (slot >= 0) {
             // where the task's bases are: pass 2 then starts from the item alone
             const int64_t unit = L.unit0 + (idx >> 5);
@@ -636,6 +645,7 @@ __global__ void k_scatter1(const PcbLaunch L)
         key = major_of(L, v[0] >> 6, groups) * NB + bucket1(v[1]);
     }
     const int64_t slot = sorted_slot(M, key, lane);
+    PCF_CHECK(L, slot < 64 * (L.unit1 - L.unit0) && n <= 64 * (L.unit1 - L.unit0));
     if (slot >= 0) put_item(L.sorted + slot, v[0], v[1], v[2], v[3], v[4], v[5], (uint64_t)v[6] | ((uint64_t)v[7] << 32));
 }
 
@@ -668,6 +678,9 @@ template <int FW>
 __device__ __forceinline__ void walk_step(const uint32_t *s_fl, const int h, int &ar, int &jc, uint32_t &pos2, Walk &w)
 {
     const uint32_t f = walk_flags<FW>(s_fl, h, ar, jc);
+#ifdef PCF_CHECKED
+    if (ar < 0 || (ar >> 2) >= FW || jc < 0 || jc >= 16) asm volatile("trap;");
+#endif
     const uint32_t fh = f & 1u, fg = (f >> 1) & 1u, fv = (f >> 16) & 1u, fd = (f >> 17) & 1u;
     const uint32_t sM = w.s == 0 ? 1u : 0u, sV = w.s == 1 ? 1u : 0u;
     const uint32_t isD = sM & fd, isV = sV | (sM & (fd ^ 1u) & fg), isH = (isD | isV) ^ 1u;
@@ -741,6 +754,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             valid[h] = i0 + h < a_item1;
+            PCF_CHECK(L, a_item1 <= 64 * (L.unit1 - L.unit0) && a_item0 <= a_item1);
             uint32_t v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
             if (valid[h]) ld256(reinterpret_cast<const uint32_t *>(L.sorted + i0 + h), v);
             ref[h] = v[0]; endc[h] = v[2];
@@ -773,6 +787,9 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
                     const uint32_t sel = ((ref[0] & 1u) ? 0x0032u : 0x0010u) | ((ref[1] & 1u) ? 0x7600u : 0x5400u);
                     const uint32_t T1s = (GEB + 0x00010001u) * 8192u;
                     const bool ld0 = go0 && k0 > 0, ld1 = go1 && k1 > 0;
+                    PCF_CHECK(L, !ld0 || ((int64_t)(ref[0] >> 6) < L.unit1 - L.unit0 && (uint64_t)k0 * G8 * 8u <= ckw));
+                    PCF_CHECK(L, !ld1 || ((int64_t)(ref[1] >> 6) < L.unit1 - L.unit0 && (uint64_t)k1 * G8 * 8u <= ckw));
+                    PCF_CHECK(L, tmax <= C && rlim <= NR);
 #pragma unroll
                     for (int g = 0; g < G8; ++g) {
                         if (8 * g < rlim) {
@@ -877,6 +894,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
                 res.adapter_start = ps.adapter_start; res.adapter_end = ps.adapter_end;
                 res.raw_score = score; res.matches = ps.matches;
                 res.aligned_len = ps.aligned_len; res.full_len = ps.full_len;
+                PCF_CHECK(L, oidx >= 0 && (L.n_out <= 0 || oidx < L.n_out));
                 L.out[oidx] = res;
             }
             if (!gen0) {
@@ -891,6 +909,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
                 if (lane == 0) first = atomicAdd(M.counters, nk);
                 first = __shfl_sync(0xffffffffu, first, 0);
                 const uint32_t lt = (1u << lane) - 1u;
+                PCF_CHECK(L, first + nk <= 64 * (L.unit1 - L.unit0));
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const Walk &w = wk[h];

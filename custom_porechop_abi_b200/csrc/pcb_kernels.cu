@@ -32,7 +32,7 @@
 namespace {
 
 // ------------------------------------------------------------------------------------------------
-// packed signed 16x2 helpers (all single native instructions on sm_100a, see profiles/sass_notes.md)
+// packed signed 16x2 helpers (all single native instructions on sm_100a, see profiles/sass_k_fast_r2.md)
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t vadd(uint32_t a, uint32_t b) { return __vadd2(a, b); }          // VIADD.16x2
 __device__ __forceinline__ uint32_t vmax(uint32_t a, uint32_t b) { return __vmaxs2(a, b); }         // VIMNMX.S16x2

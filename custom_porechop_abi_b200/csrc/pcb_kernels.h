@@ -123,6 +123,7 @@ struct PcbLaunch {
     int32_t    *meta;            /* pass 2: bucket counts, bases, chunk table (pcf_meta_words)      */
     int32_t     n_major;         /* pass 2: majors = adapters of the launch (cross product: its id list; task lists: the adapter set) */
     int32_t     gen;             /* pass 2: 0 = first block of every traceback, 1 = all later blocks */
+    int64_t     n_out;           /* records in `out` (index checks of the -DPCF_CHECKED build)       */
 };
 
 /* words of scratch per thread slot */

@@ -97,7 +97,7 @@ class AlignmentEngine(object):
         self._check(w.C_LIB.pcb_set_scoring(self._h, *self.scoring), 'pcb_set_scoring')
 
     def select_slot(self, slot):
-        """Pick one of the 4 staging slots (inputs + results) the following stage/run/fetch calls act on."""
+        """Pick one of the 8 staging slots (inputs + results) the following stage/run/fetch calls act on."""
         self._check(w.C_LIB.pcb_select_slot(self._h, int(slot)), 'pcb_select_slot')
         self._slot = int(slot)
 
@@ -231,7 +231,7 @@ class AlignmentEngine(object):
         if blob is None:
             if getattr(self, '_uploaded', None) is None:
                 raise w.AlignmentError('align_tasks(None, ...) without upload_reads')
-            held, self._uploaded = self._uploaded, None
+            held = self._uploaded                     # stays announced until the batch is collected: several task calls may use it
             ptr, size = None, held.size
         else:
             self._uploaded = None
@@ -286,6 +286,11 @@ class AlignmentEngine(object):
             self._check(w.C_LIB.pcb_wait(self._h), 'pcb_wait')
         finally:
             self._held = []
+            self._uploaded = None
+
+    def wait_slot(self, slot):
+        """Collects one slot's queued align_windows_hits call; everything queued in other slots keeps running."""
+        self._check(w.C_LIB.pcb_wait_slot(self._h, int(slot)), 'pcb_wait_slot')
 
     @contextlib.contextmanager
     def deferred(self):

@@ -27,12 +27,16 @@ extern "C" {
 /* ---- 1. the reference's own two symbols (adapter_align.h:12-16) ------------------------------ */
 
 /* Returns a malloc'd "readStart,readEnd,adapterStart,adapterEnd,rawScore,alignedId,fullId" string
- * (alignment.cpp:112-120), to be released with freeCString.  On a device error it returns the
- * reference's own failure encoding (readStart == -1, alignment.cpp:7-21) and pcb_last_error(NULL)
- * holds the reason. */
+ * (alignment.cpp:112-120), to be released with freeCString.  The reference's function cannot fail on
+ * non-empty input and has no error channel, so a library failure (no device, CUDA error, scoring scheme
+ * outside the 16-bit range) ends the process with the reason on stderr -- an unmodified caller would
+ * otherwise read the failure record as "no adapter" and write wrong output.  After
+ * pcb_set_dropin_fatal(0) the call instead returns the reference's failure encoding (readStart == -1,
+ * alignment.cpp:7-21) and pcb_last_error(NULL) holds the reason (per thread). */
 char *adapterAlignment(char *readSeq, char *adapterSeq,
                        int matchScore, int mismatchScore, int gapOpenScore, int gapExtensionScore);
 void freeCString(char *p);
+int pcb_set_dropin_fatal(int on);
 
 /* ---- 2. batched form ------------------------------------------------------------------------- */
 
@@ -154,10 +158,14 @@ int pcb_upload_reads(pcb_context *ctx, const char *seq_blob, int64_t blob_len);
  * most one pcb_align_tasks is queued.  pcb_set_deferred waits for queued work before it switches. */
 int pcb_set_deferred(pcb_context *ctx, int on);
 int pcb_wait(pcb_context *ctx);
+/* Collects ONE slot's queued pcb_align_windows_hits call while the calls queued in other slots keep running: the caller
+ * can derive that part's trims and queue its phase C beside the phase B of the next part (the reference's pool works
+ * through reads in order in the same way).  Device-side errors are reported by the pcb_wait that ends the batch. */
+int pcb_wait_slot(pcb_context *ctx, int slot);
 
 /* ---- 3. device-resident form (same kernels; used to time the kernels without PCIe) ---------- */
 
-/* A context holds 4 independent staging slots (inputs + results); all stage/run/fetch calls, and the host-buffer
+/* A context holds 8 independent staging slots (inputs + results); all stage/run/fetch calls, and the host-buffer
  * calls above, act on the selected one (default 0).  Lets start windows, end windows and full-length tasks stay
  * resident side by side. */
 int pcb_select_slot(pcb_context *ctx, int slot);

@@ -294,11 +294,11 @@ def test_ultra_long_reads_and_barcode_sets(engine):
 
 
 def test_trace_queue_many_units_per_warp_and_long_paths():
-    """The fast trace is two kernels per batch of units: pass 1 leaves checkpoints and end cells in scratch, the rounds
-    kernel takes every task through pass 2 with a per-warp queue of continuation entries (pcb_fast.cu: trace_round).
-    A context limited to two CTAs gives every warp dozens of units, so the queue runs full rounds across unit boundaries and
-    wraps; a 1 MB scratch budget cuts the launch into many batches; cheap gaps make paths that cross up to ten flag blocks
-    (entries that stay queued for many rounds); adapters of several classes alternate.  Every record against the oracle."""
+    """The fast trace per batch of units: pass 1 leaves checkpoints and end cells in scratch, pass 2 sorts the tracebacks
+    (first blocks by width, later blocks by rows) and runs them 64 of a kind per warp (pcb_fast.cu: k_rounds).
+    A context limited to two CTAs gives every warp dozens of chunks across adapter boundaries; a 1 MB scratch budget cuts
+    the launch into many batches; cheap gaps make paths that cross a dozen flag blocks (items that stay with their warp for
+    many rounds of generation 1); adapters of several classes alternate.  Every record against the oracle."""
     import os
     from custom_porechop_abi_b200.engine import AlignmentEngine
     rng = random.Random(77)
@@ -408,3 +408,21 @@ def test_reduced_outputs_match_full_records(engine, thr, at_end, min_trim):
     engine.select_slot(0)
     assert res2.n_hits == res.n_hits and np.array_equal(res2.hits, res.hits) and np.array_equal(res2.ident, res.ident)
     assert np.array_equal(best2, best)
+
+
+@pytest.mark.parametrize('scores', [(7, -6, -5, -1), (10, -10, -10, -1), (4, -3, -7, -3)])
+def test_user_schemes_on_kilobase_segments(engine, scores):
+    """--scoring_scheme values for which the trace window of a long read (warm-up + span) is wider than
+    the fast trace kernels take, or that the fast kernels do not take at all: ordinary 1-3 kb reads must still align (direct
+    tasks up to the fast limit, then scan + window, the window on the general kernel where it is too wide)."""
+    rng = random.Random(sum(scores) & 0xff)
+    ads = [''.join(rng.choice('ACGT') for _ in range(n)) for n in (24, 52, 33)]
+    pairs = []
+    for L in (900, 1001, 1400, 1790, 2600, 3000):
+        for aid, a in enumerate(ads):
+            r = ''.join(rng.choice('ACGT') for _ in range(L))
+            p = rng.randrange(100, L - 100)
+            from oracle_lib import mutate
+            r = r[:p] + mutate(rng, a, 0.1) + r[p + len(a):]
+            pairs.append((r, aid))
+    _check_pairs(engine, pairs, ads, scores)
