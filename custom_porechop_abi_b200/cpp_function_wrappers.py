@@ -87,6 +87,9 @@ C_LIB.pcb_align_windows.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_
 C_LIB.pcb_align_windows_best.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, c_void_p]
 C_LIB.pcb_align_windows_hits.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, POINTER(PcbHitFilter),
                                          c_void_p, c_void_p, c_int64, POINTER(c_int64), c_void_p]
+C_LIB.check_compatibility.argtypes = [c_char_p, c_char_p]
+C_LIB.check_compatibility.restype = c_int
+C_LIB.pcb_check_compatibility.argtypes = [_P, c_char_p, POINTER(c_int64), c_int32, c_void_p, c_void_p, c_int64, c_void_p]
 C_LIB.pcb_fetch_top2.argtypes = [_P, c_void_p, c_int64]
 C_LIB.pcb_align_tasks.argtypes = [_P, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
 C_LIB.pcb_upload_reads.argtypes = [_P, c_void_p, c_int64]
@@ -136,6 +139,15 @@ def c_string_to_python_string(c_string):
     python_string = cast(c_string, c_char_p).value.decode()
     C_LIB.freeCString(c_string)
     return python_string
+
+
+def check_compatibility(seq1, seq2):
+    """compatibility.so's check_compatibility (consensus.py:72-100 binds it the same way): 0 / 1 / 2."""
+    flag = C_LIB.check_compatibility(seq1.encode('utf-8'), seq2.encode('utf-8'))
+    err = C_LIB.pcb_last_error(None)
+    if err:
+        raise AlignmentError(err.decode())
+    return flag
 
 
 def format_result(rec):

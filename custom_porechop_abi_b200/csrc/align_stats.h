@@ -33,55 +33,80 @@ struct PathAcc {
     int32_t kR_first_rev;
     int32_t A_last_isD;      /* is that column a D (i.e. does it also hold a read base) */
     int32_t R_last_isD;
+    int32_t A_last_match;    /* ... and do its two bases match (general kernels only; the compatibility flag needs it) */
+    int32_t R_last_match;
 };
 
 PCB_HD void path_acc_init(PathAcc &a)
 {
     a.K = 0; a.matches = 0;
     a.kA_last_rev = -1; a.kA_first_rev = -1; a.kR_last_rev = -1; a.kR_first_rev = -1;
-    a.A_last_isD = 0; a.R_last_isD = 0;
+    a.A_last_isD = 0; a.R_last_isD = 0; a.A_last_match = 0; a.R_last_match = 0;
 }
 
 /* op: 0 = D, 1 = V (adapter base, read gap), 2 = H (read base, adapter gap) */
 PCB_HD void path_acc_step(PathAcc &a, int op, int is_match)
 {
     const int k = a.K;
-    if (op != 2) { if (a.kA_last_rev < 0) { a.kA_last_rev = k; a.A_last_isD = (op == 0); } a.kA_first_rev = k; }
-    if (op != 1) { if (a.kR_last_rev < 0) { a.kR_last_rev = k; a.R_last_isD = (op == 0); } a.kR_first_rev = k; }
+    if (op != 2) { if (a.kA_last_rev < 0) { a.kA_last_rev = k; a.A_last_isD = (op == 0); a.A_last_match = (op == 0 && is_match); } a.kA_first_rev = k; }
+    if (op != 1) { if (a.kR_last_rev < 0) { a.kR_last_rev = k; a.R_last_isD = (op == 0); a.R_last_match = (op == 0 && is_match); } a.kR_first_rev = k; }
     if (op == 0 && is_match) a.matches++;
     a.K = k + 1;
 }
 
-/* Cheaper accumulation for the fast kernels' walk: instead of step indices it keeps cell coordinates, and the step
- * indices PathAcc wants are recovered at the end (rows and columns only ever decrease along the reverse walk):
- *   kA = max over ops holding an adapter base (D, V) of 2*j + isV, j = column before the op: the FIRST such op has the
- *        largest j, and if V ops share that column they come before the D that leaves it;
- *   kR = the same for read bases (D, H) with rows: 2*i + isH;
- *   jA / iR = column / row after the LAST op holding an adapter / read base.  */
-struct WalkAcc {
-    int32_t nD, matches, kA, kR, jA, iR;
-};
-PCB_HD void walk_acc_init(WalkAcc &a) { a.nD = 0; a.matches = 0; a.kA = -1; a.kR = -1; a.jA = 0; a.iR = 0; }
-PCB_HD void walk_acc_D(WalkAcc &a, int i, int j, int is_match)
+/* Accumulation of the fast kernels' walk (pcb_fast.cu), packed so that a step has no branch; the step indices PathAcc
+ * wants are recovered at the end (rows and columns only ever decrease along the reverse walk):
+ *   kAR : low half = 1 + max over the ops that hold an adapter base (D, V) of 2 * column + isV, column = the one before the
+ *         op (the FIRST such op has the largest; 0 = none yet); high half = the same for read bases (D, H) with rows
+ *   tHV : low = H ops since the last op with an adapter base, high = V ops since the last op with a read base
+ *   nHV : low = H ops, high = V ops;   op : gap openings
+ * pos2 = (2 * column + 1) | (2 * row + 1) << 16 of the cell the op leaves.  isD / isV / isH: exactly one is 1. */
+struct WalkAcc { uint32_t kAR, tHV, nHV; int32_t op; };
+PCB_HD void walk_acc_init(WalkAcc &a) { a.kAR = 0; a.tHV = 0; a.nHV = 0; a.op = 0; }
+PCB_HD uint32_t walk_max16x2(uint32_t a, uint32_t b)
 {
-    a.nD++; a.matches += is_match;
-    a.kA = a.kA > 2 * j ? a.kA : 2 * j; a.kR = a.kR > 2 * i ? a.kR : 2 * i;
-    a.jA = j - 1; a.iR = i - 1;
+#if defined(__CUDA_ARCH__)
+    return __vmaxs2(a, b);
+#else
+    const uint32_t lo = (a & 0xFFFFu) > (b & 0xFFFFu) ? (a & 0xFFFFu) : (b & 0xFFFFu), hi = (a >> 16) > (b >> 16) ? (a >> 16) : (b >> 16);
+    return lo | (hi << 16);
+#endif
 }
-PCB_HD void walk_acc_V(WalkAcc &a, int i, int j) { (void)i; a.kA = a.kA > 2 * j + 1 ? a.kA : 2 * j + 1; a.jA = j; }
-PCB_HD void walk_acc_H(WalkAcc &a, int i, int j) { (void)j; a.kR = a.kR > 2 * i + 1 ? a.kR : 2 * i + 1; a.iR = i; }
-/* (endi, endj): cell the walk started from; (ci, cj): cell it stopped at. */
-PCB_HD void walk_acc_finish(const WalkAcc &w, int endi, int endj, int ci, int cj, PathAcc &a)
+PCB_HD void walk_acc_step(WalkAcc &a, uint32_t &pos2, uint32_t isD, uint32_t isV, uint32_t isH, uint32_t ext)
 {
-    const int K = (endi - ci) + (endj - cj) - w.nD;
-    a.K = K; a.matches = w.matches;
+    const uint32_t inc = isH | (isV << 16), incs = isV | (isH << 16);
+    const uint32_t keep = inc * 0xFFFFu;                          /* H: 0x0000FFFF, V: 0xFFFF0000, D: 0 */
+    a.kAR = walk_max16x2(a.kAR, (pos2 + incs) & ~keep);
+    a.tHV = (a.tHV & keep) + inc;
+    a.nHV += inc;
+    pos2 = pos2 - 0x00020002u + 2u * incs;
+    a.op += (int32_t)((isD | ext) ^ 1u);
+}
+/* (endi, endj): cell the walk started from; (ci, cj): cell it stopped at.  matches: counted by the caller, or derived from
+ * the end cell's score (every D op scores match or mismatch, every gap of g ops gapOpen + (g - 1) gapExtend). */
+PCB_HD void walk_acc_finish(const WalkAcc &w, int endi, int endj, int ci, int cj, int matches, PathAcc &a)
+{
+    const int nH = (int)(w.nHV & 0xFFFFu), nV = (int)(w.nHV >> 16), kA = (int)(w.kAR & 0xFFFFu) - 1, kR = (int)(w.kAR >> 16) - 1;
+    const int nD = (endi - ci) - nV;
+    a.K = nD + nV + nH; a.matches = matches;
     a.kA_last_rev = -1; a.kA_first_rev = -1; a.kR_last_rev = -1; a.kR_first_rev = -1; a.A_last_isD = 0; a.R_last_isD = 0;
-    if (w.kA >= 0) { a.kA_last_rev = endj - (w.kA >> 1); a.A_last_isD = !(w.kA & 1); a.kA_first_rev = K - 1 - (w.jA - cj); }
-    if (w.kR >= 0) { a.kR_last_rev = endi - (w.kR >> 1); a.R_last_isD = !(w.kR & 1); a.kR_first_rev = K - 1 - (w.iR - ci); }
+    a.A_last_match = 0; a.R_last_match = 0;
+    if (kA >= 0) { a.kA_last_rev = endj - (kA >> 1); a.A_last_isD = !(kA & 1); a.kA_first_rev = a.K - 1 - (int)(w.tHV & 0xFFFFu); }
+    if (kR >= 0) { a.kR_last_rev = endi - (kR >> 1); a.R_last_isD = !(kR & 1); a.kR_first_rev = a.K - 1 - (int)(w.tHV >> 16); }
+    (void)cj;
+}
+PCB_HD int walk_acc_matches(const WalkAcc &w, int endi, int endj, int ci, int cj, int score, int match, int mismatch,
+                            int gap_open, int gap_extend, int *ok)
+{
+    const int nH = (int)(w.nHV & 0xFFFFu), nV = (int)(w.nHV >> 16), nD = (endi - ci) - nV;
+    const int num = score - mismatch * nD - gap_open * w.op - gap_extend * (nV + nH - w.op), den = match - mismatch;
+    *ok = nD == (endj - cj) - nH && num >= 0 && den > 0 && num % den == 0;
+    return den > 0 ? num / den : 0;
 }
 
 struct PathStats {
     int32_t read_start, read_end, adapter_start, adapter_end, matches, aligned_len, full_len;
+    int32_t end_match;       /* the last column of the aligned region holds two equal bases (general kernels only) */
 };
 
 /* m, n: full read / adapter lengths (head_h + #D + #H + tail_h == m, head_v + #D + #V + tail_v == n). */
@@ -116,6 +141,8 @@ PCB_HD void path_finalize(const PathAcc &a, int64_t head_h, int64_t head_v, int6
     o.read_end    = (int32_t)(m - readAtOrAfter);
     o.adapter_end = (int32_t)(n - adAtOrAfter);
     o.matches     = a.matches;
+    /* the column endPos: the last read base's column or the last adapter base's, whichever comes first */
+    o.end_match   = (lastRead <= lastAd) ? ((tail_h > 0 || !hasR) ? 0 : a.R_last_match) : ((tail_v > 0 || !hasA) ? 0 : a.A_last_match);
     o.aligned_len = (int32_t)(endPos - startPos + 1);
     o.full_len    = (int32_t)(lastAd - firstAd + 1);
 }

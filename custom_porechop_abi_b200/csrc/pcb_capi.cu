@@ -92,6 +92,8 @@ struct pcb_context {
         DevBuf<uint16_t> d_ident;
         DevBuf<long long> d_total;
         DevBuf<pcb_top2> d_top2;
+        DevBuf<uint8_t> d_aux;            // check_compatibility: end-column match of every task
+        bool want_aux = false;
         int32_t n_want = 0;
         std::vector<int32_t> h_identcol;
     };
@@ -230,7 +232,7 @@ extern "C" void pcb_destroy(pcb_context *c)
     c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_ascii_t.release(); c->d_arena_t.release();
     for (auto &sl : c->slots) {
         sl.d_arena.release(); sl.d_ascii.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release();
-        sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release(); sl.d_top2.release();
+        sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release(); sl.d_top2.release(); sl.d_aux.release();
         if (sl.staged) cudaEventDestroy(sl.staged);
         if (sl.done) cudaEventDestroy(sl.done);
     }
@@ -352,6 +354,7 @@ static void fill_launch_common(pcb_context *c, PcbLaunch &L, bool task_arena = f
     L.sc = c->sc;
     L.arena = task_arena ? c->d_arena_t.p : c->S().d_arena.p; L.arena_len = task_arena ? c->arena_t_len : c->S().arena_len;
     L.out = c->S().d_out.p; L.scan_out = nullptr; L.n_out = c->S().n_results;
+    L.aux = c->S().want_aux ? c->S().d_aux.p : nullptr;
     L.scratch = c->d_scratch.p; L.err_flag = c->d_err.p;
 }
 
@@ -1145,19 +1148,22 @@ extern "C" int pcb_stats_from_path(const char *ops, int64_t n_ops, int64_t head_
     int ei = 0, ej = 0;                                      // core path size: rows / columns it covers
     for (int64_t k = 0; k < n_ops; ++k) { if (ops[k] != 'H') ++ei; if (ops[k] != 'V') ++ej; }
     WalkAcc wa; walk_acc_init(wa);
-    int i = ei, j = ej;
+    uint32_t pos2 = (uint32_t)(2 * ej + 1) | ((uint32_t)(2 * ei + 1) << 16);
+    int matches = 0;
     for (int64_t k = n_ops - 1; k >= 0; --k) {              // the kernels walk the path back to front
         const int op = ops[k] == 'D' ? 0 : (ops[k] == 'V' ? 1 : 2);
         path_acc_step(acc, op, match_flags[k]);
-        if (op == 0) { walk_acc_D(wa, i, j, match_flags[k] ? 1 : 0); --i; --j; }
-        else if (op == 1) { walk_acc_V(wa, i, j); --i; }
-        else { walk_acc_H(wa, i, j); --j; }
+        matches += op == 0 && match_flags[k];
+        // a gap op extends when the op before it (in path order) is of the same kind
+        const uint32_t ext = op != 0 && k > 0 && ops[k - 1] == ops[k];
+        walk_acc_step(wa, pos2, op == 0, op == 1, op == 2, ext);
         if (op != 2) ++n;
         if (op != 1) ++m;
     }
     // both accumulators (general kernels: PathAcc; fast kernels: WalkAcc) must describe the same path
-    PathAcc acc2; walk_acc_finish(wa, ei, ej, 0, 0, acc2);
-    if (memcmp(&acc, &acc2, sizeof acc) != 0) return PCB_ERR_RANGE;
+    PathAcc acc2; walk_acc_finish(wa, ei, ej, 0, 0, matches, acc2);
+    acc2.A_last_match = acc.A_last_match; acc2.R_last_match = acc.R_last_match;     // (the fast kernels do not track these)
+    if (memcmp(&acc, &acc2, sizeof acc) != 0 || pos2 != 0x00010001u) return PCB_ERR_RANGE;
     PathStats st; path_finalize(acc, head_h, head_v, tail_h, tail_v, m, n, st);
     out->read_start = st.read_start; out->read_end = st.read_end; out->adapter_start = st.adapter_start;
     out->adapter_end = st.adapter_end; out->raw_score = raw_score; out->matches = st.matches;
@@ -1167,6 +1173,88 @@ extern "C" int pcb_stats_from_path(const char *ops, int64_t n_ops, int64_t head_
 
 static std::mutex g_mu;
 static pcb_context *g_ctx = nullptr;
+
+// ------------------------------------------------------------------------------------------------
+// check_compatibility (porechop_abi/ab_initio_src/compatibility.cpp:160-168): the second call site of the same DP in the
+// reference -- candidate adapters against each other, linear gaps, match 2 / mismatch -1 / gap -1 (compatibility.h:9-12).
+// ------------------------------------------------------------------------------------------------
+extern "C" int pcb_check_compatibility(pcb_context *c, const char *blob, const int64_t *offsets, int32_t n_seqs,
+                                       const int32_t *pair_a, const int32_t *pair_b, int64_t n_pairs, int32_t *flags)
+{
+    if (!c || n_seqs < 0 || n_pairs < 0 || (n_seqs > 0 && (!blob || !offsets)) || (n_pairs > 0 && (!pair_a || !pair_b || !flags))) return PCB_ERR_ARG;
+    if (n_pairs == 0) return PCB_OK;
+    if (c->deferred) return c->fail(PCB_ERR_ARG, "pcb_check_compatibility is not a deferred call");
+    // String<Dna> (compatibility.h:24): a/c/g/t/u in either case, everything else becomes A
+    const int64_t base = offsets[0], total = offsets[n_seqs] - base;
+    std::string dna((size_t)total, 'A');
+    for (int64_t k = 0; k < total; ++k) {
+        const char ch = blob[base + k];
+        if (strchr("ACGTUacgtu", ch) && ch) dna[(size_t)k] = ch;
+    }
+    std::vector<int64_t> off((size_t)n_seqs + 1), seg_off((size_t)n_pairs);
+    for (int i = 0; i <= n_seqs; ++i) off[(size_t)i] = offsets[i] - base;
+    std::vector<int32_t> seg_len((size_t)n_pairs), seg_ad((size_t)n_pairs), len1((size_t)n_pairs);
+    for (int64_t p = 0; p < n_pairs; ++p) {
+        int32_t a = pair_a[p], b = pair_b[p];
+        if (a < 0 || a >= n_seqs || b < 0 || b >= n_seqs) return c->fail(PCB_ERR_ARG, "pair %lld: sequence index out of range", (long long)p);
+        const int64_t la = off[(size_t)a + 1] - off[(size_t)a], lb = off[(size_t)b + 1] - off[(size_t)b];
+        if (la == 0 || lb == 0) return c->fail(PCB_ERR_ARG, "pair %lld: empty sequence", (long long)p);
+        if (la < lb) std::swap(a, b);                          // the longer sequence is row 0 (make_stringSet, compatibility.cpp:19-31)
+        seg_off[(size_t)p] = off[(size_t)a]; seg_len[(size_t)p] = (int32_t)(off[(size_t)a + 1] - off[(size_t)a]); seg_ad[(size_t)p] = b;
+        len1[(size_t)p] = seg_len[(size_t)p];
+    }
+    const PcbScores saved = c->sc;
+    int rc = pcb_set_scoring(c, 2, -1, -1, -1);                // compatibility.h:9-12
+    if (!rc) rc = pcb_set_adapters(c, dna.data(), off.data(), n_seqs);
+    std::vector<pcb_result> rec((size_t)n_pairs);
+    std::vector<uint8_t> aux((size_t)n_pairs);
+    pcb_context::Slot &S = c->S();
+    if (!rc && S.d_aux.reserve((size_t)n_pairs) != cudaSuccess) rc = c->fail(PCB_ERR_NOMEM, "cudaMalloc failed");
+    S.want_aux = true;
+    if (!rc) rc = pcb_align_tasks(c, dna.data(), total, seg_off.data(), seg_len.data(), seg_ad.data(), n_pairs, rec.data());
+    S.want_aux = false;
+    if (!rc && cudaMemcpy(aux.data(), S.d_aux.p, (size_t)n_pairs, cudaMemcpyDeviceToHost) != cudaSuccess) rc = c->fail(PCB_ERR_CUDA, "cudaMemcpy failed");
+    c->sc = saved; c->stamp++;
+    if (rc) return rc;
+    for (int64_t p = 0; p < n_pairs; ++p) {
+        const pcb_result &r = rec[(size_t)p];
+        // get_flag (compatibility.cpp:121-156): errors are counted on [start, end) -- the last column is left out --, the
+        // identity is an integer division
+        const int mapped = r.aligned_len;
+        const int dist = (r.aligned_len - 1) - (r.matches - (int)aux[(size_t)p]);
+        const float identity = (float)((mapped - dist) * 100 / mapped);
+        int flag = identity >= 87.5f ? 1 : 0;                  // compatibility.h:15
+        const bool included = r.read_start > 3 || (len1[(size_t)p] - r.read_end) > 3;      // is_included, OVERLAP_LIMIT 3
+        if (included && flag == 1) flag = 2;
+        flags[p] = flag;
+    }
+    return PCB_OK;
+}
+
+extern "C" int check_compatibility(char *raw_seq1, char *raw_seq2)
+{
+    std::lock_guard<std::mutex> lock(g_mu);
+    g_global_err.clear();
+    int flag = 0;
+    const auto failed = [&](const char *why) {
+        g_global_err = why;
+        fprintf(stderr, "cpp_functions.so (B200): check_compatibility failed: %s\n", why);
+        if (g_dropin_fatal) exit(1);
+        return 0;
+    };
+    if (!raw_seq1 || !raw_seq2) return failed("null sequence");
+    if (!g_ctx) {
+        int dev = 0;
+        if (const char *e = getenv("PCB_DEVICE")) dev = atoi(e);
+        if (pcb_create(dev, &g_ctx) != PCB_OK) return failed(g_global_err.c_str());
+    }
+    const std::string both = std::string(raw_seq1) + raw_seq2;
+    const int64_t off[3] = { 0, (int64_t)strlen(raw_seq1), (int64_t)both.size() };
+    const int32_t a = 0, b = 1;
+    if (pcb_check_compatibility(g_ctx, both.data(), off, 2, &a, &b, 1, &flag) != PCB_OK) return failed(g_ctx->err.c_str());
+    return flag;
+}
+
 
 static char *dup_cstring(const char *s)
 {

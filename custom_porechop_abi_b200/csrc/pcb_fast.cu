@@ -649,21 +649,17 @@ __global__ void k_scatter1(const PcbLaunch L)
     if (slot >= 0) put_item(L.sorted + slot, v[0], v[1], v[2], v[3], v[4], v[5], (uint64_t)v[6] | ((uint64_t)v[7] << 32));
 }
 
-// The walk's state and accumulators for one traceback (dp_traceback_impl.h:379-451), packed so that a step is branch-free.
-//   i, j : cell the walk stands in;  s : state, 0 = M, 1 = V, 2 = H
-//   kAR  : low half = 1 + max over the ops that hold an adapter base (D, V) of 2 * column + isV (the FIRST such op has the
-//          largest; 0 = none yet), high half = the same for read bases (D, H) with rows
-//   tHV  : low = H ops since the last op with an adapter base, high = V ops since the last op with a read base
-//   nHV  : low = H ops, high = V ops;   op : gap openings (gap ops after which the walk is back in state M)
-struct Walk { int i, j, s; uint32_t kAR, tHV, nHV; int op; };
+// The walk's state for one traceback (dp_traceback_impl.h:379-451): i, j = cell the walk stands in; s = state, 0 = M, 1 = V,
+// 2 = H; the accumulators (align_stats.h: WalkAcc) are packed so that a step is branch-free.
+struct Walk { int i, j, s; WalkAcc acc; };
 __device__ __forceinline__ void walk_unpack(Walk &w, uint32_t pos, uint32_t a0, uint32_t a1, uint32_t a2)
 {
-    w.i = (int)(pos & 63u); w.j = (int)((pos >> 6) & 0xFFFu); w.s = (int)((pos >> 18) & 7u); w.op = (int)(pos >> 21);
-    w.kAR = a0; w.tHV = a1; w.nHV = a2;
+    w.i = (int)(pos & 63u); w.j = (int)((pos >> 6) & 0xFFFu); w.s = (int)((pos >> 18) & 7u); w.acc.op = (int)(pos >> 21);
+    w.acc.kAR = a0; w.acc.tHV = a1; w.acc.nHV = a2;
 }
 __device__ __forceinline__ uint32_t walk_pos(const Walk &w)
 {
-    return (uint32_t)w.i | ((uint32_t)w.j << 6) | ((uint32_t)w.s << 18) | ((uint32_t)w.op << 21);
+    return (uint32_t)w.i | ((uint32_t)w.j << 6) | ((uint32_t)w.s << 18) | ((uint32_t)w.acc.op << 21);
 }
 // One op of the reverse walk; flag word layout as col_flags writes it.  ar = register row of the walk's adapter row, jc = its
 // column inside the flag block, pos2 = (2 * column + 1) | (2 * row + 1) << 16.  In state M a cell whose diagonal flag is off
@@ -684,14 +680,8 @@ __device__ __forceinline__ void walk_step(const uint32_t *s_fl, const int h, int
     const uint32_t fh = f & 1u, fg = (f >> 1) & 1u, fv = (f >> 16) & 1u, fd = (f >> 17) & 1u;
     const uint32_t sM = w.s == 0 ? 1u : 0u, sV = w.s == 1 ? 1u : 0u;
     const uint32_t isD = sM & fd, isV = sV | (sM & (fd ^ 1u) & fg), isH = (isD | isV) ^ 1u;
-    const uint32_t inc = isH | (isV << 16), incs = isV | (isH << 16);
-    const uint32_t keep = inc * 0xFFFFu;                          // H: 0x0000FFFF, V: 0xFFFF0000, D: 0
-    w.kAR = __vmaxs2(w.kAR, (pos2 + incs) & ~keep);
-    w.tHV = (w.tHV & keep) + inc;
-    w.nHV += inc;
-    pos2 = pos2 - 0x00020002u + 2u * incs;
     const uint32_t extV = isV & fv, extH = isH & fh;
-    w.op += (int)((isD | extV | extH) ^ 1u);
+    walk_acc_step(w.acc, pos2, isD, isV, isH, extV | extH);
     w.s = (int)(extV | (extH << 1));
     ar -= (int)(isH ^ 1u); jc -= (int)(isV ^ 1u);
 }
@@ -877,16 +867,11 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
                 if (w.j == 0 && w.i > 0 && col0 > 0) atomicOr(L.err_flag, 1);      // window too narrow for this path
                 // the path as align_stats.h wants it.  Matches are not counted on the way: the path's ops and the end
                 // cell's score determine them (every D op scores match or mismatch, every gap of g ops go + (g-1) ge)
-                const int nH = (int)(w.nHV & 0xFFFFu), nV = (int)(w.nHV >> 16), kA = (int)(w.kAR & 0xFFFFu) - 1, kR = (int)(w.kAR >> 16) - 1;
-                const int rows = endi - w.i, cols = endj - w.j, nD = rows - nV;
-                const int num = score - L.sc.mismatch * nD - L.sc.gap_open * w.op - L.sc.gap_extend * (nV + nH - w.op);
-                const int den = L.sc.match - L.sc.mismatch;
-                if (nD != cols - nH || num < 0 || num % den != 0) atomicOr(L.err_flag, 16);
+                int ok;
+                const int matches = walk_acc_matches(w.acc, endi, endj, w.i, w.j, score, L.sc.match, L.sc.mismatch, L.sc.gap_open, L.sc.gap_extend, &ok);
+                if (!ok) atomicOr(L.err_flag, 16);
                 PathAcc pa;
-                pa.K = nD + nV + nH; pa.matches = num / den;
-                pa.kA_last_rev = -1; pa.kA_first_rev = -1; pa.kR_last_rev = -1; pa.kR_first_rev = -1; pa.A_last_isD = 0; pa.R_last_isD = 0;
-                if (kA >= 0) { pa.kA_last_rev = endj - (kA >> 1); pa.A_last_isD = !(kA & 1); pa.kA_first_rev = pa.K - 1 - (int)(w.tHV & 0xFFFFu); }
-                if (kR >= 0) { pa.kR_last_rev = endi - (kR >> 1); pa.R_last_isD = !(kR & 1); pa.kR_first_rev = pa.K - 1 - (int)(w.tHV >> 16); }
+                walk_acc_finish(w.acc, endi, endj, w.i, w.j, matches, pa);
                 PathStats ps;
                 path_finalize(pa, (int64_t)col0 + w.j, w.i, (int64_t)mtrue - (col0 + endj), n - endi, mtrue, n, ps);
                 pcb_result res;
@@ -919,7 +904,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
                     if (keep[h]) {
                         if (lane == __ffs(mk) - 1) atomicAdd(M.hist1 + key, __popc(mk));
                         const int slot = first + (h ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt));
-                        put_item(L.surv + slot, ref[h], pos, endc[h], w.kAR, w.tHV, w.nHV, off[h]);
+                        put_item(L.surv + slot, ref[h], pos, endc[h], w.acc.kAR, w.acc.tHV, w.acc.nHV, off[h]);
                     }
                 }
             }

@@ -386,6 +386,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCB_MIN_BLOCKS) k_align(const PcbLa
             res.raw_score = score; res.matches = st.matches;
             res.aligned_len = st.aligned_len; res.full_len = st.full_len;
             L.out[t.out_idx] = res;
+            if (L.aux) L.aux[t.out_idx] = (uint8_t)st.end_match;
         }
     }
 }

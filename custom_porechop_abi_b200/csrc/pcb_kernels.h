@@ -110,6 +110,7 @@ struct PcbLaunch {
     uint64_t arena_len;
     pcb_result *out;             /* trace kernel                                                  */
     int32_t    *scan_out;        /* scan kernel: one key per task (indexed by out_idx)            */
+    uint8_t    *aux;             /* general trace kernel, may be NULL: 1 = the last column of the aligned region is a match */
     uint32_t   *scratch;         /* per-thread-slot scratch, see kernels                          */
     int32_t     mmax;            /* scratch sized for segments up to this many columns            */
     int32_t     smax;            /* ... and adapters up to this many stripes                      */

@@ -265,6 +265,21 @@ class AlignmentEngine(object):
             off[1:] = np.cumsum(lens[:-1], dtype=np.int64)
         return self.align_tasks(b''.join(seqs), off, lens, [p[1] for p in pairs])
 
+    def check_compatibility(self, sequences, pairs):
+        """flags (0 / 1 / 2, compatibility.cpp:121-156) for the index pairs of `sequences`, in one submit.  Replaces the
+        engine's adapter set."""
+        seqs = [s.encode() if isinstance(s, str) else bytes(s) for s in sequences]
+        off = np.zeros(len(seqs) + 1, dtype=np.int64)
+        if seqs:
+            off[1:] = np.cumsum([len(s) for s in seqs])
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+        pa, pb_ = np.ascontiguousarray(pairs[:, 0]), np.ascontiguousarray(pairs[:, 1])
+        flags = np.zeros(len(pairs), dtype=np.int32)
+        self._check(w.C_LIB.pcb_check_compatibility(self._h, b''.join(seqs), off.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)), len(seqs),
+                                                    _ptr(pa), _ptr(pb_), len(pairs), _ptr(flags)), 'pcb_check_compatibility')
+        self.adapters = seqs
+        return flags
+
     # -- timing / counters ---------------------------------------------------------------------
     def timer_start(self):
         self._check(w.C_LIB.pcb_timer_start(self._h), 'pcb_timer_start')

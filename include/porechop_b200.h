@@ -163,6 +163,18 @@ int pcb_wait(pcb_context *ctx);
  * through reads in order in the same way).  Device-side errors are reported by the pcb_wait that ends the batch. */
 int pcb_wait_slot(pcb_context *ctx, int slot);
 
+/* ---- 2c. the other call site of the same DP: check_compatibility --------------------------------------------
+ * porechop_abi/ab_initio_src/compatibility.h:56-58 / compatibility.cpp:160-168 (compatibility.so, bound by
+ * consensus.py:72-100): semi-global alignment of two candidate adapters as String<Dna>, longer sequence first, linear gaps,
+ * match 2 / mismatch -1 / gap -1; flag 0 = not compatible, 1 = compatible (integer identity of the aligned region >=
+ * 87.5 %, errors counted without its last column, as the reference does), 2 = compatible and the shorter sequence lies
+ * inside the longer one (more than 3 bases from either end).  check_compatibility has the reference's signature;
+ * pcb_check_compatibility takes all sequences and a list of index pairs at once (the reference calls it all-vs-all).
+ * Both replace the context's adapter set; sequences must not be empty. */
+int check_compatibility(char *raw_seq1, char *raw_seq2);
+int pcb_check_compatibility(pcb_context *ctx, const char *blob, const int64_t *offsets, int32_t n_seqs,
+                            const int32_t *pair_a, const int32_t *pair_b, int64_t n_pairs, int32_t *flags);
+
 /* ---- 3. device-resident form (same kernels; used to time the kernels without PCIe) ---------- */
 
 /* A context holds 8 independent staging slots (inputs + results); all stage/run/fetch calls, and the host-buffer

@@ -131,3 +131,72 @@ def rec_matches_oracle(rec, o):
             int(rec['raw_score']) == o.raw_score and int(rec['matches']) == o.aligned_matches and
             int(rec['matches']) == o.full_matches and int(rec['aligned_len']) == o.aligned_len and
             int(rec['full_len']) == o.full_len)
+
+
+# ---- check_compatibility (porechop_abi/ab_initio_src/compatibility.cpp), restated on top of the oracle's alignment path ----
+_DNA = {ord(c): c.upper() for c in 'ACGTacgt'}
+_DNA.update({ord('U'): 'T', ord('u'): 'T'})
+
+
+def oracle_compat(seq1, seq2):
+    """The flag get_flag computes (compatibility.cpp:121-156): String<Dna> conversion, longer sequence first
+    (make_stringSet, :19-31), semi-global alignment with linear gaps 2 / -1 / -1 (compatibility.h:9-12), then the
+    reference's own scans over the two gapped rows (:37-117), with its integer identity and its [start, end) error count."""
+    a = ''.join(_DNA.get(ord(c), 'A') for c in seq1)
+    b = ''.join(_DNA.get(ord(c), 'A') for c in seq2)
+    s1, s2 = (b, a) if len(a) < len(b) else (a, b)
+    ops, _, hh, hv, th, tv, _ = oracle_path(s1, s2, (2, -1, -1, -1))
+    row1, row2 = [], []
+    i = j = 0
+    for _ in range(hh):
+        row1.append(s1[i]); row2.append('-'); i += 1
+    for _ in range(hv):
+        row1.append('-'); row2.append(s2[j]); j += 1
+    for op in ops.decode():
+        if op == 'D':
+            row1.append(s1[i]); row2.append(s2[j]); i += 1; j += 1
+        elif op == 'V':
+            row1.append('-'); row2.append(s2[j]); j += 1
+        else:
+            row1.append(s1[i]); row2.append('-'); i += 1
+    for _ in range(th):
+        row1.append(s1[i]); row2.append('-'); i += 1
+    for _ in range(tv):
+        row1.append('-'); row2.append(s2[j]); j += 1
+    assert i == len(s1) and j == len(s2)
+    n = len(row1)
+    start = end = -1
+    s1_started = s2_started = False
+    for k in range(n):
+        s1_started |= row1[k] != '-'; s2_started |= row2[k] != '-'
+        if s1_started and s2_started:
+            start = k; break
+    e1 = e2 = False
+    for k in range(n - 1, -1, -1):
+        e1 |= row1[k] != '-'; e2 |= row2[k] != '-'
+        if e1 and e2:
+            end = k; break
+    mapped = end - start + 1
+    dist = sum(1 for k in range(start, end) if row1[k] != row2[k])
+    identity = float(int((mapped - dist) * 100 / mapped)) if (mapped - dist) * 100 >= 0 else float(-(-(mapped - dist) * 100 // mapped))
+    s1_start = sum(1 for k in range(start) if row1[k] != '-')          # toSourcePosition(row1, start)
+    s1_end = sum(1 for k in range(end) if row1[k] != '-')
+    included = s1_start > 3 or (len(s1) - s1_end) > 3
+    flag = 1 if identity >= 87.5 else 0
+    if included and flag == 1:
+        flag = 2
+    return flag
+
+
+COMPAT_REF_SO = os.path.join(ORACLE_DIR, '_ref', 'compatibility_ref.so')
+_compat_ref = None
+
+
+def reference_compat(seq1, seq2):
+    """The reference's own check_compatibility, compiled from its source into oracle/_ref (oracle/Makefile)."""
+    global _compat_ref
+    if _compat_ref is None:
+        _compat_ref = ctypes.CDLL(COMPAT_REF_SO)
+        _compat_ref.check_compatibility.argtypes = [ctypes.c_char_p, ctypes.c_char_p]
+        _compat_ref.check_compatibility.restype = ctypes.c_int
+    return int(_compat_ref.check_compatibility(_b(seq1), _b(seq2)))
