@@ -1,5 +1,5 @@
 /*
- * pcb_fast.cu -- the fast sm_100a kernels of the adapter-alignment hot path (affine schemes, ACGT adapters of <= 52 bases).
+ * pcb_fast.cu -- the fast sm_100a kernels of the adapter-alignment hot path (affine schemes, ACGT adapters of <= 72 bases).
  *
  * Same result contract as pcb_kernels.cu (reference: porechop_abi/src/adapter_align.cpp:11-31 = SeqAn 2.4.0 globalAlignment
  * with all four end gaps free, Gotoh recursion seqan/align/dp_formula_affine.h:65-124, single trace, then
@@ -28,7 +28,8 @@
  *      re-based every 1024 columns.
  *   4. no copies, no waits.  The column body is straight-line code over NR rows (template parameter: 24 = the length of
  *      almost every Porechop adapter and barcode, exact; 24 / 32 / 40 / 52 = any shorter-or-equal adapter, bottom-aligned,
- *      the rows above the adapter being exact copies of DP row 0), so ptxas updates the DP registers in place; read bases
+ *      72 for the 63- and 68-base native full-sequence barcode sets -- the rows above the adapter being exact copies of DP
+ *      row 0), so ptxas updates the DP registers in place; read bases
  *      are fetched four columns at a time, one group ahead of their use, so that no column waits on a global load.
  *
  * One thread = two tasks (the halves of each 32-bit register), one warp = 64 tasks sharing an adapter, as in pcb_kernels.cu.
@@ -264,7 +265,7 @@ __device__ __forceinline__ uint64_t ckw_of(int mmax, int C, int NR) { return (ui
 // walked strided.
 // dynamic smem: [W][NR*25] score tables, [W][NR] adapter codes, then 2*NR words per thread (strided by PCB_BLOCK) for the
 //               final-column dump.
-// Entry of a task (two words): x = end row | end column << 6 | start state << 18 | 1 << 31 (0: no entry, the failed record
+// Entry of a task (two words): x = end row | end column << 7 | start state << 17 | 1 << 31 (0: no entry, the failed record
 // is already written), y = raw score + OFF.  Start state 4 = "decide from V == M / H == M of the end cell".
 // ------------------------------------------------------------------------------------------------
 template <int MODE, int NR, bool EXACT, int C>
@@ -484,7 +485,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(MODE, NR)) k_fast(const Pc
             int pci, pcj, pst;
             if (fc) { pci = ord - t.len; pcj = t.len; const int e = h ? finE1 : finE0; pst = (e & 2) ? 1 : ((e & 1) ? 2 : 0); }
             else    { pci = n; pcj = ord; pst = 4; }      // 4: the end cell's V == M / H == M still decide the start state
-            ex[h] = (uint32_t)pci | ((uint32_t)pcj << 6) | ((uint32_t)pst << 18) | 0x80000000u;
+            ex[h] = (uint32_t)pci | ((uint32_t)pcj << 7) | ((uint32_t)pst << 17) | 0x80000000u;
             ey[h] = (uint32_t)sc;
         }
         *entp = make_uint4(ex[0], ey[0], ex[1], ey[1]);
@@ -528,11 +529,11 @@ __device__ __forceinline__ int32_t major_of(const PcbLaunch &L, int64_t u /* uni
 // 17 + (rows - 1) / 4 for paths that end in the read's final column (fewer rows, all of one width)
 __device__ __forceinline__ int bucket0(uint32_t x, int C)
 {
-    const int ci = (int)(x & 63u), cj = (int)((x >> 6) & 0xFFFu), st = (int)((x >> 18) & 7u);
+    const int ci = (int)(x & 127u), cj = (int)((x >> 7) & 0x3FFu), st = (int)((x >> 17) & 7u);
     if (ci == 0 || cj == 0) return 0;
-    return st == 4 ? cj - ((cj - 1) / C) * C : 17 + ((ci - 1) >> 2);
+    return st == 4 ? cj - ((cj - 1) / C) * C : min(NB - 1, 17 + ((ci - 1) >> 2));
 }
-__device__ __forceinline__ int bucket1(uint32_t pos) { return (int)(((pos & 63u) - 1u) >> 2); }
+__device__ __forceinline__ int bucket1(uint32_t pos) { return (int)(((pos & 127u) - 1u) >> 2); }
 
 // one thread per (unit, lane): counts the first blocks per (major, bucket)
 __global__ void k_count0(const PcbLaunch L, int C)
@@ -626,7 +627,7 @@ __global__ void k_scatter0(const PcbLaunch L, int C)
             const int64_t unit = L.unit0 + (idx >> 5);
             const uint64_t off = L.src.units ? L.src.tasks[L.src.units[unit].task0 + 2 * lane + h].off
                                              : (uint64_t)((unit - (int64_t)a * groups) * 64 + 2 * lane + h) * (uint64_t)L.src.stride;
-            put_item(L.sorted + slot, ((uint32_t)(idx >> 5) << 6) | (uint32_t)(2 * lane + h), x & 0x1FFFFFu, (x & 0x3FFFFu) | (y << 18), 0u, 0u, 0u, off);
+            put_item(L.sorted + slot, ((uint32_t)(idx >> 5) << 6) | (uint32_t)(2 * lane + h), x & 0xFFFFFu, (x & 0x1FFFFu) | (y << 17), 0u, 0u, 0u, off);
         }
     }
 }
@@ -654,12 +655,12 @@ __global__ void k_scatter1(const PcbLaunch L)
 struct Walk { int i, j, s; WalkAcc acc; };
 __device__ __forceinline__ void walk_unpack(Walk &w, uint32_t pos, uint32_t a0, uint32_t a1, uint32_t a2)
 {
-    w.i = (int)(pos & 63u); w.j = (int)((pos >> 6) & 0xFFFu); w.s = (int)((pos >> 18) & 7u); w.acc.op = (int)(pos >> 21);
+    w.i = (int)(pos & 127u); w.j = (int)((pos >> 7) & 0x3FFu); w.s = (int)((pos >> 17) & 7u); w.acc.op = (int)(pos >> 20);
     w.acc.kAR = a0; w.acc.tHV = a1; w.acc.nHV = a2;
 }
 __device__ __forceinline__ uint32_t walk_pos(const Walk &w)
 {
-    return (uint32_t)w.i | ((uint32_t)w.j << 6) | ((uint32_t)w.s << 18) | ((uint32_t)w.acc.op << 21);
+    return (uint32_t)w.i | ((uint32_t)w.j << 7) | ((uint32_t)w.s << 17) | ((uint32_t)w.acc.op << 20);
 }
 // One op of the reverse walk; flag word layout as col_flags writes it.  ar = register row of the walk's adapter row, jc = its
 // column inside the flag block, pos2 = (2 * column + 1) | (2 * row + 1) << 16.  In state M a cell whose diagonal flag is off
@@ -863,7 +864,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
                     const PcbTask &k = L.src.tasks[L.src.units[L.unit0 + (int64_t)(ref[h] >> 6)].task0 + (int64_t)(ref[h] & 63u)];
                     col0 = k.col0; mtrue = k.m_true; oidx = k.out_idx;
                 }
-                const int endi = (int)(endc[h] & 63u), endj = (int)((endc[h] >> 6) & 0xFFFu), score = (int)(endc[h] >> 18) - OFF;
+                const int endi = (int)(endc[h] & 127u), endj = (int)((endc[h] >> 7) & 0x3FFu), score = (int)(endc[h] >> 17) - OFF;
                 if (w.j == 0 && w.i > 0 && col0 > 0) atomicOr(L.err_flag, 1);      // window too narrow for this path
                 // the path as align_stats.h wants it.  Matches are not counted on the way: the path's ops and the end
                 // cell's score determine them (every D op scores match or mismatch, every gap of g ops go + (g-1) ge)
@@ -976,7 +977,8 @@ static int occ_one()
     case 1:  { constexpr int NR = 24; constexpr bool EX = false; constexpr int C = PCF_C_SMALL; __VA_ARGS__; } break; \
     case 2:  { constexpr int NR = 32; constexpr bool EX = false; constexpr int C = PCF_C_SMALL; __VA_ARGS__; } break; \
     case 3:  { constexpr int NR = 40; constexpr bool EX = false; constexpr int C = PCF_C_LARGE; __VA_ARGS__; } break; \
-    default: { constexpr int NR = 52; constexpr bool EX = false; constexpr int C = PCF_C_LARGE; __VA_ARGS__; } break; \
+    case 4:  { constexpr int NR = 52; constexpr bool EX = false; constexpr int C = PCF_C_LARGE; __VA_ARGS__; } break; \
+    default: { constexpr int NR = 72; constexpr bool EX = false; constexpr int C = PCF_C_LARGE; __VA_ARGS__; } break; \
     }
 
 cudaError_t pcf_launch_scan(const PcbLaunch &L, int cls, cudaStream_t st)

@@ -17,14 +17,19 @@
 #define PCB_NEG_INF     (-8192)   /* "minus infinity" in a signed 16-bit lane                     */
 #define PCB_MAX_TRACE_M 8000      /* widest segment the trace kernel takes (order key is 14 bit)  */
 
-/* fast kernels (pcb_fast.cu): affine schemes, adapters of <= 52 bases.  An adapter's kernel class picks the number of
+/* fast kernels (pcb_fast.cu): affine schemes, adapters of <= 72 bases.  An adapter's kernel class picks the number of
  * adapter rows the kernel holds in registers (NR) and the checkpoint distance / flag-block width of the two-pass trace (C):
  *   class 0: exactly 24 bases (almost every Porechop adapter and barcode)   NR 24, exact
  *   class 1: 1..23 bases      NR 24      class 2: 25..32 bases   NR 32
  *   class 3: 33..40 bases     NR 40      class 4: 41..52 bases   NR 52
+ *   class 5: 53..72 bases     NR 72   (the native "full sequence" barcode sets, adapters.py:466-476: 68 and 63 bases)
  *   class PCF_NCLS: everything else -> general kernels (pcb_kernels.cu) */
-#define PCF_NCLS          5
-#define PCF_MAX_N         52
+#define PCF_NCLS          6
+#define PCF_MAX_N         72
+/* a traceback's position word: row | column << 7 | state << 17 | gap openings << 20; its end cell: row | column << 7 |
+ * (raw score + 2048) << 17 */
+#define PCF_ROW_BITS      7
+#define PCF_COL_BITS      10
 #define PCF_MAX_TRACE_M   1000    /* widest segment of the two-pass trace kernel (no bias re-basing) */
 #define PCF_MAX_SCAN_M    12000   /* widest scan chunk (order key is 14 bit)                      */
 #ifndef PCF_C_SMALL
@@ -33,12 +38,12 @@
 #ifndef PCF_C_LARGE
 #define PCF_C_LARGE       8       /* C for NR > 32  */
 #endif
-static inline int pcf_class_nr(int cls) { return cls <= 1 ? 24 : (cls == 2 ? 32 : (cls == 3 ? 40 : 52)); }
+static inline int pcf_class_nr(int cls) { return cls <= 1 ? 24 : (cls == 2 ? 32 : (cls == 3 ? 40 : (cls == 4 ? 52 : 72))); }
 static inline int pcf_class_c(int cls) { return pcf_class_nr(cls) <= 32 ? PCF_C_SMALL : PCF_C_LARGE; }
 static inline int pcf_class_of_len(long len)
 {
     if (len < 1 || len > PCF_MAX_N) return PCF_NCLS;
-    return len == 24 ? 0 : (len < 24 ? 1 : (len <= 32 ? 2 : (len <= 40 ? 3 : 4)));
+    return len == 24 ? 0 : (len < 24 ? 1 : (len <= 32 ? 2 : (len <= 40 ? 3 : (len <= 52 ? 4 : 5))));
 }
 
 /* One alignment task as the kernels see it. 32 bytes. */
@@ -90,9 +95,9 @@ struct PcbAdapters {
 /* Work item of pass 2 of the fast trace (pcb_fast.cu): one traceback in progress.  32 bytes = one sector. */
 struct PcfItem {
     uint32_t ref;        /* (unit - unit0) << 6 | task slot in the unit                                   */
-    uint32_t pos;        /* where the walk stands: row | column << 6 | state << 18 (state 4: still to be   */
-                         /* decided from V == M / H == M of the end cell)                                  */
-    uint32_t endc;       /* end cell: row | column << 6 | (raw score + 2048) << 18                         */
+    uint32_t pos;        /* where the walk stands: row | column << 7 | state << 17 | gap openings << 20   */
+                         /* (state 4: still to be decided from V == M / H == M of the end cell)            */
+    uint32_t endc;       /* end cell: row | column << 7 | (raw score + 2048) << 17                         */
     uint32_t a0, a1, a2; /* the walk's accumulators, see trace_finish                                      */
     uint32_t pad0, pad1;
 };
