@@ -586,7 +586,7 @@ def run_gpu_arm(args):
                        'scan_phase_frac': scan and scan['cells'] / (scan['ms'] / 1000.0) / 1e9 / int_peak, 'sm_mhz': sm_mhz},
         }
         if world == 1 and not args.no_phase_e2e and args.workload == 'ont':
-            line['phase_e2e'] = phase_e2e(eng, wl)
+            line['phase_e2e'] = phase_e2e(eng, wl, blob)
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             kind, fn, free = cpu_library()
@@ -632,14 +632,14 @@ def profile_traffic():
         return {}
 
 
-def phase_e2e(eng, wl, n_reads=32768):
+def phase_e2e(eng, wl, pinned_blob, n_reads=65536):
     """reads/s through the reference-facing phase functions (porechop_batch.find_*) on reference-shaped read objects built
     from a ReadBlob: what a maintainer who swaps the three loops gets, Python included."""
     from custom_porechop_abi_b200 import porechop_batch as pb
     from custom_porechop_abi_b200.read_blob import ReadBlob
     n = min(n_reads, wl['n_reads'])
     t_make = time.perf_counter()
-    rb = ReadBlob.from_buffer(wl['blob'][:wl['off'][n]], wl['off'][:n + 1])
+    rb = ReadBlob.from_buffer(pinned_blob[:wl['off'][n]], wl['off'][:n + 1])      # the reads as loaded: one (pinned) buffer + offsets
     reads = rb.make_reads()
     from custom_porechop_abi_b200 import synthetic
     sets = synthetic.adapter_sets(wl['adapters'], wl['start_ids'], wl['end_ids'])

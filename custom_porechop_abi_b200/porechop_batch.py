@@ -244,8 +244,8 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
             full = _ratio_percent(h['matches'], h['full_len'])
             ok = partial > end_threshold                   # the device keeps a tie at six decimals; the parsed value decides
             ii, kk = h['window'][ok], h['id_pos'][ok]
-            fulls, parts = full[ok].tolist(), partial[ok].tolist()
-            starts_, ends_ = h['read_start'][ok].tolist(), (h['read_end'][ok] + 1).tolist()
+            fulls, parts = full[ok], partial[ok]
+            starts_, ends_ = h['read_start'][ok], h['read_end'][ok] + 1
             if check_barcodes and want.any():
                 m, length = res.identities()
                 scores = _ratio_percent(m, length)         # [reads, wanted sets]
@@ -257,11 +257,17 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
                 edge_ok = (r_start != 0) if at_end else (r_end != end_size)
                 hit = (partial > end_threshold) & edge_ok & (r_end - r_start >= min_trim_size)
             ii, kk = np.nonzero(hit)                       # row-major: per read, in adapter order, as the reference appends
-            fulls, parts = full[ii, kk].tolist(), partial[ii, kk].tolist()
-            starts_, ends_ = r_start[ii, kk].tolist(), r_end[ii, kk].tolist()
+            fulls, parts = full[ii, kk], partial[ii, kk]
+            starts_, ends_ = r_start[ii, kk], r_end[ii, kk]
             if check_barcodes and want.any():
                 scores = full[:, np.flatnonzero(want)]
-        for i, k, f, pa, rs_, re_ in zip(ii.tolist(), kk.tolist(), fulls, parts, starts_, ends_):
+        if read_blob is not None and read_blob.owns(reads):
+            # the reads are views of the blob: trims and alignment lists for all of them at once
+            read_blob.apply_end_hits(at_end, sets, np.asarray(ii), np.asarray(kk), np.asarray(fulls), np.asarray(parts),
+                                     np.asarray(starts_, dtype=np.int64), np.asarray(ends_, dtype=np.int64), end_size, extra_trim_size)
+            ii = kk = fulls = parts = starts_ = ends_ = np.zeros(0, dtype=np.int64)
+        for i, k, f, pa, rs_, re_ in zip(ii.tolist(), kk.tolist(), np.asarray(fulls).tolist(), np.asarray(parts).tolist(),
+                                         np.asarray(starts_).tolist(), np.asarray(ends_).tolist()):
             read = reads[i]
             entry = (sets[k], f, pa, rs_, re_)
             if at_end:
@@ -323,9 +329,12 @@ def find_adapters_in_read_middles(reads, matching_sets, verbosity, middle_thresh
         # one submit: every queued read against its remaining adapters
         if first_round and read_blob is not None:           # the file's own bytes are the blob: nothing to join or encode
             blob = read_blob.buf
-            offs, lens = read_blob.trimmed_segments(
-                np.fromiter((r.start_trim_amount for r in reads), dtype=np.int64, count=len(reads)),
-                np.fromiter((r.end_trim_amount for r in reads), dtype=np.int64, count=len(reads)))
+            if read_blob.owns(reads):
+                offs, lens = read_blob.trimmed_segments(read_blob.start_trim, read_blob.end_trim)
+            else:
+                offs, lens = read_blob.trimmed_segments(
+                    np.fromiter((r.start_trim_amount for r in reads), dtype=np.int64, count=len(reads)),
+                    np.fromiter((r.end_trim_amount for r in reads), dtype=np.int64, count=len(reads)))
             first_round = False
         elif first_round:
             bounds = np.array([_trimmed_bounds(r) for r in reads], dtype=np.int64).reshape(len(reads), 2)

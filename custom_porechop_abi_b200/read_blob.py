@@ -54,6 +54,11 @@ class ReadBlob(object):
         self.name_off, self.name_len = name_off, name_len
         self.qual_off, self.qual_len = qual_off, qual_len
         self.file_type = file_type
+        # per-read state of the phases, as arrays: the BlobRead objects of make_reads() read and write these, and the
+        # batched phases update them with numpy instead of touching a Python object per hit
+        self.start_trim = np.zeros(len(self.seq_off), dtype=np.int64)
+        self.end_trim = np.zeros(len(self.seq_off), dtype=np.int64)
+        self.end_hits = {False: None, True: None}      # at_end -> (first hit of every read [n + 1], sets, k, full, partial, start, end)
 
     def __len__(self):
         return len(self.seq_off)
@@ -70,6 +75,32 @@ class ReadBlob(object):
         """The first k reads (views, nothing is copied)."""
         q = (None, None) if self.qual_off is None else (self.qual_off[:k], self.qual_len[:k])
         return ReadBlob(self.buf, self.seq_off[:k], self.seq_len[:k], self.name_off[:k], self.name_len[:k], q[0], q[1], self.file_type)
+
+    def owns(self, reads):
+        """Are these the BlobRead objects of this blob, in order (then their state is this blob's arrays)?"""
+        return len(reads) == len(self) and len(reads) > 0 and getattr(reads[0], '_blob', None) is self and getattr(reads[-1], '_blob', None) is self
+
+    def apply_end_hits(self, at_end, sets, read_idx, set_idx, full, partial, r_start, r_end, end_size, extra_trim_size):
+        """find_start_trim / find_end_trim for all reads at once (nanopore_read.py:187-195, :209-217): the kept alignments
+        (ordered by read, then by set) become the reads' start / end alignment lists, the trim amounts their maxima."""
+        n = len(self)
+        amount = (end_size - r_start) + extra_trim_size if at_end else r_end + extra_trim_size
+        trim = self.end_trim if at_end else self.start_trim
+        if len(read_idx):
+            first = np.flatnonzero(np.r_[True, read_idx[1:] != read_idx[:-1]])
+            reads_hit = read_idx[first]
+            trim[reads_hit] = np.maximum(trim[reads_hit], np.maximum.reduceat(amount.astype(np.int64), first))
+        bounds = np.searchsorted(read_idx, np.arange(n + 1))
+        self.end_hits[at_end] = (bounds, list(sets), set_idx, full, partial, r_start, r_end)
+
+    def alignments(self, i, at_end):
+        """The (adapter set, full score, partial score, read start, read end) tuples of read i, as the reference appends them."""
+        h = self.end_hits[at_end]
+        if h is None:
+            return []
+        bounds, sets, k, full, partial, rs, re = h
+        a, b = int(bounds[i]), int(bounds[i + 1])
+        return [(sets[int(k[t])], float(full[t]), float(partial[t]), int(rs[t]), int(re[t])) for t in range(a, b)]
 
     def make_reads(self):
         """One BlobRead per record: what the phase functions need of the reference's NanoporeRead, the sequence on demand."""
@@ -125,17 +156,14 @@ class ReadBlob(object):
 class BlobRead(object):
     """A read of a ReadBlob with the attributes of the reference's NanoporeRead that the three phases touch
     (nanopore_read.py:32-75).  The sequence string is only built when someone asks for it (a read with a middle hit)."""
-    __slots__ = ('_blob', '_i', '_seq', 'start_trim_amount', 'end_trim_amount', 'start_adapter_alignments', 'end_adapter_alignments',
+    __slots__ = ('_blob', '_i', '_seq', '_start_al', '_end_al',
                  'middle_adapter_positions', 'middle_trim_positions', 'middle_hit_str', 'start_barcode_scores', 'end_barcode_scores',
                  'barcode_call', 'albacore_barcode_call', 'best_start_barcode', 'second_best_start_barcode', 'best_end_barcode',
                  'second_best_end_barcode')
 
     def __init__(self, blob, i):
         self._blob, self._i, self._seq = blob, i, None
-        self.start_trim_amount = 0
-        self.end_trim_amount = 0
-        self.start_adapter_alignments = []
-        self.end_adapter_alignments = []
+        self._start_al = self._end_al = None
         self.middle_adapter_positions = set()
         self.middle_trim_positions = set()
         self.middle_hit_str = ''
@@ -151,6 +179,35 @@ class BlobRead(object):
     @property
     def name(self):
         return self._blob.name(self._i) if self._blob.name_len[self._i] else 'r%d' % self._i
+
+    # trims live in the blob's arrays; the alignment lists are built from the blob's hit arrays when someone looks at them
+    @property
+    def start_trim_amount(self):
+        return int(self._blob.start_trim[self._i])
+
+    @start_trim_amount.setter
+    def start_trim_amount(self, v):
+        self._blob.start_trim[self._i] = v
+
+    @property
+    def end_trim_amount(self):
+        return int(self._blob.end_trim[self._i])
+
+    @end_trim_amount.setter
+    def end_trim_amount(self, v):
+        self._blob.end_trim[self._i] = v
+
+    @property
+    def start_adapter_alignments(self):
+        if self._start_al is None:
+            self._start_al = self._blob.alignments(self._i, False)
+        return self._start_al
+
+    @property
+    def end_adapter_alignments(self):
+        if self._end_al is None:
+            self._end_al = self._blob.alignments(self._i, True)
+        return self._end_al
 
     @property
     def seq(self):

@@ -60,14 +60,34 @@ def ncu_csv(rep, page, extra=()):
 
 
 def kernel(tag):
-    rep = os.path.join(OUT, 'prof_%s.ncu-rep' % tag)
-    if not os.path.isfile(rep):
+    """every gpurun_out/prof_<tag>*.ncu-rep (pass 1, the two rounds launches, the scan ...) in one summary"""
+    import glob
+    reps = sorted(glob.glob(os.path.join(OUT, 'prof_%s*.ncu-rep' % tag)))
+    if not reps:
         return None
-    text = kernel_one(rep, tag)
-    rep2 = os.path.join(OUT, 'prof_%s_scan.ncu-rep' % tag)
-    if os.path.isfile(rep2):
-        text += '\n' + kernel_one(rep2, tag + ' (scan)')
-    return text
+    return '\n'.join(kernel_one(r, os.path.basename(r)[5:-8]) for r in reps)
+
+
+def traffic(tag, pairs, what):
+    """profiles/traffic_<tag>.json: DRAM bytes (read + write) of the captured trace kernels (pass 1 + both rounds launches) and
+    the (window, adapter) pairs they processed; bench.py scales it to its own launch."""
+    import glob
+    import json
+    total = 0.0
+    found = []
+    for rep in sorted(glob.glob(os.path.join(OUT, 'prof_%s_p*.ncu-rep' % tag))):
+        raw = ncu_csv(rep, 'raw')
+        h, units, data = raw[0], raw[1], raw[2:]
+        for r in data:
+            for key in ('dram__bytes_read.sum', 'dram__bytes_write.sum'):
+                v, u = float(r[h.index(key)]), units[h.index(key)]
+                total += v * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[u]
+            found.append(r[h.index('Kernel Name')])
+    if not found:
+        return
+    with open(os.path.join(PROF, 'traffic_%s.json' % tag), 'w') as f:
+        json.dump({'dram_bytes': total, 'pairs': pairs, 'kernels': found, 'what': what}, f, indent=1)
+    print('wrote profiles/traffic_%s.json (%.1f B per pair)' % (tag, total / pairs))
 
 
 def kernel_one(rep, tag):
@@ -112,6 +132,8 @@ def main():
             with open(os.path.join(PROF, '%s_%s.md' % (name, tag)), 'w') as f:
                 f.write(text)
             print('wrote profiles/%s_%s.md' % (name, tag))
+    if len(sys.argv) > 3:
+        traffic(tag, int(sys.argv[2]), sys.argv[3])
 
 
 if __name__ == '__main__':

@@ -283,6 +283,38 @@ def test_phase_logic_with_read_blob(idx, tmp_path):
     run_case(c, OracleEngine(), read_blob=load_read_blob(path))
 
 
+@pytest.mark.parametrize('idx', [0, 3, 5, 9])
+def test_phase_logic_with_blob_reads(idx, tmp_path):
+    """The reads as BlobRead objects of the ReadBlob itself: trims live in the blob's arrays, alignment lists are built on
+    demand from its hit arrays (read_blob.apply_end_hits); same state as the reference's objects end up with."""
+    from custom_porechop_abi_b200 import porechop_batch as pb
+    from custom_porechop_abi_b200.read_blob import load_read_blob
+    c = cases()[idx]
+    p = c['params']
+    path = str(tmp_path / 'reads.fastq')
+    _write_fastq(path, c['reads'])
+    blob = load_read_blob(path)
+    reads = blob.make_reads()
+    for r, alb in zip(reads, c.get('albacore', [None] * len(reads))):
+        r.albacore_barcode_call = alb
+    used = [AdapterSet(d) for d in c['matching_used']]
+    eng = ReducedOracleEngine()
+    pb.find_adapters_at_read_ends(reads, used, 0, p['end_size'], p['extra_end_trim'], p['end_threshold'], p['scoring'], None,
+                                  p['min_trim_size'], 1, c['check_barcodes'], p['barcode_threshold'], p['barcode_diff'],
+                                  c['require_two_barcodes'], c['forward_or_reverse'], engine=eng, read_blob=blob)
+    for r, g in zip(reads, c['phase_b']):
+        assert r.start_trim_amount == g['start_trim_amount'] and r.end_trim_amount == g['end_trim_amount'], r.name
+        assert [[a.name, f, pa, s, e] for a, f, pa, s, e in r.start_adapter_alignments] == g['start_alignments'], r.name
+        assert [[a.name, f, pa, s, e] for a, f, pa, s, e in r.end_adapter_alignments] == g['end_alignments'], r.name
+        if c['check_barcodes']:
+            assert r.barcode_call == g['barcode_call'], r.name
+    pb.find_adapters_in_read_middles(reads, used, 0, p['middle_threshold'], p['good_side'], p['bad_side'], p['scoring'], None, 1,
+                                     False, engine=eng, read_blob=blob)
+    for r, g in zip(reads, c['phase_c']):
+        assert sorted(r.middle_adapter_positions) == g['middle_adapter_positions'] and r.middle_hit_str == g['middle_hit_str'], r.name
+        assert r.adapters_found() == g['adapters_found'], r.name
+
+
 @pytest.mark.gpu
 def test_phases_on_gpu(engine, tmp_path):
     from custom_porechop_abi_b200.read_blob import load_read_blob
