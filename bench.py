@@ -548,7 +548,7 @@ def run_gpu_arm(args):
         strict_peak = 148 * 4 * 64 / (3.0 * clk_dpx) * sm_mhz * 1e6 / 1e9
         traffic = profile_traffic()
         dom = kern if kern is not None else scan
-        dom_name = ('k_fast<pass 1,24,EXACT> + k_rounds<24,EXACT> (+ sort kernels): end windows x %d 24-base end sequences, %d launches'
+        dom_name = ('k_fast<pass 1,24,EXACT> + k_rounds<24,EXACT> (+ sort kernels): end windows x %d 24-base end sequences, %d launches dealt to the library\'s 4 streams'
                     % (kern['n_ids'], kern['launches'])) if kern is not None else 'k_fast<scan,24> + planner / merge / window traces (full-length search)'
         line = {
             'metric': METRIC, 'value': n_job / (ms_step / 1000.0), 'unit': 'reads/s', 'n_gpus': world,

@@ -48,6 +48,10 @@ struct pcb_context {
     cudaStream_t ustream = nullptr;       // read-blob uploads (H2D + encode) that run beside them
     int64_t uploaded_len = -1;            // pcb_upload_reads announced a blob of this length
     cudaStream_t hstream = nullptr;       // hit lists of single slots (pcb_wait_slot), beside everything else
+    enum { N_SIDE = 3 };
+    cudaStream_t sstream[N_SIDE] = {};    // cross product: the parts of a call run as independent pipelines side by side (run_windows)
+    cudaEvent_t ev_fork = nullptr, ev_join[N_SIDE] = {};
+    int n_pipes = 4;                      // pipelines a cross product is dealt to (main stream + side streams; PCB_STREAMS)
     cudaStream_t pstream = nullptr;       // deferred mode: task staging + planning, beside the kernels of earlier calls
     cudaEvent_t tasks_done = nullptr;     // the task kernels of the last run no longer read the plan / segment arrays
     bool deferred = false;                // pcb_set_deferred: host-buffer calls only enqueue; pcb_wait collects
@@ -133,6 +137,8 @@ struct pcb_context {
     // outputs / scratch
     DevBuf<uint32_t> d_scratch;
     DevBuf<int32_t> d_meta;               // fast trace, pass 2: bucket counts and chunk table (pcf_meta_words)
+    DevBuf<uint32_t> d_scratch_s[N_SIDE]; // the same two for the side streams
+    DevBuf<int32_t> d_meta_s[N_SIDE];
     DevBuf<int32_t> d_err;
     int grid_trace = 0, grid_scan = 0, grid_fp1[PCF_NCLS] = {}, grid_fp2[PCF_NCLS] = {}, grid_fscan[PCF_NCLS] = {};   // fast kernels: pass 1, rounds, scan
     uint64_t scratch_budget = 6144ull << 18;   // words of checkpoint scratch a batch of the fast trace may use (PCB_SCRATCH_MB)
@@ -195,6 +201,7 @@ extern "C" int pcb_create(int device, pcb_context **out)
         (e = cudaStreamCreateWithFlags(&c->ustream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaStreamCreateWithPriority(&c->pstream, cudaStreamNonBlocking, -1)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&c->hstream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&c->tasks_done, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
         (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
@@ -203,6 +210,11 @@ extern "C" int pcb_create(int device, pcb_context **out)
         return PCB_ERR_CUDA;
     }
     for (auto &ev : c->pipe_ev) if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { g_global_err = "event creation failed"; delete c; return PCB_ERR_CUDA; }
+    for (int k = 0; k < pcb_context::N_SIDE; ++k)
+        if (cudaStreamCreateWithFlags(&c->sstream[k], cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming) != cudaSuccess) {
+            g_global_err = "stream creation failed"; delete c; return PCB_ERR_CUDA;
+        }
+    if (const char *ns = getenv("PCB_STREAMS")) c->n_pipes = std::max(1, std::min(1 + (int)pcb_context::N_SIDE, atoi(ns)));
     for (auto &sl : c->slots) if (cudaEventCreateWithFlags(&sl.staged, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming) != cudaSuccess) { g_global_err = "event creation failed"; delete c; return PCB_ERR_CUDA; }
     c->grid_trace = pcb_occupancy_grid(0);
     c->grid_scan = pcb_occupancy_grid(1);
@@ -240,12 +252,18 @@ extern "C" void pcb_destroy(pcb_context *c)
     for (auto &pl : c->plans) { pl.release(); if (pl.ready) cudaEventDestroy(pl.ready); }
     c->d_seg_off.release(); c->d_plan_i64.release(); c->d_seg_len.release(); c->d_seg_ad.release(); c->d_plan_i32.release(); c->d_adinfo.release();
     c->d_scratch.release(); c->d_meta.release(); c->d_err.release();
+    for (int k = 0; k < pcb_context::N_SIDE; ++k) { c->d_scratch_s[k].release(); c->d_meta_s[k].release(); }
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->kev0); cudaEventDestroy(c->kev1);
     for (auto &ev : c->pipe_ev) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(c->cstream);
     cudaStreamDestroy(c->ustream);
     cudaStreamDestroy(c->pstream);
     if (c->hstream) cudaStreamDestroy(c->hstream);
+    for (int k = 0; k < pcb_context::N_SIDE; ++k) {
+        if (c->sstream[k]) { cudaStreamSynchronize(c->sstream[k]); cudaStreamDestroy(c->sstream[k]); }
+        if (c->ev_join[k]) cudaEventDestroy(c->ev_join[k]);
+    }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->tasks_done) cudaEventDestroy(c->tasks_done);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -362,10 +380,15 @@ static void fill_launch_common(pcb_context *c, PcbLaunch &L, bool task_arena = f
 // cls: 0 .. PCF_NCLS-1 = fast kernels (pcb_fast.cu), PCF_NCLS = general kernels (pcb_kernels.cu)
 // A fast trace is two kernels per batch of units (pass 1 -> checkpoints + end cells in scratch, then the rounds); a batch is
 // as many units as the scratch budget holds.
-static int launch_dp(pcb_context *c, PcbLaunch &L, bool trace, int64_t cells, int cls = PCF_NCLS)
+static int launch_dp(pcb_context *c, PcbLaunch &L, bool trace, int64_t cells, int cls = PCF_NCLS, int pipe = 0 /* 0: main stream, k: side stream k - 1 */)
 {
     const int64_t n_units = L.src.n_units;
     if (n_units == 0) return PCB_OK;
+    cudaStream_t st = pipe ? c->sstream[pipe - 1] : c->stream;
+    DevBuf<uint32_t> &scr = pipe ? c->d_scratch_s[pipe - 1] : c->d_scratch;
+    DevBuf<int32_t> &meta = pipe ? c->d_meta_s[pipe - 1] : c->d_meta;
+    const bool piped = c->n_pipes > 1 && !c->ktiming && !getenv("PCB_NO_SIDE") && !L.src.units;      // cross products share the budget between their pipelines
+    const uint64_t budget = piped ? c->scratch_budget / (uint64_t)c->n_pipes : c->scratch_budget;
     if (c->ktiming) PCB_CUDA(c, cudaEventRecord(c->kev0, c->stream));
     int launches = 1;
     if (cls < PCF_NCLS && trace) {
@@ -374,13 +397,13 @@ static int launch_dp(pcb_context *c, PcbLaunch &L, bool trace, int64_t cells, in
         //  the CTA slots each: 18.5 ms instead of 15.7 ms for 131072 windows x 108 adapters.)
         const uint64_t per_unit = pcf_unit_words_trace(L.mmax, cls), ck_unit = per_unit - 128 - 1024;
         const int W = PCB_BLOCK / 32;
-        const int64_t per_batch = (int64_t)std::max<uint64_t>(1, std::min<uint64_t>({(uint64_t)n_units, c->scratch_budget / per_unit, 1ull << 24}));
-        cudaError_t e = c->d_scratch.reserve((size_t)(per_unit * (uint64_t)per_batch));
+        const int64_t per_batch = (int64_t)std::max<uint64_t>(1, std::min<uint64_t>({(uint64_t)n_units, budget / per_unit, 1ull << 24}));
+        cudaError_t e = scr.reserve((size_t)(per_unit * (uint64_t)per_batch));
         if (e != cudaSuccess) { cudaGetLastError(); return c->fail(PCB_ERR_NOMEM, "trace scratch of %.1f MB: %s", per_unit * per_batch * 4 / 1e6, cudaGetErrorString(e)); }
         L.n_major = L.src.units ? c->n_adapters : L.src.n_ids;
-        PCB_CUDA(c, c->d_meta.reserve((size_t)pcf_meta_words(L.n_major)));
-        uint32_t *const sp = c->d_scratch.p;
-        L.meta = c->d_meta.p;
+        PCB_CUDA(c, meta.reserve((size_t)pcf_meta_words(L.n_major)));
+        uint32_t *const sp = scr.p;
+        L.meta = meta.p;
         L.scratch = sp;
         L.entries = reinterpret_cast<uint4 *>(sp + ck_unit * (uint64_t)per_batch);
         L.sorted = reinterpret_cast<PcfItem *>(sp + (ck_unit + 128) * (uint64_t)per_batch);
@@ -390,8 +413,8 @@ static int launch_dp(pcb_context *c, PcbLaunch &L, bool trace, int64_t cells, in
             L.unit0 = u0; L.unit1 = std::min(n_units, u0 + per_batch);
             const int64_t ctas = (L.unit1 - L.unit0 + W - 1) / W;
             L.grid = (int)std::min<int64_t>(c->grid_fp1[cls], ctas);
-            PCB_CUDA(c, pcf_launch_pass1(L, cls, c->stream));
-            PCB_CUDA(c, pcf_launch_pass2(L, cls, (int)std::min<int64_t>(c->grid_fp2[cls], ctas), c->stream));
+            PCB_CUDA(c, pcf_launch_pass1(L, cls, st));
+            PCB_CUDA(c, pcf_launch_pass2(L, cls, (int)std::min<int64_t>(c->grid_fp2[cls], ctas), st));
             launches += pcf_trace_launches();
         }
     } else {
@@ -524,11 +547,55 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
         order[n_used++] = cls;
     }
     std::sort(order, order + n_used, [&](int x, int y) { return work[x] < work[y]; });
-    for (int oi = 0; oi < n_used; ++oi) {
-        const int cls = order[oi];
-        const int cnt = S.n_cls[cls];
-        int start = 0;
-        for (int q = 0; q < cls; ++q) start += S.n_cls[q];
+    // Several pipelines.  A fast class's trace is nine launches that wait for each other (pass 1, sort, rounds, sort, rounds),
+    // half of them small: alone they leave SMs idle at every kernel boundary and tail.  So a cross product is dealt to
+    // n_pipes streams (own scratch each): the classes in descending order of work, the biggest cut into n_pipes parts by
+    // adapters when results stay on the device, each job to the least loaded stream.  Measured on B200 (131,072 windows x
+    // the 119 start sequences): 19.3 ms on one stream, 15.6 on two, 15.2 on three or four, 15.3 on eight.  The general
+    // class shares the main stream's scratch and stays there.
+    struct Job { int cls, start, cnt, pipe; bool last; };
+    std::vector<Job> jobs;
+    const int n_pipes = (c->ktiming || getenv("PCB_NO_SIDE")) ? 1 : c->n_pipes;
+    {
+        int64_t load[1 + pcb_context::N_SIDE] = {};
+        auto place = [&](int cls, int start, int cnt, bool main_only, bool last) {
+            int best = 0;
+            if (!main_only) for (int p = 1; p < n_pipes; ++p) if (load[p] < load[best]) best = p;
+            load[best] += (int64_t)cnt * (cls < PCF_NCLS ? pcf_class_nr(cls) : 4 * PCB_RT);
+            jobs.push_back({cls, start, cnt, best, last});
+        };
+        for (int oi = n_used - 1; oi >= 0; --oi) {           // biggest first
+            const int cls = order[oi], cnt = S.n_cls[cls];
+            int start = 0;
+            for (int q = 0; q < cls; ++q) start += S.n_cls[q];
+            const bool biggest = oi == n_used - 1;
+            const int parts = (biggest && n_pipes > 1 && !host_out && cls < PCF_NCLS && !getenv("PCB_NO_SPLIT")) ? std::max(1, std::min(n_pipes, cnt / 8)) : 1;
+            for (int q = 0; q < parts; ++q) {
+                const int a = (int)((int64_t)cnt * q / parts), b = (int)((int64_t)cnt * (q + 1) / parts);
+                place(cls, start + a, b - a, cls == PCF_NCLS || (biggest && host_out), biggest && q == parts - 1 && host_out);
+            }
+        }
+        // side jobs are queued first, the main stream's last (its result copies wait for the side streams)
+        std::stable_sort(jobs.begin(), jobs.end(), [](const Job &x, const Job &y) { return (x.pipe != 0) > (y.pipe != 0) || ((x.pipe != 0) == (y.pipe != 0) && !x.last && y.last); });
+    }
+    bool forked = false, joined = false;
+    for (const Job &job : jobs) forked |= job.pipe != 0;
+    if (forked) {
+        PCB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+        for (int p = 1; p < n_pipes; ++p) PCB_CUDA(c, cudaStreamWaitEvent(c->sstream[p - 1], c->ev_fork, 0));
+    }
+    auto join_side = [&]() -> int {                          // the side jobs are all queued: result copies wait for them too
+        for (int p = 1; p < n_pipes; ++p) {
+            PCB_CUDA(c, cudaEventRecord(c->ev_join[p - 1], c->sstream[p - 1]));
+            PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, c->ev_join[p - 1], 0));
+        }
+        joined = true;
+        return PCB_OK;
+    };
+    bool first_cells = true;
+    for (const Job &job : jobs) {
+        const int cls = job.cls, cnt = job.cnt, start = job.start;
+        if (job.pipe == 0 && forked && !joined && (rc = join_side())) return rc;
         const int32_t *h_list = S.h_split.data() + start;
         const int nmax = max_adapter_len(c, h_list, cnt);
         const int smax = std::max(1, (nmax + PCB_RT - 1) / PCB_RT);
@@ -537,12 +604,13 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
         const int64_t warps = (int64_t)gmax * (PCB_BLOCK / 32);
         int64_t sum_n = 0;                 // algorithmic cell count: sum over windows of len x sum over ids of adapter length
         for (int i = 0; i < cnt; ++i) sum_n += c->ad_off[h_list[i] + 1] - c->ad_off[h_list[i]];
+        (void)first_cells;
         // window ranges of this launch (multiples of 64 windows; each range keeps every warp busy for >= 8 units)
         const int64_t groups_all = (S.n_windows + 63) / 64;
         int64_t n_ranges = 1;
         // deferred mode: the copy of a call's results runs under the next call's kernels anyway, and every extra launch costs a tail
         const int max_ranges = c->deferred ? 2 : 8;
-        if (host_out && oi == n_used - 1) n_ranges = std::max<int64_t>(1, std::min<int64_t>(max_ranges, groups_all * cnt / (8 * warps)));
+        if (host_out && job.last) n_ranges = std::max<int64_t>(1, std::min<int64_t>(max_ranges, groups_all * cnt / (8 * warps)));
         const int64_t groups_per = (groups_all + n_ranges - 1) / n_ranges;
         for (int64_t r = 0; r < n_ranges; ++r) {
             const int64_t w0 = r * groups_per * 64, w1 = std::min<int64_t>(S.n_windows, (r + 1) * groups_per * 64);
@@ -559,8 +627,8 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
             L.src.id_pos = S.d_ids.p + n + start; L.src.n_ids_total = n;
             L.src.n_units = n_units;
             L.ad.max_len = nmax; L.mmax = mmax; L.smax = smax; L.grid = grid;
-            if ((rc = launch_dp(c, L, true, r == 0 ? S.sum_winlen * sum_n : 0, cls))) return rc;
-            if (host_out && oi == n_used - 1) {
+            if ((rc = launch_dp(c, L, true, r == 0 ? S.sum_winlen * sum_n : 0, cls, job.pipe))) return rc;
+            if (host_out && job.last) {
                 cudaEvent_t ev = c->pipe_ev[r % 8];
                 PCB_CUDA(c, cudaEventRecord(ev, c->stream));
                 PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, ev, 0));
@@ -569,6 +637,8 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
             }
         }
     }
+    if (forked && !joined && (rc = join_side())) return rc;
+    if (forked) for (int p = 1; p < n_pipes; ++p) PCB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join[p - 1], 0));      // the whole call is complete when the main stream gets here
     if (host_out) {
         c->cnt.d2h_bytes += (int64_t)sizeof(pcb_result) * n_res;
         if (!c->deferred) PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
