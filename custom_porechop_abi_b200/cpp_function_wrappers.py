@@ -97,6 +97,7 @@ C_LIB.pcb_set_deferred.argtypes = [_P, c_int]
 C_LIB.pcb_wait.argtypes = [_P]
 C_LIB.pcb_wait_slot.argtypes = [_P, c_int]
 C_LIB.pcb_stage_windows.argtypes = [_P, c_void_p, c_int64, c_int32, c_void_p]
+C_LIB.pcb_stage_windows_from_reads.argtypes = [_P, c_void_p, c_void_p, c_int64, c_int32, c_int32]
 C_LIB.pcb_stage_ids.argtypes = [_P, c_void_p, c_int32]
 C_LIB.pcb_run_windows_resident.argtypes = [_P]
 C_LIB.pcb_fetch_results.argtypes = [_P, c_void_p, c_int64]

@@ -96,6 +96,8 @@ struct pcb_context {
         DevBuf<uint16_t> d_ident;
         DevBuf<long long> d_total;
         DevBuf<pcb_top2> d_top2;
+        DevBuf<int64_t> d_roff;           // pcb_stage_windows_from_reads: where the reads are in the blob
+        DevBuf<int32_t> d_rlen;
         DevBuf<uint8_t> d_aux;            // check_compatibility: end-column match of every task
         bool want_aux = false;
         int32_t n_want = 0;
@@ -244,7 +246,7 @@ extern "C" void pcb_destroy(pcb_context *c)
     c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_ascii_t.release(); c->d_arena_t.release();
     for (auto &sl : c->slots) {
         sl.d_arena.release(); sl.d_ascii.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release();
-        sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release(); sl.d_top2.release(); sl.d_aux.release();
+        sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release(); sl.d_top2.release(); sl.d_aux.release(); sl.d_roff.release(); sl.d_rlen.release();
         if (sl.staged) cudaEventDestroy(sl.staged);
         if (sl.done) cudaEventDestroy(sl.done);
     }
@@ -710,11 +712,19 @@ extern "C" int pcb_align_windows(pcb_context *c, const char *windows, int64_t n_
 // ------------------------------------------------------------------------------------------------
 // the cross product, reduced on the device (pcb_reduce.cu)
 // ------------------------------------------------------------------------------------------------
+// windows == NULL: the slot's windows are staged already (pcb_stage_windows / pcb_stage_windows_from_reads)
+static int stage_or_staged(pcb_context *c, const char *windows, int64_t n_windows, int32_t stride, const int32_t *win_len)
+{
+    if (windows || !c) return pcb_stage_windows(c, windows, n_windows, stride, win_len);
+    if (n_windows != c->S().n_windows) return c->fail(PCB_ERR_ARG, "%lld windows asked for, %lld staged in this slot", (long long)n_windows, (long long)c->S().n_windows);
+    return PCB_OK;
+}
+
 extern "C" int pcb_align_windows_best(pcb_context *c, const char *windows, int64_t n_windows, int32_t stride,
                                       const int32_t *win_len, const int32_t *adapter_ids, int32_t n_ids, pcb_best *best)
 {
     int rc;
-    if ((rc = pcb_stage_windows(c, windows, n_windows, stride, win_len))) return rc;
+    if ((rc = stage_or_staged(c, windows, n_windows, stride, win_len))) return rc;
     if ((rc = pcb_stage_ids(c, adapter_ids, n_ids))) return rc;
     if (n_ids > 0 && !best) return PCB_ERR_ARG;
     if ((rc = run_windows(c, nullptr))) return rc;
@@ -736,7 +746,7 @@ extern "C" int pcb_align_windows_hits(pcb_context *c, const char *windows, int64
 {
     int rc;
     if (!c || !filter || !n_hits || hits_cap < 0 || (hits_cap > 0 && !hits)) return PCB_ERR_ARG;
-    if ((rc = pcb_stage_windows(c, windows, n_windows, stride, win_len))) return rc;
+    if ((rc = stage_or_staged(c, windows, n_windows, stride, win_len))) return rc;
     if ((rc = pcb_stage_ids(c, adapter_ids, n_ids))) return rc;
     if ((rc = run_windows(c, nullptr))) return rc;
     pcb_context::Slot &S = c->S();
@@ -958,6 +968,60 @@ extern "C" int pcb_upload_reads(pcb_context *c, const char *seq_blob, int64_t bl
     int rc = setup_blob(c, seq_blob, blob_len, blob_pieces(blob_len), 0, true);
     if (rc) return rc;
     c->uploaded_len = blob_len;
+    return PCB_OK;
+}
+
+// The announced blob, all of it, on the device and encoded (main stream order).
+static int blob_resident(pcb_context *c)
+{
+    int rc = send_pieces(c, c->n_pieces);
+    if (rc) return rc;
+    for (int p = 0; p < c->n_pieces; ++p) {
+        pcb_context::TaskPlan &P = c->plans[p];
+        if (P.has_ready) PCB_CUDA(c, cudaStreamWaitEvent(c->stream, P.ready, 0));
+        if (!P.encoded) {
+            if (P.b1 > P.b0) {
+                PCB_CUDA(c, pcb_launch_encode(c->d_ascii_t.p + P.b0, c->d_arena_t.p + P.b0, (uint64_t)(P.b1 - P.b0), c->stream));
+                c->cnt.kernel_launches++;
+            }
+            P.encoded = true;
+        }
+    }
+    return PCB_OK;
+}
+
+extern "C" int pcb_stage_windows_from_reads(pcb_context *c, const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                                            int32_t end_size, int32_t at_end)
+{
+    if (!c || n_reads < 0 || end_size <= 0 || (n_reads > 0 && (!read_off || !read_len))) return PCB_ERR_ARG;
+    if (c->uploaded_len < 0) return c->fail(PCB_ERR_ARG, "pcb_stage_windows_from_reads needs the read blob (pcb_upload_reads)");
+    cudaSetDevice(c->device);
+    pcb_context::Slot &S = c->S();
+    const int32_t stride = (end_size + 15) / 16 * 16;
+    int mmax = 0; int64_t sumlen = 0;
+    for (int64_t r = 0; r < n_reads; ++r) {
+        if (read_len[r] < 0 || read_off[r] < 0 || read_off[r] + read_len[r] > c->uploaded_len)
+            return c->fail(PCB_ERR_ARG, "read %lld: [%lld, +%d) outside the blob", (long long)r, (long long)read_off[r], read_len[r]);
+        const int wl = std::min(read_len[r], end_size);
+        mmax = std::max(mmax, wl); sumlen += wl;
+    }
+    int rc = blob_resident(c);
+    if (rc) return rc;
+    const uint64_t bytes = (uint64_t)n_reads * stride;
+    PCB_CUDA(c, S.d_arena.reserve((size_t)bytes + 64));
+    PCB_CUDA(c, S.d_winlen.reserve((size_t)n_reads + 1));
+    PCB_CUDA(c, S.d_roff.reserve((size_t)n_reads + 1));
+    PCB_CUDA(c, S.d_rlen.reserve((size_t)n_reads + 1));
+    if (n_reads) {
+        PCB_CUDA(c, cudaMemcpyAsync(S.d_roff.p, read_off, sizeof(int64_t) * n_reads, cudaMemcpyHostToDevice, c->stream));
+        PCB_CUDA(c, cudaMemcpyAsync(S.d_rlen.p, read_len, sizeof(int32_t) * n_reads, cudaMemcpyHostToDevice, c->stream));
+        PCB_CUDA(c, pcb_launch_gather_windows(c->d_arena_t.p, S.d_roff.p, S.d_rlen.p, n_reads, end_size, at_end, stride, S.d_arena.p, S.d_winlen.p, c->stream));
+        c->cnt.kernel_launches++;
+    }
+    PCB_CUDA(c, cudaMemsetAsync(S.d_arena.p + bytes, 0, 64, c->stream));
+    c->cnt.h2d_bytes += 12 * n_reads;
+    S.arena_len = bytes; S.n_windows = n_reads; S.stride = stride; S.win_mmax = mmax; S.sum_winlen = sumlen;
+    if (!c->deferred) PCB_CUDA(c, cudaStreamSynchronize(c->stream));       // the caller's arrays may go away
     return PCB_OK;
 }
 

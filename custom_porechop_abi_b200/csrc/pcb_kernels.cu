@@ -84,6 +84,26 @@ __global__ void k_encode(const char *__restrict__ ascii, uint8_t *__restrict__ c
     }
 }
 
+// End windows cut out of the read blob on the device (nanopore_read.py:164,170,181,203: seq[:end_size] / seq[-end_size:]):
+// the reads are in the task arena already (pcb_upload_reads), so neither a host-side gather nor a second copy is needed.
+// One thread per (read, 4 bytes of its window record).
+__global__ void k_gather_windows(const uint8_t *__restrict__ arena_t, const int64_t *__restrict__ roff, const int32_t *__restrict__ rlen,
+                                 int64_t n, int end_size, int at_end, int stride, uint8_t *__restrict__ arena, int32_t *__restrict__ win_len)
+{
+    const int groups = stride / 4;
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t w = idx / groups;
+    if (w >= n) return;
+    const int g = (int)(idx - w * groups);
+    const int len = rlen[w], wl = len < end_size ? len : end_size;
+    const uint8_t *src = arena_t + roff[w] + (at_end ? len - wl : 0);
+    uint32_t word = 0;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) { const int i = 4 * g + b; if (i < wl) word |= (uint32_t)src[i] << (8 * b); }
+    reinterpret_cast<uint32_t *>(arena + w * stride)[g] = word;
+    if (g == 0) win_len[w] = wl;
+}
+
 // order key of a tracked cell: larger score wins, then the cell SeqAn's scout visits first
 // (dp_scout.h:167-180: strict '>' in visiting order).  ord = column for last-row cells, len + row for
 // cells of the final column (dp_meta_info.h:205-216).  Two low bits carry V==M and H==M of that cell
@@ -507,6 +527,15 @@ cudaError_t pcb_launch_merge(const PcbLong *longs, int64_t n_long, const int32_t
 {
     if (n_long == 0) return cudaSuccess;
     k_merge_scan<<<(unsigned)((n_long + 127) / 128), 128, 0, st>>>(longs, n_long, keys, wins, err_flag);
+    return cudaGetLastError();
+}
+
+cudaError_t pcb_launch_gather_windows(const uint8_t *arena_t, const int64_t *roff, const int32_t *rlen, int64_t n, int end_size, int at_end,
+                                      int stride, uint8_t *arena, int32_t *win_len, cudaStream_t st)
+{
+    if (n == 0) return cudaSuccess;
+    const int64_t threads = n * (stride / 4);
+    k_gather_windows<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(arena_t, roff, rlen, n, end_size, at_end, stride, arena, win_len);
     return cudaGetLastError();
 }
 

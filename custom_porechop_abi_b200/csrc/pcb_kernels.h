@@ -197,6 +197,8 @@ cudaError_t pcb_launch_hits(const pcb_result *rec, int64_t n_windows, int32_t n_
 cudaError_t pcb_launch_top2(const uint16_t *ident, int64_t n_windows, int32_t n_want, pcb_top2 *out, cudaStream_t st);
 
 cudaError_t pcb_launch_encode(const char *ascii, uint8_t *codes, uint64_t n, cudaStream_t st);
+cudaError_t pcb_launch_gather_windows(const uint8_t *arena_t, const int64_t *roff, const int32_t *rlen, int64_t n, int end_size, int at_end,
+                                      int stride, uint8_t *arena, int32_t *win_len, cudaStream_t st);
 cudaError_t pcb_launch_trace(const PcbLaunch &L, cudaStream_t st);
 cudaError_t pcb_launch_scan(const PcbLaunch &L, cudaStream_t st);
 int pcb_occupancy_grid(int which /*0 trace, 1 scan*/);

@@ -138,16 +138,35 @@ class AlignmentEngine(object):
             self._held.append((win_buf, win_len, out))
         return out
 
+    def _window_args(self, win_buf, win_len):
+        """(buffer, lengths, n, stride) of a window argument; win_buf None = the slot's staged windows (stage_windows_from_reads),
+        win_len then is their number."""
+        if win_buf is None:
+            return None, None, int(win_len), 0
+        win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)
+        return win_buf, np.ascontiguousarray(win_len, dtype=np.int32), win_buf.shape[0], win_buf.shape[1]
+
+    def stage_windows_from_reads(self, read_off, read_len, end_size, at_end):
+        """The end windows of the reads, cut out of the announced blob (upload_reads) on the device into the selected slot
+        (pcb_stage_windows_from_reads).  Then align_windows_best / align_windows_hits(None, n_reads, ...)."""
+        read_off = np.ascontiguousarray(read_off, dtype=np.int64)
+        read_len = np.ascontiguousarray(read_len, dtype=np.int32)
+        self._check(w.C_LIB.pcb_stage_windows_from_reads(self._h, _ptr(read_off), _ptr(read_len), len(read_off), int(end_size),
+                                                         1 if at_end else 0), 'pcb_stage_windows_from_reads')
+        if getattr(self, '_deferred', False):
+            self._held.append((read_off, read_len))
+        self._shapes[self._slot] = (len(read_off), None)
+        return len(read_off)
+
     def align_windows_best(self, win_buf, win_len, adapter_ids):
         """Phase A in one call: per listed adapter the (matches, full_len) of its best full-adapter identity over all windows
         (pcb_align_windows_best).  Returns a BEST_DTYPE array of len(adapter_ids)."""
-        win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)
-        win_len = np.ascontiguousarray(win_len, dtype=np.int32)
+        win_buf, win_len, n, stride = self._window_args(win_buf, win_len)
         ids = np.ascontiguousarray(adapter_ids, dtype=np.int32)
-        n, stride = win_buf.shape
         out = np.zeros(len(ids), dtype=BEST_DTYPE)
-        self._check(w.C_LIB.pcb_align_windows_best(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids),
-                                                   _ptr(out)), 'pcb_align_windows_best')
+        self._check(w.C_LIB.pcb_align_windows_best(self._h, None if win_buf is None else _ptr(win_buf), n, stride,
+                                                   None if win_len is None else _ptr(win_len), _ptr(ids), len(ids), _ptr(out)),
+                    'pcb_align_windows_best')
         if getattr(self, '_deferred', False):
             self._held.append((win_buf, win_len, ids, out))
         return out
@@ -156,10 +175,8 @@ class AlignmentEngine(object):
                            want_ident=None, hits_cap=None, hits_buf=None, ident_buf=None):
         """Phase B in one call (pcb_align_windows_hits): only the pairs find_start_trim / find_end_trim would keep, plus the
         full-adapter identity of every window for the adapters flagged in want_ident.  Returns a WindowHits."""
-        win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)
-        win_len = np.ascontiguousarray(win_len, dtype=np.int32)
+        win_buf, win_len, n, stride = self._window_args(win_buf, win_len)
         ids = np.ascontiguousarray(adapter_ids, dtype=np.int32)
-        n, stride = win_buf.shape
         flt = w.PcbHitFilter(threshold_e6(end_threshold), 1 if at_end else 0, int(end_size), int(min_trim_size), 0)
         want = None if want_ident is None else np.ascontiguousarray(want_ident, dtype=np.uint8)
         n_want = 0 if want is None else int(np.count_nonzero(want))
@@ -170,12 +187,13 @@ class AlignmentEngine(object):
         ident = ident_buf if (ident_buf is not None and keep_ident) else np.zeros((n, n_want if keep_ident else 0), dtype=np.uint16)
         n_hits = ctypes.c_int64(0)
         deferred = getattr(self, '_deferred', False)
-        rc = w.C_LIB.pcb_align_windows_hits(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids), byref(flt),
+        wp, lp = (None if win_buf is None else _ptr(win_buf)), (None if win_len is None else _ptr(win_len))
+        rc = w.C_LIB.pcb_align_windows_hits(self._h, wp, n, stride, lp, _ptr(ids), len(ids), byref(flt),
                                             None if want is None else _ptr(want), _ptr(hits_buf), len(hits_buf), byref(n_hits),
                                             _ptr(ident) if (n_want and keep_ident) else None)
         if rc == 3 and not deferred and n_hits.value > len(hits_buf):      # more hits than room: once more with room for all
             hits_buf = np.empty(int(n_hits.value), dtype=HIT_DTYPE)
-            rc = w.C_LIB.pcb_align_windows_hits(self._h, _ptr(win_buf), n, stride, _ptr(win_len), _ptr(ids), len(ids), byref(flt),
+            rc = w.C_LIB.pcb_align_windows_hits(self._h, wp, n, stride, lp, _ptr(ids), len(ids), byref(flt),
                                                 None if want is None else _ptr(want), _ptr(hits_buf), len(hits_buf), byref(n_hits),
                                                 _ptr(ident) if (n_want and keep_ident) else None)
         self._check(rc, 'pcb_align_windows_hits')
@@ -301,7 +319,6 @@ class AlignmentEngine(object):
             self._check(w.C_LIB.pcb_wait(self._h), 'pcb_wait')
         finally:
             self._held = []
-            self._uploaded = None
 
     def wait_slot(self, slot):
         """Collects one slot's queued align_windows_hits call; everything queued in other slots keeps running."""

@@ -102,6 +102,17 @@ def _collect_after(eng):
     return eng.deferred() if hasattr(eng, 'deferred') else contextlib.nullcontext()
 
 
+def _stage_windows(eng, reads, read_blob, end_size, at_end):
+    """The windows of a phase for the engine: (buffer, lengths) packed on the host, or (None, n) when the engine can cut
+    them out of the read blob on the device (the blob is announced once and serves all three phases)."""
+    if read_blob is not None and hasattr(eng, 'stage_windows_from_reads'):
+        if getattr(eng, '_blob_id', None) != id(read_blob.buf) or getattr(eng, '_uploaded', None) is None:
+            eng.upload_reads(read_blob.buf)
+            eng._blob_id = id(read_blob.buf)
+        return None, eng.stage_windows_from_reads(read_blob.seq_off, read_blob.seq_len, end_size, at_end)
+    return read_blob.windows(end_size, at_end) if read_blob is not None else _windows(reads, end_size, at_end)
+
+
 def _engine(engine, scoring_scheme_vals):
     eng = engine if engine is not None else AlignmentEngine(0)
     eng.set_scoring(scoring_scheme_vals)
@@ -137,9 +148,13 @@ def find_matching_adapter_sets(check_reads, verbosity, end_size, scoring_scheme_
                     continue
                 if hasattr(eng, 'select_slot'):
                     eng.select_slot(slot)
-                buf, lens = read_blob.windows(end_size, at_end) if read_blob is not None else _windows(check_reads, end_size, at_end)
                 ids = np.arange(id0, id0 + len(sets), dtype=np.int32)
-                submitted[at_end] = eng.align_windows_best(buf, lens, ids) if reduced else eng.align_windows(buf, lens, ids)
+                if reduced:
+                    buf, lens = _stage_windows(eng, check_reads, read_blob, end_size, at_end)
+                    submitted[at_end] = eng.align_windows_best(buf, lens, ids)
+                else:
+                    buf, lens = read_blob.windows(end_size, at_end) if read_blob is not None else _windows(check_reads, end_size, at_end)
+                    submitted[at_end] = eng.align_windows(buf, lens, ids)
         if hasattr(eng, 'select_slot'):
             eng.select_slot(0)
         for at_end, sets in ((False, with_start), (True, with_end)):
@@ -220,12 +235,13 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
                 continue
             if hasattr(eng, 'select_slot'):
                 eng.select_slot(slot)
-            buf, lens = read_blob.windows(end_size, at_end) if read_blob is not None else _windows(reads, end_size, at_end)
             ids = np.arange(id0, id0 + len(sets), dtype=np.int32)
             if reduced:                                    # room for every pair when the list is short, else 16 per read (and once more if not)
+                buf, lens = _stage_windows(eng, reads, read_blob, end_size, at_end)
                 submitted[at_end] = eng.align_windows_hits(buf, lens, ids, end_threshold, at_end, end_size, min_trim_size,
                                                            want_ident=wanted(sets), hits_cap=len(reads) * min(len(sets), 16))
             else:
+                buf, lens = read_blob.windows(end_size, at_end) if read_blob is not None else _windows(reads, end_size, at_end)
                 submitted[at_end] = eng.align_windows(buf, lens, ids)
     if hasattr(eng, 'select_slot'):
         eng.select_slot(0)
@@ -236,7 +252,7 @@ def find_adapters_at_read_ends(reads, matching_sets, verbosity, end_size, extra_
         if reduced:
             res = submitted[at_end]
             if res.n_hits > len(res.hits):                 # more hits than the deferred call had room for: once more, alone
-                buf, lens = read_blob.windows(end_size, at_end) if read_blob is not None else _windows(reads, end_size, at_end)
+                buf, lens = _stage_windows(eng, reads, read_blob, end_size, at_end)
                 res = eng.align_windows_hits(buf, lens, np.arange(id0, id0 + len(sets), dtype=np.int32), end_threshold, at_end,
                                              end_size, min_trim_size, want_ident=want, hits_cap=res.n_hits)
             h = res.hits
@@ -357,7 +373,10 @@ def find_adapters_in_read_middles(reads, matching_sets, verbosity, middle_thresh
         np.cumsum(counts, out=first[1:])
         entry = np.repeat(np.arange(len(q_read), dtype=np.int64), counts)    # queue entry of every task
         seg_ad = np.arange(int(first[-1]), dtype=np.int64) - first[entry] + q_k0[entry]
-        rec = eng.align_tasks(blob, offs[entry], lens[entry].astype(np.int32), seg_ad.astype(np.int32))
+        # (the reads may be on the device already: phases A / B announced the same blob for their windows)
+        resident = read_blob is not None and blob is read_blob.buf and getattr(eng, '_blob_id', None) == id(blob) and \
+            getattr(eng, '_uploaded', None) is not None
+        rec = eng.align_tasks(None if resident else blob, offs[entry], lens[entry].astype(np.int32), seg_ad.astype(np.int32))
         _, full = _parsed_identities(rec, aligned=False)
         r_start, r_end = rec['read_start'], _read_ends(rec)
         # first hit of every queued read (tasks are in adapter order per read); NaN compares False, as in the reference

@@ -126,6 +126,14 @@ int pcb_align_windows_hits(pcb_context *ctx, const char *windows, int64_t n_wind
                            const pcb_hit_filter *filter, const uint8_t *want_ident,
                            pcb_hit *hits, int64_t hits_cap, int64_t *n_hits, uint16_t *ident);
 
+/* End windows cut out of the announced read blob ON THE DEVICE: window r = the first (at_end = 0) or last (at_end = 1)
+ * min(end_size, read_len[r]) bases of blob[read_off[r] .. +read_len[r]) (nanopore_read.py:164,170,181,203).  Needs
+ * pcb_upload_reads; stages the selected slot like pcb_stage_windows, after which pcb_align_windows_best / _hits are called
+ * with windows == NULL (n_windows = n_reads) and pcb_run_windows_resident works as usual.  The reads then cross PCIe once
+ * for all three phases, and the host never gathers windows. */
+int pcb_stage_windows_from_reads(pcb_context *ctx, const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                                 int32_t end_size, int32_t at_end);
+
 /* Barcode binning (nanopore_read.py:408-482): determine_barcode sorts a read's barcode scores in descending order
  * (stable: the first in adapter order among equals) and decides on the first two.  After a pcb_align_windows_hits call
  * with want_ident, top2[w] = positions (among the wanted adapters) and identity words of the best and second-best

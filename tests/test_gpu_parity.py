@@ -426,3 +426,36 @@ def test_user_schemes_on_kilobase_segments(engine, scores):
             r = r[:p] + mutate(rng, a, 0.1) + r[p + len(a):]
             pairs.append((r, aid))
     _check_pairs(engine, pairs, ads, scores)
+
+
+def test_windows_cut_from_the_read_blob_on_the_device(engine):
+    """pcb_stage_windows_from_reads: seq[:end_size] / seq[-end_size:] of every read taken out of the announced blob by a
+    kernel give the same records as windows packed on the host (short and empty reads, lower case, a blob in pieces)."""
+    import os
+    from custom_porechop_abi_b200 import synthetic
+    engine.set_scoring(DEFAULT)
+    adapters, s_ids, e_ids = synthetic.adapter_set()
+    lengths = np.r_[np.arange(0, 40), np.full(300, 700), [149, 150, 151, 3000]]
+    blob, off = synthetic.make_reads(len(lengths), adapters, s_ids, e_ids, seed=21, lengths=lengths)
+    blob = blob.copy(); blob[off[50]:off[60]] += 32           # lower case reads
+    sbuf, ebuf, wlen = synthetic.end_windows(blob, off, 150, 160)
+    engine.set_adapters(adapters)
+    ids = np.array(s_ids[:9] + e_ids[:9], dtype=np.int32)
+    for piece_min in (None, '4096'):
+        if piece_min:
+            os.environ['PCB_PIECE_MIN_BYTES'] = piece_min
+        try:
+            for at_end, buf in ((False, sbuf), (True, ebuf)):
+                want = engine.align_windows(buf, wlen, ids)
+                engine.upload_reads(blob)
+                n = engine.stage_windows_from_reads(off[:-1], np.diff(off), 150, at_end)
+                best = engine.align_windows_best(None, n, ids)
+                res = engine.align_windows_hits(None, n, ids, 75.0, at_end, 150, 4, hits_cap=want.size)
+                engine.run_windows_resident()
+                got = engine.fetch((n, len(ids)))
+                assert got.tobytes() == want.tobytes()
+                ref_best = engine.align_windows_best(buf, wlen, ids)
+                ref_hits = engine.align_windows_hits(buf, wlen, ids, 75.0, at_end, 150, 4, hits_cap=want.size)
+                assert np.array_equal(best, ref_best) and np.array_equal(res.hits, ref_hits.hits)
+        finally:
+            os.environ.pop('PCB_PIECE_MIN_BYTES', None)
