@@ -303,7 +303,7 @@ extern "C" int pcb_set_adapters(pcb_context *c, const char *blob, const int64_t 
     c->ad_fast.assign((size_t)n_adapters, 0);
     for (int i = 0; i < n_adapters; ++i) {
         const int64_t len = c->ad_off[i + 1] - c->ad_off[i];
-        bool ok = len >= 1 && len <= PCF_MAX_N;
+        bool ok = len >= 1 && len <= PCF_MAX_N2;
         for (int64_t k = c->ad_off[i]; ok && k < c->ad_off[i + 1]; ++k) ok = strchr("ACGTUacgtu", blob[base + k]) != nullptr && blob[base + k] != 0;
         c->ad_fast[(size_t)i] = (uint8_t)(ok ? pcf_class_of_len((long)len) : PCF_NCLS);
     }
@@ -350,6 +350,19 @@ static bool fast_scheme(const PcbScores &s)
     return s.gap_open < 0 && s.gap_extend < 0 && s.gap_extend > s.gap_open && b <= 7 && s.match > 0 &&
            s.match > s.mismatch && s.mismatch + 2 * b >= 0 && s.match + 2 * b <= 127 &&
            64 + b * (PCF_MAX_N + PCF_MAX_TRACE_M) + PCF_MAX_N * s.match < 8192;
+}
+// ... and the two-stripe class: 144 register rows, one more iteration than columns
+static bool fast_scheme2(const PcbScores &s)
+{
+    return fast_scheme(s) && 64 + (-s.gap_open) * (144 + PCF_MAX_TRACE_M + 1) + PCF_MAX_N2 * s.match < 8192;
+}
+
+// kernel class of adapter a under the context's scheme (PCB_NO_TWO: the two-stripe class goes to the general kernels)
+static int class_of(pcb_context *c, int a, bool fast_ok)
+{
+    int cls = fast_ok ? c->ad_fast[(size_t)a] : PCF_NCLS;
+    if (pcf_class_two(cls) && (!fast_scheme2(c->sc) || getenv("PCB_NO_TWO"))) cls = PCF_NCLS;
+    return cls;
 }
 
 static int ensure_scratch(pcb_context *c, uint64_t words_per_slot, int grid)
@@ -501,7 +514,7 @@ static int split_ids(pcb_context *c, bool fast_ok)
     std::vector<int32_t> id[PCF_NCLS + 1], pos[PCF_NCLS + 1];
     for (int k = 0; k < n; ++k) {
         const int32_t a = S.h_ids[(size_t)k];
-        const int cls = fast_ok ? c->ad_fast[(size_t)a] : PCF_NCLS;
+        const int cls = class_of(c, a, fast_ok);
         id[cls].push_back(a); pos[cls].push_back(k);
     }
     S.h_split.clear();
@@ -545,7 +558,7 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
     int64_t work[PCF_NCLS + 1];
     for (int cls = 0; cls <= PCF_NCLS; ++cls) {
         if (S.n_cls[cls] == 0) continue;
-        work[cls] = (int64_t)S.n_cls[cls] * (cls < PCF_NCLS ? pcf_class_nr(cls) : 4 * PCB_RT);
+        work[cls] = (int64_t)S.n_cls[cls] * (cls < PCF_NCLS ? pcf_class_rows(cls) : 4 * PCB_RT);
         order[n_used++] = cls;
     }
     std::sort(order, order + n_used, [&](int x, int y) { return work[x] < work[y]; });
@@ -563,7 +576,7 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
         auto place = [&](int cls, int start, int cnt, bool main_only, bool last) {
             int best = 0;
             if (!main_only) for (int p = 1; p < n_pipes; ++p) if (load[p] < load[best]) best = p;
-            load[best] += (int64_t)cnt * (cls < PCF_NCLS ? pcf_class_nr(cls) : 4 * PCB_RT);
+            load[best] += (int64_t)cnt * (cls < PCF_NCLS ? pcf_class_rows(cls) : 4 * PCB_RT);
             jobs.push_back({cls, start, cnt, best, last});
         };
         for (int oi = n_used - 1; oi >= 0; --oi) {           // biggest first
@@ -1052,7 +1065,7 @@ static int build_task_plan(pcb_context *c, pcb_context::TaskPlan &P, bool first_
     for (int a = 0; a < A; ++a) {
         PcbAdInfo &x = ad[(size_t)a];
         x.n = (int)(c->ad_off[(size_t)a + 1] - c->ad_off[(size_t)a]);
-        x.cls = fast_sc ? c->ad_fast[(size_t)a] : PCF_NCLS;
+        x.cls = class_of(c, a, fast_sc);
         const WindowBounds wb = window_bounds(c->sc, x.n);
         x.warm = wb.warm; x.span = wb.span; x.chunked = wb.ok ? 1 : 0;
         x.direct_max = std::max(direct_default, wb.ok ? wb.warm + wb.span + 8 : 0);

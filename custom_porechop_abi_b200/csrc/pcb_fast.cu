@@ -527,16 +527,20 @@ __device__ __forceinline__ int32_t major_of(const PcbLaunch &L, int64_t u /* uni
 }
 // bucket of a first block: 0 = no block at all (empty path), 1..C = its width for paths that end in the last adapter row,
 // 17 + (rows - 1) / 4 for paths that end in the read's final column (fewer rows, all of one width)
-__device__ __forceinline__ int bucket0(uint32_t x, int C)
+// (skew = 1 for the two-stripe kernels, whose last adapter row runs one iteration behind its column)
+__device__ __forceinline__ int bucket0(uint32_t x, int C, int skew)
 {
     const int ci = (int)(x & 127u), cj = (int)((x >> 7) & 0x3FFu), st = (int)((x >> 17) & 7u);
     if (ci == 0 || cj == 0) return 0;
-    return st == 4 ? cj - ((cj - 1) / C) * C : min(NB - 1, 17 + ((ci - 1) >> 2));
+    return st == 4 ? cj + skew - ((cj + skew - 1) / C) * C : min(NB - 1, 17 + ((ci - 1) >> 2));
 }
 __device__ __forceinline__ int bucket1(uint32_t pos) { return (int)(((pos & 127u) - 1u) >> 2); }
+// two-stripe kernels: a path is over when it reaches row 0 or column 0, and with > 72 rows the columns often run out first;
+// rounds of equal remaining length finish together
+__device__ __forceinline__ int bucket1_two(uint32_t pos) { return (int)((min(pos & 127u, (pos >> 7) & 0x3FFu) - 1u) >> 2); }
 
 // one thread per (unit, lane): counts the first blocks per (major, bucket)
-__global__ void k_count0(const PcbLaunch L, int C)
+__global__ void k_count0(const PcbLaunch L, int C, int skew)
 {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nu = L.unit1 - L.unit0;
     if ((idx >> 5) >= nu) return;                                     // whole warps leave together
@@ -548,7 +552,7 @@ __global__ void k_count0(const PcbLaunch L, int C)
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const uint32_t x = h ? e.z : e.x;
-        const int key = (x >> 31) ? bucket0(x, C) : -1;
+        const int key = (x >> 31) ? bucket0(x, C, skew) : -1;
         const uint32_t m = __match_any_sync(0xffffffffu, key);
         if (key >= 0 && lane == __ffs(m) - 1) atomicAdd(M.hist0 + (int64_t)a * NB + key, __popc(m));
     }
@@ -607,7 +611,7 @@ __device__ __forceinline__ int64_t sorted_slot(const Meta &M, int key, int lane)
     return key >= 0 ? (int64_t)M.base[key] + first + __popc(m & ((1u << lane) - 1u)) : -1;
 }
 // generation 0: one thread per (unit, lane); the end cells of pass 1 become items, in sorted order
-__global__ void k_scatter0(const PcbLaunch L, int C)
+__global__ void k_scatter0(const PcbLaunch L, int C, int skew)
 {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nu = L.unit1 - L.unit0;
     if ((idx >> 5) >= nu) return;
@@ -619,7 +623,7 @@ __global__ void k_scatter0(const PcbLaunch L, int C)
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const uint32_t x = h ? e.z : e.x, y = h ? e.w : e.y;
-        const int key = (x >> 31) ? a * NB + bucket0(x, C) : -1;
+        const int key = (x >> 31) ? a * NB + bucket0(x, C, skew) : -1;
         const int64_t slot = sorted_slot(M, key, lane);
         PCF_CHECK(L, slot < 64 * nu);
         if (slot >= 0) {
@@ -632,7 +636,7 @@ __global__ void k_scatter0(const PcbLaunch L, int C)
     }
 }
 // generation 1: one thread per surviving item
-__global__ void k_scatter1(const PcbLaunch L)
+__global__ void k_scatter1(const PcbLaunch L, int two)
 {
     const Meta M = meta_of(L);
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, n = M.counters[0];
@@ -643,7 +647,7 @@ __global__ void k_scatter1(const PcbLaunch L)
     int key = -1;
     if (idx < n) {
         ld256(reinterpret_cast<const uint32_t *>(L.surv + idx), v);
-        key = major_of(L, v[0] >> 6, groups) * NB + bucket1(v[1]);
+        key = major_of(L, v[0] >> 6, groups) * NB + (two ? bucket1_two(v[1]) : bucket1(v[1]));
     }
     const int64_t slot = sorted_slot(M, key, lane);
     PCF_CHECK(L, slot < 64 * (L.unit1 - L.unit0) && n <= 64 * (L.unit1 - L.unit0));
@@ -914,14 +918,539 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Two-stripe kernels for adapters of 73..127 bases (the rapid full-sequence barcode sets, adapters.py:479-498: 102 and 111).
+//
+// 144 adapter rows do not fit one thread's registers as two tasks x 72 rows -- but they do as ONE task x two stripes of 72
+// rows: the low halves of the packed registers hold rows 1..72, the high halves rows 73..144, and the high half runs one
+// column BEHIND the low half (iteration t: low half = column t, high half = column t - 1).  What row 73 needs from row 72
+// -- M(72, t-1), M(72, t-2), V(72, t-1) -- are low-half values of the two iterations before, kept in three registers and
+// moved into the high half with a PRMT.  Every DPX instruction still does two cells, the code per row is the one-stripe
+// code, and the substitution table simply holds (score(base[t], adapter[r]), score(base[t-1], adapter[72 + r])).
+// A lane's two tasks of a unit are run one after the other; flag words, checkpoints and the walk use "iteration"
+// t = column + stripe wherever the one-stripe kernels use the column.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t swap16(uint32_t x) { return prmt(x, x, 0x1032u); }
+__device__ __forceinline__ uint32_t lo_hi(uint32_t lo_src, uint32_t hi_src) { return prmt(lo_src, hi_src, 0x7610u); }   // low half of the first, high half of the second
+
+// col_score with the row above the first register row given: Din = M diagonal of that row (biased), Vu0 = V of the first row
+template <int NR>
+__device__ __forceinline__ void col_score2(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *tp,
+                                           uint32_t Din, uint32_t Vu0, uint32_t GEB, uint32_t &Ml, uint32_t &Vl)
+{
+    uint32_t Dn = Din + tp[0];
+    uint32_t Vu = Vu0;
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        const uint32_t Hn = __viaddmax_s16x2(Hl[r], GEB, Mo[r]);
+        if (r > 0) Vu = __viaddmax_s16x2(Vu, GEB, Mo[r - 1]);
+        const uint32_t D = Dn;
+        if (r < NR - 1) Dn = Mo[r] + tp[(r + 1) * TP];
+        Mo[r] = __vimax3_s16x2(D, Vu, Hn); Hl[r] = Hn;
+    }
+    Ml = Mo[NR - 1]; Vl = Vu;
+}
+
+// col_flags with the row above given: Din as above, Mup0 / Vup0 = M and V of the row above the first register row
+template <int NR>
+__device__ __forceinline__ void col_flags2(uint32_t (&Mo)[NR], uint32_t (&Hl)[NR], const uint32_t *tp,
+                                           uint32_t Din, uint32_t Mup0, uint32_t Vup0, uint32_t GEB, uint32_t *fp, const int rlim,
+                                           uint32_t &Ml, uint32_t &Vl, uint32_t &Hlast)
+{
+    constexpr int PF = PCF_PF;
+    uint32_t tv[PF];
+#pragma unroll
+    for (int d = 0; d < PF; ++d) tv[d] = tp[d * TP];
+    uint32_t Dn = Din + tv[0];
+    uint32_t Vu = Vup0, Wacc = 0;
+    const uint32_t GEBG = GEB + GUARD;
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        if ((r & 3) == 0 && r > 0 && r >= rlim) break;
+        const uint32_t D = Dn;
+        if (r + PF < NR) tv[r % PF] = tp[(r + PF) * TP];
+        const uint32_t Mup = (r == 0) ? Mup0 : Mo[(r > 0) ? r - 1 : 0];
+        const uint32_t ch = Hl[r] + GEBG - Mo[r], cv = Vu + GEBG - Mup;
+        const uint32_t Hn = __viaddmax_s16x2(Hl[r], GEB, Mo[r]), Vn = __viaddmax_s16x2(Vu, GEB, Mup);
+        const uint32_t G = __vmaxs2(Vn, Hn);
+        const uint32_t W = (sign4(ch, cv) & 0x55555555u) | (sign4(cmpge(Vn, Hn), cmpge(D, G)) & 0xAAAAAAAAu);
+        if ((r & 3) == 0) Wacc = W;
+        else if ((r & 3) == 1) Wacc = (Wacc & 0x03030303u) | (W & 0xFCFCFCFCu);
+        else if ((r & 3) == 2) Wacc = (Wacc & 0x0F0F0F0Fu) | (W & 0xF0F0F0F0u);
+        else Wacc = (Wacc & 0x3F3F3F3Fu) | (W & 0xC0C0C0C0u);
+        if ((r & 3) == 3 || r == NR - 1) fp[(r >> 2) * PCB_BLOCK] = Wacc;
+        if (r < NR - 1) Dn = Mo[r] + tv[(r + 1) % PF];
+        Vu = Vn; Mo[r] = __vmaxs2(D, G); Hl[r] = Hn;
+    }
+    Ml = Mo[NR - 1]; Vl = Vu; Hlast = Hl[NR - 1];
+}
+
+// checkpoint words per thread and unit of the two-stripe kernels: 2 tasks x checkpoints x (row chunks + 1 chunk of boundary registers)
+__device__ __forceinline__ uint64_t ckw2_of(int mmax, int C, int NR) { return 2ull * (uint64_t)((mmax + 1 + C - 1) / C) * (uint64_t)((NR + 7) / 8 + 1) * 8ull; }
+
+// Score table of the two stripes: tbl[r * 25 + 5 * code(base[t]) + code(base[t-1])] = (score vs adapter row r, score vs row NR + r)
+template <int NR>
+__device__ __forceinline__ void build_table2(const PcbLaunch &L, uint32_t *tbl, uint32_t *s_code, int64_t aoff, int n, int r0, int lane,
+                                             int s_match, int s_mis, int b)
+{
+    __syncwarp();
+    for (int i = lane; i < 2 * NR; i += 32) s_code[i] = i >= r0 ? (uint32_t)(L.ad.codes[aoff + i - r0] / PCB_CODE_SCALE) : 0u;
+    __syncwarp();
+    for (int e = lane; e < NR * TP; e += 32) {
+        const int r = e / TP, p = e - r * TP;
+        const uint32_t a_lo = s_code[r], a_hi = s_code[NR + r], c0 = (uint32_t)(p / 5), c1 = (uint32_t)(p % 5);
+        const int lo = r >= r0 ? (c0 == a_lo ? s_match : s_mis) : 2 * b;        // rows above the adapter: copies of DP row 0
+        tbl[e] = pk(lo, c1 == a_hi ? s_match : s_mis);
+    }
+    __syncwarp();
+}
+
+// k_fast2<MODE, NR, C>: the score-only pass of the two-stripe kernels (MODE 0: scan keys, MODE 1: pass 1 of the trace).
+// Same launch interface, unit / task mapping, entries and scan keys as k_fast.  Checkpoint k = state after iteration
+// k * C: [unit - unit0][task & 1][k - 1][row chunks of 8 | boundary registers][lane][8 words].
+// dynamic smem: [W][NR*25] score tables, [W][2*NR] adapter codes, then 2*NR words per thread for the final-column dump.
+template <int MODE, int NR, int C>
+__global__ void __launch_bounds__(PCB_BLOCK, 2) k_fast2(const PcbLaunch L)
+{
+    constexpr bool TRACE = MODE != 0;
+    constexpr int R2 = 2 * NR, G8 = (NR + 7) / 8;
+    extern __shared__ uint32_t smem[];
+    constexpr int W = PCB_BLOCK / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t *const tbl = smem + warp * (NR * TP);
+    uint32_t *const s_code = smem + W * (NR * TP) + warp * R2;
+    uint32_t *const s_fl = smem + W * (NR * TP + R2) + threadIdx.x;
+    const uint64_t ckw = ckw2_of(L.mmax, C, NR);
+
+    const int b = -L.sc.gap_open;
+    const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b);
+    const int s_match = L.sc.match + 2 * b, s_mis = L.sc.mismatch + 2 * b;
+    const int geb = L.sc.gap_extend + b;
+
+    const int64_t nwarps = (int64_t)gridDim.x * W, gw = (int64_t)blockIdx.x * W + warp;
+    const bool cross = L.src.units == nullptr;
+    const int64_t groups = cross ? (L.src.n_windows + 63) / 64 : 0;
+    const int64_t nu = L.unit1 - L.unit0;
+    int64_t u_begin, u_end, u_step;
+    if (cross) { u_begin = L.unit0 + gw * nu / nwarps; u_end = L.unit0 + (gw + 1) * nu / nwarps; u_step = 1; }
+    else       { u_begin = L.unit0 + gw; u_end = L.unit1; u_step = nwarps; }
+    int32_t tbl_adapter = -1;
+
+    for (int64_t unit = u_begin; unit < u_end; unit += u_step) {
+        int32_t adapter = 0;
+        HalfTask tk[2];
+        if (cross) {
+            const int64_t k = unit / groups, g = unit - k * groups;
+            adapter = L.src.ids[k];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                HalfTask &t = tk[h];
+                t.off = 0; t.len = 0; t.col0 = 0; t.m_true = 0; t.forced = -1; t.own0 = 0; t.out_idx = -1;
+                const int64_t w = g * 64 + 2 * lane + h;
+                if (w < L.src.n_windows) {
+                    t.off = (uint64_t)w * (uint64_t)L.src.stride;
+                    t.len = L.src.win_len[w]; t.m_true = t.len;
+                    t.out_idx = w * L.src.n_ids_total + (L.src.id_pos ? L.src.id_pos[k] : (int32_t)k);
+                }
+            }
+        } else {
+            fetch_task(L.src, unit, 2 * lane, adapter, tk[0]);
+            fetch_task(L.src, unit, 2 * lane + 1, adapter, tk[1]);
+        }
+        uint4 *const entp = TRACE ? L.entries + (unit - L.unit0) * 32 + lane : nullptr;
+        const int64_t aoff = L.ad.off[adapter];
+        const int n = (int)(L.ad.off[adapter + 1] - aoff);
+        if (n <= NR || n > R2 || n > 127) {                              // the host never sends these here; fail loudly if it does
+            atomicOr(L.err_flag, 4);
+            for (int h = 0; h < 2; ++h) if (tk[h].out_idx >= 0) {
+                if (TRACE) write_failed(L.out, tk[h].out_idx); else L.scan_out[tk[h].out_idx] = (int)0x80000000;
+            }
+            if (TRACE) *entp = make_uint4(0u, 0u, 0u, 0u);
+            continue;
+        }
+        const int r0 = R2 - n;                                 // bottom-aligned: adapter row i = register row r0 + i - 1 of 0 .. 2*NR - 1
+        if (adapter != tbl_adapter) { build_table2<NR>(L, tbl, s_code, aoff, n, r0, lane, s_match, s_mis, b); tbl_adapter = adapter; }
+
+        uint32_t ex[2] = {0u, 0u}, ey[2] = {0u, 0u};
+#pragma unroll 1
+        for (int sub = 0; sub < 2; ++sub) {
+            const HalfTask t = tk[sub];
+            const int len = t.len;
+            const int mw = __reduce_max_sync(0xffffffffu, len);
+            if (mw == 0) {                                     // nobody has a task in this half
+                if (t.out_idx >= 0) { if (TRACE) write_failed(L.out, t.out_idx); else L.scan_out[t.out_idx] = (int)0x80000000; }
+                continue;
+            }
+            const bool fin = len > 0 && t.col0 + len == t.m_true;
+            int lo1 = t.own0 + 1, hi1 = fin ? len - 1 : len;   // candidate columns of the last adapter row
+            if (t.forced >= 0) { if (t.forced <= hi1) { lo1 = max(lo1, t.forced); hi1 = t.forced; } else hi1 = -1; }
+            const bool act = t.out_idx >= 0 && len > 0;
+            const int ulo = __reduce_max_sync(0xffffffffu, act ? lo1 : 0);
+            const int ufin = __reduce_min_sync(0xffffffffu, fin ? len : 0x7fffffff);
+            const int uhi = min(__reduce_min_sync(0xffffffffu, act ? hi1 : 0x7fffffff), ufin - 2);
+            const bool z = len > 0 && t.col0 == 0 && t.own0 == 0 && (t.forced < 0 || t.forced == 0);
+            uint32_t bestS = pk(0, z ? OFF : 0);               // the last adapter row lives in the high half
+            int ord = 0, finS = 0, finI = 0, finE = 0;
+            const uint8_t *const seq = L.arena + t.off;
+            const int lim = max(len - 1, 0);
+
+            uint32_t Mo[NR], Hl[NR];
+#pragma unroll
+            for (int r = 0; r < NR; ++r) { Mo[r] = pk(B0 + b * (r + 1), B0 + b * (NR + r + 1)); Hl[r] = 0; }
+            uint32_t rowT = pk2(B0);
+            uint32_t bM1 = pk2(B0 + b * NR), bM2 = bM1, bV1 = 0;     // row NR at columns t-1, t-2 (high halves count)
+            const uint32_t candK = pk2(OFF - b * R2 + b);     // candidate = M(n, t-1) + candK - rowT(t) = score + OFF
+            uint32_t *const ckp = TRACE ? L.scratch + (uint64_t)(unit - L.unit0) * 32u * ckw + (uint64_t)sub * 16u * ckw + (uint64_t)lane * 8u : nullptr;
+            uint32_t ckoff = 0;
+            int ckc = 0;
+            Raw4 nx = load4(seq, 0, lim);
+            uint32_t prev = 0;
+
+            auto column = [&](const int j, const uint32_t c_lo, const uint32_t c_hi, const bool general) {
+                const uint32_t *tp = tbl + pair_index(c_lo, c_hi);
+                const uint32_t rowTp = rowT;
+                rowT += Bp;
+                const uint32_t vb = __viaddmax_s16x2(bV1, GEB, bM1);       // V(NR + 1, t - 1) from the row above
+                uint32_t Ml, Vl;
+                col_score2<NR>(Mo, Hl, tp, lo_hi(rowTp, bM2), lo_hi(rowT, vb), GEB, Ml, Vl);
+                bM2 = bM1; bM1 = swap16(Ml); bV1 = swap16(Vl);
+                uint32_t cand = (Ml + candK - rowT) & 0xFFFF0000u;
+                if (general) { if (!(j - 1 >= lo1 && j - 1 <= hi1)) cand = 0u; }
+                bool keep_hi, keep_lo;
+                bestS = vmax_keep(bestS, cand, keep_hi, keep_lo);
+                if (!keep_hi) ord = j - 1;
+                if (general) {
+                    if (j == 1) {                                // the high half has not started yet: back to its column 0
+#pragma unroll
+                        for (int r = 0; r < NR; ++r) { Mo[r] = (Mo[r] & 0xFFFFu) | ((uint32_t)(B0 + b * (NR + r + 1)) << 16); Hl[r] &= 0xFFFFu; }
+                    }
+                    if (fin && j == len) {                       // final column, rows of the first stripe
+#pragma unroll
+                        for (int r = 0; r < NR; ++r) { s_fl[(2 * r) * PCB_BLOCK] = Mo[r]; s_fl[(2 * r + 1) * PCB_BLOCK] = Hl[r]; }
+                    }
+                    if (fin && j == len + 1) {                   // ... and of the second, one iteration later
+#pragma unroll
+                        for (int r = 0; r < NR; ++r) {
+                            s_fl[(2 * r) * PCB_BLOCK] = lo_hi(s_fl[(2 * r) * PCB_BLOCK], Mo[r]);
+                            s_fl[(2 * r + 1) * PCB_BLOCK] = lo_hi(s_fl[(2 * r + 1) * PCB_BLOCK], Hl[r]);
+                        }
+                        // cells (i, len), i = 1..n, in order; V rebuilt as the forward pass computed it (as in k_fast)
+                        int Tn = lo16(rowT) - b + b * r0, Vp = 0, Mp = Tn, best = 0, bi = 0, be = 0;     // rowT: bias of row 0 at column len + 1
+                        for (int i = 1; i <= n; ++i) {
+                            const int rr = r0 + i - 1, h = rr >= NR ? 1 : 0, r = rr - NR * h;
+                            const int M = half16(s_fl[(2 * r) * PCB_BLOCK], h), H = half16(s_fl[(2 * r + 1) * PCB_BLOCK], h);
+                            const int V = max(Vp + geb, Mp);
+                            Tn += b;
+                            const int c = M + OFF - Tn;
+                            if ((t.forced < 0 || t.forced == len + i) && c > best) { best = c; bi = i; be = ((V == M) ? 2 : 0) | ((H == M) ? 1 : 0); }
+                            Vp = V; Mp = M;
+                        }
+                        finS = best; finI = bi; finE = be;
+                    }
+                }
+            };
+
+            for (int j0 = 1; j0 <= mw + 1; j0 += 4) {
+                const uint32_t cur = join4(nx);
+                nx = load4(seq, j0 + 3, lim);
+                uint32_t c_lo = cur, c_hi = __funnelshift_l(prev, cur, 8);      // the high half is one column behind
+                prev = cur;
+                if (TRACE && ckc == 0 && j0 > 1) {               // checkpoint k = state after iteration j0 - 1 = k * C
+                    uint32_t *const cq = ckp + ckoff;
+                    PCF_CHECK(L, (uint64_t)ckoff + (G8 + 1) * 256u <= 16u * ckw);
+                    const uint32_t T1 = GEB + 0x00010001u;
+#pragma unroll
+                    for (int g = 0; g < G8; ++g) {
+                        uint32_t v[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) { const int r = 8 * g + e; v[e] = r < NR ? Mo[r < NR ? r : 0] + __vminu2(Mo[r < NR ? r : 0] - Hl[r < NR ? r : 0], T1) * 8192u : 0u; }
+                        st256(cq + g * 256, v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
+                    }
+                    st256(cq + G8 * 256, bM1, bM2, bV1, 0u, 0u, 0u, 0u, 0u);
+                    ckoff += (G8 + 1) * 256;
+                }
+                if (TRACE) { ckc += 4; if (ckc == C) ckc = 0; }
+                if (!TRACE && ((j0 - 1) & (REBASE - 1)) == 0 && j0 > 1 && !(fin && j0 - 1 == len)) {   // keep the growing bias inside 15 bits (not between the two halves of a final-column dump)
+                    const uint32_t d = pk2(b * REBASE);
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) { Mo[r] -= d; Hl[r] -= d; }
+                    rowT -= d; bM1 -= d; bM2 -= d; bV1 -= d;
+                }
+                if (j0 - 1 >= ulo && j0 + 2 <= uhi && j0 > 1) {
+#pragma unroll UNR
+                    for (int k = 0; k < 4; ++k) { column(j0 + k, c_lo & 0xFFu, c_hi & 0xFFu, false); c_lo >>= 8; c_hi >>= 8; }
+                } else {
+#pragma unroll 1
+                    for (int k = 0; k < 4; ++k) { column(j0 + k, c_lo & 0xFFu, c_hi & 0xFFu, true); c_lo >>= 8; c_hi >>= 8; }
+                }
+            }
+
+            int sc = (int)(bestS >> 16);
+            bool fc = false;
+            if (finS > sc) { sc = finS; ord = len + finI; fc = true; }
+            if (!TRACE) {
+                if (t.out_idx >= 0) L.scan_out[t.out_idx] = (len > 0 && sc > 0) ? (int)(((uint32_t)(sc - OFF) << 16) | ((uint32_t)(0x3FFF - ord) << 2)) : (int)0x80000000;
+                continue;
+            }
+            if (t.out_idx < 0) continue;
+            if (len <= 0) { write_failed(L.out, t.out_idx); continue; }
+            if (sc <= 0) { atomicOr(L.err_flag, 2); write_failed(L.out, t.out_idx); continue; }
+            int pci, pcj, pst;
+            if (fc) { pci = ord - len; pcj = len; pst = (finE & 2) ? 1 : ((finE & 1) ? 2 : 0); }
+            else    { pci = n; pcj = ord; pst = 4; }
+            ex[sub] = (uint32_t)pci | ((uint32_t)pcj << 7) | ((uint32_t)pst << 17) | 0x80000000u;
+            ey[sub] = (uint32_t)sc;
+        }
+        if (TRACE) *entp = make_uint4(ex[0], ey[0], ex[1], ey[1]);
+    }
+}
+
+// One op of the reverse walk of the two-stripe kernels: arg = register row 0 .. 2*NR-1 of the walk's adapter row, jcol = its
+// column - (first column of the block).  The flags of stripe h, row arg - NR*h, column jcol are in iteration slot jcol + h.
+template <int NR>
+__device__ __forceinline__ void walk_step2(const uint32_t *s_fl, int &arg, int &jcol, uint32_t &pos2, Walk &w)
+{
+    constexpr int FW = NR / 4;
+    const int h = arg >= NR ? 1 : 0, ar = arg - NR * h;
+#ifdef PCF_CHECKED
+    if (ar < 0 || (ar >> 2) >= FW || jcol + h < 0 || jcol + h >= 16) asm volatile("trap;");
+#endif
+    const uint32_t f = walk_flags<FW>(s_fl, h, ar, jcol + h);
+    const uint32_t fh = f & 1u, fg = (f >> 1) & 1u, fv = (f >> 16) & 1u, fd = (f >> 17) & 1u;
+    const uint32_t sM = w.s == 0 ? 1u : 0u, sV = w.s == 1 ? 1u : 0u;
+    const uint32_t isD = sM & fd, isV = sV | (sM & (fd ^ 1u) & fg), isH = (isD | isV) ^ 1u;
+    const uint32_t extV = isV & fv, extH = isH & fh;
+    walk_acc_step(w.acc, pos2, isD, isV, isH, extV | extH);
+    w.s = (int)(extV | (extH << 1));
+    arg -= (int)(isH ^ 1u); jcol -= (int)(isV ^ 1u);
+}
+
+// k_rounds2<NR, C>: pass 2 of the two-stripe trace.  Work items, sorting, generations and results as k_rounds; a lane takes
+// ONE item at a time (its two stripes fill the packed halves), so a chunk of 64 items is two sub-rounds of 32.
+// A block = iterations k*C+1 .. k*C+C: columns k*C+1.. of the first stripe, k*C.. of the second.
+// dynamic smem: [W][NR*25] score tables, [W][2*NR] adapter codes, then per thread C*NR/4 flag words.
+template <int NR, int C>
+__global__ void __launch_bounds__(PCB_BLOCK, 1) k_rounds2(const PcbLaunch L)
+{
+    extern __shared__ uint32_t smem[];
+    constexpr int FW = NR / 4, W = PCB_BLOCK / 32, R2 = 2 * NR, G8 = (NR + 7) / 8;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t *const tbl = smem + warp * (NR * TP);
+    uint32_t *const s_code = smem + W * (NR * TP) + warp * R2;
+    uint32_t *const s_fl = smem + W * (NR * TP + R2) + threadIdx.x;
+
+    const Meta M = meta_of(L);
+    const int A = L.n_major;
+    const bool gen0 = L.gen == 0;
+    const int b = -L.sc.gap_open;
+    const int s_match = L.sc.match + 2 * b, s_mis = L.sc.mismatch + 2 * b;
+    const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b);
+    const bool cross = L.src.units == nullptr;
+    const int64_t groups = cross ? (L.src.n_windows + 63) / 64 : 0;
+    const uint64_t ckw = ckw2_of(L.mmax, C, NR);
+
+    // Work is handed out 32 items (half a chunk) at a time from a queue head in meta, the LAST chunks first: inside a major
+    // the sort puts the longest paths last, and a round costs its longest path, so the expensive rounds start early and the
+    // cheap ones fill the tail.  (A static split of the chunk list left SMs idle for half of the kernel: some warps drew
+    // nothing but 13-block rounds.)
+    const int64_t total = M.chunk_base[A];
+    int32_t *const qhead = M.counters + 1 + (gen0 ? 0 : 1);
+    int a = -1, n = 0, r0 = 0;
+    int32_t tbl_adapter = -1, out_col = 0;
+    int64_t a_item0 = 0, a_item1 = 0, a_chunk0 = 0;
+
+    for (;;) {
+        int64_t q = 0;
+        if (lane == 0) q = atomicAdd(qhead, 1);
+        q = __shfl_sync(0xffffffffu, q, 0);
+        if (q >= 2 * total) break;
+        const int64_t qq = 2 * total - 1 - q, c = qq >> 1;
+        const int sub = (int)(qq & 1);
+        if (a < 0 || c < a_chunk0 || c >= M.chunk_base[a + 1]) {     // another major: the one whose chunk range holds c
+            int lo = 0, hi = A - 1;
+            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (M.chunk_base[mid] <= c) lo = mid; else hi = mid - 1; }
+            a = lo;
+            a_item0 = M.base[(int64_t)a * NB]; a_item1 = M.base[(int64_t)(a + 1) * NB]; a_chunk0 = M.chunk_base[a];
+            const int32_t adapter = cross ? L.src.ids[a] : a;
+            if (cross) out_col = L.src.id_pos ? L.src.id_pos[a] : a;
+            const int64_t aoff = L.ad.off[adapter];
+            n = (int)(L.ad.off[adapter + 1] - aoff);
+            r0 = R2 - n;
+            if (adapter != tbl_adapter) { build_table2<NR>(L, tbl, s_code, aoff, n, r0, lane, s_match, s_mis, b); tbl_adapter = adapter; }
+        }
+        {
+            const int64_t i0 = a_item0 + (c - a_chunk0) * 64 + 32 * sub + lane;
+            bool valid = i0 < a_item1;
+            uint32_t ref, endc;
+            Walk wk;
+            uint64_t off;
+            {
+                uint32_t v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                if (valid) ld256(reinterpret_cast<const uint32_t *>(L.sorted + i0), v);
+                ref = v[0]; endc = v[2];
+                walk_unpack(wk, v[1], v[3], v[4], v[5]);
+                off = (uint64_t)v[6] | ((uint64_t)v[7] << 32);
+            }
+            if (!__any_sync(0xffffffffu, valid)) continue;
+            const uint8_t *const seq = L.arena + off;
+            constexpr int lim = 0x7fffffff;
+            // this task's checkpoints: written by lane (slot >> 1) as its task (slot & 1)
+            const uint32_t *const ckp = L.scratch + ((uint64_t)(ref >> 6) * 32u * ckw + (uint64_t)(ref & 1u) * 16u * ckw + (uint64_t)((ref & 63u) >> 1) * 8u);
+
+            for (;;) {
+                const bool go = valid && wk.i > 0 && wk.j > 0;
+                const int arg0 = r0 + wk.i - 1, h0 = arg0 >= NR ? 1 : 0;
+                const int k = go ? (wk.j + h0 - 1) / C : 0, jb = k * C;
+                const int tmax = __reduce_max_sync(0xffffffffu, go ? wk.j + h0 - jb : 0);
+                const int rlim = __reduce_max_sync(0xffffffffu, go ? (h0 ? NR : ((arg0 + 4) & ~3)) : 0);
+                if (tmax > 0) {
+                    PCF_CHECK(L, tmax <= C && rlim <= NR);
+                    // the block's read bases: low stripe = columns jb+1.., high stripe one column behind
+                    uint32_t ql[C / 4], qh[C / 4];
+                    {
+                        const uint32_t before = k > 0 ? join4(load4(seq, jb - 4, lim)) : 0u;
+#pragma unroll
+                        for (int g = 0; g < C / 4; ++g) ql[g] = join4(load4(seq, jb + 4 * g, lim));
+#pragma unroll
+                        for (int g = 0; g < C / 4; ++g) qh[g] = __funnelshift_l(g ? ql[g > 0 ? g - 1 : 0] : before, ql[g], 8);
+                    }
+                    uint32_t Mo[NR], Hl[NR];
+                    uint32_t bM1 = pk2(B0 + b * NR), bM2 = bM1, bV1 = 0u;
+                    {
+                        const bool ld = go && k > 0;
+                        const uint32_t *const p = ckp + (uint64_t)max(k - 1, 0) * (G8 + 1) * 256u;
+                        const uint32_t T1s = (GEB + 0x00010001u) * 8192u;
+                        PCF_CHECK(L, !ld || ((int64_t)(ref >> 6) < L.unit1 - L.unit0 && (uint64_t)k * (G8 + 1) * 16u <= ckw));
+#pragma unroll
+                        for (int g = 0; g < G8; ++g) {
+                            if (8 * g < rlim) {
+                                uint32_t x[8];
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) x[e] = pk(B0 + b * (8 * g + e + 1), B0 + b * (NR + 8 * g + e + 1)) + T1s;
+                                if (ld) ld256(p + g * 256, x);
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) {
+                                    if (8 * g + e < NR) {
+                                        const uint32_t m = x[e] & 0x1FFF1FFFu;
+                                        Mo[8 * g + e] = m; Hl[8 * g + e] = m - ((x[e] >> 13) & 0x00070007u);
+                                    }
+                                }
+                            } else {
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) if (8 * g + e < NR) { Mo[8 * g + e] = 0u; Hl[8 * g + e] = 0u; }
+                            }
+                        }
+                        if (ld) { uint32_t x[8]; ld256(p + G8 * 256, x); bM1 = x[0]; bM2 = x[1]; bV1 = x[2]; }
+                    }
+                    uint32_t rT = pk2(B0 + b * jb);
+                    const bool pend = go && (wk.s & 4);
+                    const bool anypend = __any_sync(0xffffffffu, pend);
+                    int s = wk.s & 3;
+#pragma unroll 1
+                    for (int t = 1; t <= tmax; ++t) {
+                        const uint32_t *tp = tbl + pair_index(ql[0] & 0xFFu, qh[0] & 0xFFu);
+#pragma unroll
+                        for (int g = 0; g < C / 4; ++g) {                  // shift the base queues by one byte
+                            ql[g] = __funnelshift_r(ql[g], g + 1 < C / 4 ? ql[(g + 1) % (C / 4)] : 0u, 8);
+                            qh[g] = __funnelshift_r(qh[g], g + 1 < C / 4 ? qh[(g + 1) % (C / 4)] : 0u, 8);
+                        }
+                        const uint32_t rowTp = rT;
+                        rT += Bp;
+                        uint32_t Ml, Vl, Hlast;
+                        col_flags2<NR>(Mo, Hl, tp, lo_hi(rowTp, bM2), lo_hi(rT, bM1), bV1 & 0xFFFF0000u, GEB,
+                                       s_fl + (t - 1) * FW * PCB_BLOCK, rlim, Ml, Vl, Hlast);
+                        bM2 = bM1; bM1 = swap16(Ml); bV1 = swap16(Vl);
+                        if (k == 0 && t == 1) {                            // the high stripe starts from its column 0 next iteration
+#pragma unroll
+                            for (int r = 0; r < NR; ++r) { Mo[r] = (Mo[r] & 0xFFFFu) | ((uint32_t)(B0 + b * (NR + r + 1)) << 16); Hl[r] &= 0xFFFFu; }
+                        }
+                        if (anypend) {
+                            // end cell in the last adapter row (second stripe, last register row): V == M / H == M decide how
+                            // the trace starts (_correctTraceValue, dp_algorithm_impl.h:1169-1185)
+                            if (pend && jb + t == wk.j + 1) s = ((Ml ^ Vl) >> 16) == 0 ? 1 : ((((Ml ^ Hlast) >> 16) == 0) ? 2 : 0);
+                        }
+                    }
+                    __syncwarp();
+                    wk.s = s;                                              // the pending bit is spent
+                    {
+                        int arg = arg0, jcol = wk.j - jb - 1;
+                        uint32_t pz = (uint32_t)(2 * wk.j + 1) | ((uint32_t)(2 * wk.i + 1) << 16);
+                        bool act = go;
+                        while (act) {
+                            walk_step2<NR>(s_fl, arg, jcol, pz, wk);
+                            act = arg >= r0 && jcol + jb >= 0 && jcol + (arg >= NR ? 1 : 0) >= 0;
+                        }
+                        if (go) { wk.i = arg - r0 + 1; wk.j = jcol + jb + 1; }
+                    }
+                    __syncwarp();                                          // the flag words are rewritten by the next round
+                }
+
+                // paths that reached row 0 / column 0 are complete (this also covers the empty path)
+                const bool keep = valid && wk.i > 0 && wk.j > 0;
+                if (valid && !keep) {
+                    valid = false;
+                    int col0 = 0, mtrue;
+                    int64_t oidx;
+                    if (cross) {
+                        const int64_t wi = (L.unit0 + (int64_t)(ref >> 6) - (int64_t)a * groups) * 64 + (int64_t)(ref & 63u);
+                        mtrue = L.src.win_len[wi]; oidx = wi * L.src.n_ids_total + out_col;
+                    } else {
+                        const PcbTask &tk = L.src.tasks[L.src.units[L.unit0 + (int64_t)(ref >> 6)].task0 + (int64_t)(ref & 63u)];
+                        col0 = tk.col0; mtrue = tk.m_true; oidx = tk.out_idx;
+                    }
+                    const int endi = (int)(endc & 127u), endj = (int)((endc >> 7) & 0x3FFu), score = (int)(endc >> 17) - OFF;
+                    if (wk.j == 0 && wk.i > 0 && col0 > 0) atomicOr(L.err_flag, 1);      // window too narrow for this path
+                    int ok;
+                    const int matches = walk_acc_matches(wk.acc, endi, endj, wk.i, wk.j, score, L.sc.match, L.sc.mismatch, L.sc.gap_open, L.sc.gap_extend, &ok);
+                    if (!ok) atomicOr(L.err_flag, 16);
+                    PathAcc pa;
+                    walk_acc_finish(wk.acc, endi, endj, wk.i, wk.j, matches, pa);
+                    PathStats ps;
+                    path_finalize(pa, (int64_t)col0 + wk.j, wk.i, (int64_t)mtrue - (col0 + endj), n - endi, mtrue, n, ps);
+                    pcb_result res;
+                    res.read_start = ps.read_start; res.read_end = ps.read_end;
+                    res.adapter_start = ps.adapter_start; res.adapter_end = ps.adapter_end;
+                    res.raw_score = score; res.matches = ps.matches;
+                    res.aligned_len = ps.aligned_len; res.full_len = ps.full_len;
+                    PCF_CHECK(L, oidx >= 0 && (L.n_out <= 0 || oidx < L.n_out));
+                    L.out[oidx] = res;
+                }
+                if (!gen0) {
+                    if (!__any_sync(0xffffffffu, keep)) break;
+                    continue;                                              // these 32 stay together until the last is done
+                }
+                // generation 0: the others go to generation 1, counted per (major, rows)
+                const uint32_t m0 = __ballot_sync(0xffffffffu, keep);
+                const int nk = __popc(m0);
+                if (nk) {
+                    int first = 0;
+                    if (lane == 0) first = atomicAdd(M.counters, nk);
+                    first = __shfl_sync(0xffffffffu, first, 0);
+                    PCF_CHECK(L, first + nk <= 64 * (L.unit1 - L.unit0));
+                    const uint32_t pos = walk_pos(wk);
+                    const int key = keep ? a * NB + bucket1_two(pos) : -1;
+                    const uint32_t mk = __match_any_sync(0xffffffffu, key);
+                    if (keep) {
+                        if (lane == __ffs(mk) - 1) atomicAdd(M.hist1 + key, __popc(mk));
+                        put_item(L.surv + first + __popc(m0 & ((1u << lane) - 1u)), ref, pos, endc, wk.acc.kAR, wk.acc.tHV, wk.acc.nHV, off);
+                    }
+                }
+                break;
+            }
+        }
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
 // host-side launchers, by kernel class
 // ------------------------------------------------------------------------------------------------
-static size_t fast_smem(int kind, int nr, int c)
+static size_t fast_smem(int kind, int nr, int c, bool two = false)
 {
     const size_t W = PCB_BLOCK / 32;
+    if (two)             // two-stripe kernels: codes of 2 * nr rows; flag words or column dump as below
+        return (W * (size_t)(nr * TP + 2 * nr) + (size_t)PCB_BLOCK * (kind == 2 ? (size_t)c * (nr / 4) : (size_t)2 * nr)) * sizeof(uint32_t);
     if (kind == 2)       // rounds: tables, codes, then the flag words per thread
         return (W * (size_t)(nr * TP + nr) + (size_t)PCB_BLOCK * ((size_t)c * (nr / 4))) * sizeof(uint32_t);
     return (W * (size_t)(nr * TP + nr) + (size_t)PCB_BLOCK * 2 * nr) * sizeof(uint32_t);      // column dump
@@ -955,6 +1484,50 @@ static cudaError_t launch_rounds(const PcbLaunch &L, int grid, cudaStream_t st)
     return cudaGetLastError();
 }
 
+// the two-stripe classes: 56 or 72 register rows x 2 stripes
+constexpr int C2 = PCF_C_LARGE;
+template <int MODE, int NR>
+static cudaError_t launch_fast2(const PcbLaunch &L, int grid, cudaStream_t st)
+{
+    static bool attr = false;
+    const size_t sm = fast_smem(MODE, NR, C2, true);
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(k_fast2<MODE, NR, C2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if (e != cudaSuccess) return e;
+        attr = true;
+    }
+    k_fast2<MODE, NR, C2><<<grid, PCB_BLOCK, sm, st>>>(L);
+    return cudaGetLastError();
+}
+template <int NR>
+static cudaError_t launch_rounds2(const PcbLaunch &L, int grid, cudaStream_t st)
+{
+    static bool attr = false;
+    const size_t sm = fast_smem(2, NR, C2, true);
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(k_rounds2<NR, C2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if (e != cudaSuccess) return e;
+        attr = true;
+    }
+    k_rounds2<NR, C2><<<grid, PCB_BLOCK, sm, st>>>(L);
+    return cudaGetLastError();
+}
+template <int KIND, int NR>
+static int occ_two()
+{
+    int per = 0;
+    const size_t sm = fast_smem(KIND, NR, C2, true);
+    if (KIND == 2) {
+        cudaFuncSetAttribute(k_rounds2<NR, C2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_rounds2<NR, C2>, PCB_BLOCK, sm);
+    } else {
+        cudaFuncSetAttribute(k_fast2<(KIND == 1), NR, C2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_fast2<(KIND == 1), NR, C2>, PCB_BLOCK, sm);
+    }
+    return per < 1 ? 1 : per;
+}
+#define PCF_BY_TWO(...) do { if (cls == 6) { constexpr int NR = 56; __VA_ARGS__; } else { constexpr int NR = 72; __VA_ARGS__; } } while (0)
+
 template <int KIND, int NR, bool EXACT, int C>
 static int occ_one()
 {
@@ -985,6 +1558,7 @@ cudaError_t pcf_launch_scan(const PcbLaunch &L, int cls, cudaStream_t st)
 {
     if (L.unit1 <= L.unit0) return cudaSuccess;
     if (cls < 0 || cls >= PCF_NCLS) return cudaErrorInvalidValue;
+    if (pcf_class_two(cls)) { PCF_BY_TWO(return (launch_fast2<0, NR>(L, L.grid, st))); }
     PCF_BY_CLASS(return (launch_fast<0, NR, EX, C>(L, L.grid, st)))
     return cudaSuccess;
 }
@@ -995,6 +1569,7 @@ cudaError_t pcf_launch_pass1(const PcbLaunch &L, int cls, cudaStream_t st)
     if (L.unit1 <= L.unit0) return cudaSuccess;
     if (cls < 0 || cls >= PCF_NCLS) return cudaErrorInvalidValue;
     cudaError_t e = cudaSuccess;
+    if (pcf_class_two(cls)) { PCF_BY_TWO(return (launch_fast2<1, NR>(L, L.grid, st))); }
     PCF_BY_CLASS(e = launch_fast<1, NR, EX, C>(L, L.grid, st))
     return e;
 }
@@ -1005,23 +1580,25 @@ cudaError_t pcf_launch_pass2(const PcbLaunch &L0, int cls, int grid_rounds, cuda
     if (L0.unit1 <= L0.unit0) return cudaSuccess;
     if (cls < 0 || cls >= PCF_NCLS) return cudaErrorInvalidValue;
     PcbLaunch L = L0;
-    const int C = pcf_class_c(cls);
+    const int C = pcf_class_c(cls), two = pcf_class_two(cls);
     const int64_t nu = L.unit1 - L.unit0;
     cudaError_t e = cudaMemsetAsync(L.meta, 0, pcf_meta_words(L.n_major) * sizeof(int32_t), st);
     if (e != cudaSuccess) return e;
     const unsigned g0 = (unsigned)((nu * 32 + 255) / 256);
-    k_count0<<<g0, 256, 0, st>>>(L, C);
+    k_count0<<<g0, 256, 0, st>>>(L, C, two);
     k_bucket_scan<<<1, 1024, 0, st>>>(L, 0);
-    k_scatter0<<<g0, 256, 0, st>>>(L, C);
+    k_scatter0<<<g0, 256, 0, st>>>(L, C, two);
     L.gen = 0;
-    PCF_BY_CLASS(e = launch_rounds<NR, EX, C>(L, grid_rounds, st))
+    if (two) PCF_BY_TWO(e = launch_rounds2<NR>(L, grid_rounds, st));
+    else { PCF_BY_CLASS(e = launch_rounds<NR, EX, C>(L, grid_rounds, st)) }
     if (e != cudaSuccess) return e;
     k_bucket_scan<<<1, 1024, 0, st>>>(L, 1);
     // the survivors are counted on the device: the scatter is sized for the worst case and leaves early
     const unsigned g1 = (unsigned)((nu * 64 + 255) / 256);
-    k_scatter1<<<g1, 256, 0, st>>>(L);
+    k_scatter1<<<g1, 256, 0, st>>>(L, two);
     L.gen = 1;
-    PCF_BY_CLASS(e = launch_rounds<NR, EX, C>(L, grid_rounds, st))
+    if (two) PCF_BY_TWO(e = launch_rounds2<NR>(L, grid_rounds, st));
+    else { PCF_BY_CLASS(e = launch_rounds<NR, EX, C>(L, grid_rounds, st)) }
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
@@ -1033,7 +1610,8 @@ int pcf_occupancy_grid(int kind, int cls)
     int dev = 0, sms = 0, per = 1;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (kind == 0)      { PCF_BY_CLASS(per = (occ_one<0, NR, EX, C>())) }
+    if (pcf_class_two(cls)) PCF_BY_TWO(per = kind == 0 ? occ_two<0, NR>() : (kind == 1 ? occ_two<1, NR>() : occ_two<2, NR>()));
+    else if (kind == 0) { PCF_BY_CLASS(per = (occ_one<0, NR, EX, C>())) }
     else if (kind == 1) { PCF_BY_CLASS(per = (occ_one<1, NR, EX, C>())) }
     else                { PCF_BY_CLASS(per = (occ_one<2, NR, EX, C>())) }
     return sms * per;

@@ -23,9 +23,14 @@
  *   class 1: 1..23 bases      NR 24      class 2: 25..32 bases   NR 32
  *   class 3: 33..40 bases     NR 40      class 4: 41..52 bases   NR 52
  *   class 5: 53..72 bases     NR 72   (the native "full sequence" barcode sets, adapters.py:466-476: 68 and 63 bases)
+ *   class 6: 73..112 bases    NR 56 x two stripes: one task per thread and pass instead of two, the second 56 rows in the
+ *            high halves one column behind the first (the rapid "full sequence" barcode sets, adapters.py:479-498: 102, 111)
+ *   class 7: 113..127 bases   NR 72 x two stripes
  *   class PCF_NCLS: everything else -> general kernels (pcb_kernels.cu) */
-#define PCF_NCLS          6
-#define PCF_MAX_N         72
+#define PCF_NCLS          8
+#define PCF_CLS_TWO       6       /* first two-stripe class */
+#define PCF_MAX_N         72      /* rows of the one-stripe classes */
+#define PCF_MAX_N2        127     /* rows of the two-stripe class (the position word has 7 row bits) */
 /* a traceback's position word: row | column << 7 | state << 17 | gap openings << 20; its end cell: row | column << 7 |
  * (raw score + 2048) << 17 */
 #define PCF_ROW_BITS      7
@@ -38,11 +43,14 @@
 #ifndef PCF_C_LARGE
 #define PCF_C_LARGE       8       /* C for NR > 32  */
 #endif
-static inline int pcf_class_nr(int cls) { return cls <= 1 ? 24 : (cls == 2 ? 32 : (cls == 3 ? 40 : (cls == 4 ? 52 : 72))); }
+static inline int pcf_class_nr(int cls) { return cls <= 1 ? 24 : (cls == 2 ? 32 : (cls == 3 ? 40 : (cls == 4 ? 52 : (cls == 6 ? 56 : 72)))); }
+static inline int pcf_class_two(int cls) { return cls >= PCF_CLS_TWO && cls < PCF_NCLS; }
+static inline int pcf_class_rows(int cls) { return pcf_class_two(cls) ? 2 * pcf_class_nr(cls) : pcf_class_nr(cls); }   /* adapter rows a thread computes per column */
 static inline int pcf_class_c(int cls) { return pcf_class_nr(cls) <= 32 ? PCF_C_SMALL : PCF_C_LARGE; }
 static inline int pcf_class_of_len(long len)
 {
-    if (len < 1 || len > PCF_MAX_N) return PCF_NCLS;
+    if (len < 1 || len > PCF_MAX_N2) return PCF_NCLS;
+    if (len > PCF_MAX_N) return len <= 112 ? 6 : 7;
     return len == 24 ? 0 : (len < 24 ? 1 : (len <= 32 ? 2 : (len <= 40 ? 3 : (len <= 52 ? 4 : 5))));
 }
 
@@ -218,9 +226,12 @@ int pcf_trace_launches(void);       /* kernel launches of one pcf_launch_trace c
 #define PCF_NB 32                 /* sort buckets per major (first blocks: by width / rows; later blocks: by rows) */
 static inline uint64_t pcf_ck_words(int mmax, int C, int NR) { return (uint64_t)((mmax + C - 1) / C) * (uint64_t)((NR + 7) / 8) * 8ull; }
 /* words per unit: checkpoints, entries (4 per thread), sorted items and surviving items (8 words per task each) */
+/* two-stripe class: 2 tasks x checkpoints (one more iteration than columns) x (row chunks + 1 chunk of boundary registers) */
+static inline uint64_t pcf_ck_words2(int mmax, int C, int NR) { return 2ull * (uint64_t)((mmax + 1 + C - 1) / C) * (uint64_t)((NR + 7) / 8 + 1) * 8ull; }
 static inline uint64_t pcf_unit_words_trace(int mmax, int cls)
 {
-    return 32ull * (pcf_ck_words(mmax, pcf_class_c(cls), pcf_class_nr(cls)) + 4) + 2ull * 64 * 8;
+    const uint64_t ck = pcf_class_two(cls) ? pcf_ck_words2(mmax, pcf_class_c(cls), pcf_class_nr(cls)) : pcf_ck_words(mmax, pcf_class_c(cls), pcf_class_nr(cls));
+    return 32ull * (ck + 4) + 2ull * 64 * 8;
 }
 /* meta (int32): hist[2][A * NB] | base[A * NB + 1] | cursor[A * NB] | chunk_base[A + 1] | counters[8] */
 static inline uint64_t pcf_meta_words(int n_major) { return 4ull * n_major * PCF_NB + n_major + 16; }

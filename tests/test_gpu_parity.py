@@ -84,6 +84,64 @@ def test_long_adapters_multi_stripe(engine):
     _check_pairs(engine, pairs, adapters, DEFAULT)
 
 
+def _with_adapter(rng, adapter, m, rates=(0, 0.05, 0.2)):
+    from oracle_lib import mutate
+    r = ''.join(rng.choice('ACGT') for _ in range(m))
+    if rng.random() < 0.75:
+        p = rng.randrange(-len(adapter), m)
+        ins = mutate(rng, adapter, rng.choice(rates))
+        r = (ins[-p:] + r)[:m] if p < 0 else (r[:p] + ins + r[p:])[:m]
+    return r or 'A'
+
+
+@pytest.mark.parametrize('scores', [DEFAULT, (2, -3, -4, -1), (1, -1, -3, -2), (5, -4, -6, -1), (4, -3, -7, -3)])
+def test_two_stripe_class_pairs(engine, scores):
+    """Adapters of 73..127 bases (the rapid full-sequence barcodes, adapters.py:479-498) take the two-stripe kernels;
+    72 and 128 are their neighbours on either side.  Paths that end in the read's last column, in the last adapter row,
+    cross the stripe boundary, start at column 0, and segments up to the widest the trace takes."""
+    rng = random.Random(73)
+    adapters = [''.join(rng.choice('ACGT') for _ in range(n)) for n in (72, 73, 74, 80, 96, 102, 111, 112, 113, 126, 127, 128)]
+    pairs = []
+    for _ in range(700):
+        aid = rng.randrange(len(adapters))
+        m = rng.choice([1, 2, 3, 7, 8, 9, 16, 17, 40, 71, 72, 73, 150, 150, 150, 400, 999, 1000])
+        pairs.append((_with_adapter(rng, adapters[aid], m), aid))
+    # the adapter itself, prefixes and suffixes of it, and reads the adapter hangs over on both sides
+    for aid, a in enumerate(adapters):
+        pairs += [(a, aid), (a[:50], aid), (a[-50:], aid), (a[30:-30] or 'A', aid), ('ACGT' + a + 'TTGA', aid), (a[5:] + 'GGGTTT', aid)]
+    _check_pairs(engine, pairs, adapters, scores)
+
+
+def test_two_stripe_class_windows_and_long_reads(engine):
+    rng = random.Random(111)
+    adapters = [''.join(rng.choice('ACGT') for _ in range(n)) for n in (102, 111, 24, 90, 127, 73)]
+    windows = []
+    for _ in range(300):
+        m = rng.choice([150] * 6 + [0, 1, 17, 149])
+        windows.append(_with_adapter(rng, rng.choice(adapters), m, rates=(0.05, 0.1)) if m else '')
+    engine.set_scoring(DEFAULT)
+    engine.set_adapters(adapters)
+    buf, lens = engine.pack_windows(windows, stride=160)
+    ids = [0, 1, 2, 4, 5, 3]
+    out = engine.align_windows(buf, lens, ids)
+    for w, r in enumerate(windows):
+        for k, aid in enumerate(ids):
+            assert rec_matches_oracle(out[w, k], oracle_align(r, adapters[aid], DEFAULT)), (r, adapters[aid])
+    # long reads: scanned in chunks, then traced on a window around the best end cell
+    pairs = []
+    for _ in range(50):
+        m = rng.choice([1001, 1100, 2048, 2049, 5000, 12000, 30000])
+        aid = rng.randrange(len(adapters))
+        r = ''.join(rng.choice('ACGT') for _ in range(m))
+        for _ in range(rng.choice([0, 1, 1, 2])):
+            from oracle_lib import mutate
+            p = rng.randrange(-40, m)
+            ins = mutate(rng, adapters[aid], rng.choice([0, 0.05, 0.15]))
+            r = (ins[-p:] + r)[:m] if p < 0 else (r[:p] + ins + r[p:])[:m]
+        pairs.append((r, aid))
+    _check_pairs(engine, pairs, adapters, DEFAULT)
+
+
 def test_windows_cross_product(engine):
     rng = random.Random(9)
     adapters = [''.join(rng.choice('ACGT') for _ in range(rng.choice([22, 24, 28, 30, 50]))) for _ in range(9)]
