@@ -711,16 +711,37 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
     const int64_t groups = cross ? (L.src.n_windows + 63) / 64 : 0;
     const uint64_t ckw = ckw_of(L.mmax, C, NR);                  // checkpoint words per thread and unit
 
+    // Which chunks a warp takes.  NR = 24 (the class that is cut into concurrent pipelines, whose kernels fill each other's
+    // idle SMs): an equal share of the chunk list.  Larger NR: chunks are handed out from a queue head in meta, the LAST
+    // chunks first -- inside a major the sort puts the most expensive rounds last, so they start early and the cheap ones
+    // fill the tail of the launch (measured: 25..32 bases 0.89 -> 0.81 ms, 33..40 bases 0.85 -> 0.74 ms; 24 bases 13.2 ->
+    // 13.7 ms, hence the split).
+    constexpr bool DYN = NR > 24;
     const int64_t nwarps = (int64_t)gridDim.x * W, gw = (int64_t)blockIdx.x * W + warp;
     const int64_t total = M.chunk_base[A];
-    const int64_t c_begin = gw * total / nwarps, c_end = (gw + 1) * total / nwarps;
+    int64_t c_cur = DYN ? 0 : gw * total / nwarps;
+    const int64_t c_end = DYN ? 0 : (gw + 1) * total / nwarps;
+    int32_t *const qhead = M.counters + 1 + (gen0 ? 0 : 1);
     int a = -1, n = 0, r0 = 0;
     int32_t tbl_adapter = -1, out_col = 0;
     int64_t a_item0 = 0, a_item1 = 0, a_chunk0 = 0, a_chunk1 = 0;
 
-    for (int64_t c = c_begin; c < c_end; ++c) {
-        if (c >= a_chunk1) {                                     // the chunks of the next major(s) begin
-            do { ++a; a_chunk1 = M.chunk_base[a + 1]; } while (c >= a_chunk1);
+    for (;;) {
+        int64_t c;
+        if (DYN) {
+            int64_t q = 0;
+            if (lane == 0) q = atomicAdd(qhead, 1);
+            q = __shfl_sync(0xffffffffu, q, 0);
+            if (q >= total) break;
+            c = total - 1 - q;
+        } else {
+            if (c_cur >= c_end) break;
+            c = c_cur++;
+        }
+        if (a < 0 || c < a_chunk0 || c >= a_chunk1) {             // another major: the one whose chunk range holds c
+            int lo = 0, hi = A - 1;
+            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (M.chunk_base[mid] <= c) lo = mid; else hi = mid - 1; }
+            a = lo; a_chunk1 = M.chunk_base[a + 1];
             a_item0 = M.base[(int64_t)a * NB]; a_item1 = M.base[(int64_t)(a + 1) * NB]; a_chunk0 = M.chunk_base[a];
             const int32_t adapter = cross ? L.src.ids[a] : a;
             if (cross) out_col = L.src.id_pos ? L.src.id_pos[a] : a;
