@@ -113,6 +113,10 @@ C_LIB.pcb_format_result.argtypes = [POINTER(PcbResult), c_char_p, c_uint64]
 C_LIB.pcb_format_result.restype = None
 C_LIB.pcb_stats_from_path.argtypes = [c_char_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_char_p, c_int32,
                                       POINTER(PcbResult)]
+# the entry point that allocates nothing (device pointers in and out; include/porechop_b200.h)
+C_LIB.pcb_align_windows_static.argtypes = [c_int, c_char_p, c_int32, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                           c_int64, c_int32, c_void_p, c_void_p]
+C_LIB.pcb_align_windows_static.restype = c_int
 
 
 def adapter_alignment(read_sequence, adapter_sequence, scoring_scheme_vals):

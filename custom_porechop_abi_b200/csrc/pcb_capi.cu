@@ -1447,3 +1447,150 @@ extern "C" char *adapterAlignment(char *readSeq, char *adapterSeq, int matchScor
 }
 
 extern "C" void freeCString(char *p) { free(p); }
+
+// ------------------------------------------------------------------------------------------------
+// pcb_align_windows_static: windows x ONE adapter without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  The two-pass trace of the fast classes (pcf_launch_pass1 / pcf_launch_pass2) runs with
+// every byte of its working memory -- encoded windows, adapter codes, checkpoints, end cells, work items, sort tables,
+// error flag -- carved out of ONE file-scope device array.  Every GPU that loads the library holds the array until the
+// process exits; every call shares it and finds the last call's contents in it: what must start at zero is cleared by
+// the call itself, on the caller's stream.  Two calls that overlap on one GPU would race, so a process-wide lock is held
+// until the call's stream work is complete.
+// ------------------------------------------------------------------------------------------------
+#define PCB_STATIC_BYTES       ((unsigned)PCB_STATIC_SCRATCH_MB << 20)       /* limits: include/porechop_b200.h */
+static __device__ __align__(256) unsigned char g_static_scratch[PCB_STATIC_BYTES];
+
+namespace {
+// byte offsets into g_static_scratch (each a multiple of 256)
+constexpr size_t SO_ERR = 0, SO_AD_ASCII = 256, SO_AD_CODES = 512, SO_AD_OFF = 768, SO_IDS = 1024, SO_META = 1280,
+                 SO_WINLEN = 4096, SO_ARENA = SO_WINLEN + sizeof(int32_t) * PCB_STATIC_MAX_WINDOWS,
+                 SO_TRACE = SO_ARENA + (size_t)PCB_STATIC_MAX_WINDOWS * PCB_STATIC_MAX_STRIDE + 256;
+static_assert(SO_TRACE % 256 == 0 && SO_TRACE < PCB_STATIC_BYTES, "layout of the static scratch");
+static_assert((4 * PCF_NB + 1 + 16) * sizeof(int32_t) <= SO_WINLEN - SO_META, "sort tables of one adapter (pcf_meta_words(1))");
+
+struct StaticAdapter { char seq[128]; int32_t n; };
+
+// Device code may name the array directly.  Writes the adapter (ASCII, encoded by the next kernel), its offsets and id,
+// and copies the window lengths, clamped to [0, stride] (error bit 128 when one was outside: the
+// caller's array is device memory the host cannot check).
+__global__ void k_static_setup(const StaticAdapter ad, const int32_t *win_len, int64_t n_windows, int32_t stride)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        int64_t *off = reinterpret_cast<int64_t *>(g_static_scratch + SO_AD_OFF);
+        off[0] = 0; off[1] = ad.n;
+        *reinterpret_cast<int32_t *>(g_static_scratch + SO_IDS) = 0;
+    }
+    if (i < 256) {
+        g_static_scratch[SO_AD_ASCII + i] = i < ad.n ? (unsigned char)ad.seq[i] : (unsigned char)'A';
+    }
+    if (i < n_windows) {
+        const int32_t l = win_len[i], lc = min(max(l, 0), stride);
+        reinterpret_cast<int32_t *>(g_static_scratch + SO_WINLEN)[i] = lc;
+        if (l != lc) atomicOr(reinterpret_cast<int32_t *>(g_static_scratch + SO_ERR), 128);
+    }
+}
+
+struct StaticDev { unsigned char *ptr = nullptr; int grid1[PCF_NCLS] = {}, grid2[PCF_NCLS] = {}; };
+StaticDev g_static_dev[64];
+std::mutex g_static_mu;
+
+int static_fail(int code, const char *fmt, ...)
+{
+    char buf[400];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    g_global_err = buf;
+    return code;
+}
+#define PCB_CUDA_S(call) \
+    do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { cudaGetLastError(); return static_fail(PCB_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e__)); } } while (0)
+}  // namespace
+
+extern "C" int pcb_align_windows_static(int device, const char *adapter, int32_t adapter_len, int match, int mismatch,
+                                        int gap_open, int gap_extend, const char *d_windows, const int32_t *d_win_len,
+                                        int64_t n_windows, int32_t stride, pcb_result *d_out, void *cuda_stream)
+{
+    if (!adapter || n_windows < 0 || (n_windows > 0 && (!d_windows || !d_win_len || !d_out)))
+        return static_fail(PCB_ERR_ARG, "pcb_align_windows_static: null argument");
+    if (n_windows > PCB_STATIC_MAX_WINDOWS || stride < 1 || stride > PCB_STATIC_MAX_STRIDE)
+        return static_fail(PCB_ERR_RANGE, "pcb_align_windows_static takes at most %d windows of stride 1..%d per call: "
+                           "got %lld windows of stride %d; its scratch is a fixed %u MB array", PCB_STATIC_MAX_WINDOWS,
+                           PCB_STATIC_MAX_STRIDE, (long long)n_windows, stride, PCB_STATIC_BYTES >> 20);
+    if (adapter_len < 1 || adapter_len > PCF_MAX_N2)
+        return static_fail(PCB_ERR_RANGE, "pcb_align_windows_static takes adapters of 1..%d bases, got %d", PCF_MAX_N2, adapter_len);
+    for (int i = 0; i < adapter_len; ++i)
+        if (adapter[i] == 0 || !strchr("ACGTUacgtu", adapter[i]))
+            return static_fail(PCB_ERR_RANGE, "pcb_align_windows_static takes adapters of A, C, G, T only (base %d is '%c')", i, adapter[i]);
+    PcbScores sc; sc.match = match; sc.mismatch = mismatch; sc.gap_open = gap_open; sc.gap_extend = gap_extend; sc.linear = gap_open == gap_extend;
+    const int cls = pcf_class_of_len(adapter_len);
+    if (!fast_scheme(sc) || (pcf_class_two(cls) && !fast_scheme2(sc)))
+        return static_fail(PCB_ERR_RANGE, "pcb_align_windows_static takes affine schemes with -7 <= gap_open < gap_extend < 0 < match only, got %d,%d,%d,%d",
+                           match, mismatch, gap_open, gap_extend);
+    if (device < 0 || device >= 64) return static_fail(PCB_ERR_ARG, "pcb_align_windows_static: device %d", device);
+    if (n_windows == 0) return PCB_OK;
+
+    std::lock_guard<std::mutex> lock(g_static_mu);             // calls share the array: one at a time, until its stream work is done
+    PCB_CUDA_S(cudaSetDevice(device));
+    StaticDev &D = g_static_dev[device];
+    if (!D.ptr) {
+        // set-up, once per device, with that device current: in host code the array's name is a stand-in, not an address
+        unsigned char *p = nullptr;
+        PCB_CUDA_S(cudaGetSymbolAddress((void **)&p, g_static_scratch));
+        if (!p || ((uintptr_t)p & 255)) return static_fail(PCB_ERR_CUDA, "static scratch at %p", (void *)p);
+        D.ptr = p;
+    }
+    if (!D.grid1[cls]) {                                        // occupancy query (also sets the kernels' shared-memory attribute on this device)
+        const int g1 = pcf_occupancy_grid(1, cls), g2 = pcf_occupancy_grid(2, cls);
+        if (g1 < 1 || g2 < 1) return static_fail(PCB_ERR_CUDA, "occupancy query failed for kernel class %d", cls);
+        D.grid1[cls] = g1; D.grid2[cls] = g2;
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    unsigned char *const base = D.ptr;
+    const uint64_t bytes = (uint64_t)n_windows * stride;
+
+    PCB_CUDA_S(cudaMemsetAsync(base + SO_ERR, 0, 256, st));
+    StaticAdapter ad; memset(&ad, 0, sizeof ad); memcpy(ad.seq, adapter, (size_t)adapter_len); ad.n = adapter_len;
+    const unsigned gs = (unsigned)std::max<int64_t>(1, (n_windows + 255) / 256);
+    k_static_setup<<<gs, 256, 0, st>>>(ad, d_win_len, n_windows, stride);
+    PCB_CUDA_S(cudaGetLastError());
+    PCB_CUDA_S(pcb_launch_encode(reinterpret_cast<const char *>(base + SO_AD_ASCII), base + SO_AD_CODES, 256, st));
+    PCB_CUDA_S(pcb_launch_encode(d_windows, base + SO_ARENA, bytes, st));
+    PCB_CUDA_S(cudaMemsetAsync(base + SO_ARENA + bytes, 0, 64, st));   // the kernels fetch bases a few bytes past a window's end
+
+    PcbLaunch L; memset(&L, 0, sizeof L);
+    L.ad.codes = base + SO_AD_CODES; L.ad.off = reinterpret_cast<const int64_t *>(base + SO_AD_OFF); L.ad.n = 1; L.ad.max_len = adapter_len;
+    L.sc = sc;
+    L.arena = base + SO_ARENA; L.arena_len = bytes;
+    L.out = d_out; L.n_out = n_windows; L.err_flag = reinterpret_cast<int32_t *>(base + SO_ERR);
+    L.src.n_windows = n_windows; L.src.stride = stride; L.src.win_len = reinterpret_cast<const int32_t *>(base + SO_WINLEN);
+    L.src.ids = reinterpret_cast<const int32_t *>(base + SO_IDS); L.src.n_ids = 1; L.src.id_pos = nullptr; L.src.n_ids_total = 1;
+    const int64_t n_units = (n_windows + 63) / 64;
+    L.src.n_units = n_units;
+    L.mmax = stride; L.smax = 1;
+    L.meta = reinterpret_cast<int32_t *>(base + SO_META); L.n_major = 1;
+    // trace scratch of a batch of units, as launch_dp lays it out: checkpoints | end cells | sorted items | surviving items
+    const uint64_t per_unit = pcf_unit_words_trace(L.mmax, cls), ck_unit = per_unit - 128 - 1024;
+    const uint64_t budget = (PCB_STATIC_BYTES - SO_TRACE) / sizeof(uint32_t);
+    const int64_t per_batch = (int64_t)std::min<uint64_t>((uint64_t)n_units, budget / per_unit);
+    if (per_batch < 1) return static_fail(PCB_ERR_RANGE, "pcb_align_windows_static: one unit of class %d needs %llu bytes of scratch", cls, (unsigned long long)per_unit * 4);
+    uint32_t *const sp = reinterpret_cast<uint32_t *>(base + SO_TRACE);
+    L.scratch = sp;
+    L.entries = reinterpret_cast<uint4 *>(sp + ck_unit * (uint64_t)per_batch);
+    L.sorted = reinterpret_cast<PcfItem *>(sp + (ck_unit + 128) * (uint64_t)per_batch);
+    L.surv = reinterpret_cast<PcfItem *>(sp + (ck_unit + 128 + 512) * (uint64_t)per_batch);
+    const int W = PCB_BLOCK / 32;
+    for (int64_t u0 = 0; u0 < n_units; u0 += per_batch) {
+        L.unit0 = u0; L.unit1 = std::min(n_units, u0 + per_batch);
+        const int64_t ctas = (L.unit1 - L.unit0 + W - 1) / W;
+        L.grid = (int)std::min<int64_t>(D.grid1[cls], ctas);
+        PCB_CUDA_S(pcf_launch_pass1(L, cls, st));
+        PCB_CUDA_S(pcf_launch_pass2(L, cls, (int)std::min<int64_t>(D.grid2[cls], ctas), st));
+    }
+    int32_t f = 0;
+    PCB_CUDA_S(cudaMemcpyAsync(&f, base + SO_ERR, sizeof f, cudaMemcpyDeviceToHost, st));
+    PCB_CUDA_S(cudaStreamSynchronize(st));
+    if (f & 128) return static_fail(PCB_ERR_ARG, "pcb_align_windows_static: a window length outside [0, stride]");
+    if (f) return static_fail(PCB_ERR_RANGE, "device reported alignment-window violation (flag %d)", f);
+    return PCB_OK;
+}

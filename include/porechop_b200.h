@@ -223,6 +223,29 @@ int pcb_reset_counters(pcb_context *ctx);
 /* When on, every DP kernel launch is bracketed by its own event pair (adds sync at fetch time). */
 int pcb_set_kernel_timing(pcb_context *ctx, int on);
 
+/* ---- windows x one adapter without any allocation -------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Needs no pcb_context.
+ * Same kernels and the same records as pcb_align_windows with a one-adapter list (the two-pass trace of the fast kernel
+ * classes), but every byte of working memory -- encoded windows, checkpoints, work items, sort tables, error flag --
+ * lives in one file-scope device array of PCB_STATIC_SCRATCH_MB that every GPU loading the library holds until the
+ * process exits.  The call itself calls no cudaMalloc / cudaFree or allocating library routine.
+ *   d_windows, d_win_len, d_out: DEVICE memory of the caller on `device`: n_windows records of `stride` ASCII bytes,
+ *   their lengths (0..stride), and n_windows result records.  adapter: HOST string of adapter_len bases.
+ *   cuda_stream: a cudaStream_t of that device (NULL = the default stream); the call returns when its work on that
+ *   stream is complete, d_out is valid then.
+ * Limits (PCB_ERR_RANGE with a text in pcb_last_error(NULL) beyond them): n_windows <= PCB_STATIC_MAX_WINDOWS, stride <=
+ * PCB_STATIC_MAX_STRIDE, adapters of 1..127 bases of ACGT, affine schemes with -7 <= gap_open < gap_extend < 0 < match.
+ * All calls share the array and find the previous call's contents in it; the call clears what must start at zero.
+ * Calls that overlap on one GPU would race on it: the calls of one process are serialised by a lock that is held until
+ * the call's stream work is done (every process has its own copy of the array). */
+#define PCB_STATIC_SCRATCH_MB   16
+#define PCB_STATIC_MAX_WINDOWS  8192
+#define PCB_STATIC_MAX_STRIDE   256
+int pcb_align_windows_static(int device, const char *adapter, int32_t adapter_len, int match, int mismatch,
+                             int gap_open, int gap_extend, const char *d_windows, const int32_t *d_win_len,
+                             int64_t n_windows, int32_t stride, pcb_result *d_out, void *cuda_stream);
+
 /* Formats one record exactly as ScoredAlignment::getString(); buf >= 160 bytes. */
 void pcb_format_result(const pcb_result *r, char *buf, uint64_t buflen);
 
