@@ -106,9 +106,9 @@ def _stage_windows(eng, reads, read_blob, end_size, at_end):
     """The windows of a phase for the engine: (buffer, lengths) packed on the host, or (None, n) when the engine can cut
     them out of the read blob on the device (the blob is announced once and serves all three phases)."""
     if read_blob is not None and hasattr(eng, 'stage_windows_from_reads'):
-        if getattr(eng, '_blob_id', None) != id(read_blob.buf) or getattr(eng, '_uploaded', None) is None:
+        # (the engine holds the announced array itself: identity of a live object, not an id() that a freed one may pass on)
+        if getattr(eng, '_uploaded', None) is not read_blob.buf:
             eng.upload_reads(read_blob.buf)
-            eng._blob_id = id(read_blob.buf)
         return None, eng.stage_windows_from_reads(read_blob.seq_off, read_blob.seq_len, end_size, at_end)
     return read_blob.windows(end_size, at_end) if read_blob is not None else _windows(reads, end_size, at_end)
 
@@ -374,8 +374,7 @@ def find_adapters_in_read_middles(reads, matching_sets, verbosity, middle_thresh
         entry = np.repeat(np.arange(len(q_read), dtype=np.int64), counts)    # queue entry of every task
         seg_ad = np.arange(int(first[-1]), dtype=np.int64) - first[entry] + q_k0[entry]
         # (the reads may be on the device already: phases A / B announced the same blob for their windows)
-        resident = read_blob is not None and blob is read_blob.buf and getattr(eng, '_blob_id', None) == id(blob) and \
-            getattr(eng, '_uploaded', None) is not None
+        resident = read_blob is not None and blob is read_blob.buf and getattr(eng, '_uploaded', None) is blob
         rec = eng.align_tasks(None if resident else blob, offs[entry], lens[entry].astype(np.int32), seg_ad.astype(np.int32))
         _, full = _parsed_identities(rec, aligned=False)
         r_start, r_end = rec['read_start'], _read_ends(rec)

@@ -108,9 +108,13 @@ class ReadBlob(object):
 
     def seq(self, i):
         """The sequence as NanoporeRead stores it (nanopore_read.py:36-39): upper case, U -> T when U outnumbers T."""
-        s = self.buf[self.seq_off[i]:self.seq_off[i] + self.seq_len[i]].tobytes().decode().upper()
-        if s.count('U') > s.count('T'):
-            s = s.replace('U', 'T')
+        raw = self.buf[self.seq_off[i]:self.seq_off[i] + self.seq_len[i]].tobytes()
+        s = raw.decode()
+        if not s.isupper():
+            s = s.upper()
+        if b'U' in raw or b'u' in raw:                       # (a memchr: counting is only needed when there is a U at all)
+            if s.count('U') > s.count('T'):
+                s = s.replace('U', 'T')
         return s
 
     def full_name(self, i):
