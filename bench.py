@@ -287,6 +287,11 @@ def trims_from_hits(n, hs, he):
     return start, end
 
 
+def trims_from_device(trim_s, trim_e):
+    """The same from pcb_fetch_trims (the maximum is taken on the device: 4 bytes per read end, -1 = nothing kept)."""
+    return np.where(trim_s >= 0, trim_s.astype(np.int64) + EXTRA_END_TRIM, 0), np.where(trim_e >= 0, trim_e.astype(np.int64) + EXTRA_END_TRIM, 0)
+
+
 def two_barcode_calls(top_s, top_e):
     """determine_barcode with require_two_barcodes (nanopore_read.py:408-447) for every read at once, from the two best
     barcode identities per end (pcb_fetch_top2: descending, the first in adapter order among equals, as the reference's
@@ -359,6 +364,7 @@ def run_gpu_arm(args):
         ident_s = pin(np.zeros((n, int(want_s.sum())), dtype=np.uint16))
         ident_e = pin(np.zeros((n, int(want_e.sum())), dtype=np.uint16))
         top_s, top_e = pin(np.zeros(n, dtype=TOP2_DTYPE)), pin(np.zeros(n, dtype=TOP2_DTYPE))
+        trim_s, trim_e = pin(np.full(n, -1, dtype=np.int32)), pin(np.full(n, -1, dtype=np.int32))
     if has_tasks:
         blob, task_ad = pin(wl['blob']), pin(wl['task_ad'])
         seg_off, seg_len = pin(wl['seg_off']), pin(wl['seg_len'])
@@ -425,7 +431,11 @@ def run_gpu_arm(args):
     cut = [n * p // PARTS for p in range(PARTS + 1)]
     A = N_MIDDLE_ADAPTERS
 
-    def e2e_step():
+    stamps = []
+
+    def e2e_step(trace=False):
+        mark = (lambda what: stamps.append((what, time.perf_counter()))) if trace else (lambda what: None)
+        mark('start')
         if has_tasks:
             # the reads are all in host memory before the first alignment (porechop_abi.py:61-71): announce the blob, so
             # that it crosses PCIe under the window kernels; every byte still travels inside the timed region, every step
@@ -439,12 +449,17 @@ def run_gpu_arm(args):
                                             hits_buf=hits_s[16 * a:16 * b], ident_buf=False if binning else ident_s[a:b])
                 if binning:
                     eng.fetch_top2(b - a, out=top_s[a:b])
+                if has_tasks:
+                    eng.fetch_trims(b - a, out=trim_s[a:b])
                 eng.select_slot(2 * p + 1)
                 he = eng.align_windows_hits(ebuf[a:b], wlen[a:b], wl['end_ids'], END_THRESHOLD, True, END_SIZE, MIN_TRIM_SIZE, want_ident=want_e,
                                             hits_buf=hits_e[16 * a:16 * b], ident_buf=False if binning else ident_e[a:b])
                 if binning:
                     eng.fetch_top2(b - a, out=top_e[a:b])
+                if has_tasks:
+                    eng.fetch_trims(b - a, out=trim_e[a:b])
                 res.append((hs, he))
+                mark('B%d queued' % p)
         n_hits = [0, 0]
         for p in range(PARTS):
             a, b = cut[p], cut[p + 1]
@@ -455,16 +470,23 @@ def run_gpu_arm(args):
                 else:
                     eng.wait()
                 n_hits[0] += hs.n_hits; n_hits[1] += he.n_hits
+                mark('B%d on the host' % p)
             if has_tasks:
                 if has_windows:          # the trimmed reads are what phase C aligns (nanopore_read.py:66-72, :225)
-                    st, et = trims_from_hits(b - a, hs, he)
+                    st, et = trims_from_device(trim_s[a:b], trim_e[a:b])
                     lo = np.minimum(st, lens64[a:b])
                     hi = np.maximum(lens64[a:b] - et, lo)
                     seg_off[A * a:A * b] = np.repeat(off64[a:b] + lo, A)
                     seg_len[A * a:A * b] = np.repeat(hi - lo, A)
                 eng.select_slot(4 + p)
+                mark('trims %d' % p)
                 eng.align_tasks(None, seg_off[A * a:A * b], seg_len[A * a:A * b], task_ad[A * a:A * b], out=out_m[A * a:A * b])
+                mark('C%d queued' % p)
+                if trace and has_windows:                   # (the untimed trace step also checks the device's trims against the hit lists)
+                    st2, et2 = trims_from_hits(b - a, hs, he)
+                    assert np.array_equal(st, st2) and np.array_equal(et, et2)
         eng.wait()
+        mark('all collected')
         state['hits'] = tuple(n_hits)
         state['parts'] = res
         if binning:
@@ -483,6 +505,9 @@ def run_gpu_arm(args):
     e2e_s = max(time.perf_counter() - t0, e2e_ms_ev / 1000.0)
     barrier()
     c1 = eng.counters()
+    if os.environ.get('PCB_E2E_TRACE') and rank == 0:          # host-side time line of one more (untimed) step, to stderr
+        e2e_step(trace=True)
+        print('e2e step: ' + ', '.join('%s %.1f ms' % (w_, (t_ - stamps[0][1]) * 1e3) for w_, t_ in stamps[1:]), file=sys.stderr)
     eng.set_deferred(False)
     sampler.stop_flag = True; sampler.join(timeout=3)
     e2e_s = max_over_ranks(e2e_s)
@@ -562,7 +587,7 @@ def run_gpu_arm(args):
                     'h2d_bytes_per_step': int((c1['h2d_bytes'] - c0['h2d_bytes']) / args.steps),
                     'd2h_bytes_per_step': int((c1['d2h_bytes'] - c0['d2h_bytes']) / args.steps),
                     'gcups': cells_job * args.steps / e2e_s / 1e9, 'checksum': checksum,
-                    'phases': 'in %d parts: B (reduced: hits + 16-bit barcode identities) -> that part collected -> trims on the host -> C (32-byte records) beside the next part\'s B' % PARTS
+                    'phases': 'in %d parts: B (reduced: hits, trim amounts, 16-bit barcode identities) -> that part collected on the host -> C on the trimmed reads (32-byte records) beside the next part\'s B' % PARTS
                               if has_windows and has_tasks else ('B (reduced: hits + the two best barcode identities per read and end) -> wait -> binning decision on the host' if has_windows else 'C'),
                     'job_counters': {'reads': merged_counts[0], 'start_hits': merged_counts[1], 'end_hits': merged_counts[2],
                                      **({'reads_binned': merged_counts[3]} if len(merged_counts) > 3 else {})}},

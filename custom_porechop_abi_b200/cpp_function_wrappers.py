@@ -91,6 +91,7 @@ C_LIB.check_compatibility.argtypes = [c_char_p, c_char_p]
 C_LIB.check_compatibility.restype = c_int
 C_LIB.pcb_check_compatibility.argtypes = [_P, c_char_p, POINTER(c_int64), c_int32, c_void_p, c_void_p, c_int64, c_void_p]
 C_LIB.pcb_fetch_top2.argtypes = [_P, c_void_p, c_int64]
+C_LIB.pcb_fetch_trims.argtypes = [_P, c_void_p, c_int64]
 C_LIB.pcb_align_tasks.argtypes = [_P, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
 C_LIB.pcb_upload_reads.argtypes = [_P, c_void_p, c_int64]
 C_LIB.pcb_set_deferred.argtypes = [_P, c_int]

@@ -53,7 +53,7 @@ struct pcb_context {
     cudaEvent_t ev_fork = nullptr, ev_join[N_SIDE] = {};
     int n_pipes = 4;                      // pipelines a cross product is dealt to (main stream + side streams; PCB_STREAMS)
     cudaStream_t pstream = nullptr;       // deferred mode: task staging + planning, beside the kernels of earlier calls
-    cudaEvent_t tasks_done = nullptr;     // the task kernels of the last run no longer read the plan / segment arrays
+    cudaEvent_t tasks_done[2] = {};       // the task kernels that ran on plan set 0 / 1 no longer read its arrays
     bool deferred = false;                // pcb_set_deferred: host-buffer calls only enqueue; pcb_wait collects
     cudaStream_t in_stream() const { return deferred ? ustream : stream; }     // window / id staging copies
     cudaStream_t plan_stream() const { return deferred ? pstream : stream; }   // segment copies + planner kernels
@@ -96,6 +96,9 @@ struct pcb_context {
         DevBuf<uint16_t> d_ident;
         DevBuf<long long> d_total;
         DevBuf<pcb_top2> d_top2;
+        DevBuf<int32_t> d_trim;           // pcb_fetch_trims
+        pcb_hit_filter hit_filter{};      // filter of the slot's last pcb_align_windows_hits call
+        bool has_filter = false;
         DevBuf<int64_t> d_roff;           // pcb_stage_windows_from_reads: where the reads are in the blob
         DevBuf<int32_t> d_rlen;
         DevBuf<uint8_t> d_aux;            // check_compatibility: end-column match of every task
@@ -129,8 +132,14 @@ struct pcb_context {
         uint64_t scratch_words = 0, stamp = 0;
         bool valid = false;
     };
-    enum { MAX_PIECES = 4 };
+    enum { MAX_PIECES = 16, PLAN_PIECES = 4 };   // pieces an announced blob travels in / pieces (= plans) of a blob that comes with its tasks
     TaskPlan plans[MAX_PIECES];
+    // Two task calls on one announced blob (a step that goes through in parts): the second call's planner fills `alt_plan`
+    // while the first call's kernels still read plans[0], and the other way round the next time (plan_flip); the pieces
+    // of the blob are described by plans[] either way.
+    TaskPlan alt_plan;
+    int plan_flip = 0;
+    TaskPlan &one_plan() { return plan_flip ? alt_plan : plans[0]; }
     int n_pieces = 1, pieces_sent = 0;
     int plan_pieces = 1;                 // plans over the blob: one per piece (kernels of piece p under the copy of piece p+1), or one for
                                          // the whole blob when it was announced early and is on the device before its tasks are (pcb_upload_reads)
@@ -204,7 +213,8 @@ extern "C" int pcb_create(int device, pcb_context **out)
         (e = cudaStreamCreateWithPriority(&c->pstream, cudaStreamNonBlocking, -1)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&c->hstream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
-        (e = cudaEventCreateWithFlags(&c->tasks_done, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&c->tasks_done[0], cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&c->tasks_done[1], cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
         (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
         g_global_err = std::string("context setup failed: ") + cudaGetErrorString(e);
@@ -252,6 +262,7 @@ extern "C" void pcb_destroy(pcb_context *c)
     }
     if (c->h_totals) cudaFreeHost(c->h_totals);
     for (auto &pl : c->plans) { pl.release(); if (pl.ready) cudaEventDestroy(pl.ready); }
+    c->alt_plan.release();
     c->d_seg_off.release(); c->d_plan_i64.release(); c->d_seg_len.release(); c->d_seg_ad.release(); c->d_plan_i32.release(); c->d_adinfo.release();
     c->d_scratch.release(); c->d_meta.release(); c->d_err.release();
     for (int k = 0; k < pcb_context::N_SIDE; ++k) { c->d_scratch_s[k].release(); c->d_meta_s[k].release(); }
@@ -266,7 +277,7 @@ extern "C" void pcb_destroy(pcb_context *c)
         if (c->ev_join[k]) cudaEventDestroy(c->ev_join[k]);
     }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    if (c->tasks_done) cudaEventDestroy(c->tasks_done);
+    for (cudaEvent_t ev : c->tasks_done) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -550,7 +561,17 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
     if (!c->deferred) PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
     // an announced read blob (pcb_upload_reads) travels under this call's kernels: its pieces go out now, behind this
     // call's own copies on the copy engine
-    if ((host_out || c->deferred) && c->uploaded_len >= 0 && c->pending_blob && (rc = send_pieces(c, c->pieces_sent + (c->n_pieces + 1) / 2))) return rc;
+    // How much of it: what the copy engine moves while this call's kernels run (about 4.4 T cell updates/s against 50 GB/s:
+    // a byte per 88 cells), so that the NEXT window call's own small copies do not wait behind more blob than that.
+    // (Half of the blob per call, the first policy, made the second and third window call of a step wait 4 ms each.)
+    if ((host_out || c->deferred) && c->uploaded_len >= 0 && c->pending_blob) {
+        int64_t sum_n = 0;
+        for (int k = 0; k < S.n_ids; ++k) sum_n += c->ad_off[(size_t)S.h_ids[(size_t)k] + 1] - c->ad_off[(size_t)S.h_ids[(size_t)k]];
+        const int64_t piece = std::max<int64_t>(1, (c->uploaded_len + c->n_pieces - 1) / c->n_pieces);
+        const int64_t now = S.sum_winlen * sum_n / 88;
+        const int k = (int)std::max<int64_t>(1, std::min<int64_t>(c->n_pieces, (now + piece - 1) / piece));
+        if ((rc = send_pieces(c, c->pieces_sent + k))) return rc;
+    }
     const int n = S.n_ids;
     // classes in ascending order of work: the small launches first (their tails then overlap nothing bigger than
     // themselves), the biggest last (it is the one that is pipelined against the copies)
@@ -768,6 +789,7 @@ extern "C" int pcb_align_windows_hits(pcb_context *c, const char *windows, int64
     S.h_identcol.assign((size_t)std::max(1, n_ids), -1);
     if (want_ident) for (int k = 0; k < n_ids; ++k) if (want_ident[k]) S.h_identcol[(size_t)k] = n_want++;
     S.n_want = n_want;                                      // ident == NULL: the identities stay on the device (pcb_fetch_top2)
+    S.hit_filter = *filter; S.has_filter = true;
     if (n_windows == 0 || n_ids == 0) return PCB_OK;
     const int64_t nb = (n_windows + 1023) / 1024;
     PCB_CUDA(c, S.d_cnt.reserve((size_t)(n_windows + nb + 2)));
@@ -805,6 +827,29 @@ extern "C" int pcb_fetch_top2(pcb_context *c, pcb_top2 *top2, int64_t n_windows)
     PCB_CUDA(c, cudaMemcpyAsync(top2, S.d_top2.p, sizeof(pcb_top2) * (size_t)n_windows, cudaMemcpyDeviceToHost, c->stream));
     c->cnt.d2h_bytes += (int64_t)sizeof(pcb_top2) * n_windows;
     if (!c->deferred) PCB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PCB_OK;
+}
+
+// The trim amounts of the slot's last pcb_align_windows_hits call (same filter), reduced on the device; delivered like that
+// call's fixed-size results: at return, or in deferred mode with pcb_wait_slot / pcb_wait.
+extern "C" int pcb_fetch_trims(pcb_context *c, int32_t *trim, int64_t n_windows)
+{
+    if (!c || n_windows < 0 || (n_windows > 0 && !trim)) return PCB_ERR_ARG;
+    cudaSetDevice(c->device);
+    pcb_context::Slot &S = c->S();
+    if (!S.has_filter) return c->fail(PCB_ERR_ARG, "pcb_fetch_trims without a pcb_align_windows_hits call in this slot");
+    if (n_windows != S.n_windows) return c->fail(PCB_ERR_ARG, "asked for %lld windows, the slot's last call had %lld", (long long)n_windows, (long long)S.n_windows);
+    if (n_windows == 0) return PCB_OK;
+    PCB_CUDA(c, S.d_trim.reserve((size_t)n_windows));
+    if (S.n_ids > 0) PCB_CUDA(c, pcb_launch_trims(S.d_out.p, n_windows, S.n_ids, S.hit_filter, S.d_trim.p, c->stream));
+    else PCB_CUDA(c, cudaMemsetAsync(S.d_trim.p, 0xFF, sizeof(int32_t) * (size_t)n_windows, c->stream));
+    c->cnt.kernel_launches++;
+    PCB_CUDA(c, cudaEventRecord(S.done, c->stream));
+    PCB_CUDA(c, cudaStreamWaitEvent(c->cstream, S.done, 0));
+    PCB_CUDA(c, cudaMemcpyAsync(trim, S.d_trim.p, sizeof(int32_t) * (size_t)n_windows, cudaMemcpyDeviceToHost, c->cstream));
+    c->cnt.d2h_bytes += (int64_t)sizeof(int32_t) * n_windows;
+    PCB_CUDA(c, cudaEventRecord(S.done, c->cstream));       // pcb_wait_slot waits for this copy too
+    if (!c->deferred) PCB_CUDA(c, cudaStreamSynchronize(c->cstream));
     return PCB_OK;
 }
 
@@ -922,6 +967,7 @@ static int stage_segments(pcb_context *c, int64_t blob_len, const int64_t *seg_o
                           const int32_t *task_adapter, int64_t n_tasks)
 {
     for (auto &pl : c->plans) pl.valid = false;
+    c->alt_plan.valid = false;
     c->n_tasks = 0;
     // result slots, task and chunk indices are 32-bit on the device (PcbTask.out_idx, PcbLong.chunk0 / win_slot)
     if (n_tasks >= (1ll << 31) - 64) return c->fail(PCB_ERR_RANGE, "%lld tasks in one call: the task path indexes with 32 bits", (long long)n_tasks);
@@ -929,7 +975,17 @@ static int stage_segments(pcb_context *c, int64_t blob_len, const int64_t *seg_o
     PCB_CUDA(c, c->d_seg_len.reserve((size_t)n_tasks + 1));
     PCB_CUDA(c, c->d_seg_ad.reserve((size_t)n_tasks + 1));
     // deferred mode: the copies and the planner run on their own stream, beside the kernels of earlier calls
-    if (c->deferred) PCB_CUDA(c, cudaStreamWaitEvent(c->pstream, c->tasks_done, 0));
+    // (the plan set alternates between the task calls on an announced blob, so the planner of this call only waits for
+    //  the kernels of the call before the last one)
+    if (c->deferred && c->plan_pieces == 1 && c->uploaded_len >= 0) {
+        c->plan_flip ^= 1;
+        c->alt_plan.b0 = c->plans[0].b0; c->alt_plan.b1 = c->plans[0].b1;
+        c->alt_plan.end_lo = c->plans[0].end_lo; c->alt_plan.end_hi = c->plans[0].end_hi;
+        PCB_CUDA(c, cudaStreamWaitEvent(c->pstream, c->tasks_done[c->plan_flip], 0));
+    } else {
+        c->plan_flip = 0;
+        if (c->deferred) for (cudaEvent_t ev : c->tasks_done) PCB_CUDA(c, cudaStreamWaitEvent(c->pstream, ev, 0));
+    }
     if (n_tasks) {          // asynchronous from pinned memory: the host-side checks below run under the copies
         PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_off.p, seg_off, sizeof(int64_t) * n_tasks, cudaMemcpyHostToDevice, c->plan_stream()));
         PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_len.p, seg_len, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->plan_stream()));
@@ -956,7 +1012,7 @@ static int blob_pieces(int64_t blob_len)
 {
     const char *pm = getenv("PCB_PIECE_MIN_BYTES");           // tests lower it to reach the pieced path with small inputs
     const int64_t piece_min = pm ? atoll(pm) : (64ll << 20);
-    return blob_len >= piece_min && blob_len >= 4096 ? pcb_context::MAX_PIECES : 1;
+    return blob_len >= piece_min && blob_len >= 4096 ? pcb_context::PLAN_PIECES : 1;
 }
 
 static int stage_tasks(pcb_context *c, const char *seq_blob, int64_t blob_len, const int64_t *seg_off,
@@ -978,7 +1034,7 @@ extern "C" int pcb_upload_reads(pcb_context *c, const char *seq_blob, int64_t bl
     c->n_tasks = 0;
     // nothing is sent yet: the window calls that follow pump the pieces AFTER their own (small) copies, so that those
     // do not wait behind the blob on the copy engine; pcb_align_tasks sends whatever is left
-    int rc = setup_blob(c, seq_blob, blob_len, blob_pieces(blob_len), 0, true);
+    int rc = setup_blob(c, seq_blob, blob_len, blob_pieces(blob_len) > 1 ? (int)pcb_context::MAX_PIECES : 1, 0, true);
     if (rc) return rc;
     c->uploaded_len = blob_len;
     return PCB_OK;
@@ -1182,12 +1238,13 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
     c->S().n_results = (int64_t)nt;
     if (nt == 0) return PCB_OK;
     int rc;
+    auto plan_of = [&](int p) -> pcb_context::TaskPlan & { return c->plan_pieces == 1 ? c->one_plan() : c->plans[p]; };
     for (int p = 0; p < c->plan_pieces; ++p)
-        if ((!c->plans[p].valid || c->plans[p].stamp != c->stamp) && (rc = build_task_plan(c, c->plans[p], p == 0))) return rc;
+        if ((!plan_of(p).valid || plan_of(p).stamp != c->stamp) && (rc = build_task_plan(c, plan_of(p), p == 0))) return rc;
     if ((rc = send_pieces(c, c->n_pieces))) return rc;
     PCB_CUDA(c, c->S().d_out.reserve(nt));
     uint64_t scratch = 0;
-    for (int p = 0; p < c->plan_pieces; ++p) scratch = std::max(scratch, c->plans[p].scratch_words);
+    for (int p = 0; p < c->plan_pieces; ++p) scratch = std::max(scratch, plan_of(p).scratch_words);
     PCB_CUDA(c, c->d_scratch.reserve((size_t)scratch));
     if (!c->deferred) PCB_CUDA(c, cudaMemsetAsync(c->d_err.p, 0, sizeof(int32_t), c->stream));
     auto arrive = [&](pcb_context::TaskPlan &P) -> int {   // this piece of the blob is on the device, as codes
@@ -1203,8 +1260,8 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
     };
     if (c->plan_pieces == 1) for (int p = 1; p < c->n_pieces; ++p) if ((rc = arrive(c->plans[p]))) return rc;
     for (int p = 0; p < c->plan_pieces; ++p) {
-        pcb_context::TaskPlan &P = c->plans[p];
-        if ((rc = arrive(P))) return rc;
+        pcb_context::TaskPlan &P = plan_of(p);
+        if ((rc = arrive(c->plans[p]))) return rc;
         bool merged = false;
         for (const auto &pl : P.launches) {
             if (pl.kind == 2 && !merged) {
@@ -1219,7 +1276,7 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
             if ((rc = launch_dp(c, L, pl.trace, pl.cells, pl.cls))) return rc;
         }
     }
-    PCB_CUDA(c, cudaEventRecord(c->tasks_done, c->stream));
+    PCB_CUDA(c, cudaEventRecord(c->tasks_done[c->plan_pieces == 1 ? c->plan_flip : 0], c->stream));
     return PCB_OK;
 }
 

@@ -202,6 +202,7 @@ cudaError_t pcb_launch_hits(const pcb_result *rec, int64_t n_windows, int32_t n_
                             long long *total, pcb_hit *hits, int64_t cap, const int32_t *ident_col, int32_t n_want, uint16_t *ident,
                             int32_t *err_flag, cudaStream_t st);
 
+cudaError_t pcb_launch_trims(const pcb_result *rec, int64_t n_windows, int32_t n_ids, const pcb_hit_filter &f, int32_t *trim, cudaStream_t st);
 cudaError_t pcb_launch_top2(const uint16_t *ident, int64_t n_windows, int32_t n_want, pcb_top2 *out, cudaStream_t st);
 
 cudaError_t pcb_launch_encode(const char *ascii, uint8_t *codes, uint64_t n, cudaStream_t st);

@@ -87,6 +87,23 @@ __global__ void k_hits_count(const pcb_result *__restrict__ rec, int64_t n_windo
     if (lane == 0) cnt[w] = n;
 }
 
+// one warp per window: the trim amount its kept alignments ask for (find_start_trim / find_end_trim, nanopore_read.py:187-190,
+// :209-212, before extra_trim_size is added): max of read_end (exclusive) at the start, of end_size - read_start at the end;
+// -1 = no alignment kept
+__global__ void k_trims(const pcb_result *__restrict__ rec, int64_t n_windows, int32_t n_ids, pcb_hit_filter f, int32_t *__restrict__ trim)
+{
+    const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= n_windows) return;
+    const int lane = threadIdx.x & 31;
+    int best = -1;
+    for (int k = lane; k < n_ids; k += 32) {
+        const pcb_result r = rec[w * n_ids + k];
+        if (hit_pass(r, f)) best = max(best, f.at_end ? f.end_size - r.read_start : r.read_end + 1);
+    }
+    best = __reduce_max_sync(0xffffffffu, best);
+    if (lane == 0) trim[w] = best;
+}
+
 // exclusive prefix sum of int32 counts, three steps (1024 per block)
 __global__ void k_scan_blocks(int32_t *__restrict__ v, int64_t n, int32_t *__restrict__ bsum)
 {
@@ -203,6 +220,13 @@ __global__ void k_top2(const uint16_t *__restrict__ ident, int64_t n_windows, in
 }
 
 }  // namespace
+
+cudaError_t pcb_launch_trims(const pcb_result *rec, int64_t n_windows, int32_t n_ids, const pcb_hit_filter &f, int32_t *trim, cudaStream_t st)
+{
+    if (n_windows <= 0) return cudaSuccess;
+    k_trims<<<(unsigned)((n_windows * 32 + 255) / 256), 256, 0, st>>>(rec, n_windows, n_ids, f, trim);
+    return cudaGetLastError();
+}
 
 cudaError_t pcb_launch_top2(const uint16_t *ident, int64_t n_windows, int32_t n_want, pcb_top2 *out, cudaStream_t st)
 {

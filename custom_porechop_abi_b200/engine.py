@@ -211,6 +211,15 @@ class AlignmentEngine(object):
             self._held.append((out,))
         return out
 
+    def fetch_trims(self, n_windows, out=None):
+        """Per window of this slot's last align_windows_hits call the trim amount its kept alignments ask for, before
+        extra_trim_size (pcb_fetch_trims): int32, -1 = none kept."""
+        out = np.empty(n_windows, dtype=np.int32) if out is None else out
+        self._check(w.C_LIB.pcb_fetch_trims(self._h, _ptr(out), n_windows), 'pcb_fetch_trims')
+        if getattr(self, '_deferred', False):
+            self._held.append((out,))
+        return out
+
     def stage_windows(self, win_buf, win_len, adapter_ids):
         win_buf = np.ascontiguousarray(win_buf, dtype=np.uint8)
         win_len = np.ascontiguousarray(win_len, dtype=np.int32)

@@ -142,6 +142,12 @@ int pcb_stage_windows_from_reads(pcb_context *ctx, const int64_t *read_off, cons
 typedef struct pcb_top2 { int16_t best, second; uint16_t best_ident, second_ident; } pcb_top2;
 int pcb_fetch_top2(pcb_context *ctx, pcb_top2 *top2, int64_t n_windows);
 
+/* The trim amount the kept alignments of window w ask for, before extra_trim_size is added (find_start_trim /
+ * find_end_trim, nanopore_read.py:187-190, :209-212: the maximum of read_end at the start, of end_size - read_start at the
+ * end), -1 when none was kept: what phase C needs of phase B, 4 bytes per read end.  Same slot and filter as the
+ * pcb_align_windows_hits call before it; in deferred mode valid after pcb_wait_slot / pcb_wait. */
+int pcb_fetch_trims(pcb_context *ctx, int32_t *trim, int64_t n_windows);
+
 /* Explicit task list (phase C, porechop_abi.py:457-522, and anything irregular): task t aligns
  * seq_blob[seg_off[t] .. seg_off[t]+seg_len[t]) against adapter task_adapter[t].  Any length.
  * HOST buffers. */
@@ -162,8 +168,10 @@ int pcb_upload_reads(pcb_context *ctx, const char *seq_blob, int64_t blob_len);
  * same shape: pcb_align_windows / pcb_align_tasks return once their copies and kernels are queued, so the copies of
  * one call run under the kernels of the one before, and pcb_wait(ctx) returns when every queued call is complete,
  * its results are in the callers' buffers, and reports the first device-side error of the batch.  Between two
- * pcb_wait calls: input and output buffers stay untouched, every call uses its own slot (pcb_select_slot), and at
- * most one pcb_align_tasks is queued.  pcb_set_deferred waits for queued work before it switches. */
+ * pcb_wait calls: input and output buffers stay untouched and every call uses its own slot (pcb_select_slot).  Several
+ * pcb_align_tasks(ctx, NULL, ...) calls on one announced blob may be queued (a batch that goes through in parts): their
+ * plans alternate between two sets of device arrays, so the planner of one runs beside the kernels of the one before.
+ * pcb_set_deferred waits for queued work before it switches. */
 int pcb_set_deferred(pcb_context *ctx, int on);
 int pcb_wait(pcb_context *ctx);
 /* Collects ONE slot's queued pcb_align_windows_hits call while the calls queued in other slots keep running: the caller

@@ -457,15 +457,20 @@ def test_reduced_outputs_match_full_records(engine, thr, at_end, min_trim):
     assert np.array_equal(top['best'], order[:, 0]) and np.array_equal(top['second'], order[:, 1])
     rows = np.arange(len(lens))
     assert np.array_equal(top['best_ident'], res.ident[rows, order[:, 0]]) and np.array_equal(top['second_ident'], res.ident[rows, order[:, 1]])
+    # what phase C needs of phase B: the trim amount per window (find_start_trim / find_end_trim before extra_trim_size)
+    trim = engine.fetch_trims(len(lens))
+    value = np.where(hit, (150 - rec['read_start']) if at_end else (rec['read_end'] + 1), -1)
+    assert np.array_equal(trim, value.max(axis=1))
     # the same through submit / collect
     with engine.deferred():                      # every queued call in its own slot
         engine.select_slot(1)
         res2 = engine.align_windows_hits(buf, lens, ids, thr, at_end, 150, min_trim, want_ident=want, hits_cap=rec.size)
+        trim2 = engine.fetch_trims(len(lens))
         engine.select_slot(2)
         best2 = engine.align_windows_best(buf, lens, ids)
     engine.select_slot(0)
     assert res2.n_hits == res.n_hits and np.array_equal(res2.hits, res.hits) and np.array_equal(res2.ident, res.ident)
-    assert np.array_equal(best2, best)
+    assert np.array_equal(best2, best) and np.array_equal(trim2, trim)
 
 
 @pytest.mark.parametrize('scores', [(7, -6, -5, -1), (10, -10, -10, -1), (4, -3, -7, -3)])
