@@ -436,7 +436,7 @@ def run_gpu_arm(args):
     def e2e_step(trace=False):
         mark = (lambda what: stamps.append((what, time.perf_counter()))) if trace else (lambda what: None)
         mark('start')
-        if has_tasks:
+        if has_tasks and has_windows:
             # the reads are all in host memory before the first alignment (porechop_abi.py:61-71): announce the blob, so
             # that it crosses PCIe under the window kernels; every byte still travels inside the timed region, every step
             eng.upload_reads(blob)
@@ -480,7 +480,9 @@ def run_gpu_arm(args):
                     seg_len[A * a:A * b] = np.repeat(hi - lo, A)
                 eng.select_slot(4 + p)
                 mark('trims %d' % p)
-                eng.align_tasks(None, seg_off[A * a:A * b], seg_len[A * a:A * b], task_ad[A * a:A * b], out=out_m[A * a:A * b])
+                # (without window calls to hide it behind, the blob goes with the task call itself: in pieces, each with its own
+                #  plan, so that the kernels of one piece run under the copy of the next)
+                eng.align_tasks(None if has_windows else blob, seg_off[A * a:A * b], seg_len[A * a:A * b], task_ad[A * a:A * b], out=out_m[A * a:A * b])
                 mark('C%d queued' % p)
                 if trace and has_windows:                   # (the untimed trace step also checks the device's trims against the hit lists)
                     st2, et2 = trims_from_hits(b - a, hs, he)

@@ -257,10 +257,14 @@ def test_pipelined_host_buffer_paths_equal_resident(engine):
     one = engine.align_tasks(blob, seg_off, seg_len, ad)
     os.environ['PCB_PIECE_MIN_BYTES'] = '4096'
     try:
-        pieced = engine.align_tasks(blob, seg_off, seg_len, ad)
+        for pieces in (None, '5', '16'):            # (by default a blob of this size goes in 2 pieces)
+            if pieces:
+                os.environ['PCB_PLAN_PIECES'] = pieces
+            pieced = engine.align_tasks(blob, seg_off, seg_len, ad)
+            assert pieced.tobytes() == one.tobytes(), pieces
     finally:
         del os.environ['PCB_PIECE_MIN_BYTES']
-    assert pieced.tobytes() == one.tobytes()
+        os.environ.pop('PCB_PLAN_PIECES', None)
     # announced blob (pcb_upload_reads): it travels under the window calls made in between; NULL blob in the task call
     for env in (None, '4096'):
         if env:
@@ -295,6 +299,15 @@ def test_pipelined_host_buffer_paths_equal_resident(engine):
                 engine.select_slot(0); d1 = engine.align_windows(ebuf, lens, e_ids)
                 engine.select_slot(1); d2 = engine.align_windows(sbuf, lens, s_ids)
                 engine.select_slot(2); d3 = engine.align_tasks(None, seg_off, seg_len, ad)
+            with engine.deferred():                             # a batch that goes through in parts: three task calls on one announced blob
+                engine.upload_reads(blob)
+                engine.select_slot(0); engine.align_windows(ebuf, lens, e_ids)
+                third = (len(ad) // 3 // len(ids)) * len(ids)
+                parts = []
+                for q, (a0, a1) in enumerate(((0, third), (third, 2 * third), (2 * third, len(ad)))):
+                    engine.select_slot(3 + q)
+                    parts.append(engine.align_tasks(None, seg_off[a0:a1], seg_len[a0:a1], ad[a0:a1]))
+            assert np.concatenate(parts).tobytes() == one.tobytes()
             with engine.deferred():                             # a second batch reuses the slots and the plan buffers
                 engine.select_slot(1); d4 = engine.align_windows(ebuf, lens, e_ids)
                 engine.select_slot(2); d5 = engine.align_tasks(blob, seg_off + cut, seg_len - 2 * cut, ad)
