@@ -111,7 +111,7 @@ struct pcb_context {
     int cur = 0;
     Slot &S() { return slots[cur]; }
     // explicit tasks
-    int64_t n_tasks = 0, task_long_cols = 0, task_cells = 0;
+    int64_t n_tasks = 0, task_long_cols = 0, task_cells = 0, task_max_end = 0;   // task_max_end: where the last segment of the staged list ends in the blob
     DevBuf<int64_t> d_seg_off, d_plan_i64;
     DevBuf<int32_t> d_seg_len, d_seg_ad, d_plan_i32;
     DevBuf<PcbAdInfo> d_adinfo;
@@ -991,7 +991,7 @@ static int stage_segments(pcb_context *c, int64_t blob_len, const int64_t *seg_o
         PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_len.p, seg_len, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->plan_stream()));
         PCB_CUDA(c, cudaMemcpyAsync(c->d_seg_ad.p, task_adapter, sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, c->plan_stream()));
     }
-    int64_t long_cols = 0, cells = 0;
+    int64_t long_cols = 0, cells = 0, max_end = 0;
     for (int64_t t = 0; t < n_tasks; ++t) {
         const bool bad_seg = seg_len[t] < 0 || seg_off[t] < 0 || seg_off[t] + seg_len[t] > blob_len;
         const bool bad_ad = task_adapter[t] < 0 || task_adapter[t] >= c->n_adapters;
@@ -1001,9 +1001,10 @@ static int stage_segments(pcb_context *c, int64_t blob_len, const int64_t *seg_o
             return c->fail(PCB_ERR_ARG, "task %lld: adapter id %d out of range", (long long)t, task_adapter[t]);
         }
         if (seg_len[t] > 960) long_cols += seg_len[t];
+        max_end = std::max<int64_t>(max_end, seg_off[t] + seg_len[t]);
         cells += (int64_t)seg_len[t] * (c->ad_off[(size_t)task_adapter[t] + 1] - c->ad_off[(size_t)task_adapter[t]]);
     }
-    c->n_tasks = n_tasks; c->task_long_cols = long_cols; c->task_cells = cells;
+    c->n_tasks = n_tasks; c->task_long_cols = long_cols; c->task_cells = cells; c->task_max_end = max_end;
     c->cnt.h2d_bytes += 16 * n_tasks;
     return PCB_OK;
 }
@@ -1262,7 +1263,10 @@ extern "C" int pcb_run_tasks_resident(pcb_context *c)
         }
         return PCB_OK;
     };
-    if (c->plan_pieces == 1) for (int p = 1; p < c->n_pieces; ++p) if ((rc = arrive(c->plans[p]))) return rc;
+    // one plan over an announced blob: it waits for the pieces its segments reach into, not for the whole blob (a batch that
+    // goes through in parts starts the first part's tasks while the later reads are still on the bus; the kernels fetch
+    // bases up to 8 bytes past a segment's end)
+    if (c->plan_pieces == 1) for (int p = 1; p < c->n_pieces; ++p) if (c->plans[p].b0 < c->task_max_end + 16 && (rc = arrive(c->plans[p]))) return rc;
     for (int p = 0; p < c->plan_pieces; ++p) {
         pcb_context::TaskPlan &P = plan_of(p);
         if ((rc = arrive(c->plans[p]))) return rc;
