@@ -256,7 +256,7 @@ extern "C" void pcb_destroy(pcb_context *c)
     c->d_ad_codes.release(); c->d_ad_off.release(); c->d_ascii.release(); c->d_ascii_t.release(); c->d_arena_t.release();
     for (auto &sl : c->slots) {
         sl.d_arena.release(); sl.d_ascii.release(); sl.d_winlen.release(); sl.d_ids.release(); sl.d_out.release();
-        sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release(); sl.d_top2.release(); sl.d_aux.release(); sl.d_roff.release(); sl.d_rlen.release();
+        sl.d_keys.release(); sl.d_best.release(); sl.d_cnt.release(); sl.d_identcol.release(); sl.d_hits.release(); sl.d_ident.release(); sl.d_total.release(); sl.d_top2.release(); sl.d_trim.release(); sl.d_aux.release(); sl.d_roff.release(); sl.d_rlen.release();
         if (sl.staged) cudaEventDestroy(sl.staged);
         if (sl.done) cudaEventDestroy(sl.done);
     }
