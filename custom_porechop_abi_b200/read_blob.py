@@ -117,6 +117,13 @@ class ReadBlob(object):
                 s = s.replace('U', 'T')
         return s
 
+    def is_rna(self, i):
+        raw = self.buf[self.seq_off[i]:self.seq_off[i] + self.seq_len[i]].tobytes()
+        if b'U' not in raw and b'u' not in raw:
+            return False
+        s = raw.decode().upper()
+        return s.count('U') > s.count('T')
+
     def full_name(self, i):
         return self.buf[self.name_off[i]:self.name_off[i] + self.name_len[i]].tobytes().decode()
 
@@ -182,7 +189,8 @@ class BlobRead(object):
 
     @property
     def name(self):
-        return self._blob.name(self._i) if self._blob.name_len[self._i] else 'r%d' % self._i
+        """The whole header line, as NanoporeRead.name holds it (porechop_abi.py:143-146: x[4] / x[2] of the loader's tuples)."""
+        return self._blob.full_name(self._i) if self._blob.name_len[self._i] else 'r%d' % self._i
 
     # trims live in the blob's arrays; the alignment lists are built from the blob's hit arrays when someone looks at them
     @property
@@ -219,6 +227,18 @@ class BlobRead(object):
             self._seq = self._blob.seq(self._i)
         return self._seq
 
+    @property
+    def quals(self):
+        """Quality string, padded with '+' to the sequence's length as NanoporeRead pads it (nanopore_read.py:44-46)."""
+        q = self._blob.quals(self._i)
+        n = int(self._blob.seq_len[self._i])
+        return q + '+' * (n - len(q)) if len(q) < n else q
+
+    @property
+    def rna(self):
+        """More U than T in the sequence as loaded (nanopore_read.py:36-41): output turns T back into U."""
+        return self._blob.is_rna(self._i)
+
     def get_seq_with_start_end_adapters_trimmed(self):
         if not self.start_trim_amount and not self.end_trim_amount:
             return self.seq
@@ -227,6 +247,23 @@ class BlobRead(object):
     def adapters_found(self):
         """The fork's filter (nanopore_read.py:23-30, porechop_abi.py:36-39): an adapter at BOTH ends."""
         return bool(self.start_adapter_alignments) and bool(self.end_adapter_alignments)
+
+    # what the reference's output_reads (porechop_abi.py:535-668) calls on a read: with these a BlobRead list goes through the
+    # reference's own writer unchanged (read_output.output_reads is the same writer for this repo's callers)
+    def seq_length_with_start_end_adapters_trimmed(self):
+        return len(self.get_seq_with_start_end_adapters_trimmed())
+
+    def get_split_read_parts(self, min_split_read_size):
+        from .read_output import get_split_read_parts
+        return get_split_read_parts(self, min_split_read_size)
+
+    def get_fasta(self, min_split_read_size, discard_middle, untrimmed=False):
+        from .read_output import get_fasta
+        return get_fasta(self, min_split_read_size, discard_middle, untrimmed)
+
+    def get_fastq(self, min_split_read_size, discard_middle, untrimmed=False):
+        from .read_output import get_fastq
+        return get_fastq(self, min_split_read_size, discard_middle, untrimmed)
 
 
 def load_read_blob(filename):

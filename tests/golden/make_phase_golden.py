@@ -8,6 +8,7 @@ The package is imported from a scratch copy (the reference tree is read-only and
 it is copied into the repo -- only inputs (reads, adapter sets) and the resulting per-read / per-set state, as JSON.
 Run in the build container only:  python tests/golden/make_phase_golden.py
 """
+import hashlib
 import json
 import os
 import shutil
@@ -51,6 +52,8 @@ def main():
     devnull = open(os.devnull, 'w')
     P = DEFAULTS
     cases = []
+    out_cases, quals_of = [], {}
+    sha = lambda text: hashlib.sha1(text.encode()).hexdigest() if text else ''
     for fastq, check_barcodes, variants in (
             ('test_one_adapter_set.fastq', False, [dict(), dict(min_trim_size=7, end_size=100), dict(middle_threshold=80.0, extra_end_trim=0)]),
             ('test_two_adapter_sets.fastq', False, [dict()]),
@@ -91,6 +94,35 @@ def main():
             phase_c = [{'middle_adapter_positions': sorted(r.middle_adapter_positions),
                         'middle_trim_positions': sorted(r.middle_trim_positions),
                         'middle_hit_str': r.middle_hit_str, 'adapters_found': bool(r.adapters_found())} for r in reads]
+            # ---- the far side of the path: what the reference writes for these reads (output_golden.json) ----
+            quals_of[fastq] = [q for _, _, q, _ in records]
+            per_variant = []
+            for fmt in ('fasta', 'fastq'):
+                for min_split in (1000, 20):
+                    for discard_middle in (False, True):
+                        for untrimmed in (False, True):
+                            texts = [(r.get_fasta if fmt == 'fasta' else r.get_fastq)(min_split, discard_middle, untrimmed) for r in reads]
+                            per_variant.append({'format': fmt, 'min_split': min_split, 'discard_middle': discard_middle, 'untrimmed': untrimmed,
+                                                'sha1': [sha(t) for t in texts], 'n_chars': sum(len(t) for t in texts)})
+            filtered = pc.filter_reads_by_adapter(reads)
+            files = {}
+            out_dir = tempfile.mkdtemp(prefix='pc_out_')
+            read_type = 'FASTA' if fastq.endswith('.fasta') else 'FASTQ'
+            for tag, kw in (('file_auto', dict(out_format='auto', output=os.path.join(out_dir, 'out.fastq'), barcode_dir=None, untrimmed=False, discard_unassigned=False, discard_middle=False, min_split=20)),
+                            ('file_fasta', dict(out_format='fasta', output=os.path.join(out_dir, 'out2.txt'), barcode_dir=None, untrimmed=False, discard_unassigned=False, discard_middle=True, min_split=1000)),
+                            ('bins', dict(out_format='auto', output=None, barcode_dir=os.path.join(out_dir, 'bins'), untrimmed=False, discard_unassigned=False, discard_middle=False, min_split=20)),
+                            ('bins_untrimmed', dict(out_format='fastq', output=None, barcode_dir=os.path.join(out_dir, 'bins2'), untrimmed=True, discard_unassigned=True, discard_middle=False, min_split=1000))):
+                pc.output_reads(filtered, kw['out_format'], kw['output'], read_type, 0, kw['discard_middle'], kw['min_split'], devnull,
+                                kw['barcode_dir'], os.path.join(REF, 'test', fastq), kw['untrimmed'], 1, kw['discard_unassigned'])
+                got = {}
+                if kw['barcode_dir']:
+                    for fn in sorted(os.listdir(kw['barcode_dir'])):
+                        got[fn] = hashlib.sha256(open(os.path.join(kw['barcode_dir'], fn), 'rb').read()).hexdigest()
+                else:
+                    got[os.path.basename(kw['output'])] = hashlib.sha256(open(kw['output'], 'rb').read()).hexdigest()
+                files[tag] = {'args': {k: (os.path.basename(v) if isinstance(v, str) and os.sep in v else v) for k, v in kw.items()}, 'sha256': got}
+            shutil.rmtree(out_dir)
+            out_cases.append({'fastq': fastq, 'read_type': read_type, 'filtered': [reads.index(r) for r in filtered], 'records': per_variant, 'files': files})
             cases.append({'fastq': fastq, 'params': p, 'check_barcodes': check_barcodes, 'require_two_barcodes': require_two,
                           'forward_or_reverse': forward_or_reverse,
                           'reads': [[n, s] for n, s, _, _ in records], 'albacore': [a for _, _, _, a in records],
@@ -100,6 +132,32 @@ def main():
     out = os.path.join(HERE, 'phases_golden.json')
     with open(out, 'w') as f:
         json.dump({'generator': 'tests/golden/make_phase_golden.py', 'cases': cases}, f, separators=(',', ':'))
+    # hand-made reads for the corners the fixtures do not reach: RNA, names with tab / space / neither, short quality strings,
+    # trims longer than the read (Python's negative-index slicing decides), trim positions outside the read, min_split 0
+    edge_in = [('r1 some desc', 'ACGU' * 30 + 'UUUU', 'I' * 124, 3, 5, []),
+               ('r2\tx y', 'ACGT' * 50, '5' * 150, 0, 0, list(range(50, 61)) + [-3, 1000, 199]),
+               ('r3', 'ACGT' * 10, '', 30, 30, []),
+               ('r4 a b', 'ACGT' * 100, 'ABCDEFGH' * 50, 10, 395, [2, 3]),
+               ('r5', 'acgtn' * 40, '!' * 200, 7, 0, [0, 1, 2, 3, 4, 5, 190, 191, 192, 100]),
+               ('r6_u', 'AUGC' * 20, 'I' * 80, 0, 2, list(range(30, 40))),
+               ('r7', 'ACGT' * 20, 'I' * 80, 0, 0, list(range(0, 80)))]
+    edge = []
+    for name, seq, quals, st, et, mid in edge_in:
+        r = NanoporeRead(name, seq, quals)
+        r.start_trim_amount, r.end_trim_amount, r.middle_trim_positions = st, et, set(mid)
+        outs = []
+        for fmt in ('fasta', 'fastq'):
+            for min_split in (0, 20, 1000):
+                for discard_middle in (False, True):
+                    for untrimmed in (False, True):
+                        outs.append([fmt, min_split, discard_middle, untrimmed,
+                                     (r.get_fasta if fmt == 'fasta' else r.get_fastq)(min_split, discard_middle, untrimmed)])
+        edge.append({'name': name, 'seq': seq, 'quals': quals, 'start_trim': st, 'end_trim': et, 'middle_trim_positions': mid,
+                     'parts': [[min_split, r.get_split_read_parts(min_split)] for min_split in (0, 20, 1000)], 'outputs': outs})
+    out2 = os.path.join(HERE, 'output_golden.json')
+    with open(out2, 'w') as f:
+        json.dump({'generator': 'tests/golden/make_phase_golden.py', 'quals': quals_of, 'cases': out_cases, 'edge': edge}, f, separators=(',', ':'))
+    print('wrote %s: %d cases, %.0f KB' % (out2, len(out_cases), os.path.getsize(out2) / 1e3))
     shutil.rmtree(tmp)
     n_hits = sum(len(r['middle_adapter_positions']) > 0 for c in cases for r in c['phase_c'])
     print('wrote %s: %d cases, %d reads with middle hits, %.0f KB' % (out, len(cases), n_hits, os.path.getsize(out) / 1e3))

@@ -10,16 +10,19 @@ import pytest
 from oracle_lib import oracle_align
 
 GOLDEN = os.path.join(os.path.dirname(__file__), 'golden', 'phases_golden.json')
+OUT_GOLDEN = os.path.join(os.path.dirname(__file__), 'golden', 'output_golden.json')
 
 
 class Read(object):
     """The attributes of the reference's NanoporeRead that the three phases touch (nanopore_read.py:32-75)."""
 
-    def __init__(self, name, seq):
+    def __init__(self, name, seq, quals=''):
         self.name = name
         self.seq = seq.upper()
-        if self.seq.count('U') > self.seq.count('T'):
+        self.rna = self.seq.count('U') > self.seq.count('T')
+        if self.rna:
             self.seq = self.seq.replace('U', 'T')
+        self.quals = quals + '+' * max(0, len(seq) - len(quals))
         self.start_trim_amount = 0
         self.end_trim_amount = 0
         self.start_adapter_alignments = []
@@ -149,10 +152,49 @@ def cases():
         return json.load(f)['cases']
 
 
+_OUT = {}
+
+
+def out_golden():
+    if not _OUT:
+        with open(OUT_GOLDEN) as f:
+            _OUT.update(json.load(f))
+    return _OUT
+
+
+def check_output(idx, reads, tmp_path):
+    """What the reference writes for reads in this state (tests/golden/output_golden.json: its own get_fasta / get_fastq per
+    read under 16 option sets, its filter_reads_by_adapter, and four output_reads runs -- one file, one FASTA file, barcode
+    bins, untrimmed bins -- as hashes) against read_output.py."""
+    import hashlib
+    from custom_porechop_abi_b200 import read_output as ro
+    g = out_golden()['cases'][idx]
+    sha = lambda text: hashlib.sha1(text.encode()).hexdigest() if text else ''
+    for v in g['records']:
+        fn = ro.get_fasta if v['format'] == 'fasta' else ro.get_fastq
+        texts = [fn(r, v['min_split'], v['discard_middle'], v['untrimmed']) for r in reads]
+        bad = [r.name for r, t, want in zip(reads, texts, v['sha1']) if sha(t) != want]
+        assert not bad and sum(len(t) for t in texts) == v['n_chars'], (v['format'], v['min_split'], v['discard_middle'], v['untrimmed'], bad)
+    kept = ro.filter_reads_by_adapter(reads)
+    assert [reads.index(r) for r in kept] == g['filtered']
+    for tag, f in g['files'].items():
+        a = f['args']
+        d = tmp_path / ('out_%d_%s' % (idx, tag))
+        d.mkdir()
+        output = str(d / a['output']) if a['output'] else None
+        bdir = str(d / a['barcode_dir']) if a['barcode_dir'] else None
+        ro.output_reads(kept, a['out_format'], output, g['read_type'], 0, a['discard_middle'], a['min_split'], None, bdir,
+                        g['fastq'], a['untrimmed'], 1, a['discard_unassigned'])
+        where = bdir if bdir else str(d)
+        got = {fn: hashlib.sha256(open(os.path.join(where, fn), 'rb').read()).hexdigest() for fn in sorted(os.listdir(where))}
+        assert got == f['sha256'], (tag, sorted(got), sorted(f['sha256']))
+
+
 def run_case(c, eng, read_blob=None):
     from custom_porechop_abi_b200 import porechop_batch as pb
     p = c['params']
-    reads = [Read(n, s) for n, s in c['reads']]
+    quals = out_golden()['quals'][c['fastq']]
+    reads = [Read(n, s, q) for (n, s), q in zip(c['reads'], quals)]
     for r, alb in zip(reads, c.get('albacore', [None] * len(reads))):
         r.albacore_barcode_call = alb                       # Albacore's bin, from the directory the read came from
     search = [AdapterSet(d) for d in c['search_adapters']]
@@ -181,6 +223,7 @@ def run_case(c, eng, read_blob=None):
         assert r.middle_hit_str == g['middle_hit_str'], r.name
         # the fork's read filter (porechop_abi.py:36-39, nanopore_read.py:23-30): an adapter alignment at both ends
         assert (bool(r.start_adapter_alignments) and bool(r.end_adapter_alignments)) == g['adapters_found'], r.name
+    return reads
 
 
 def test_golden_has_hits():
@@ -195,8 +238,9 @@ def test_golden_has_hits():
 
 
 @pytest.mark.parametrize('idx', range(13))
-def test_phase_logic_with_oracle_engine(idx):
-    run_case(cases()[idx], OracleEngine())
+def test_phase_logic_with_oracle_engine(idx, tmp_path):
+    reads = run_case(cases()[idx], OracleEngine())
+    check_output(idx, reads, tmp_path)             # ... and what is written for reads in that state
 
 
 @pytest.mark.parametrize('idx', range(13))
@@ -315,11 +359,82 @@ def test_phase_logic_with_blob_reads(idx, tmp_path):
         assert r.adapters_found() == g['adapters_found'], r.name
 
 
+def _write_records(path, c):
+    """The case's reads as the fixture holds them: full header, sequence, qualities (FASTA: 70 per line)."""
+    quals = out_golden()['quals'][c['fastq']]
+    fasta = c['fastq'].endswith('.fasta')
+    with open(path, 'w') as f:
+        for (name, seq), q in zip(c['reads'], quals):
+            if fasta:
+                f.write('>' + name + '\n' + ''.join(seq[i:i + 70] + '\n' for i in range(0, len(seq), 70)))
+            else:
+                f.write('@' + name + '\n' + seq + '\n+\n' + q + '\n')
+
+
+def blob_reads_through_phases(c, eng, tmp_path):
+    from custom_porechop_abi_b200 import porechop_batch as pb
+    from custom_porechop_abi_b200.read_blob import load_read_blob
+    p = c['params']
+    path = str(tmp_path / ('records.' + ('fasta' if c['fastq'].endswith('.fasta') else 'fastq')))
+    _write_records(path, c)
+    blob = load_read_blob(path)
+    reads = blob.make_reads()
+    assert [r.name for r in reads] == [n for n, _ in c['reads']]
+    for r, alb in zip(reads, c.get('albacore', [None] * len(reads))):
+        r.albacore_barcode_call = alb
+    used = [AdapterSet(d) for d in c['matching_used']]
+    pb.find_adapters_at_read_ends(reads, used, 0, p['end_size'], p['extra_end_trim'], p['end_threshold'], p['scoring'], None,
+                                  p['min_trim_size'], 1, c['check_barcodes'], p['barcode_threshold'], p['barcode_diff'],
+                                  c['require_two_barcodes'], c['forward_or_reverse'], engine=eng, read_blob=blob)
+    pb.find_adapters_in_read_middles(reads, used, 0, p['middle_threshold'], p['good_side'], p['bad_side'], p['scoring'], None, 1,
+                                     False, engine=eng, read_blob=blob)
+    return reads
+
+
+def test_output_corner_cases(tmp_path):
+    """Hand-made reads run through the reference's own get_fasta / get_fastq / get_split_read_parts (output_golden.json:
+    'edge'): RNA, names with tab / space / neither, short quality strings, trims longer than the read, trim positions
+    outside the read, min_split 0 -- on reference-shaped objects and on BlobRead objects of a file that holds them."""
+    from custom_porechop_abi_b200 import read_output as ro
+    from custom_porechop_abi_b200.read_blob import load_read_blob
+    edge = out_golden()['edge']
+    path = str(tmp_path / 'edge.fastq')
+    with open(path, 'w') as f:
+        for e in edge:
+            f.write('@' + e['name'] + '\n' + e['seq'] + '\n+\n' + e['quals'] + '\n')
+    blob_reads = load_read_blob(path).make_reads()
+    for e, b in zip(edge, blob_reads):
+        r = Read(e['name'], e['seq'], e['quals'])
+        for x in (r, b):
+            x.start_trim_amount, x.end_trim_amount = e['start_trim'], e['end_trim']
+            x.middle_trim_positions = set(e['middle_trim_positions'])
+            for min_split, parts in e['parts']:
+                assert [list(p) for p in ro.get_split_read_parts(x, min_split)] == parts, (e['name'], min_split, type(x).__name__)
+            for fmt, min_split, discard_middle, untrimmed, want in e['outputs']:
+                got = (ro.get_fasta if fmt == 'fasta' else ro.get_fastq)(x, min_split, discard_middle, untrimmed)
+                assert got == want, (e['name'], fmt, min_split, discard_middle, untrimmed, type(x).__name__)
+
+
+@pytest.mark.parametrize('idx', range(13))
+def test_output_of_blob_reads(idx, tmp_path):
+    """File -> ReadBlob -> BlobRead objects -> phases B and C -> the records and files the reference writes, byte for byte."""
+    from custom_porechop_abi_b200 import read_output as ro
+    reads = blob_reads_through_phases(cases()[idx], ReducedOracleEngine(), tmp_path)
+    check_output(idx, reads, tmp_path)
+    for r in reads:                                # the methods the reference's own output_reads calls on a read
+        assert r.get_fastq(20, False) == ro.get_fastq(r, 20, False) and r.get_fasta(1000, True, True) == ro.get_fasta(r, 1000, True, True)
+        assert r.seq_length_with_start_end_adapters_trimmed() == len(r.get_seq_with_start_end_adapters_trimmed())
+        assert r.get_split_read_parts(20) == ro.get_split_read_parts(r, 20)
+
+
 @pytest.mark.gpu
 def test_phases_on_gpu(engine, tmp_path):
     from custom_porechop_abi_b200.read_blob import load_read_blob
     for k, c in enumerate(cases()):
-        run_case(c, engine)
+        da, db = tmp_path / ('a%d' % k), tmp_path / ('b%d' % k)
+        da.mkdir(); db.mkdir()
+        check_output(k, run_case(c, engine), da)                              # reference-shaped objects -> records and files
+        check_output(k, blob_reads_through_phases(c, engine, db), db)         # file -> ReadBlob -> BlobRead -> the same bytes
         path = str(tmp_path / ('reads%d.fastq' % k))
         _write_fastq(path, c['reads'], lower=(k % 2 == 1))
         run_case(c, engine, read_blob=load_read_blob(path))
