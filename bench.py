@@ -346,7 +346,9 @@ def run_gpu_arm(args):
         if a.dtype.names:                        # torch has no structured dtypes: pin as int32 words and view back
             t = torch.empty(a.shape + (a.dtype.itemsize // 4,), dtype=torch.int32).pin_memory()
             keep.append(t)
-            return t.numpy().view(a.dtype).reshape(a.shape)
+            v = t.numpy().view(a.dtype).reshape(a.shape)
+            v[...] = a                               # (an uninitialised top2 buffer once made the checksum differ from run to run)
+            return v
         if a.dtype == np.uint16:
             t = torch.empty(a.shape, dtype=torch.int16).pin_memory()
             keep.append(t)
@@ -510,6 +512,17 @@ def run_gpu_arm(args):
     if os.environ.get('PCB_E2E_TRACE') and rank == 0:          # host-side time line of one more (untimed) step, to stderr
         e2e_step(trace=True)
         print('e2e step: ' + ', '.join('%s %.1f ms' % (w_, (t_ - stamps[0][1]) * 1e3) for w_, t_ in stamps[1:]), file=sys.stderr)
+        for rep in range(4):                                   # ... and the parts of the checksum, step after step (they must not move)
+            e2e_step()
+            parts_sum = {}
+            if has_tasks:
+                for f_ in ('raw_score', 'read_start', 'read_end', 'matches'):
+                    parts_sum['C ' + f_] = int(out_m[f_].astype(np.int64).sum())
+            if has_windows:
+                parts_sum['hits'] = [int(h.hits['raw_score'].astype(np.int64).sum()) for pair in state['parts'] for h in pair]
+                parts_sum['ident'] = [int(ident_s.astype(np.int64).sum()), int(ident_e.astype(np.int64).sum())]
+                parts_sum['trim'] = [int(trim_s.astype(np.int64).sum()), int(trim_e.astype(np.int64).sum())]
+            print('e2e parts %d: %s' % (rep, parts_sum), file=sys.stderr)
     eng.set_deferred(False)
     sampler.stop_flag = True; sampler.join(timeout=3)
     e2e_s = max_over_ranks(e2e_s)
