@@ -166,26 +166,31 @@ class ReadBlob(object):
 
 class BlobRead(object):
     """A read of a ReadBlob with the attributes of the reference's NanoporeRead that the three phases touch
-    (nanopore_read.py:32-75).  The sequence string is only built when someone asks for it (a read with a middle hit)."""
+    (nanopore_read.py:32-75).  Building one costs two assignments: the per-read sets, dicts and strings NanoporeRead.__init__
+    creates come into being when someone first looks at them (most reads never have a middle hit or a barcode score), and
+    the sequence string is only built when someone asks for it (a read with a middle hit, the writer)."""
     __slots__ = ('_blob', '_i', '_seq', '_start_al', '_end_al',
                  'middle_adapter_positions', 'middle_trim_positions', 'middle_hit_str', 'start_barcode_scores', 'end_barcode_scores',
                  'barcode_call', 'albacore_barcode_call', 'best_start_barcode', 'second_best_start_barcode', 'best_end_barcode',
                  'second_best_end_barcode')
+    _FRESH = {'_seq': lambda: None, '_start_al': lambda: None, '_end_al': lambda: None,
+              'middle_adapter_positions': set, 'middle_trim_positions': set, 'middle_hit_str': str,
+              'start_barcode_scores': dict, 'end_barcode_scores': dict,
+              'barcode_call': lambda: 'none', 'albacore_barcode_call': lambda: None,
+              'best_start_barcode': lambda: ('none', 0.0), 'second_best_start_barcode': lambda: ('none', 0.0),
+              'best_end_barcode': lambda: ('none', 0.0), 'second_best_end_barcode': lambda: ('none', 0.0)}
 
     def __init__(self, blob, i):
-        self._blob, self._i, self._seq = blob, i, None
-        self._start_al = self._end_al = None
-        self.middle_adapter_positions = set()
-        self.middle_trim_positions = set()
-        self.middle_hit_str = ''
-        self.start_barcode_scores = {}
-        self.end_barcode_scores = {}
-        self.barcode_call = 'none'
-        self.albacore_barcode_call = None
-        self.best_start_barcode = ('none', 0.0)
-        self.second_best_start_barcode = ('none', 0.0)
-        self.best_end_barcode = ('none', 0.0)
-        self.second_best_end_barcode = ('none', 0.0)
+        self._blob, self._i = blob, i
+
+    def __getattr__(self, name):
+        # only reached for a slot nobody has written yet: give it the value NanoporeRead.__init__ would have given it
+        fresh = BlobRead._FRESH.get(name)
+        if fresh is None:
+            raise AttributeError(name)
+        value = fresh()
+        object.__setattr__(self, name, value)
+        return value
 
     @property
     def name(self):
