@@ -108,9 +108,10 @@ class ReadBlob(object):
 
     def seq(self, i):
         """The sequence as NanoporeRead stores it (nanopore_read.py:36-39): upper case, U -> T when U outnumbers T."""
-        raw = self.buf[self.seq_off[i]:self.seq_off[i] + self.seq_len[i]].tobytes()
+        seg = self.buf[self.seq_off[i]:self.seq_off[i] + self.seq_len[i]]
+        raw = seg.tobytes()
         s = raw.decode()
-        if not s.isupper():
+        if len(seg) and seg.max() > 96:                     # a lower-case letter somewhere (str.isupper costs 3 x str.upper)
             s = s.upper()
         if b'U' in raw or b'u' in raw:                       # (a memchr: counting is only needed when there is a U at all)
             if s.count('U') > s.count('T'):
