@@ -441,7 +441,7 @@ static int launch_dp(pcb_context *c, PcbLaunch &L, bool trace, int64_t cells, in
             L.grid = (int)std::min<int64_t>(c->grid_fp1[cls], ctas);
             PCB_CUDA(c, pcf_launch_pass1(L, cls, st));
             PCB_CUDA(c, pcf_launch_pass2(L, cls, (int)std::min<int64_t>(c->grid_fp2[cls], ctas), st));
-            launches += pcf_trace_launches();
+            launches += pcf_trace_launches(cls);
         }
     } else {
         L.unit0 = 0; L.unit1 = n_units;

@@ -40,6 +40,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cstdlib>
 
 namespace {
 
@@ -520,7 +521,7 @@ __device__ __forceinline__ Meta meta_of(const PcbLaunch &L)
     m.chunk_base = m.cursor + A * NB; m.counters = m.chunk_base + A + 1;
     return m;
 }
-// counters: 0 = items in `surv`
+// counters: 0 / 4 = items in `surv` after an even / odd generation, 1..3 and 5.. = work-queue heads of generations 0..2 and 3..
 __device__ __forceinline__ int32_t major_of(const PcbLaunch &L, int64_t u /* unit - unit0 */, int64_t groups)
 {
     return L.src.units ? L.src.units[L.unit0 + u].adapter : (int32_t)((L.unit0 + u) / groups);
@@ -593,7 +594,8 @@ __global__ void k_bucket_scan(const PcbLaunch L, int which)
         if (tid == 1023) { carry_n += s_n[1023]; carry_c += s_c[1023]; }
         __syncthreads();
     }
-    if (tid == 0) { M.base[(int64_t)A * NB] = carry_n; M.chunk_base[A] = carry_c; if (which == 0) M.counters[0] = 0; }
+    // (the survivor counter the NEXT rounds launch fills: 0 after a scan of hist0, 4 after a scan of hist1)
+    if (tid == 0) { M.base[(int64_t)A * NB] = carry_n; M.chunk_base[A] = carry_c; M.counters[which == 0 ? 0 : 4] = 0; }
 }
 
 __device__ __forceinline__ void put_item(PcfItem *dst, uint32_t ref, uint32_t pos, uint32_t endc, uint32_t a0, uint32_t a1, uint32_t a2, uint64_t off)
@@ -636,10 +638,10 @@ __global__ void k_scatter0(const PcbLaunch L, int C, int skew)
     }
 }
 // generation 1: one thread per surviving item
-__global__ void k_scatter1(const PcbLaunch L, int two)
+__global__ void k_scatter1(const PcbLaunch L, int two, int counter)
 {
     const Meta M = meta_of(L);
-    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, n = M.counters[0];
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, n = M.counters[counter];
     if ((idx & ~(int64_t)31) >= n) return;
     const int64_t groups = L.src.units ? 0 : (L.src.n_windows + 63) / 64;
     const int lane = threadIdx.x & 31;
@@ -703,7 +705,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
 
     const Meta M = meta_of(L);
     const int A = L.n_major;
-    const bool gen0 = L.gen == 0;
+    const bool finish = L.finish != 0;                          // the last generation: a round keeps its items until all are done
     const int b = -L.sc.gap_open;
     const int s_match = L.sc.match + 2 * b, s_mis = L.sc.mismatch + 2 * b;
     const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b);
@@ -716,12 +718,16 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
     // chunks first -- inside a major the sort puts the most expensive rounds last, so they start early and the cheap ones
     // fill the tail of the launch (measured: 25..32 bases 0.89 -> 0.81 ms, 33..40 bases 0.85 -> 0.74 ms; 24 bases 13.2 ->
     // 13.7 ms, hence the split).
+#ifdef PCF_DYN_ALL
+    constexpr bool DYN = true;
+#else
     constexpr bool DYN = NR > 24;
+#endif
     const int64_t nwarps = (int64_t)gridDim.x * W, gw = (int64_t)blockIdx.x * W + warp;
     const int64_t total = M.chunk_base[A];
     int64_t c_cur = DYN ? 0 : gw * total / nwarps;
     const int64_t c_end = DYN ? 0 : (gw + 1) * total / nwarps;
-    int32_t *const qhead = M.counters + 1 + (gen0 ? 0 : 1);
+    int32_t *const qhead = M.counters + (L.gen < 3 ? 1 : 2) + L.gen;
     int a = -1, n = 0, r0 = 0;
     int32_t tbl_adapter = -1, out_col = 0;
     int64_t a_item0 = 0, a_item1 = 0, a_chunk0 = 0, a_chunk1 = 0;
@@ -908,16 +914,18 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
                 PCF_CHECK(L, oidx >= 0 && (L.n_out <= 0 || oidx < L.n_out));
                 L.out[oidx] = res;
             }
-            if (!gen0) {
+            if (finish) {
                 if (!__any_sync(0xffffffffu, keep[0] || keep[1])) break;
                 continue;                                                // these 64 stay together until the last is done
             }
-            // generation 0: the others go to generation 1, counted per (major, rows)
+            // the others go to the next generation, counted per (major, rows): even generations count in hist1 / counters[0],
+            // odd ones in hist0 / counters[4] (free again by then: k_bucket_scan clears what it has read)
+            int32_t *const n_surv = M.counters + ((L.gen & 1) ? 4 : 0), *const hist_next = (L.gen & 1) ? M.hist0 : M.hist1;
             const uint32_t m0 = __ballot_sync(0xffffffffu, keep[0]), m1 = __ballot_sync(0xffffffffu, keep[1]);
             const int nk = __popc(m0) + __popc(m1);
             if (nk) {
                 int first = 0;
-                if (lane == 0) first = atomicAdd(M.counters, nk);
+                if (lane == 0) first = atomicAdd(n_surv, nk);
                 first = __shfl_sync(0xffffffffu, first, 0);
                 const uint32_t lt = (1u << lane) - 1u;
                 PCF_CHECK(L, first + nk <= 64 * (L.unit1 - L.unit0));
@@ -928,7 +936,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB_P2(NR)) k_rounds(const Pcb
                     const int key = keep[h] ? a * NB + bucket1(pos) : -1;
                     const uint32_t mk = __match_any_sync(0xffffffffu, key);
                     if (keep[h]) {
-                        if (lane == __ffs(mk) - 1) atomicAdd(M.hist1 + key, __popc(mk));
+                        if (lane == __ffs(mk) - 1) atomicAdd(hist_next + key, __popc(mk));
                         const int slot = first + (h ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt));
                         put_item(L.surv + slot, ref[h], pos, endc[h], w.acc.kAR, w.acc.tHV, w.acc.nHV, off[h]);
                     }
@@ -1262,7 +1270,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, 1) k_rounds2(const PcbLaunch L)
 
     const Meta M = meta_of(L);
     const int A = L.n_major;
-    const bool gen0 = L.gen == 0;
+    const bool gen0 = L.finish == 0;
     const int b = -L.sc.gap_open;
     const int s_match = L.sc.match + 2 * b, s_mis = L.sc.mismatch + 2 * b;
     const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b);
@@ -1609,22 +1617,40 @@ cudaError_t pcf_launch_pass2(const PcbLaunch &L0, int cls, int grid_rounds, cuda
     k_count0<<<g0, 256, 0, st>>>(L, C, two);
     k_bucket_scan<<<1, 1024, 0, st>>>(L, 0);
     k_scatter0<<<g0, 256, 0, st>>>(L, C, two);
-    L.gen = 0;
-    if (two) PCF_BY_TWO(e = launch_rounds2<NR>(L, grid_rounds, st));
-    else { PCF_BY_CLASS(e = launch_rounds<NR, EX, C>(L, grid_rounds, st)) }
-    if (e != cudaSuccess) return e;
-    k_bucket_scan<<<1, 1024, 0, st>>>(L, 1);
-    // the survivors are counted on the device: the scatter is sized for the worst case and leaves early
+    const int gens = pcf_generations(cls);
+    auto rounds = [&](int gen) -> cudaError_t {
+        L.gen = gen; L.finish = gen == gens - 1;
+        cudaError_t r = cudaSuccess;
+        if (two) PCF_BY_TWO(r = launch_rounds2<NR>(L, grid_rounds, st));
+        else { PCF_BY_CLASS(r = launch_rounds<NR, EX, C>(L, grid_rounds, st)) }
+        return r;
+    };
+    if ((e = rounds(0)) != cudaSuccess) return e;
+    // the survivors are counted on the device: the scatters are sized for the worst case and leave early
     const unsigned g1 = (unsigned)((nu * 64 + 255) / 256);
-    k_scatter1<<<g1, 256, 0, st>>>(L, two);
-    L.gen = 1;
-    if (two) PCF_BY_TWO(e = launch_rounds2<NR>(L, grid_rounds, st));
-    else { PCF_BY_CLASS(e = launch_rounds<NR, EX, C>(L, grid_rounds, st)) }
-    if (e != cudaSuccess) return e;
+    k_bucket_scan<<<1, 1024, 0, st>>>(L, 1);
+    k_scatter1<<<g1, 256, 0, st>>>(L, two, 0);
+    if ((e = rounds(1)) != cudaSuccess) return e;
+    for (int g = 2; g < gens; ++g) {        // later blocks one by one too: what is left after each is sorted again
+        k_bucket_scan<<<1, 1024, 0, st>>>(L, (g - 1) & 1 ? 0 : 1);
+        k_scatter1<<<g1, 256, 0, st>>>(L, two, (g - 1) & 1 ? 4 : 0);
+        if ((e = rounds(g)) != cudaSuccess) return e;
+    }
     return cudaGetLastError();
 }
 
-int pcf_trace_launches() { return 8; }
+// generations of pass 2: the two-stripe classes take two (first block, then the rest); the others PCB_GENS (default below)
+int pcf_generations(int cls)
+{
+    static const int env = [] { const char *g = getenv("PCB_GENS"); return g ? atoi(g) : 0; }();
+    static const int env_small = [] { const char *g = getenv("PCB_GENS_SMALL"); return g ? atoi(g) : 0; }();
+    if (pcf_class_two(cls)) return 2;
+    // measured (131,072 windows x 108 24-base sequences): 2 / 3 / 4 / 5 generations = 13.08 / 12.58 / 12.44 / 12.43 ms; 16,384 windows
+    // x 12 68-base sets: 0.850 / 0.817 / 0.844 / 0.865 ms; the small classes lose with a third (more launches than items)
+    if (cls == 0 || cls == 5) return env >= 2 && env <= 5 ? env : (cls == 0 ? 4 : 3);
+    return env_small >= 2 && env_small <= 5 ? env_small : 2;
+}
+int pcf_trace_launches(int cls) { return 5 + 3 * (pcf_generations(cls) - 1); }
 
 int pcf_occupancy_grid(int kind, int cls)
 {

@@ -136,7 +136,8 @@ struct PcbLaunch {
     PcfItem    *sorted, *surv;   /* pass 2: items in processing order; items that go on to the next generation */
     int32_t    *meta;            /* pass 2: bucket counts, bases, chunk table (pcf_meta_words)      */
     int32_t     n_major;         /* pass 2: majors = adapters of the launch (cross product: its id list; task lists: the adapter set) */
-    int32_t     gen;             /* pass 2: 0 = first block of every traceback, 1 = all later blocks */
+    int32_t     gen;             /* pass 2: generation 0 = first block of every traceback, 1, 2 = later blocks */
+    int32_t     finish;          /* pass 2: the last generation (rounds keep their items until every path is complete) */
     int64_t     n_out;           /* records in `out` (index checks of the -DPCF_CHECKED build)       */
 };
 
@@ -218,7 +219,8 @@ cudaError_t pcf_launch_scan(const PcbLaunch &L, int cls, cudaStream_t st);
 cudaError_t pcf_launch_pass1(const PcbLaunch &L, int cls, cudaStream_t st);
 cudaError_t pcf_launch_pass2(const PcbLaunch &L, int cls, int grid_rounds, cudaStream_t st);
 int pcf_occupancy_grid(int kind /* 0 scan, 1 pass 1, 2 rounds */, int cls);
-int pcf_trace_launches(void);       /* kernel launches of one pcf_launch_trace call */
+int pcf_generations(int cls);       /* generations of pass 2 (sorted lists of tracebacks) */
+int pcf_trace_launches(int cls);    /* kernel launches of one pass 1 + pass 2 */
 /* Trace of the fast classes over a batch of units (pcf_launch_trace): pass 1 (score only) leaves the DP column of every
  * task at every C-th column in scratch (per unit and checkpoint NR/8 warp-wide 1 KB lines: 8 rows per thread, 16 bits per
  * cell and task = M in 13 bits, M - H clamped in 3)
