@@ -1270,7 +1270,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, 1) k_rounds2(const PcbLaunch L)
 
     const Meta M = meta_of(L);
     const int A = L.n_major;
-    const bool gen0 = L.finish == 0;
+    const bool finish = L.finish != 0;
     const int b = -L.sc.gap_open;
     const int s_match = L.sc.match + 2 * b, s_mis = L.sc.mismatch + 2 * b;
     const uint32_t GEB = pk2(L.sc.gap_extend + b), Bp = pk2(b);
@@ -1283,7 +1283,7 @@ __global__ void __launch_bounds__(PCB_BLOCK, 1) k_rounds2(const PcbLaunch L)
     // cheap ones fill the tail.  (A static split of the chunk list left SMs idle for half of the kernel: some warps drew
     // nothing but 13-block rounds.)
     const int64_t total = M.chunk_base[A];
-    int32_t *const qhead = M.counters + 1 + (gen0 ? 0 : 1);
+    int32_t *const qhead = M.counters + (L.gen < 3 ? 1 : 2) + L.gen;
     int a = -1, n = 0, r0 = 0;
     int32_t tbl_adapter = -1, out_col = 0;
     int64_t a_item0 = 0, a_item1 = 0, a_chunk0 = 0;
@@ -1444,23 +1444,24 @@ __global__ void __launch_bounds__(PCB_BLOCK, 1) k_rounds2(const PcbLaunch L)
                     PCF_CHECK(L, oidx >= 0 && (L.n_out <= 0 || oidx < L.n_out));
                     L.out[oidx] = res;
                 }
-                if (!gen0) {
+                if (finish) {
                     if (!__any_sync(0xffffffffu, keep)) break;
                     continue;                                              // these 32 stay together until the last is done
                 }
-                // generation 0: the others go to generation 1, counted per (major, rows)
+                // the others go to the next generation, counted per (major, what is left of the path); counters as in k_rounds
+                int32_t *const n_surv = M.counters + ((L.gen & 1) ? 4 : 0), *const hist_next = (L.gen & 1) ? M.hist0 : M.hist1;
                 const uint32_t m0 = __ballot_sync(0xffffffffu, keep);
                 const int nk = __popc(m0);
                 if (nk) {
                     int first = 0;
-                    if (lane == 0) first = atomicAdd(M.counters, nk);
+                    if (lane == 0) first = atomicAdd(n_surv, nk);
                     first = __shfl_sync(0xffffffffu, first, 0);
                     PCF_CHECK(L, first + nk <= 64 * (L.unit1 - L.unit0));
                     const uint32_t pos = walk_pos(wk);
                     const int key = keep ? a * NB + bucket1_two(pos) : -1;
                     const uint32_t mk = __match_any_sync(0xffffffffu, key);
                     if (keep) {
-                        if (lane == __ffs(mk) - 1) atomicAdd(M.hist1 + key, __popc(mk));
+                        if (lane == __ffs(mk) - 1) atomicAdd(hist_next + key, __popc(mk));
                         put_item(L.surv + first + __popc(m0 & ((1u << lane) - 1u)), ref, pos, endc, wk.acc.kAR, wk.acc.tHV, wk.acc.nHV, off);
                     }
                 }
@@ -1644,7 +1645,8 @@ int pcf_generations(int cls)
 {
     static const int env = [] { const char *g = getenv("PCB_GENS"); return g ? atoi(g) : 0; }();
     static const int env_small = [] { const char *g = getenv("PCB_GENS_SMALL"); return g ? atoi(g) : 0; }();
-    if (pcf_class_two(cls)) return 2;
+    static const int env_two = [] { const char *g = getenv("PCB_GENS_TWO"); return g ? atoi(g) : 0; }();
+    if (pcf_class_two(cls)) return env_two >= 2 && env_two <= 5 ? env_two : 2;
     // measured (131,072 windows x 108 24-base sequences): 2 / 3 / 4 / 5 generations = 13.08 / 12.58 / 12.44 / 12.43 ms; 16,384 windows
     // x 12 68-base sets: 0.850 / 0.817 / 0.844 / 0.865 ms; the small classes lose with a third (more launches than items)
     if (cls == 0 || cls == 5) return env >= 2 && env <= 5 ? env : (cls == 0 ? 4 : 3);
