@@ -152,7 +152,10 @@ struct pcb_context {
     DevBuf<int32_t> d_meta_s[N_SIDE];
     DevBuf<int32_t> d_err;
     int grid_trace = 0, grid_scan = 0, grid_fp1[PCF_NCLS] = {}, grid_fp2[PCF_NCLS] = {}, grid_fscan[PCF_NCLS] = {};   // fast kernels: pass 1, rounds, scan
-    uint64_t scratch_budget = 6144ull << 18;   // words of checkpoint scratch a batch of the fast trace may use (PCB_SCRATCH_MB)
+    // words of checkpoint scratch the batches of the fast trace may use together (PCB_SCRATCH_MB).  16 GB of the 180: a class's
+    // units then go through in one batch per pipeline where 6 GB made three (131,072 windows x 108 sequences: 13.00 / 12.42 /
+    // 12.08 / 12.08 ms with 3 / 6 / 16 / 32 GB); the buffers grow on demand, small inputs take what they need
+    uint64_t scratch_budget = 16384ull << 18;
     pcb_counters cnt{};
     bool ktiming = false;
     // deferred pcb_align_windows_hits calls: their hit lists are copied once the counts are known (pcb_wait)
