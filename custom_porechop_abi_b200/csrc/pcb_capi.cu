@@ -608,7 +608,9 @@ static int run_windows(pcb_context *c, pcb_result *host_out)
             int start = 0;
             for (int q = 0; q < cls; ++q) start += S.n_cls[q];
             const bool biggest = oi == n_used - 1;
-            const int parts = (biggest && n_pipes > 1 && !host_out && cls < PCF_NCLS && !getenv("PCB_NO_SPLIT")) ? std::max(1, std::min(n_pipes, cnt / 8)) : 1;
+            static const int env_parts = [] { const char *e = getenv("PCB_PARTS"); return e ? atoi(e) : 0; }();
+            const int want_parts = env_parts > 0 ? env_parts : n_pipes;
+            const int parts = (biggest && n_pipes > 1 && !host_out && cls < PCF_NCLS && !getenv("PCB_NO_SPLIT")) ? std::max(1, std::min(want_parts, cnt / 8)) : 1;
             for (int q = 0; q < parts; ++q) {
                 const int a = (int)((int64_t)cnt * q / parts), b = (int)((int64_t)cnt * (q + 1) / parts);
                 place(cls, start + a, b - a, cls == PCF_NCLS || (biggest && host_out), biggest && q == parts - 1 && host_out);
