@@ -500,12 +500,13 @@ __global__ void __launch_bounds__(PCB_BLOCK, PCF_MINB(MODE, NR)) k_fast(const Pc
 // end cell sits anywhere in it) and needs all adapter rows, every later block is C columns wide but only needs the rows
 // above the row in which the path enters it (13 of 24 on average, 5 for a third block).  A warp recomputes a block for 64
 // tracebacks in lockstep, so what a round costs is the LARGEST width x the LARGEST row count among them.  Hence:
-//   generation 0 = the first block of every traceback, generation 1 = all later blocks.  Before a generation runs, its
+//   generation 0 = the first block of every traceback, generation g = the next block of what is still under way, the last
+//   generation (L.finish) = all blocks that are left; 2 to 5 generations (pcf_generations).  Before a generation runs, its
 //   items are sorted (counting sort: k_count0 / in-kernel counts, k_bucket_scan, k_scatter) by adapter and then by
 //   width (first blocks of paths that end in the last adapter row) or by rows (everything else), and a round takes 64
 //   neighbours of that order: 300 instead of 690 flag cells per traceback.
-//   A generation-0 round walks each path to the left edge of its block; paths that end there are finished (statistics,
-//   result record), the others go to the list of generation 1 with the state of their walk.  A generation-1 round keeps
+//   A round walks each path to the left edge of its block; paths that end there are finished (statistics, result record),
+//   the others go to the list of the next generation with the state of their walk.  A round of the last generation keeps
 //   its 64 items until all of them are finished (sorted by rows, the ones that go on are neighbours).
 // dynamic smem of k_rounds: [W][NR*25] score tables, [W][NR] adapter codes, then per thread (strided by PCB_BLOCK) C*NR/4
 //   flag words.
@@ -637,7 +638,7 @@ __global__ void k_scatter0(const PcbLaunch L, int C, int skew)
         }
     }
 }
-// generation 1: one thread per surviving item
+// later generations: one thread per surviving item (`counter`: which of the two survivor counts holds their number)
 __global__ void k_scatter1(const PcbLaunch L, int two, int counter)
 {
     const Meta M = meta_of(L);
