@@ -627,6 +627,11 @@ def run_gpu_arm(args):
         }
         if world == 1 and not args.no_phase_e2e and args.workload == 'ont':
             line['phase_e2e'] = phase_e2e(eng, wl, blob)
+            if os.environ.get('PCB_PHASE_DEBUG'):              # a second time, and on an engine of its own
+                phase_e2e(eng, wl, blob)
+                eng2 = AlignmentEngine(local)
+                phase_e2e(eng2, wl, blob)
+                eng2.close()
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             kind, fn, free = cpu_library()
@@ -683,7 +688,9 @@ def phase_e2e(eng, wl, pinned_blob, n_reads=0, reps=3):
     n = min(n_reads or wl['n_reads'], wl['n_reads'])
     sets = synthetic.adapter_sets(wl['adapters'], wl['start_ids'], wl['end_ids'])
     passes = []
+    import gc
     for rep in range(reps + 1):
+        gc.collect()            # every pass starts like a fresh job (a full collection of the last pass's 131,072 objects once landed in phase A: 81 instead of 24 ms)
         h2d0 = eng.counters()['h2d_bytes']
         t_make = time.perf_counter()
         rb = ReadBlob.from_buffer(pinned_blob[:wl['off'][n]], wl['off'][:n + 1])  # the reads as loaded: one (pinned) buffer + offsets
@@ -700,6 +707,9 @@ def phase_e2e(eng, wl, pinned_blob, n_reads=0, reps=3):
         passes.append({'objects': t0 - t_make, 'phase_a': t1 - t0, 'phase_b': t2 - t1, 'phase_c': t3 - t2, 'total': t3 - t0,
                        'h2d_bytes': int(eng.counters()['h2d_bytes'] - h2d0)})
         del reads, rb
+    if os.environ.get('PCB_PHASE_DEBUG'):
+        for k_, p_ in enumerate(passes):
+            print('phase_e2e pass %d: %s' % (k_, {a_: round(b_ * 1e3, 1) if a_ != 'h2d_bytes' else b_ for a_, b_ in p_.items()}), file=sys.stderr)
     timed = passes[1:]
     total = sum(p['total'] for p in timed)
     mean = {k: sum(p[k] for p in timed) / len(timed) for k in ('objects', 'phase_a', 'phase_b', 'phase_c')}
