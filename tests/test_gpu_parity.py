@@ -1,5 +1,6 @@
 """GPU parity: the CUDA path, called through the C ABI, against the CPU oracle on the same seeded inputs.
 Bit-exact bar: every integer field; the printed string (identities via "%f") must be identical too."""
+import os
 import random
 
 import numpy as np
@@ -484,6 +485,76 @@ def test_reduced_outputs_match_full_records(engine, thr, at_end, min_trim):
     engine.select_slot(0)
     assert res2.n_hits == res.n_hits and np.array_equal(res2.hits, res.hits) and np.array_equal(res2.ident, res.ident)
     assert np.array_equal(best2, best) and np.array_equal(trim2, trim)
+
+
+def test_batch_in_parts_as_the_end_to_end_step_runs_it(engine):
+    """bench.py's end-to-end step as a parity test: a read set goes through in two parts; phase B of both parts is queued
+    (reduced outputs: hits, identities, trims), part by part its results are collected with pcb_wait_slot while the rest keeps
+    running, the trims become that part's phase-C segments, and the two task calls share one announced blob.  Every array
+    against the same calls made one by one."""
+    from custom_porechop_abi_b200 import synthetic
+    engine.set_scoring(DEFAULT)
+    adapters, s_ids, e_ids = synthetic.adapter_set()
+    lengths = np.r_[np.full(1500, 2500), np.arange(1, 301) * 9]
+    blob, off = synthetic.make_reads(len(lengths), adapters, s_ids, e_ids, seed=23, lengths=lengths, middle_rate=0.2)
+    sbuf, ebuf, lens = synthetic.end_windows(blob, off, 150, 160)
+    n = len(lens)
+    engine.set_adapters(adapters)
+    s_ids, e_ids = np.array(s_ids[:40], dtype=np.int32), np.array(e_ids[:40], dtype=np.int32)
+    mids = np.array([s_ids[0], e_ids[0], s_ids[5]], dtype=np.int32)
+    want = np.zeros(40, dtype=np.uint8); want[::4] = 1
+    cut = [0, n // 2, n]
+    rlen = np.diff(off)
+
+    def segments(a, b, trim_s, trim_e):
+        st = np.where(trim_s >= 0, trim_s.astype(np.int64) + 2, 0)
+        et = np.where(trim_e >= 0, trim_e.astype(np.int64) + 2, 0)
+        lo = np.minimum(st, rlen[a:b]); hi = np.maximum(rlen[a:b] - et, lo)
+        return np.repeat(off[a:b] + lo, len(mids)), np.repeat(hi - lo, len(mids)).astype(np.int32), np.tile(mids, b - a)
+
+    # one by one
+    ref = []
+    for p in range(2):
+        a, b = cut[p], cut[p + 1]
+        hs = engine.align_windows_hits(sbuf[a:b], lens[a:b], s_ids, 75.0, False, 150, 4, want_ident=want)
+        ts = engine.fetch_trims(b - a)
+        he = engine.align_windows_hits(ebuf[a:b], lens[a:b], e_ids, 75.0, True, 150, 4, want_ident=want)
+        te = engine.fetch_trims(b - a)
+        so, sl, sa = segments(a, b, ts, te)
+        ref.append((hs.hits.copy(), hs.ident.copy(), ts, he.hits.copy(), he.ident.copy(), te, engine.align_tasks(blob, so, sl, sa)))
+    assert sum(len(r[0]) + len(r[3]) for r in ref) > 500 and any((r[2] >= 0).any() for r in ref)
+    # queued, as the step does it
+    os.environ['PCB_PIECE_MIN_BYTES'] = '4096'            # the blob travels in 16 pieces, paced by the window calls
+    try:
+        engine.set_deferred(True)
+        engine.upload_reads(blob)
+        q = []
+        for p in range(2):
+            a, b = cut[p], cut[p + 1]
+            engine.select_slot(2 * p)
+            hs = engine.align_windows_hits(sbuf[a:b], lens[a:b], s_ids, 75.0, False, 150, 4, want_ident=want, hits_cap=40 * (b - a))
+            ts = engine.fetch_trims(b - a)
+            engine.select_slot(2 * p + 1)
+            he = engine.align_windows_hits(ebuf[a:b], lens[a:b], e_ids, 75.0, True, 150, 4, want_ident=want, hits_cap=40 * (b - a))
+            te = engine.fetch_trims(b - a)
+            q.append((hs, ts, he, te))
+        outs = []
+        for p in range(2):
+            a, b = cut[p], cut[p + 1]
+            hs, ts, he, te = q[p]
+            engine.wait_slot(2 * p); engine.wait_slot(2 * p + 1)          # this part is on the host, the other still runs
+            assert np.array_equal(hs.hits, ref[p][0]) and np.array_equal(hs.ident, ref[p][1]) and np.array_equal(ts, ref[p][2]), p
+            assert np.array_equal(he.hits, ref[p][3]) and np.array_equal(he.ident, ref[p][4]) and np.array_equal(te, ref[p][5]), p
+            so, sl, sa = segments(a, b, ts, te)
+            engine.select_slot(4 + p)
+            outs.append(engine.align_tasks(None, so, sl, sa))
+        engine.wait()
+    finally:
+        os.environ.pop('PCB_PIECE_MIN_BYTES', None)
+        engine.set_deferred(False)
+        engine.select_slot(0)
+    for p in range(2):
+        assert outs[p].tobytes() == ref[p][6].tobytes(), p
 
 
 @pytest.mark.parametrize('scores', [(7, -6, -5, -1), (10, -10, -10, -1), (4, -3, -7, -3)])
