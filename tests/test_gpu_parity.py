@@ -143,6 +143,38 @@ def test_two_stripe_class_windows_and_long_reads(engine):
     _check_pairs(engine, pairs, adapters, DEFAULT)
 
 
+def test_fast_classes_agree_with_the_general_kernels_at_size(engine):
+    """Cross-path agreement where the oracle would take minutes: 6,000 ragged windows x adapters of every kernel class
+    (24 exact, < 24, 32, 40, 52, 72 rows, both two-stripe classes) through the fast kernels and, with PCB_NO_FAST, through the
+    general kernels -- two independent implementations of the trace; every record identical."""
+    rng = np.random.default_rng(77)
+    letters = np.frombuffer(b'ACGT', dtype=np.uint8)
+    adapters = [letters[rng.integers(0, 4, k)].tobytes().decode() for k in (24, 24, 17, 30, 38, 50, 68, 72, 73, 102, 111, 113, 127)]
+    n, stride = 6000, 160
+    lens = rng.choice([150] * 12 + [0, 1, 33, 149], n).astype(np.int32)
+    buf = letters[rng.integers(0, 4, (n, stride))].astype(np.uint8)
+    for w in range(0, n, 3):                      # every third window carries (most of) one of the adapters somewhere
+        a = np.frombuffer(adapters[int(rng.integers(0, len(adapters)))].encode(), dtype=np.uint8)
+        cut = int(rng.integers(0, len(a) // 3 + 1))
+        p = int(rng.integers(0, 60))
+        piece = a[cut:][:stride - p]
+        buf[w, p:p + len(piece)] = piece
+    engine.set_scoring(DEFAULT)
+    ids = list(range(len(adapters)))
+    try:
+        engine.set_adapters(adapters)
+        fast = engine.align_windows(buf, lens, ids)
+        os.environ['PCB_NO_FAST'] = '1'
+        engine.set_adapters(adapters)             # (the kernel class of an adapter is decided when the id list is split)
+        general = engine.align_windows(buf, lens, ids)
+    finally:
+        os.environ.pop('PCB_NO_FAST', None)
+        engine.set_adapters(adapters)
+    assert (fast['raw_score'] > 60).sum() > 1000          # real hits among them
+    bad = np.argwhere(fast != general)
+    assert len(bad) == 0, (bad[:5], fast[tuple(bad[0])], general[tuple(bad[0])])
+
+
 def test_windows_cross_product(engine):
     rng = random.Random(9)
     adapters = [''.join(rng.choice('ACGT') for _ in range(rng.choice([22, 24, 28, 30, 50]))) for _ in range(9)]
