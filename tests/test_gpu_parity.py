@@ -175,6 +175,32 @@ def test_fast_classes_agree_with_the_general_kernels_at_size(engine):
     assert len(bad) == 0, (bad[:5], fast[tuple(bad[0])], general[tuple(bad[0])])
 
 
+def test_full_length_search_fast_against_general_kernels(engine):
+    """The same for the explicit-task path: 1,500 reads of 1 base to 60 kb x adapters of five kernel classes -- direct
+    traces, chunked scans, the merge and the window traces -- on the fast kernels and, with PCB_NO_FAST, on the general ones."""
+    from custom_porechop_abi_b200 import synthetic
+    rng = np.random.default_rng(78)
+    letters = np.frombuffer(b'ACGT', dtype=np.uint8)
+    adapters = [letters[rng.integers(0, 4, k)].tobytes() for k in (24, 28, 45, 68, 102)]
+    lengths = np.clip(rng.lognormal(8.0, 1.2, 1500), 1, 60000).astype(np.int64)
+    blob, off = synthetic.make_reads(len(lengths), adapters, [0, 1, 2], [3, 4], seed=31, lengths=lengths, middle_rate=0.5)
+    ids = np.arange(len(adapters), dtype=np.int32)
+    seg_off = np.repeat(off[:-1], len(ids)); seg_len = np.repeat(lengths.astype(np.int32), len(ids)); ad = np.tile(ids, len(lengths))
+    engine.set_scoring(DEFAULT)
+    try:
+        engine.set_adapters(adapters)
+        fast = engine.align_tasks(blob, seg_off, seg_len, ad)
+        os.environ['PCB_NO_FAST'] = '1'
+        engine.set_adapters(adapters)
+        general = engine.align_tasks(blob, seg_off, seg_len, ad)
+    finally:
+        os.environ.pop('PCB_NO_FAST', None)
+        engine.set_adapters(adapters)
+    assert (fast['raw_score'] > 60).sum() > 200
+    bad = np.flatnonzero(fast != general)
+    assert len(bad) == 0, (bad[:5], fast[bad[0]], general[bad[0]], seg_len[bad[0]], ad[bad[0]])
+
+
 def test_windows_cross_product(engine):
     rng = random.Random(9)
     adapters = [''.join(rng.choice('ACGT') for _ in range(rng.choice([22, 24, 28, 30, 50]))) for _ in range(9)]
