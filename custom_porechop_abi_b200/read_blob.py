@@ -76,6 +76,27 @@ class ReadBlob(object):
         q = (None, None) if self.qual_off is None else (self.qual_off[:k], self.qual_len[:k])
         return ReadBlob(self.buf, self.seq_off[:k], self.seq_len[:k], self.name_off[:k], self.name_len[:k], q[0], q[1], self.file_type)
 
+    def take(self, idx):
+        """The reads idx (ascending), as views of the same buffer: e.g. the check reads of a directory of files."""
+        idx = np.asarray(idx, dtype=np.int64)
+        q = (None, None) if self.qual_off is None else (self.qual_off[idx], self.qual_len[idx])
+        return ReadBlob(self.buf, self.seq_off[idx], self.seq_len[idx], np.asarray(self.name_off)[idx], np.asarray(self.name_len)[idx],
+                        q[0], q[1], self.file_type)
+
+    @classmethod
+    def concat(cls, blobs):
+        """The reads of several blobs (the FASTQ files of a directory) behind one another, as ONE buffer."""
+        blobs = list(blobs)
+        if len(blobs) == 1:
+            return blobs[0]
+        shift = np.cumsum([0] + [len(b.buf) for b in blobs[:-1]])
+        cat = lambda get: np.concatenate([np.asarray(get(b), dtype=np.int64) for b in blobs])
+        cat_off = lambda get: np.concatenate([np.asarray(get(b), dtype=np.int64) + s for b, s in zip(blobs, shift)])
+        has_q = all(b.qual_off is not None for b in blobs)
+        return cls(np.concatenate([b.buf for b in blobs]), cat_off(lambda b: b.seq_off), cat(lambda b: b.seq_len),
+                   cat_off(lambda b: b.name_off), cat(lambda b: b.name_len),
+                   cat_off(lambda b: b.qual_off) if has_q else None, cat(lambda b: b.qual_len) if has_q else None, blobs[0].file_type)
+
     def owns(self, reads):
         """Are these the BlobRead objects of this blob, in order (then their state is this blob's arrays)?"""
         return len(reads) == len(self) and len(reads) > 0 and getattr(reads[0], '_blob', None) is self and getattr(reads[-1], '_blob', None) is self
@@ -315,3 +336,46 @@ def load_read_blob(filename):
         out = np.concatenate((buf[pos], names)) if n else np.zeros(0, dtype=np.uint8)
         return ReadBlob(out, seq_off[:-1], seq_len, name_off, name_len, None, None, 'FASTA')
     raise ValueError('File is neither FASTA or FASTQ')
+
+
+def get_albacore_barcode_from_path(albacore_path):
+    """Albacore's bin of a file, from the directory it lies in (porechop_abi.py:190-197)."""
+    import re
+    if '/unclassified/' in albacore_path:
+        return 'none'
+    matches = re.findall('/barcode(\\d\\d)/', albacore_path)
+    return 'BC' + matches[-1] if matches else None
+
+
+def load_reads(input_file_or_directory, check_read_count):
+    """
+    porechop_abi.py:133-187 on a ReadBlob: a file, or a directory searched recursively for .fastq / .fastq.gz files (an
+    Albacore output directory: every read gets its file's bin as albacore_barcode_call, the check reads are the first
+    round(check_read_count / files) reads of every file).
+    -> (blob, reads = its BlobRead objects, check_reads, check_blob, read_type)
+    """
+    import os
+    import sys
+    if os.path.isfile(input_file_or_directory):
+        blob = load_read_blob(input_file_or_directory)
+        reads = blob.make_reads()
+        k = min(check_read_count, len(reads))
+        return blob, reads, reads[:k], blob.head(k), blob.file_type
+    if os.path.isdir(input_file_or_directory):
+        fastqs = sorted(os.path.join(dir_path, f) for dir_path, _, filenames in os.walk(input_file_or_directory)
+                        for f in filenames if f.lower().endswith('.fastq') or f.lower().endswith('.fastq.gz'))
+        if not fastqs:
+            sys.exit('Error: could not find fastq files in ' + input_file_or_directory)
+        per_file = int(round(check_read_count / len(fastqs)))
+        blobs = [load_read_blob(f) for f in fastqs]
+        blob = ReadBlob.concat(blobs)
+        reads = blob.make_reads()
+        check_idx, first = [], 0
+        for f, b in zip(fastqs, blobs):
+            call = get_albacore_barcode_from_path(f)
+            for r in reads[first:first + len(b)]:
+                r.albacore_barcode_call = call
+            check_idx.extend(range(first, first + min(per_file, len(b))))
+            first += len(b)
+        return blob, reads, [reads[i] for i in check_idx], blob.take(check_idx), 'FASTQ'
+    sys.exit('Error: could not find ' + input_file_or_directory)

@@ -427,6 +427,70 @@ def test_output_of_blob_reads(idx, tmp_path):
         assert r.get_split_read_parts(20) == ro.get_split_read_parts(r, 20)
 
 
+def _write_input(c, tmp_path):
+    """The case's reads as input of pipeline.trim: one file, or (Albacore cases) a directory tree whose sorted file order is
+    the reads' order and whose directory names carry Albacore's bins (porechop_abi.py:190-197)."""
+    alb = c.get('albacore', [None] * len(c['reads']))
+    if not any(a is not None for a in alb):
+        path = str(tmp_path / ('input.' + ('fasta' if c['fastq'].endswith('.fasta') else 'fastq')))
+        _write_records(path, c)
+        return path
+    quals = out_golden()['quals'][c['fastq']]
+    root = tmp_path / 'albacore'
+    run, k = [], 0
+    for i in range(len(alb) + 1):
+        if i == len(alb) or (run and alb[i] != alb[run[0]]):
+            call = alb[run[0]]
+            sub = 'unclassified' if call == 'none' else ('barcode' + call[2:] if call else 'other')
+            d = root / ('%03d' % k) / sub
+            d.mkdir(parents=True)
+            with open(str(d / 'reads.fastq'), 'w') as f:
+                for j in run:
+                    f.write('@' + c['reads'][j][0] + '\n' + c['reads'][j][1] + '\n+\n' + quals[j] + '\n')
+            run, k = [], k + 1
+        if i < len(alb):
+            run.append(i)
+    return str(root)
+
+
+def check_pipeline(idx, eng, tmp_path):
+    """pipeline.trim from the input file / directory to the output file and the barcode bins, against the bytes the reference's
+    own main() steps wrote (output_golden.json: 'files'); the sets and the barcode direction the reference went on with after
+    phase A come from the golden (its rewrites depend on its adapter database)."""
+    import hashlib
+    from custom_porechop_abi_b200 import pipeline
+    c, g = cases()[idx], out_golden()['cases'][idx]
+    p = c['params']
+    src = _write_input(c, tmp_path)
+
+    def between(matching, check_barcodes):
+        assert [a.name for a in matching] == c['phase_a']['matching']
+        return [AdapterSet(d) for d in c['matching_used']], c['forward_or_reverse']
+
+    for tag in ('file_auto', 'file_fasta') + (('bins',) if c['check_barcodes'] else ()):
+        a = g['files'][tag]['args']
+        d = tmp_path / ('pipe_' + tag)
+        d.mkdir()
+        res = pipeline.trim(src, [AdapterSet(x) for x in c['search_adapters']], output=str(d / a['output']) if a['output'] else None,
+                            out_format=a['out_format'], barcode_dir=str(d / a['barcode_dir']) if a['barcode_dir'] else None,
+                            between_phases=between, engine=eng, scoring_scheme_vals=p['scoring'], end_size=p['end_size'],
+                            adapter_threshold=p['adapter_threshold'], end_threshold=p['end_threshold'], extra_end_trim=p['extra_end_trim'],
+                            min_trim_size=p['min_trim_size'], middle_threshold=p['middle_threshold'],
+                            extra_middle_trim_good_side=p['good_side'], extra_middle_trim_bad_side=p['bad_side'],
+                            discard_middle=a['discard_middle'], min_split_read_size=a['min_split'], barcode_threshold=p['barcode_threshold'],
+                            barcode_diff=p['barcode_diff'], require_two_barcodes=c['require_two_barcodes'],
+                            discard_unassigned=a['discard_unassigned'], untrimmed=a['untrimmed'])
+        where = str(d / a['barcode_dir']) if a['barcode_dir'] else str(d)
+        got = {fn: hashlib.sha256(open(os.path.join(where, fn), 'rb').read()).hexdigest() for fn in sorted(os.listdir(where))}
+        assert got == g['files'][tag]['sha256'], (tag, sorted(got), sorted(g['files'][tag]['sha256']))
+        assert [r.albacore_barcode_call for r in res['reads']] == c.get('albacore', [None] * len(c['reads']))
+
+
+@pytest.mark.parametrize('idx', [0, 2, 3, 5, 8, 9, 12])
+def test_pipeline_from_file_to_file(idx, tmp_path):
+    check_pipeline(idx, ReducedOracleEngine(), tmp_path)
+
+
 @pytest.mark.gpu
 def test_phases_on_gpu(engine, tmp_path):
     from custom_porechop_abi_b200.read_blob import load_read_blob
@@ -435,6 +499,10 @@ def test_phases_on_gpu(engine, tmp_path):
         da.mkdir(); db.mkdir()
         check_output(k, run_case(c, engine), da)                              # reference-shaped objects -> records and files
         check_output(k, blob_reads_through_phases(c, engine, db), db)         # file -> ReadBlob -> BlobRead -> the same bytes
+    for k in (0, 5, 9, 12):                                                   # ... and the whole way from input path to output files
+        d = tmp_path / ('p%d' % k)
+        d.mkdir()
+        check_pipeline(k, engine, d)
         path = str(tmp_path / ('reads%d.fastq' % k))
         _write_fastq(path, c['reads'], lower=(k % 2 == 1))
         run_case(c, engine, read_blob=load_read_blob(path))
