@@ -83,6 +83,24 @@ class ReadBlob(object):
         return ReadBlob(self.buf, self.seq_off[idx], self.seq_len[idx], np.asarray(self.name_off)[idx], np.asarray(self.name_len)[idx],
                         q[0], q[1], self.file_type)
 
+    def compact(self):
+        """The same reads in a buffer of their own that holds nothing else (a rank's shard of a file: what it sends to its GPU)."""
+        def gather(off, ln):
+            off, ln = np.asarray(off, dtype=np.int64), np.asarray(ln, dtype=np.int64)
+            new_off = np.zeros(len(ln) + 1, dtype=np.int64)
+            np.cumsum(ln, out=new_off[1:])
+            pos = np.repeat(off - new_off[:-1], ln) + np.arange(int(new_off[-1]), dtype=np.int64)
+            return self.buf[pos], new_off[:-1]
+        seq, seq_off = gather(self.seq_off, self.seq_len)
+        name, name_off = gather(self.name_off, self.name_len)
+        parts, q_off = [seq, name], None
+        if self.qual_off is not None:
+            qual, q_off = gather(self.qual_off, self.qual_len)
+            parts.append(qual)
+            q_off = q_off + len(seq) + len(name)
+        return ReadBlob(np.concatenate(parts), seq_off, self.seq_len, name_off + len(seq), np.asarray(self.name_len, dtype=np.int64),
+                        q_off, None if q_off is None else np.asarray(self.qual_len, dtype=np.int64), self.file_type)
+
     @classmethod
     def concat(cls, blobs):
         """The reads of several blobs (the FASTQ files of a directory) behind one another, as ONE buffer."""

@@ -132,6 +132,59 @@ def resolve_format(out_format, output, read_type, barcode_dir, input_filename):
     return out_format, gzipped
 
 
+def records_of(reads, out_format, output, read_type, discard_middle, min_split_size, barcode_dir, input_filename, untrimmed,
+               discard_unassigned):
+    """What output_reads would write for these reads, read by read: (barcode bin or '', text, bases counted for the bin's
+    summary); reads that produce nothing are left out.  (Apart from output_reads so that ranks can produce their shares and
+    one rank writes them: sharding.gather_records.)"""
+    out_format, _ = resolve_format(out_format, output, read_type, barcode_dir, input_filename)
+    record = get_fasta if out_format == 'fasta' else get_fastq
+    out = []
+    for read in reads:
+        if barcode_dir is not None:                          # bins: `untrimmed` counts, unassigned reads may be dropped (:588-610)
+            name = read.barcode_call
+            if discard_unassigned and name == 'none':
+                continue
+            text = record(read, min_split_size, discard_middle, untrimmed)
+            if text:
+                out.append((name, text, len(read.seq) if untrimmed else len(_trimmed(read)[0])))
+        else:                                                # stdout / one file: trimmed, whatever `untrimmed` says (:641-657)
+            text = record(read, min_split_size, discard_middle)
+            if text:
+                out.append(('', text, 0))
+    return out
+
+
+def write_records(records, out_format, output, read_type, verbosity, print_dest, barcode_dir, input_filename, stdout=None):
+    """The writing half of output_reads (porechop_abi.py:581-665): barcode bins, stdout or one file."""
+    out_format, gzipped = resolve_format(out_format, output, read_type, barcode_dir, input_filename)
+    opener = (lambda path: gzip.open(path, 'wt')) if gzipped else (lambda path: open(path, 'wt'))
+    bins = {}
+    if barcode_dir is not None:
+        os.makedirs(barcode_dir, exist_ok=True)
+        files, n_reads, n_bases = {}, defaultdict(int), defaultdict(int)
+        for name, text, bases in records:
+            if name not in files:
+                files[name] = opener(os.path.join(barcode_dir, name + '.' + out_format + ('.gz' if gzipped else '')))
+            files[name].write(text)
+            n_reads[name] += 1
+            n_bases[name] += bases
+        for name in sorted(files):
+            files[name].close()
+            bins[name] = (n_reads[name], n_bases[name])
+    elif output is None:
+        dest = stdout if stdout is not None else sys.stdout
+        for _, text, _ in records:
+            dest.write(text)
+    else:
+        with opener(output) as f:
+            for _, text, _ in records:
+                f.write(text)
+    if verbosity > 0 and print_dest is not None:
+        print('%d records written' % len(records), file=print_dest, flush=True)
+    return {'records': len(records), 'bins': bins}
+
+
 def output_reads(reads, out_format, output, read_type, verbosity, discard_middle, min_split_size, print_dest, barcode_dir,
                  input_filename, untrimmed, threads, discard_unassigned, stdout=None):
     """
@@ -139,41 +192,6 @@ def output_reads(reads, out_format, output, read_type, verbosity, discard_middle
     with Python's gzip here, so the .gz BYTES differ from pigz / gzip output while the text inside is identical).
     Returns {'records': n written, 'bins': {barcode: (reads, bases)}} for the caller's summary.
     """
-    out_format, gzipped = resolve_format(out_format, output, read_type, barcode_dir, input_filename)
-    record = (lambda r, *a: get_fasta(r, *a)) if out_format == 'fasta' else (lambda r, *a: get_fastq(r, *a))
-    opener = (lambda path: gzip.open(path, 'wt')) if gzipped else (lambda path: open(path, 'wt'))
-    written, bins = 0, {}
-    if barcode_dir is not None:                              # one file per barcode bin (:582-638)
-        os.makedirs(barcode_dir, exist_ok=True)
-        files, n_reads, n_bases = {}, defaultdict(int), defaultdict(int)
-        for read in reads:
-            name = read.barcode_call
-            if discard_unassigned and name == 'none':
-                continue
-            text = record(read, min_split_size, discard_middle, untrimmed)
-            if not text:
-                continue
-            if name not in files:
-                files[name] = opener(os.path.join(barcode_dir, name + '.' + out_format + ('.gz' if gzipped else '')))
-            files[name].write(text)
-            written += 1
-            n_reads[name] += 1
-            n_bases[name] += len(read.seq) if untrimmed else len(_trimmed(read)[0])
-        for name in sorted(files):
-            files[name].close()
-            bins[name] = (n_reads[name], n_bases[name])
-    elif output is None:                                     # stdout: trimmed, whatever `untrimmed` says (:641-647)
-        dest = stdout if stdout is not None else sys.stdout
-        for read in reads:
-            text = record(read, min_split_size, discard_middle)
-            dest.write(text)
-            written += bool(text)
-    else:                                                    # one file (:650-665)
-        with opener(output) as f:
-            for read in reads:
-                text = record(read, min_split_size, discard_middle)
-                f.write(text)
-                written += bool(text)
-    if verbosity > 0 and print_dest is not None:
-        print('%d records written' % written, file=print_dest, flush=True)
-    return {'records': written, 'bins': bins}
+    records = records_of(reads, out_format, output, read_type, discard_middle, min_split_size, barcode_dir, input_filename,
+                         untrimmed, discard_unassigned)
+    return write_records(records, out_format, output, read_type, verbosity, print_dest, barcode_dir, input_filename, stdout=stdout)

@@ -151,3 +151,55 @@ def gather_results(local_indices, local_records, n_total, device=None):
         rec = np.frombuffer(pay_parts[r][:k * row_bytes].cpu().numpy().tobytes(), dtype=local_records.dtype)
         out[idx_parts[r][:k].cpu().numpy()] = rec.reshape((k,) + local_records.shape[1:])
     return out
+
+
+def gather_records(local_indices, local_records, device=None):
+    """
+    The output side of a sharded run: every rank hands in what read_output.records_of made of ITS reads -- per kept read
+    (global read index, (bin, text, bases)) -- and rank 0 gets all of them in global read order (what one process would have
+    written); None elsewhere; identity without a process group.  Bytes and int64 arrays in tensors, no pickles.
+    local_indices[i] belongs to local_records[i]; a read with several records appears several times.
+    """
+    import torch
+    dist = _dist()
+    order = np.argsort(np.asarray(local_indices, dtype=np.int64), kind='stable')
+    if dist is None:
+        return [local_records[i] for i in order]
+    world, rank = dist.get_world_size(), dist.get_rank()
+    dev = device or 'cpu'
+    names = [local_records[i][0].encode() for i in range(len(local_records))]
+    texts = [local_records[i][1].encode() for i in range(len(local_records))]
+    meta = np.zeros((len(local_records), 4), dtype=np.int64)           # read index, bases, bytes of the bin's name, bytes of the text
+    if len(local_records):
+        meta[:, 0] = np.asarray(local_indices, dtype=np.int64)
+        meta[:, 1] = [r[2] for r in local_records]
+        meta[:, 2] = [len(x) for x in names]
+        meta[:, 3] = [len(x) for x in texts]
+    payload = np.frombuffer(b''.join(a + b for a, b in zip(names, texts)), dtype=np.uint8)
+    sizes = torch.zeros(world, 2, dtype=torch.int64, device=dev)
+    sizes[rank, 0], sizes[rank, 1] = len(meta), len(payload)
+    dist.all_reduce(sizes, op=dist.ReduceOp.SUM)
+    sizes = sizes.cpu().numpy()
+    m_max, p_max = int(sizes[:, 0].max()), int(sizes[:, 1].max())
+    m_send = torch.zeros(max(m_max, 1), 4, dtype=torch.int64, device=dev)
+    p_send = torch.zeros(max(p_max, 1), dtype=torch.uint8, device=dev)
+    if len(meta):
+        m_send[:len(meta)] = torch.from_numpy(meta).to(dev)
+    if len(payload):
+        p_send[:len(payload)] = torch.from_numpy(payload.copy()).to(dev)
+    m_all = [torch.empty_like(m_send) for _ in range(world)]
+    p_all = [torch.empty_like(p_send) for _ in range(world)]
+    dist.all_gather(m_all, m_send)
+    dist.all_gather(p_all, p_send)
+    if rank != 0:
+        return None
+    merged = []
+    for r in range(world):
+        m = m_all[r].cpu().numpy()[:int(sizes[r, 0])]
+        p = p_all[r].cpu().numpy()[:int(sizes[r, 1])].tobytes()
+        at = 0
+        for idx, bases, ln, lt in m.tolist():
+            merged.append((idx, len(merged), p[at:at + ln].decode(), p[at + ln:at + ln + lt].decode(), bases))
+            at += ln + lt
+    merged.sort(key=lambda x: (x[0], x[1]))                              # read order; a read's own records keep theirs
+    return [(name, text, bases) for _, _, name, text, bases in merged]

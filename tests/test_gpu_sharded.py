@@ -82,3 +82,76 @@ def test_two_ranks_on_a_shard_reproduce_one_gpu(tmp_path):
     assert out.returncode == 0, out.stderr[-3000:]
     assert 'NCCL_SHARDED_OK' in out.stdout
     print(out.stdout.strip().splitlines()[-1])
+
+
+PIPELINE_WORKER = textwrap.dedent('''
+    import hashlib, os, sys, pathlib
+    sys.path.insert(0, %r); sys.path.insert(0, os.path.join(%r, 'tests'))
+    import torch
+    import torch.distributed as dist
+    import test_phases as tp
+    from custom_porechop_abi_b200 import pipeline
+    from custom_porechop_abi_b200.engine import AlignmentEngine
+    local = int(os.environ['LOCAL_RANK'])
+    torch.cuda.set_device(local)
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    rank = dist.get_rank()
+    tmp = pathlib.Path(sys.argv[1])
+    eng = AlignmentEngine(local)
+    for idx in (0, 5, 9, 12):
+        c, g = tp.cases()[idx], tp.out_golden()['cases'][idx]
+        p = c['params']
+        d = tmp / ('case%%d' %% idx)
+        if rank == 0:
+            d.mkdir()
+            tp._write_input(c, d)
+        dist.barrier()
+        src = str(d / 'albacore') if (d / 'albacore').exists() else str(next(d.glob('input.*')))
+        def between(matching, check_barcodes):
+            assert [a.name for a in matching] == c['phase_a']['matching'], (rank, [a.name for a in matching])
+            return [tp.AdapterSet(x) for x in c['matching_used']], c['forward_or_reverse']
+        for tag in ('file_auto',) + (('bins',) if c['check_barcodes'] else ()):
+            a = g['files'][tag]['args']
+            out = d / ('out_' + tag)
+            if rank == 0:
+                out.mkdir()
+            dist.barrier()
+            res = pipeline.trim(src, [tp.AdapterSet(x) for x in c['search_adapters']], output=str(out / a['output']) if a['output'] else None,
+                                out_format=a['out_format'], barcode_dir=str(out / a['barcode_dir']) if a['barcode_dir'] else None,
+                                between_phases=between, engine=eng, scoring_scheme_vals=p['scoring'], end_size=p['end_size'],
+                                adapter_threshold=p['adapter_threshold'], end_threshold=p['end_threshold'], extra_end_trim=p['extra_end_trim'],
+                                min_trim_size=p['min_trim_size'], middle_threshold=p['middle_threshold'],
+                                extra_middle_trim_good_side=p['good_side'], extra_middle_trim_bad_side=p['bad_side'],
+                                discard_middle=a['discard_middle'], min_split_read_size=a['min_split'], barcode_threshold=p['barcode_threshold'],
+                                barcode_diff=p['barcode_diff'], require_two_barcodes=c['require_two_barcodes'],
+                                discard_unassigned=a['discard_unassigned'], untrimmed=a['untrimmed'], distributed=True, device='cuda')
+            dist.barrier()
+            if rank == 0:
+                where = str(out / a['barcode_dir']) if a['barcode_dir'] else str(out)
+                got = {fn: hashlib.sha256(open(os.path.join(where, fn), 'rb').read()).hexdigest() for fn in sorted(os.listdir(where))}
+                assert got == g['files'][tag]['sha256'], (idx, tag, sorted(got), sorted(g['files'][tag]['sha256']))
+    eng.close()
+    if rank == 0:
+        print('NCCL_PIPELINE_OK')
+    dist.barrier()
+    dist.destroy_process_group()
+''') % (ROOT, ROOT)
+
+
+def test_sharded_pipeline_on_two_gpus_writes_the_reference_bytes(tmp_path):
+    """pipeline.trim on two ranks over NCCL, each with its shard of the reads on its own GPU: the files rank 0 writes are the
+    ones the reference wrote (tests/golden/output_golden.json)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two CUDA devices (gpurun --gpus 2)')
+    script = tmp_path / 'pipeline_worker.py'
+    script.write_text(PIPELINE_WORKER)
+    work = tmp_path / 'work'
+    work.mkdir()
+    env = dict(os.environ, MASTER_ADDR='127.0.0.1')
+    out = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=2',
+                          '--master-addr', '127.0.0.1', '--master-port', '29542', str(script), str(work)],
+                         capture_output=True, text=True, timeout=900, env=env)
+    assert out.returncode == 0, out.stderr[-3000:]
+    assert 'NCCL_PIPELINE_OK' in out.stdout
+
