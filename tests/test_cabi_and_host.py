@@ -24,6 +24,23 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(w.C_LIB, s), s
 
 
+def test_static_entry_point_checks_its_limits_before_it_touches_a_device():
+    """pcb_align_windows_static refuses what its fixed scratch array cannot hold with PCB_ERR_RANGE and a text, on the host,
+    before any CUDA call (so this runs without a GPU; the compute side is tests/test_zz_no_alloc.py)."""
+    from custom_porechop_abi_b200 import cpp_function_wrappers as w
+    lib = w.C_LIB
+    fake = ctypes.c_void_p(4096)                    # never dereferenced on these paths
+    call = lambda ad, sc, n, stride: lib.pcb_align_windows_static(0, ad.encode(), len(ad), sc[0], sc[1], sc[2], sc[3], fake, fake, n, stride, fake, None)
+    d = (3, -6, -5, -2)
+    assert call('ACGT' * 6, d, 8193, 160) == 3 and b'8192' in lib.pcb_last_error(None)
+    assert call('ACGT' * 6, d, 16, 257) == 3 and b'stride' in lib.pcb_last_error(None)
+    assert call('A' * 128, d, 16, 160) == 3 and b'127' in lib.pcb_last_error(None)
+    assert call('ACGN', d, 16, 160) == 3
+    assert call('ACGT' * 6, (2, -3, -4, -4), 16, 160) == 3 and b'affine' in lib.pcb_last_error(None)
+    assert call('ACGT' * 6, d, 0, 160) == 0        # nothing to do is not an error
+    assert lib.pcb_align_windows_static(0, None, 0, 3, -6, -5, -2, fake, fake, 4, 160, fake, None) == 2
+
+
 def test_result_record_layout():
     from custom_porechop_abi_b200 import cpp_function_wrappers as w
     from custom_porechop_abi_b200.engine import RESULT_DTYPE
