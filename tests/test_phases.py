@@ -391,6 +391,27 @@ def blob_reads_through_phases(c, eng, tmp_path):
     return reads
 
 
+def test_output_format_rules():
+    """--format auto and the .gz rules of output_reads (porechop_abi.py:552-572), case by case as the reference decides them --
+    including its quirk that an explicit 'fasta.gz' on stdout keeps the '.gz' and therefore takes the FASTQ branch (:643)."""
+    from custom_porechop_abi_b200 import read_output as ro
+    f = ro.resolve_format
+    assert f('auto', None, 'FASTQ', None, 'in.fastq') == ('fastq', False)
+    assert f('auto', None, 'FASTA', None, 'in.fasta.gz') == ('fasta', False)
+    assert f('auto', None, 'FASTQ', 'bins', 'in.fastq.gz') == ('fastq', True)
+    assert f('auto', None, 'FASTQ', 'bins', 'in.fastq') == ('fastq', False)
+    assert f('auto', 'out.FASTA.gz', 'FASTQ', None, 'in.fastq') == ('fasta', True)
+    assert f('auto', 'out.fastq.gz', 'FASTA', None, 'in.fasta') == ('fastq', True)
+    assert f('auto', 'out.fasta', 'FASTQ', None, 'in.fastq') == ('fasta', False)
+    assert f('auto', 'reads.fq', 'FASTQ', None, 'in.fastq') == ('fastq', False)
+    assert f('auto', 'reads.txt', 'FASTA', None, 'in.fasta') == ('fasta', False)
+    assert f('fasta.gz', 'x.out', 'FASTQ', None, 'in.fastq') == ('fasta', True)
+    assert f('fasta.gz', None, 'FASTQ', None, 'in.fastq') == ('fasta.gz', False)
+    r = Read('r', 'ACGT' * 5, 'I' * 20)
+    recs = ro.records_of([r], 'fasta.gz', None, 'FASTQ', False, 1000, None, 'in.fastq', False, False)
+    assert recs == [('', '@r\n' + 'ACGT' * 5 + '\n+\n' + 'I' * 20 + '\n', 0)]
+
+
 def test_output_corner_cases(tmp_path):
     """Hand-made reads run through the reference's own get_fasta / get_fastq / get_split_read_parts (output_golden.json:
     'edge'): RNA, names with tab / space / neither, short quality strings, trims longer than the read, trim positions
